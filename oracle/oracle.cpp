@@ -669,39 +669,70 @@ ORACLE_API int oracle_ba_f64(double* poses, double* disps, const double* intr, c
                          t1, iterations, lm, ep, motion_only, eta_rows, dx_out, dz_out, o, nullptr, nullptr);
 }
 
-// frame_distance_kernel, droid_kernels.cu:518-657
+// frame_distance_kernel, droid_kernels.cu:518-657.
+// The consumers of this op threshold and argsort its fp32 output (factor_graph.py:327-354), so the
+// restatement fixes not only the summation order (thread-strided accumulation + blockReduce tree)
+// but also the FMA contraction nvcc applies to the source expressions.  The pattern below was read
+// off the SASS of the reference kernel built for sm_100a with the reference's flags (-O3, default
+// -fmad=true): `a*b - c*d` -> fma(a,b,-(c*d)); `X + q3*uv + (..)` -> fma(q3,uv,X) + (..);
+// `Y += X3*t` -> separate multiply and add (the product is shared with the translation-only branch);
+// `fx*(x/z) + cx - u` -> fma(fx, x/z, cx) - u; `du*du + dv*dv` -> fma(du,du,dv*dv);
+// `accum += beta*d` -> fma.  Division and sqrt are IEEE (no fast-math).
+static inline void fd_rot(const float* q, const float* X, float* Y) {  // actSO3 as compiled
+  float uv0 = fmaf(q[1], X[2], -(q[2] * X[1])); uv0 += uv0;
+  float uv1 = fmaf(q[2], X[0], -(q[0] * X[2])); uv1 += uv1;
+  float uv2 = fmaf(q[0], X[1], -(q[1] * X[0])); uv2 += uv2;
+  Y[0] = fmaf(q[3], uv0, X[0]) + fmaf(q[1], uv2, -(q[2] * uv1));
+  Y[1] = fmaf(q[3], uv1, X[1]) + fmaf(q[2], uv0, -(q[0] * uv2));
+  Y[2] = fmaf(q[3], uv2, X[2]) + fmaf(q[0], uv1, -(q[1] * uv0));
+}
+static inline void fd_relSE3(const float* ti, const float* qi, const float* tj, const float* qj, float* tij, float* qij) {
+  qij[0] = fmaf(qj[2], qi[1], fmaf(-qj[1], qi[2], fmaf(qj[0], qi[3], -(qj[3] * qi[0]))));
+  qij[1] = fmaf(qj[0], qi[2], fmaf(-qj[2], qi[0], fmaf(qj[1], qi[3], -(qj[3] * qi[1]))));
+  qij[2] = fmaf(qj[1], qi[0], fmaf(-qj[0], qi[1], fmaf(qj[2], qi[3], -(qj[3] * qi[2]))));
+  qij[3] = fmaf(qj[2], qi[2], fmaf(qj[1], qi[1], fmaf(qj[3], qi[3], qj[0] * qi[0])));
+  float Y[3];
+  fd_rot(qij, ti, Y);
+  tij[0] = tj[0] - Y[0]; tij[1] = tj[1] - Y[1]; tij[2] = tj[2] - Y[2];
+}
 ORACLE_API void oracle_frame_distance(const float* poses, const float* disps, const float* intr,
                                       const int64_t* ii, const int64_t* jj, int K, int ht, int wd,
                                       float beta, float* dist) {
   const int HW = ht * wd;
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const float omb = 1 - beta;
 #pragma omp parallel for schedule(dynamic, 64)
   for (int b = 0; b < K; b++) {
     const int ix = int(ii[b]), jx = int(jj[b]);
-    float tij[3], qij[4];
-    relSE3(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, qij);
+    float tij[3], q[4];
+    fd_relSE3(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, q);
     float accum[THREADS], valid[THREADS], total[THREADS];
     for (int t = 0; t < THREADS; t++) { accum[t] = 0; valid[t] = 0; total[t] = 0; }
     for (int tid = 0; tid < THREADS; tid++) {
       for (int k = tid; k < HW; k += THREADS) {
         const int i = k / wd, j = k % wd;
         const float u = float(j), v = float(i);
-        float Xi[4], Xj[4];
-        Xi[0] = (u - cx) / fx; Xi[1] = (v - cy) / fy; Xi[2] = 1; Xi[3] = disps[size_t(ix) * HW + k];
-        actSE3(tij, qij, Xi, Xj);
-        float du = fmaf(fx, Xj[0] / Xj[2], cx) - u;
-        float dv = fmaf(fy, Xj[1] / Xj[2], cy) - v;
+        const float X0 = (u - cx) / fx, X1 = (v - cy) / fy, dsp = disps[size_t(ix) * HW + k];
+        // actSO3 with X[2] == 1 folded by the compiler
+        float uv0 = fmaf(-q[2], X1, q[1]); uv0 += uv0;
+        float uv1 = fmaf(q[2], X0, -q[0]); uv1 += uv1;
+        float uv2 = fmaf(q[0], X1, -(q[1] * X0)); uv2 += uv2;
+        float Y0 = fmaf(q[3], uv0, X0) + fmaf(q[1], uv2, -(q[2] * uv1));
+        float Y1 = fmaf(q[3], uv1, X1) + fmaf(q[2], uv0, -(q[0] * uv2));
+        float Y2 = fmaf(q[3], uv2, 1.0f) + fmaf(q[0], uv1, -(q[1] * uv0));
+        const float p0 = tij[0] * dsp, p1 = tij[1] * dsp, p2 = tij[2] * dsp;
+        Y0 += p0; Y1 += p1; Y2 += p2;
+        float du = fmaf(fx, Y0 / Y2, cx) - u;
+        float dv = fmaf(fy, Y1 / Y2, cy) - v;
         float d = sqrtf(fmaf(du, du, dv * dv));
         total[tid] += beta;
-        if (double(Xj[2]) > 0.25) { accum[tid] = fmaf(beta, d, accum[tid]); valid[tid] += beta; }
-        Xj[0] = fmaf(Xi[3], tij[0], Xi[0]);
-        Xj[1] = fmaf(Xi[3], tij[1], Xi[1]);
-        Xj[2] = fmaf(Xi[3], tij[2], Xi[2]);
-        du = fmaf(fx, Xj[0] / Xj[2], cx) - u;
-        dv = fmaf(fy, Xj[1] / Xj[2], cy) - v;
+        if (Y2 > 0.25f) { accum[tid] = fmaf(d, beta, accum[tid]); valid[tid] += beta; }
+        const float Z0 = p0 + X0, Z1 = p1 + X1, Z2 = p2 + 1.0f;
+        du = fmaf(fx, Z0 / Z2, cx) - u;
+        dv = fmaf(fy, Z1 / Z2, cy) - v;
         d = sqrtf(fmaf(du, du, dv * dv));
-        total[tid] += (1 - beta);
-        if (double(Xj[2]) > 0.25) { accum[tid] = fmaf(1 - beta, d, accum[tid]); valid[tid] += (1 - beta); }
+        total[tid] += omb;
+        if (Z2 > 0.25f) { accum[tid] = fmaf(omb, d, accum[tid]); valid[tid] += omb; }
       }
     }
     const float a = block_reduce(accum), tt = block_reduce(total), vv = block_reduce(valid);
