@@ -1,0 +1,126 @@
+// ba_api.cu — C-ABI of the dense bundle adjustment (see include/droid_b200.h).
+// Mirrors droid_backends.ba (/root/reference/src/droid.cpp:88-117, droid_kernels.cu:1314-1434): in-place
+// update of poses/disps, `iterations` Gauss-Newton steps, returns dx/dz of the last step.
+#include "ba.cuh"
+
+using namespace db200;
+
+namespace {
+
+bool args_ok(const float* poses, const float* disps, const float* intr, const float* sens, const float* tg,
+             const float* wg, const float* eta, const int64_t* ii, const int64_t* jj, int N, int B, int ht, int wd, int t0,
+             int t1, int motion_only, int eta_rows) {
+  if (!poses || !disps || !intr || N < 0 || B <= 0 || ht <= 0 || wd <= 0) return false;
+  if (t0 < 0 || t1 <= t0 || t1 > B) return false;
+  if (N > 0 && (!tg || !wg || !ii || !jj)) return false;
+  if (!motion_only && (!sens || !eta || eta_rows <= 0 || eta_rows > B)) return false;
+  return true;
+}
+
+BAParams make_params(float* poses, float* disps, const float* intr, const float* sens, const float* tg, const float* wg,
+                     const float* eta, const int64_t* ii, const int64_t* jj, int N, int B, int ht, int wd, int t0, int t1,
+                     int motion_only, int eta_rows, void* ws, const BALayout& L) {
+  BAParams p = ba_params(L, ws);
+  p.poses = poses; p.disps = disps; p.intr = intr; p.sens = sens; p.target = tg; p.weight = wg; p.eta = eta;
+  p.ii = ii; p.jj = jj; p.N = N; p.B = B; p.ht = ht; p.wd = wd; p.HW = ht * wd; p.t0 = t0; p.t1 = t1; p.P = t1 - t0;
+  p.eta_rows = eta_rows; p.motion_only = motion_only;
+  return p;
+}
+
+}  // namespace
+
+extern "C" size_t db200_ba_workspace_bytes(int N, int B, int ht, int wd, int t0, int t1, int eta_rows, int motion_only) {
+  if (N < 0 || B <= 0 || ht <= 0 || wd <= 0 || t1 <= t0) return 0;
+  return ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only).total;
+}
+
+extern "C" double* db200_ba_system_ptr(void* workspace, int N, int B, int ht, int wd, int t0, int t1, int eta_rows,
+                                       int motion_only) {
+  if (!workspace) return nullptr;
+  const BALayout L = ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only);
+  return reinterpret_cast<double*>(static_cast<char*>(workspace) + L.Hb);
+}
+
+extern "C" size_t db200_ba_system_elems(int t0, int t1) {
+  const size_t n = size_t(6) * (t1 - t0);
+  return n * n + n;
+}
+
+extern "C" int db200_ba_accumulate(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                                   const float* targets, const float* weights, const float* eta, const int64_t* ii,
+                                   const int64_t* jj, int N, int B, int ht, int wd, int t0, int t1, int motion_only,
+                                   int eta_rows, int first_iteration, void* workspace, size_t workspace_bytes,
+                                   db200_stream_t stream) {
+  if (!workspace || !args_ok(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
+                             motion_only, eta_rows))
+    return DB200_ERR_ARG;
+  const BALayout L = ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only);
+  if (workspace_bytes < L.total) return DB200_ERR_WORKSPACE;
+  const BAParams p = make_params(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
+                                 motion_only, eta_rows, workspace, L);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = DB200_OK;
+  if (first_iteration) rc = ba_build_graph(p, st);
+  if (rc == DB200_OK) rc = ba_edge_prep(p, st);
+  if (rc == DB200_OK) rc = ba_accumulate_frames(p, st);
+  return rc;
+}
+
+extern "C" int db200_ba_solve_update(float* poses, float* disps, const float* intrinsics, const float* targets,
+                                     const float* weights, const int64_t* ii, const int64_t* jj, int N, int B, int ht,
+                                     int wd, int t0, int t1, float lm, float ep, int motion_only, int eta_rows,
+                                     float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes,
+                                     db200_stream_t stream) {
+  if (!workspace || !poses || !disps || !intrinsics || N < 0 || B <= 0 || ht <= 0 || wd <= 0 || t0 < 0 || t1 <= t0 || t1 > B)
+    return DB200_ERR_ARG;
+  const BALayout L = ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only);
+  if (workspace_bytes < L.total) return DB200_ERR_WORKSPACE;
+  const BAParams p = make_params(poses, disps, intrinsics, nullptr, targets, weights, nullptr, ii, jj, N, B, ht, wd, t0, t1,
+                                 motion_only, eta_rows, workspace, L);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = ba_solve(p, lm, ep, st);
+  if (rc == DB200_OK) rc = ba_post_solve(p, dx_out, st);
+  if (rc == DB200_OK && !motion_only) rc = ba_backsub_frames(p, dz_out, st);
+  return rc;
+}
+
+extern "C" int db200_ba(float* poses, float* disps, const float* intrinsics, const float* disps_sens, const float* targets,
+                        const float* weights, const float* eta, const int64_t* ii, const int64_t* jj, int N, int B, int ht,
+                        int wd, int t0, int t1, int iterations, float lm, float ep, int motion_only, int eta_rows,
+                        float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes, db200_stream_t stream) {
+  if (iterations < 0) return DB200_ERR_ARG;
+  for (int it = 0; it < iterations; it++) {
+    int rc = db200_ba_accumulate(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
+                                 motion_only, eta_rows, it == 0, workspace, workspace_bytes, stream);
+    if (rc != DB200_OK) return rc;
+    const bool last = (it == iterations - 1);
+    rc = db200_ba_solve_update(poses, disps, intrinsics, targets, weights, ii, jj, N, B, ht, wd, t0, t1, lm, ep, motion_only,
+                               eta_rows, last ? dx_out : nullptr, last ? dz_out : nullptr, workspace, workspace_bytes, stream);
+    if (rc != DB200_OK) return rc;
+  }
+  return DB200_OK;
+}
+
+extern "C" int db200_ba_status(const void* workspace, db200_stream_t stream) {
+  if (!workspace) return DB200_ERR_ARG;
+  BAHeader h{};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cudaMemcpyAsync(&h, workspace, sizeof(BAHeader), cudaMemcpyDeviceToHost, st) != cudaSuccess) return DB200_ERR_CUDA;
+  if (cudaStreamSynchronize(st) != cudaSuccess) return DB200_ERR_CUDA;
+  return h.status;
+}
+
+extern "C" int db200_version(void) { return 100; }
+
+extern "C" const char* db200_status_string(int s) {
+  switch (s) {
+    case DB200_OK: return "ok";
+    case 1: return "Cholesky breakdown in at least one iteration: zero pose update applied (reference behaviour)";
+    case DB200_ERR_ARG: return "invalid argument (null pointer, bad size, unsupported dtype/radius, or >31 pose edges share a source frame)";
+    case DB200_ERR_CUDA: return "CUDA runtime error";
+    case DB200_ERR_WORKSPACE: return "workspace too small";
+    case DB200_ERR_INDEX: return "edge index out of range [0, t1)";
+    case DB200_ERR_ETA: return "eta rows != number of unique frames in cat(arange(t0,t1), ii)";
+  }
+  return "unknown status";
+}

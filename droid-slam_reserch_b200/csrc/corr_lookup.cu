@@ -1,0 +1,208 @@
+// corr_lookup.cu — correlation-pyramid window lookup, forward and backward.
+// Replaces /root/reference/src/correlation_kernels.cu:20-124 and the per-level loop + torch.cat of
+// droid_slam/modules/corr.py:40-50.
+//
+// Layout/roofline: volume[n][y][x][h2][w2] — every source pixel (n,y,x) owns a contiguous h2*w2 slice
+// and reads a (2r+2)^2 window of it; output corr[n][ch][y][x] is x-contiguous.  The reference maps one
+// THREAD to one source pixel (neighbouring threads read slices h2*w2 elements apart, 4 RMWs per output
+// cell).  Here one WARP owns one source pixel: lanes cover the window rows (coalesced per row), the
+// window goes through shared memory, every output cell is produced once in registers in the reference's
+// accumulation order (bit-identical fp16/fp32/fp64), and a CTA covers 64 consecutive x so that each
+// output channel row is written as one full coalesced line.  HBM-bound: algorithmic bytes per lookup
+// = L*(2r+2)^2*s + 8 + L*(2r+1)^2*s.
+#include "common.cuh"
+
+namespace db200 {
+
+constexpr int kLookupTX = 64;      // source pixels (consecutive x) per CTA
+constexpr int kLookupWarps = 8;    // 256 threads
+constexpr int kMaxLevels = 4;
+
+struct LevelPtrs {
+  const void* p[kMaxLevels];
+};
+
+// One warp computes the (2r+1)^2 outputs of one source pixel for one level into `sout`
+// (sout[ch * kLookupTX + px]).  `win` is this warp's (2r+2)^2 staging buffer.
+template <typename T>
+__device__ __forceinline__ void lookup_pixel(const T* __restrict__ slice, int h2, int w2, float x0, float y0, int r,
+                                             T* __restrict__ win, T* __restrict__ sout, int px, int lane) {
+  const int rd = 2 * r + 1, wn = rd + 1;
+  const float fx = floorf(x0), fy = floorf(y0);
+  const float dx = x0 - fx, dy = y0 - fy;
+  const int xb = static_cast<int>(fx) - r, yb = static_cast<int>(fy) - r;
+  // window: win[i*wn + j] = volume[y1 = yb + j][x1 = xb + i]  (i = x offset, j = y offset)
+  for (int idx = lane; idx < wn * wn; idx += 32) {
+    const int j = idx / wn, i = idx - j * wn;   // lanes run along x (contiguous in memory)
+    const int x1 = xb + i, y1 = yb + j;
+    T v = Elem<T>::zero();
+    if (x1 >= 0 && x1 < w2 && y1 >= 0 && y1 < h2) v = slice[y1 * w2 + x1];
+    win[i * wn + j] = v;
+  }
+  __syncwarp();
+  const T w00 = Elem<T>::from_float((1.0f - dx) * (1.0f - dy));
+  const T w01 = Elem<T>::from_float((1.0f - dx) * dy);
+  const T w10 = Elem<T>::from_float(dx * (1.0f - dy));
+  const T w11 = Elem<T>::from_float(dx * dy);
+  for (int o = lane; o < rd * rd; o += 32) {
+    const int i = o / rd, j = o - i * rd;
+    // reference accumulation order for output (i,j): samples (i,j), (i,j+1), (i+1,j), (i+1,j+1);
+    // out-of-range samples are skipped there, which equals adding a zero product here only when the
+    // product is exactly +0 — keep the skip to stay bit-identical for -0/NaN inputs.
+    T acc = Elem<T>::zero();
+    const int x1 = xb + i, y1 = yb + j;
+    const bool xin0 = (x1 >= 0 && x1 < w2), xin1 = (x1 + 1 >= 0 && x1 + 1 < w2);
+    const bool yin0 = (y1 >= 0 && y1 < h2), yin1 = (y1 + 1 >= 0 && y1 + 1 < h2);
+    if (xin0 && yin0) acc = Elem<T>::mad(win[i * wn + j], w00, acc);
+    if (xin0 && yin1) acc = Elem<T>::mad(win[i * wn + j + 1], w01, acc);
+    if (xin1 && yin0) acc = Elem<T>::mad(win[(i + 1) * wn + j], w10, acc);
+    if (xin1 && yin1) acc = Elem<T>::mad(win[(i + 1) * wn + j + 1], w11, acc);
+    sout[o * kLookupTX + px] = acc;
+  }
+  __syncwarp();
+}
+
+// grid: (ceil(w1/TX), h1, N); block 256.  out[n][L*rd*rd][h1][w1]
+template <typename T>
+__global__ void __launch_bounds__(kLookupWarps * 32)
+corr_lookup_fwd_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __restrict__ out, int N, int h1, int w1,
+                       int h2, int w2, int num_levels, int r) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int rd = 2 * r + 1, wn = rd + 1, nch = rd * rd;
+  T* sout = reinterpret_cast<T*>(smem_raw);                       // [num_levels*nch][TX]
+  T* swin = sout + size_t(num_levels) * nch * kLookupTX;          // [warps][wn*wn]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x_base = blockIdx.x * kLookupTX, y = blockIdx.y, n = blockIdx.z;
+  const int npx = min(kLookupTX, w1 - x_base);
+  T* win = swin + warp * wn * wn;
+  const size_t plane = size_t(h1) * w1;
+  for (int px = warp; px < npx; px += kLookupWarps) {
+    const int x = x_base + px;
+    const float cx0 = coords[(size_t(n) * 2 + 0) * plane + size_t(y) * w1 + x];
+    const float cy0 = coords[(size_t(n) * 2 + 1) * plane + size_t(y) * w1 + x];
+    float scale = 1.0f;
+    for (int l = 0; l < num_levels; l++) {
+      const int h2l = h2 >> l, w2l = w2 >> l;
+      const T* slice = static_cast<const T*>(levels.p[l]) + ((size_t(n) * h1 + y) * w1 + x) * size_t(h2l) * w2l;
+      lookup_pixel<T>(slice, h2l, w2l, cx0 / scale, cy0 / scale, r, win, sout + size_t(l) * nch * kLookupTX, px, lane);
+      scale *= 2.0f;
+    }
+  }
+  __syncthreads();
+  // coalesced store: each channel row = npx consecutive x
+  const int total = num_levels * nch * kLookupTX;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int ch = idx / kLookupTX, px = idx - ch * kLookupTX;
+    if (px < npx) out[(size_t(n) * num_levels * nch + ch) * plane + size_t(y) * w1 + x_base + px] = sout[idx];
+  }
+}
+
+// Backward: one warp per source pixel writes the WHOLE h2*w2 slice of volume_grad (zeros outside the
+// window), so no separate memset pass is needed.  Gradient value per window sample follows
+// correlation_kernels.cu:108-121 (g accumulates the 4 contributions in that order, then 0 + g).
+template <typename T>
+__global__ void __launch_bounds__(256)
+corr_lookup_bwd_kernel(const float* __restrict__ coords, const T* __restrict__ corr_grad, T* __restrict__ volume_grad,
+                       int N, int h1, int w1, int h2, int w2, int r) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int rd = 2 * r + 1, nch = rd * rd;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  T* sg = reinterpret_cast<T*>(smem_raw) + warp * nch;  // this pixel's rd*rd incoming grads
+  const size_t plane = size_t(h1) * w1;
+  const size_t pix = size_t(blockIdx.x) * (blockDim.x >> 5) + warp;
+  if (pix >= size_t(N) * plane) return;
+  const int n = int(pix / plane);
+  const size_t yx = pix - size_t(n) * plane;
+  const float x0 = coords[(size_t(n) * 2 + 0) * plane + yx];
+  const float y0 = coords[(size_t(n) * 2 + 1) * plane + yx];
+  const float fx = floorf(x0), fy = floorf(y0);
+  const float dx = x0 - fx, dy = y0 - fy;
+  const int xb = static_cast<int>(fx) - r, yb = static_cast<int>(fy) - r;
+  for (int o = lane; o < nch; o += 32) sg[o] = corr_grad[(size_t(n) * nch + o) * plane + yx];
+  __syncwarp();
+  const T w11 = Elem<T>::from_float(dx * dy), w10 = Elem<T>::from_float(dx * (1.0f - dy));
+  const T w01 = Elem<T>::from_float((1.0f - dx) * dy), w00 = Elem<T>::from_float((1.0f - dx) * (1.0f - dy));
+  T* slice = volume_grad + pix * size_t(h2) * w2;
+  for (int e = lane; e < h2 * w2; e += 32) {
+    const int y1 = e / w2, x1 = e - y1 * w2;
+    const int i = x1 - xb, j = y1 - yb;
+    T g = Elem<T>::zero();
+    if (i >= 0 && i <= rd && j >= 0 && j <= rd) {
+      if (i > 0 && j > 0) g = Elem<T>::mad(sg[(i - 1) * rd + (j - 1)], w11, g);
+      if (i > 0 && j < rd) g = Elem<T>::mad(sg[(i - 1) * rd + j], w10, g);
+      if (i < rd && j > 0) g = Elem<T>::mad(sg[i * rd + (j - 1)], w01, g);
+      if (i < rd && j < rd) g = Elem<T>::mad(sg[i * rd + j], w00, g);
+    }
+    slice[e] = g;
+  }
+}
+
+template <typename T>
+int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h1, int w1, int h2, int w2, int L, int r,
+               cudaStream_t st) {
+  const int rd = 2 * r + 1, wn = rd + 1;
+  const size_t smem = (size_t(L) * rd * rd * kLookupTX + size_t(kLookupWarps) * wn * wn) * sizeof(T);
+  if (smem > 200 * 1024) return DB200_ERR_ARG;
+  auto kern = corr_lookup_fwd_kernel<T>;
+  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)) != cudaSuccess)
+    return DB200_ERR_CUDA;
+  dim3 grid(cdiv(w1, kLookupTX), h1, N);
+  kern<<<grid, kLookupWarps * 32, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, r);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+template <typename T>
+int launch_bwd(const float* coords, const void* g, void* vg, int N, int h1, int w1, int h2, int w2, int r, cudaStream_t st) {
+  const int rd = 2 * r + 1;
+  const size_t smem = size_t(8) * rd * rd * sizeof(T);
+  const size_t npix = size_t(N) * h1 * w1;
+  corr_lookup_bwd_kernel<T><<<unsigned((npix + 7) / 8), 256, smem, st>>>(coords, static_cast<const T*>(g),
+                                                                        static_cast<T*>(vg), N, h1, w1, h2, w2, r);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+}  // namespace db200
+
+using namespace db200;
+
+extern "C" int db200_corr_pyramid_lookup(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
+                                         int h2, int w2, int num_levels, int radius, int dtype, db200_stream_t stream) {
+  if (!levels || !coords || !out || N < 0 || h1 <= 0 || w1 <= 0 || h2 <= 0 || w2 <= 0 || radius < 0 || radius > 7 ||
+      num_levels < 1 || num_levels > kMaxLevels)
+    return DB200_ERR_ARG;
+  if (N == 0) return DB200_OK;
+  LevelPtrs lv{};
+  for (int l = 0; l < num_levels; l++) {
+    if (!levels[l]) return DB200_ERR_ARG;
+    lv.p[l] = levels[l];
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case DB200_F32: return launch_fwd<float>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
+    case DB200_F16: return launch_fwd<__half>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
+    case DB200_F64: return launch_fwd<double>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
+  }
+  return DB200_ERR_ARG;
+}
+
+extern "C" int db200_corr_index_forward(const void* volume, const float* coords, void* corr, int N, int h1, int w1,
+                                        int h2, int w2, int radius, int dtype, db200_stream_t stream) {
+  const void* lv[1] = {volume};
+  return db200_corr_pyramid_lookup(lv, coords, corr, N, h1, w1, h2, w2, 1, radius, dtype, stream);
+}
+
+extern "C" int db200_corr_index_backward(const float* coords, const void* corr_grad, void* volume_grad, int N, int h1,
+                                         int w1, int h2, int w2, int radius, int dtype, db200_stream_t stream) {
+  if (!coords || !corr_grad || !volume_grad || N < 0 || h1 <= 0 || w1 <= 0 || h2 <= 0 || w2 <= 0 || radius < 0 || radius > 7)
+    return DB200_ERR_ARG;
+  if (N == 0) return DB200_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case DB200_F32: return launch_bwd<float>(coords, corr_grad, volume_grad, N, h1, w1, h2, w2, radius, st);
+    case DB200_F16: return launch_bwd<__half>(coords, corr_grad, volume_grad, N, h1, w1, h2, w2, radius, st);
+    case DB200_F64: return launch_bwd<double>(coords, corr_grad, volume_grad, N, h1, w1, h2, w2, radius, st);
+  }
+  return DB200_ERR_ARG;
+}

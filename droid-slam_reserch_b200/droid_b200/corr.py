@@ -1,0 +1,115 @@
+"""CorrBlock / AltCorrBlock with the reference's public interface (droid_slam/modules/corr.py:22-139),
+running on the sm_100a kernels: one GEMM launch per pyramid level writes every level once
+(corr_volume_pyramid), and one launch produces all 4x49 lookup channels already concatenated
+(corr_pyramid_lookup) instead of 4 launches + torch.cat."""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+import droid_backends
+
+
+class CorrSampler(torch.autograd.Function):
+    """corr.py:6-20 — single-level lookup with autograd (training path)."""
+
+    @staticmethod
+    def forward(ctx, volume, coords, radius):
+        ctx.save_for_backward(volume, coords)
+        ctx.radius = radius
+        corr, = droid_backends.corr_index_forward(volume, coords, radius)
+        return corr
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        volume, coords = ctx.saved_tensors
+        grad_volume, = droid_backends.corr_index_backward(volume, coords, grad_output.contiguous(), ctx.radius)
+        return grad_volume, None, None
+
+
+class CorrBlock:
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=3):
+        self.num_levels, self.radius = num_levels, radius
+        batch, num, dim, ht, wd = fmap1.shape
+        f1 = fmap1.reshape(batch * num, dim, ht, wd).contiguous()
+        f2 = fmap2.reshape(batch * num, dim, ht, wd).contiguous()
+        self.corr_pyramid = droid_backends.corr_volume_pyramid(f1, f2, num_levels)
+
+    @staticmethod
+    def corr(fmap1, fmap2):
+        """all-pairs correlation (corr.py:63-71) -> [batch, num, ht, wd, ht, wd]"""
+        batch, num, dim, ht, wd = fmap1.shape
+        vol, = droid_backends.corr_volume_pyramid(fmap1.reshape(batch * num, dim, ht, wd).contiguous(),
+                                                  fmap2.reshape(batch * num, dim, ht, wd).contiguous(), 1)
+        return vol.view(batch, num, ht, wd, ht, wd)
+
+    def __call__(self, coords):
+        batch, num, ht, wd, _ = coords.shape
+        c = coords.permute(0, 1, 4, 2, 3).contiguous().view(batch * num, 2, ht, wd)
+        if torch.is_grad_enabled() and any(v.requires_grad for v in self.corr_pyramid):
+            outs = [CorrSampler.apply(self.corr_pyramid[i], c / 2 ** i, self.radius).view(batch, num, -1, ht, wd)
+                    for i in range(self.num_levels)]
+            return torch.cat(outs, dim=2)
+        out = droid_backends.corr_pyramid_lookup(self.corr_pyramid, c, self.radius)
+        return out.view(batch, num, -1, ht, wd)
+
+    def cat(self, other):
+        for i in range(self.num_levels):
+            self.corr_pyramid[i] = torch.cat([self.corr_pyramid[i], other.corr_pyramid[i]], 0)
+        return self
+
+    def __getitem__(self, index):
+        for i in range(self.num_levels):
+            self.corr_pyramid[i] = self.corr_pyramid[i][index].contiguous()
+        return self
+
+
+class CorrLayer(torch.autograd.Function):
+    """corr.py:74-88"""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, coords, r):
+        ctx.r = r
+        ctx.save_for_backward(fmap1, fmap2, coords)
+        corr, = droid_backends.altcorr_forward(fmap1, fmap2, coords, r)
+        return corr
+
+    @staticmethod
+    def backward(ctx, grad_corr):
+        fmap1, fmap2, coords = ctx.saved_tensors
+        g1, g2, gc = droid_backends.altcorr_backward(fmap1, fmap2, coords, grad_corr.contiguous(), ctx.r)
+        return g1, g2, gc, None
+
+
+class AltCorrBlock:
+    def __init__(self, fmaps, num_levels=4, radius=3):
+        self.num_levels, self.radius = num_levels, radius
+        B, N, C, H, W = fmaps.shape
+        fmaps = fmaps.view(B * N, C, H, W) / 4.0
+        self.pyramid = []
+        for i in range(num_levels):
+            self.pyramid.append(fmaps.permute(0, 2, 3, 1).contiguous().view(B, N, H // 2 ** i, W // 2 ** i, C))
+            fmaps = F.avg_pool2d(fmaps, 2, stride=2)
+
+    def corr_fn(self, coords, ii, jj):
+        B, N, H, W, S, _ = coords.shape
+        coords = coords.permute(0, 1, 4, 2, 3, 5)
+        out = []
+        for i in range(self.num_levels):
+            f1 = self.pyramid[0][:, ii]
+            f2 = self.pyramid[i][:, jj]
+            ci = (coords / 2 ** i).reshape(B * N, S, H, W, 2).contiguous()
+            f1 = f1.reshape((B * N,) + f1.shape[2:]).float().contiguous()
+            f2 = f2.reshape((B * N,) + f2.shape[2:]).float().contiguous()
+            corr = CorrLayer.apply(f1, f2, ci, self.radius)
+            out.append(corr.view(B, N, S, -1, H, W).permute(0, 1, 3, 4, 5, 2))
+        return torch.cat(out, dim=2)
+
+    def __call__(self, coords, ii, jj):
+        squeeze = coords.dim() == 5
+        if squeeze:
+            coords = coords.unsqueeze(dim=-2)
+        corr = self.corr_fn(coords, ii, jj)
+        if squeeze:
+            corr = corr.squeeze(dim=-1)
+        return corr.contiguous()

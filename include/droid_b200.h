@@ -1,0 +1,119 @@
+/* droid_b200.h — C-ABI of the B200-native DROID-SLAM hot path (libdroid_b200.so).
+ *
+ * Every entry point replaces one operator of the reference's pybind module `droid_backends`
+ * (/root/reference/src/droid.cpp:237-250) or one PyTorch step of droid_slam/modules/corr.py.
+ * Conventions: plain device pointers + sizes, an explicit cudaStream_t (passed as void*), no
+ * allocation, no exceptions, no torch types.  All tensors are contiguous (droid.cpp:84-85).
+ * Return value: 0 = ok; <0 = invalid argument / CUDA error (nothing useful was computed);
+ * Launches are asynchronous on `stream`.
+ */
+#ifndef DROID_B200_H
+#define DROID_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DB200_OK 0
+#define DB200_ERR_ARG (-1)      /* null pointer / negative size / unsupported dtype or radius */
+#define DB200_ERR_CUDA (-2)     /* a CUDA runtime call or launch failed */
+#define DB200_ERR_WORKSPACE (-3)/* workspace too small */
+#define DB200_ERR_INDEX (-4)    /* (device status) edge index out of range */
+#define DB200_ERR_ETA (-5)      /* (device status) eta rows != |unique(cat(arange(t0,t1), ii))| */
+
+#define DB200_F32 0
+#define DB200_F16 1
+#define DB200_F64 2
+
+typedef void* db200_stream_t; /* cudaStream_t */
+
+int db200_version(void);
+const char* db200_status_string(int status);
+
+/* ---- correlation lookup ------------------------------------------------------------------
+ * corr_index_forward  (droid.cpp:170-178, correlation_kernels.cu:20-70,126-155)
+ *   volume[N,h1,w1,h2,w2] (dtype), coords[N,2,h1,w1] f32 (x then y) -> corr[N,2r+1,2r+1,h1,w1] (dtype),
+ *   first output axis = x offset.  corr is fully overwritten. */
+int db200_corr_index_forward(const void* volume, const float* coords, void* corr, int N, int h1, int w1,
+                             int h2, int w2, int radius, int dtype, db200_stream_t stream);
+/* corr_index_backward (droid.cpp:180-191, correlation_kernels.cu:73-124,157-185)
+ *   corr_grad[N,2r+1,2r+1,h1,w1] -> volume_grad[N,h1,w1,h2,w2], fully overwritten (zeros outside windows). */
+int db200_corr_index_backward(const float* coords, const void* corr_grad, void* volume_grad, int N, int h1,
+                              int w1, int h2, int w2, int radius, int dtype, db200_stream_t stream);
+/* CorrBlock.__call__ fused (corr.py:40-50): all `num_levels` lookups + the channel concat in one launch.
+ *   levels[l] = device pointer of volume level l [N,h1,w1,h2>>l,w2>>l]; coords are LEVEL-0 coords
+ *   (the kernel divides by 2^l);  out[N, num_levels*(2r+1)^2, h1, w1]. */
+int db200_corr_pyramid_lookup(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
+                              int h2, int w2, int num_levels, int radius, int dtype, db200_stream_t stream);
+
+/* ---- all-pairs correlation volume + pyramid (corr.py:30-38,63-71) ---------------------------
+ *   fmap1,fmap2[N,C,ht,wd] (dtype f16 or f32) -> levels_out[l][N,ht,wd,ht>>l,wd>>l] (same dtype),
+ *   corr = (f1/4)^T (f2/4), level l+1 = avg_pool2d(level l, 2) — computed as f1^T pool(f2) (linear);
+ *   `workspace` (db200_corr_volume_workspace_bytes) holds the pooled copies of fmap2. */
+size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd, int num_levels, int dtype);
+int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C,
+                              int ht, int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
+                              db200_stream_t stream);
+
+/* ---- low-memory correlation (altcorr) ------------------------------------------------------
+ * altcorr_forward (droid.cpp:193-203, altcorr_kernel.cu:27-149,290-319), fp32:
+ *   fmap1[B,H1,W1,C], fmap2[B,H2,W2,C], coords[B,S,H1,W1,2] -> corr[B,S,(2r+1)^2,H1,W1], channel = iy + (2r+1)*ix */
+int db200_altcorr_forward(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B, int S,
+                          int H1, int W1, int H2, int W2, int C, int radius, db200_stream_t stream);
+/* altcorr_backward (droid.cpp:205-217, altcorr_kernel.cu:152-286,321-355): fmap1_grad, fmap2_grad fully
+ * overwritten; coords_grad[B,S,H1,W1,2] is zero-filled like the reference (:340). */
+int db200_altcorr_backward(const float* fmap1, const float* fmap2, const float* coords, const float* corr_grad,
+                           float* fmap1_grad, float* fmap2_grad, float* coords_grad, int B, int S, int H1, int W1,
+                           int H2, int W2, int C, int radius, db200_stream_t stream);
+
+/* ---- frame_distance (droid.cpp:120-136, droid_kernels.cu:518-657,1438-1460) ----------------- */
+int db200_frame_distance(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                         const int64_t* jj, int K, int n_poses, int B, int ht, int wd, float beta, float* dist,
+                         db200_stream_t stream);
+
+/* ---- iproj / depth_filter (droid.cpp:157-167,220-234, droid_kernels.cu:661-850) ------------- */
+int db200_iproj(const float* poses, const float* disps, const float* intrinsics, int num, int ht, int wd,
+                float* points, db200_stream_t stream);
+int db200_depth_filter(const float* poses, const float* disps, const float* intrinsics, const int64_t* inds,
+                       const float* thresh, int n_inds, int num, int ht, int wd, float* counter,
+                       db200_stream_t stream);
+
+/* ---- dense bundle adjustment (droid.cpp:88-117, droid_kernels.cu:1314-1434) -------------------
+ * poses[B,7] and disps[B,ht,wd] are updated IN PLACE.  dx_out[P,6], dz_out[M,ht*wd] receive the last
+ * iteration's updates (dz_out may be NULL when motion_only).  `eta_rows` = eta.shape[0] = M.
+ * `workspace` must hold db200_ba_workspace_bytes(...) bytes; its first int is a device status word
+ * (0 ok, DB200_ERR_INDEX, DB200_ERR_ETA, 1 = Cholesky broke down in some iteration -> zero pose update,
+ * like droid_kernels.cu:1207-1210) which db200_ba_status() copies back (synchronises the stream). */
+size_t db200_ba_workspace_bytes(int N, int B, int ht, int wd, int t0, int t1, int eta_rows, int motion_only);
+int db200_ba(float* poses, float* disps, const float* intrinsics, const float* disps_sens, const float* targets,
+             const float* weights, const float* eta, const int64_t* ii, const int64_t* jj, int N, int B, int ht,
+             int wd, int t0, int t1, int iterations, float lm, float ep, int motion_only, int eta_rows,
+             float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes, db200_stream_t stream);
+int db200_ba_status(const void* workspace, db200_stream_t stream);
+
+/* Phase-split BA for edge-sharded multi-GPU runs.  One iteration =
+ *   db200_ba_accumulate  : local edges -> this rank's partial reduced system Hb = [H (n x n, row-major,
+ *                          lower+upper), b (n)] in fp64, n = 6*(t1-t0);   (first call builds the graph)
+ *   <allreduce(sum) of Hb over ranks — NCCL, done by the caller>
+ *   db200_ba_solve_update: damped Cholesky solve, pose retraction (all poses), depth back-substitution
+ *                          and disparity update for the LOCAL source frames.
+ * `Hb` points into the workspace: db200_ba_system_ptr(). */
+int db200_ba_accumulate(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                        const float* targets, const float* weights, const float* eta, const int64_t* ii,
+                        const int64_t* jj, int N, int B, int ht, int wd, int t0, int t1, int motion_only,
+                        int eta_rows, int first_iteration, void* workspace, size_t workspace_bytes,
+                        db200_stream_t stream);
+int db200_ba_solve_update(float* poses, float* disps, const float* intrinsics, const float* targets,
+                          const float* weights, const int64_t* ii, const int64_t* jj, int N, int B, int ht, int wd,
+                          int t0, int t1, float lm, float ep, int motion_only, int eta_rows, float* dx_out,
+                          float* dz_out, void* workspace, size_t workspace_bytes, db200_stream_t stream);
+double* db200_ba_system_ptr(void* workspace, int N, int B, int ht, int wd, int t0, int t1, int eta_rows,
+                            int motion_only);
+size_t db200_ba_system_elems(int t0, int t1);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DROID_B200_H */

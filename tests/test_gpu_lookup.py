@@ -1,0 +1,133 @@
+"""GPU parity: correlation lookups / altcorr / corr volume vs the CPU oracle (through droid_backends -> C-ABI)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _coords(N, h1, w1, h2, w2, seed, spread=1.3):
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-0.3 * w2, spread * w2, (N, 1, h1, w1))
+    y = rng.uniform(-0.3 * h2, spread * h2, (N, 1, h1, w1))
+    c = np.concatenate([x, y], 1).astype(np.float32)
+    c[0, :, 0, 0] = [3.0, 5.0]          # exactly integer coordinates
+    c[0, :, 0, 1] = [-50.0, 1e4]        # fully outside
+    return c
+
+
+@pytest.mark.parametrize("dtype,shape", [(np.float32, (3, 12, 16, 12, 16)), (np.float16, (2, 12, 16, 12, 16)),
+                                         (np.float16, (1, 48, 64, 48, 64)), (np.float32, (2, 5, 7, 9, 11))])
+def test_corr_index_forward_bit_exact(dtype, shape):
+    import droid_backends
+    from oracle import oracle
+    N, h1, w1, h2, w2 = shape
+    rng = np.random.default_rng(1)
+    vol = rng.normal(0, 1, shape).astype(dtype)
+    co = _coords(N, h1, w1, h2, w2, 2)
+    ref = oracle.corr_index_forward(vol, co, 3)
+    out, = droid_backends.corr_index_forward(torch.from_numpy(vol).cuda(), torch.from_numpy(co).cuda(), 3)
+    assert out.shape == ref.shape
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint16 if dtype == np.float16 else np.uint32),
+                                  ref.view(np.uint16 if dtype == np.float16 else np.uint32))
+
+
+def test_corr_index_forward_f64():
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(3)
+    vol = rng.normal(0, 1, (2, 6, 8, 6, 8))
+    co = _coords(2, 6, 8, 6, 8, 4)
+    out, = droid_backends.corr_index_forward(torch.from_numpy(vol).cuda(), torch.from_numpy(co).cuda(), 3)
+    ref = oracle.corr_index_forward(vol.astype(np.float32), co, 3)
+    np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=1e-5, atol=1e-6)
+
+
+def test_corr_pyramid_lookup_matches_per_level():
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(5)
+    N, h, w = 3, 16, 24
+    levels = [rng.normal(0, 1, (N, h, w, h >> l, w >> l)).astype(np.float16) for l in range(4)]
+    co = _coords(N, h, w, h, w, 6)
+    ref = np.concatenate([oracle.corr_index_forward(levels[l], (co / 2 ** l).astype(np.float32), 3).reshape(N, 49, h, w)
+                          for l in range(4)], 1)
+    out = droid_backends.corr_pyramid_lookup([torch.from_numpy(v).cuda() for v in levels], torch.from_numpy(co).cuda(), 3)
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint16), ref.view(np.uint16))
+
+
+@pytest.mark.parametrize("shape", [(2, 12, 16, 12, 16), (1, 7, 9, 5, 6)])
+def test_corr_index_backward_bit_exact(shape):
+    import droid_backends
+    from oracle import oracle
+    N, h1, w1, h2, w2 = shape
+    rng = np.random.default_rng(7)
+    co = _coords(N, h1, w1, h2, w2, 8)
+    g = rng.normal(0, 1, (N, 7, 7, h1, w1)).astype(np.float32)
+    ref = oracle.corr_index_backward(shape, co, g, 3)
+    vol = torch.zeros(shape, device="cuda")
+    out, = droid_backends.corr_index_backward(vol, torch.from_numpy(co).cuda(), torch.from_numpy(g).cuda(), 3)
+    np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+
+
+@pytest.mark.parametrize("B,S,H,W,H2,W2,C", [(2, 1, 12, 16, 12, 16, 128), (1, 2, 6, 9, 3, 4, 32), (1, 1, 48, 64, 24, 32, 128)])
+def test_altcorr_forward(B, S, H, W, H2, W2, C):
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(9)
+    f1 = rng.normal(0, 1, (B, H, W, C)).astype(np.float32)
+    f2 = rng.normal(0, 1, (B, H2, W2, C)).astype(np.float32)
+    co = np.stack([_coords(B, H, W, H2, W2, 10 + s) for s in range(S)], 1).transpose(0, 1, 3, 4, 2).copy()
+    ref = oracle.altcorr_forward(f1, f2, co, 3)
+    out, = droid_backends.altcorr_forward(torch.from_numpy(f1).cuda(), torch.from_numpy(f2).cuda(), torch.from_numpy(co).cuda(), 3)
+    scale = np.sqrt(C)   # typical magnitude of a dot product of N(0,1) features
+    assert np.abs(out.cpu().numpy() - ref).max() <= 1e-4 * scale   # north_star: 1e-4 relative on fp32 correlation values
+
+
+def test_altcorr_backward():
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(11)
+    B, S, H, W, C = 2, 1, 8, 12, 64
+    f1 = rng.normal(0, 1, (B, H, W, C)).astype(np.float32)
+    f2 = rng.normal(0, 1, (B, H, W, C)).astype(np.float32)
+    co = _coords(B, H, W, H, W, 12)[:, None].transpose(0, 1, 3, 4, 2).copy()
+    g = rng.normal(0, 1, (B, S, 49, H, W)).astype(np.float32)
+    r1, r2, _ = oracle.altcorr_backward(f1, f2, co, g, 3)
+    t = lambda a: torch.from_numpy(a).cuda()
+    g1, g2, gc = droid_backends.altcorr_backward(t(f1), t(f2), t(co), t(g), 3)
+    for a, b in ((g1, r1), (g2, r2)):
+        assert np.abs(a.cpu().numpy() - b).max() <= 1e-4 * np.abs(b).max()
+    assert float(gc.abs().max()) == 0.0 and gc.shape == (B, S, H, W, 2)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float16])
+def test_corr_volume_pyramid(dtype):
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(13)
+    N, C, ht, wd = 2, 128, 16, 24
+    f1 = rng.normal(0, 1, (N, C, ht, wd)).astype(dtype)
+    f2 = rng.normal(0, 1, (N, C, ht, wd)).astype(dtype)
+    ref = oracle.corr_volume(f1.astype(np.float32), f2.astype(np.float32))
+    outs = droid_backends.corr_volume_pyramid(torch.from_numpy(f1).cuda(), torch.from_numpy(f2).cuda(), 4)
+    scale = np.sqrt(C) / 16.0
+    tol = 1e-4 if dtype == np.float32 else 3e-3   # fp16 storage: ~2 ulp of the output
+    for l in range(4):
+        assert outs[l].shape == ref[l].shape
+        assert np.abs(outs[l].float().cpu().numpy() - ref[l]).max() <= tol * scale * 4, l
+
+
+def test_altcorr_equals_lookup_of_volume():
+    """SURVEY §8c cross-check: altcorr == corr_index o corr on the same features."""
+    import droid_backends
+    rng = np.random.default_rng(15)
+    N, C, ht, wd = 2, 128, 12, 16
+    f1 = torch.from_numpy(rng.normal(0, 1, (N, C, ht, wd)).astype(np.float32)).cuda()
+    f2 = torch.from_numpy(rng.normal(0, 1, (N, C, ht, wd)).astype(np.float32)).cuda()
+    co = torch.from_numpy(_coords(N, ht, wd, ht, wd, 16)).cuda()
+    vol, = droid_backends.corr_volume_pyramid(f1, f2, 1)
+    a, = droid_backends.corr_index_forward(vol, co, 3)
+    b, = droid_backends.altcorr_forward((f1 / 4).permute(0, 2, 3, 1).contiguous(), (f2 / 4).permute(0, 2, 3, 1).contiguous(),
+                                        co.permute(0, 2, 3, 1).contiguous()[:, None], 3)
+    assert float((a.reshape(N, 49, ht, wd) - b[:, 0]).abs().max()) <= 1e-4 * np.sqrt(C) / 16 * 4
