@@ -171,7 +171,7 @@ extern "C" int db200_altcorr_backward(const float* fmap1, const float* fmap2, co
     return DB200_ERR_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (B == 0) return DB200_OK;
-  if (cudaMemsetAsync(fmap2_grad, 0, sizeof(float) * size_t(B) * H2 * W2 * C, st) != cudaSuccess) return DB200_ERR_CUDA;
+  DB200_CUDA(cudaMemsetAsync(fmap2_grad, 0, sizeof(float) * size_t(B) * H2 * W2 * C, st));
   if (coords_grad && S > 0 &&
       cudaMemsetAsync(coords_grad, 0, sizeof(float) * size_t(B) * S * H1 * W1 * 2, st) != cudaSuccess)
     return DB200_ERR_CUDA;

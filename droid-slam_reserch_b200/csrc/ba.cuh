@@ -18,7 +18,7 @@ namespace db200 {
 
 constexpr int kBAThreads = 256;       // threads per CTA of the frame kernels = pixels per sub-tile
 constexpr int kEStride = kBAThreads + 1;  // padded pixel stride of the E stash (bank-conflict free)
-constexpr int kMaxDeg = 31;           // max pose edges per source frame on the fused path
+constexpr int kMaxDeg = 28;           // max pose edges per source frame on the fused path
 constexpr int kRec = 16;              // floats per edge record
 
 // per-edge record (recomputed every iteration from the current poses), indexed by SORTED position

@@ -1,6 +1,7 @@
 // ba_api.cu — C-ABI of the dense bundle adjustment (see include/droid_b200.h).
 // Mirrors droid_backends.ba (/root/reference/src/droid.cpp:88-117, droid_kernels.cu:1314-1434): in-place
 // update of poses/disps, `iterations` Gauss-Newton steps, returns dx/dz of the last step.
+#include <cstdio>
 #include "ba.cuh"
 
 using namespace db200;
@@ -105,10 +106,16 @@ extern "C" int db200_ba_status(const void* workspace, db200_stream_t stream) {
   if (!workspace) return DB200_ERR_ARG;
   BAHeader h{};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (cudaMemcpyAsync(&h, workspace, sizeof(BAHeader), cudaMemcpyDeviceToHost, st) != cudaSuccess) return DB200_ERR_CUDA;
-  if (cudaStreamSynchronize(st) != cudaSuccess) return DB200_ERR_CUDA;
+  DB200_CUDA(cudaMemcpyAsync(&h, workspace, sizeof(BAHeader), cudaMemcpyDeviceToHost, st));
+  DB200_CUDA(cudaStreamSynchronize(st));
   return h.status;
 }
+
+static char g_last_err[256] = "none";
+extern "C" void db200_note_cuda_error(int code, const char* file, int line) {
+  snprintf(g_last_err, sizeof(g_last_err), "%s (%d) at %s:%d", cudaGetErrorString(cudaError_t(code)), code, file, line);
+}
+extern "C" const char* db200_last_cuda_error(void) { return g_last_err; }
 
 extern "C" int db200_version(void) { return 100; }
 
@@ -116,7 +123,7 @@ extern "C" const char* db200_status_string(int s) {
   switch (s) {
     case DB200_OK: return "ok";
     case 1: return "Cholesky breakdown in at least one iteration: zero pose update applied (reference behaviour)";
-    case DB200_ERR_ARG: return "invalid argument (null pointer, bad size, unsupported dtype/radius, or >31 pose edges share a source frame)";
+    case DB200_ERR_ARG: return "invalid argument (null pointer, bad size, unsupported dtype/radius, or >28 pose edges share a source frame)";
     case DB200_ERR_CUDA: return "CUDA runtime error";
     case DB200_ERR_WORKSPACE: return "workspace too small";
     case DB200_ERR_INDEX: return "edge index out of range [0, t1)";

@@ -449,15 +449,14 @@ template <int PPT, bool MOTION>
 static int launch_frames(const BAParams& p, int S, int dlo, int dcap, cudaStream_t st) {
   const size_t smem = frame_smem_bytes(dcap, MOTION);
   auto kern = ba_frame_kernel<PPT, MOTION>;
-  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)) != cudaSuccess)
-    return DB200_ERR_CUDA;
+  if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
   kern<<<p.Mcap * S, kBAThreads, smem, st>>>(p, S, dlo, dcap);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
 
 int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
-  if (cudaMemsetAsync(p.Hb, 0, sizeof(double) * (size_t(p.n) * p.n + p.n), st) != cudaSuccess) return DB200_ERR_CUDA;
+  DB200_CUDA(cudaMemsetAsync(p.Hb, 0, sizeof(double) * (size_t(p.n) * p.n + p.n), st));
   const int nsub = cdiv(p.HW, kBAThreads);
   int S = cdiv(4 * kNumSMs, p.Mcap);               // aim at >= ~4 CTAs per SM
   S = S < 1 ? 1 : (S > nsub ? nsub : S);

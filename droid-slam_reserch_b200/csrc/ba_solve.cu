@@ -251,8 +251,7 @@ int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   const size_t upd_smem = sizeof(double) * 2 * 128 * (NB + 1);
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(upd_smem)) != cudaSuccess)
-      return DB200_ERR_CUDA;
+    DB200_CUDA(cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(upd_smem)));
     attr_set = true;
   }
   for (int k = 0; k < nt; k++) {

@@ -5,10 +5,24 @@
 #include <stdint.h>
 #include "../../include/droid_b200.h"
 
+// last CUDA error seen by the library (for db200_last_cuda_error()); defined in ba_api.cu
+extern "C" void db200_note_cuda_error(int code, const char* file, int line);
+
 #define DB200_CHECK_LAUNCH()                                   \
   do {                                                         \
     cudaError_t e__ = cudaGetLastError();                      \
-    if (e__ != cudaSuccess) return DB200_ERR_CUDA;             \
+    if (e__ != cudaSuccess) {                                  \
+      db200_note_cuda_error(int(e__), __FILE__, __LINE__);     \
+      return DB200_ERR_CUDA;                                   \
+    }                                                          \
+  } while (0)
+#define DB200_CUDA(call)                                       \
+  do {                                                         \
+    cudaError_t e__ = (call);                                  \
+    if (e__ != cudaSuccess) {                                  \
+      db200_note_cuda_error(int(e__), __FILE__, __LINE__);     \
+      return DB200_ERR_CUDA;                                   \
+    }                                                          \
   } while (0)
 
 namespace db200 {

@@ -144,8 +144,7 @@ int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h
   const size_t smem = (size_t(L) * rd * rd * kLookupTX + size_t(kLookupWarps) * wn * wn) * sizeof(T);
   if (smem > 200 * 1024) return DB200_ERR_ARG;
   auto kern = corr_lookup_fwd_kernel<T>;
-  if (smem > 48 * 1024 && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)) != cudaSuccess)
-    return DB200_ERR_CUDA;
+  if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
   dim3 grid(cdiv(w1, kLookupTX), h1, N);
   kern<<<grid, kLookupWarps * 32, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, r);
   DB200_CHECK_LAUNCH();

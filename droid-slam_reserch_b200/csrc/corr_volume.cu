@@ -46,7 +46,8 @@ corr_gemm_f16_kernel(const __half* __restrict__ f1, const __half* __restrict__ f
   if (m0 >= M || n0 >= N2) return;
   const __half* A = f1 + size_t(n) * C * M;     // A(m,k) = A[k*M + m]
   const __half* B = f2 + size_t(n) * C * N2;    // B(k,j) = B[k*N2 + j]
-  const bool full = (m0 + 32 <= M) && (n0 + 32 <= N2);
+  // wmma loads need 16-byte aligned rows: leading dimensions must be multiples of 8 halfs
+  const bool full = (m0 + 32 <= M) && (n0 + 32 <= N2) && (M % 8 == 0) && (N2 % 8 == 0);
   float* st = stage[warp];
   if (full) {
     wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][2];
@@ -148,7 +149,7 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
   for (int l = 0; l < num_levels; l++) if (!levels_out[l]) return DB200_ERR_ARG;
   if (num_levels > 1 && (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)))
     return DB200_ERR_WORKSPACE;
-  if (dtype == DB200_F16 && ((ht * wd) % 8 != 0 || C % 16 != 0)) return DB200_ERR_ARG;
+  if (dtype == DB200_F16 && C % 16 != 0) return DB200_ERR_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t es = dtype == DB200_F16 ? 2 : 4;
   const int M = ht * wd;
@@ -170,9 +171,6 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
     }
     const int N2 = h * w;
     if (dtype == DB200_F16) {
-      if (N2 % 8 != 0) {
-        return DB200_ERR_ARG;
-      }
       dim3 grid(cdiv(N2, 128), cdiv(M, 64), N);
       corr_gemm_f16_kernel<<<grid, 256, 0, st>>>(static_cast<const __half*>(fmap1), static_cast<const __half*>(src),
                                                  static_cast<__half*>(levels_out[l]), C, M, N2);

@@ -19,6 +19,7 @@ _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
 _SIGNATURES = {
     "db200_version": (_i, []),
     "db200_status_string": (C.c_char_p, [_i]),
+    "db200_last_cuda_error": (C.c_char_p, []),
     "db200_corr_index_forward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_corr_index_backward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_corr_pyramid_lookup": (_i, [C.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
@@ -63,5 +64,6 @@ def status_string(code: int) -> str:
 
 def check(code: int, what: str):
     if code < 0:
-        raise RuntimeError(f"{what}: {status_string(code)} (status {code})")
+        extra = f"; last CUDA error: {lib().db200_last_cuda_error().decode()}" if code == -2 else ""
+        raise RuntimeError(f"{what}: {status_string(code)} (status {code}){extra}")
     return code

@@ -31,6 +31,7 @@ typedef void* db200_stream_t; /* cudaStream_t */
 
 int db200_version(void);
 const char* db200_status_string(int status);
+const char* db200_last_cuda_error(void); /* text of the last CUDA error the library saw (diagnostics) */
 
 /* ---- correlation lookup ------------------------------------------------------------------
  * corr_index_forward  (droid.cpp:170-178, correlation_kernels.cu:20-70,126-155)

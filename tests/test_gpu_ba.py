@@ -37,25 +37,41 @@ def check_chained(p, iters, lm, ep, motion_only=False, rtol=RTOL):
     iterations (which validity flips at the MIN_DEPTH plane can amplify) does not enter the comparison."""
     import copy
     q = copy.copy(p)
+    floor = None
     for _ in range(iters):
-        check(q, 1, lm, ep, motion_only, rtol)
+        _, _, n0 = check(q, 1, lm, ep, motion_only, rtol, floor)
+        floor = floor or 1e-2 * n0
         ref = run_oracle(q, 1, lm, ep, motion_only)
         q = copy.copy(q)
         q.poses, q.disps = ref["poses"], ref["disps"]
 
 
-def check(p, iters, lm, ep, motion_only=False, rtol=RTOL):
+def check(p, iters, lm, ep, motion_only=False, rtol=RTOL, floor=None):
+    """GPU vs oracle(fp32).  Tolerance: the north_star's 1e-4 normwise, widened only where the reference's own
+    fp32 arithmetic is less reproducible than that: tol = max(rtol, 2 * ||oracle_f32 - oracle_f64|| / ||oracle_f64||).
+    `floor` (absolute) keeps the relative error meaningful once dx has converged to round-off level."""
+    from oracle import oracle
     poses, disps, dx, dz = run_gpu(p, iters, lm, ep, motion_only)
     ref = run_oracle(p, iters, lm, ep, motion_only)
-    assert rel(dx, ref["dx"]) <= rtol, ("dx", rel(dx, ref["dx"]))
-    dpose = poses - p.poses
-    assert rel(dpose, ref["poses"] - p.poses) <= rtol
+    r64 = oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target, p.weight, p.eta, p.ii, p.jj, p.t0, p.t1,
+                    iters, lm, ep, motion_only=motion_only, dtype=np.float64)
+    fl = floor or 0.0
+
+    def relf(a, b):
+        a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+        return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), fl, 1e-30))
+
+    tol_x = max(rtol, 2 * relf(ref["dx"], r64["dx"]))
+    assert relf(dx, ref["dx"]) <= tol_x, ("dx", relf(dx, ref["dx"]), tol_x)
+    move = np.abs(ref["poses"] - p.poses).max()
+    assert np.abs(poses - ref["poses"]).max() <= tol_x * max(move, fl) + 1e-6
     if not motion_only:
-        assert rel(dz, ref["dz"]) <= rtol, ("dz", rel(dz, ref["dz"]))
-        assert rel(disps - p.disps, ref["disps"] - p.disps) <= rtol
+        tol_z = max(rtol, 2 * relf(ref["dz"], r64["dz"]))
+        assert relf(dz, ref["dz"]) <= tol_z, ("dz", relf(dz, ref["dz"]), tol_z)
+        assert np.abs(disps - ref["disps"]).max() <= tol_z * np.abs(ref["disps"] - p.disps).max() + 1e-6
     else:
         np.testing.assert_array_equal(disps, p.disps)
-    return poses, disps
+    return poses, disps, float(np.linalg.norm(ref["dx"]))
 
 
 def test_ba_c1():
@@ -71,7 +87,7 @@ def test_ba_c1_stereo_sensor_invalid():
     ii = np.concatenate([ii, np.arange(8)]); jj = np.concatenate([jj, np.arange(8)])
     p = synth.make_ba_problem(ii, jj, 8, seed=77, sensor_frac=0.5, invalid_frac=0.05)
     check_chained(p, 2, 1e-4, 0.1)
-    check(p, 2, 1e-4, 0.1, rtol=2e-3)   # 2 chained iterations: fp32 round-off flips validity tests (oracle f32 vs f64: 3e-4)
+    check(p, 2, 1e-4, 0.1)
 
 
 def test_ba_c2_window():
@@ -168,7 +184,7 @@ def test_frame_distance_bit_exact(beta):
     ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
     ii, jj = ii.reshape(-1).astype(np.int64), jj.reshape(-1).astype(np.int64)
     disps = p.disps.copy()
-    disps[3] *= 40.0   # pushes most points of frame 3 behind the MIN_DEPTH plane -> 1000.0 branch
+    disps[3] = 1e3     # frame 3's points land behind / within MIN_DEPTH of most other cameras -> 1000.0 branch
     ref = oracle.frame_distance(p.poses, disps, p.intrinsics, ii, jj, beta)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
     out = droid_backends.frame_distance(t(p.poses), t(disps), t(p.intrinsics), t(ii), t(jj), beta).cpu().numpy()
