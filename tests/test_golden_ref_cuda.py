@@ -1,0 +1,158 @@
+"""Golden vectors produced by the REFERENCE's own CUDA extension on a B200 (tests/golden/make_ref_cuda_golden.py,
+fixture tests/golden/ref_cuda_golden.npz).  CPU tests pin the oracle to them; gpu tests pin the sm_100a kernels."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+Z = np.load(os.path.join(HERE, "golden", "ref_cuda_golden.npz"))
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def bits(a):
+    return a.view(np.uint16 if a.dtype == np.float16 else np.uint32)
+
+
+def _fd_inputs():
+    from droid_b200 import synth
+    p = synth.config_c2()
+    n = p.t1
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    d = p.disps.copy(); d[3] = 1e3
+    return p, d, ii.reshape(-1).astype(np.int64), jj.reshape(-1).astype(np.int64)
+
+
+# ------------------------------------------------------------------------------------------ oracle (CPU)
+@pytest.mark.parametrize("case", ["c1", "c1s", "c2", "c2b"])
+def test_oracle_ba_vs_reference_cuda(case):
+    import make_ref_cuda_golden as G
+    from oracle import oracle
+    p, lm, ep, _ = G.ba_cases()[case]
+    # one Gauss-Newton iteration: 1e-4 normwise (north_star); two chained iterations: fp32 round-off compounds
+    for it, tol in ((1, 1e-4), (2, 3e-4)):
+        r = oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target, p.weight, p.eta, p.ii, p.jj, p.t0, p.t1, it, lm, ep)
+        assert rel(r["dx"], Z[f"ba_{case}_it{it}_dx"]) <= tol
+        assert rel(r["dz"], Z[f"ba_{case}_it{it}_dz"]) <= tol
+        assert np.abs(r["poses"][:p.t1] - Z[f"ba_{case}_it{it}_poses"]).max() <= 5e-6
+
+
+def test_oracle_moba_vs_reference_cuda():
+    import make_ref_cuda_golden as G
+    from oracle import oracle
+    p = G.moba_case()
+    r = oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target, p.weight, p.eta, p.ii, p.jj, p.t0, p.t1, 1, 1e-4, .1,
+                  motion_only=True)
+    assert rel(r["dx"], Z["moba_it1_dx"]) <= 1e-4
+    assert np.abs(r["poses"] - Z["moba_it1_poses"]).max() <= 5e-6
+
+
+@pytest.mark.parametrize("beta", [0.3, 0.25])
+def test_oracle_frame_distance_bit_exact_vs_reference_cuda(beta):
+    from oracle import oracle
+    p, d, ii, jj = _fd_inputs()
+    o = oracle.frame_distance(p.poses, d, p.intrinsics, ii, jj, beta)
+    g = Z[f"fd_beta{beta}"]
+    assert (g == 1000.0).any()
+    np.testing.assert_array_equal(bits(o), bits(g))
+
+
+@pytest.mark.parametrize("tag,shape,dt", [("f16", (2, 12, 16, 12, 16), np.float16), ("f32", (2, 12, 16, 12, 16), np.float32),
+                                          ("f16b", (1, 24, 32, 6, 8), np.float16)])
+def test_oracle_lookup_bit_exact_vs_reference_cuda(tag, shape, dt):
+    import make_ref_cuda_golden as G
+    from oracle import oracle
+    vol, co = G.lookup_inputs(21, shape, dt)
+    np.testing.assert_array_equal(bits(oracle.corr_index_forward(vol, co, 3)), bits(Z[f"lookup_{tag}"]))
+
+
+def test_oracle_lookup_backward_bit_exact_vs_reference_cuda():
+    import make_ref_cuda_golden as G
+    from oracle import oracle
+    vol, co = G.lookup_inputs(22, (2, 12, 16, 12, 16), np.float32)
+    g = np.random.default_rng(23).normal(0, 1, (2, 7, 7, 12, 16)).astype(np.float32)
+    np.testing.assert_array_equal(bits(oracle.corr_index_backward(vol.shape, co, g, 3)), bits(Z["lookup_bwd_f32"]))
+
+
+def test_oracle_altcorr_vs_reference_cuda():
+    import make_ref_cuda_golden as G
+    from oracle import oracle
+    f1, f2, co, g = G.altcorr_inputs(31)
+    o = oracle.altcorr_forward(f1, f2, co, 3)
+    assert np.abs(o - Z["altcorr_fwd"]).max() <= 1e-6 * np.abs(Z["altcorr_fwd"]).max()
+    o1, o2, oc = oracle.altcorr_backward(f1, f2, co, g, 3)
+    assert rel(o1, Z["altcorr_bwd_f1"]) <= 1e-6 and rel(o2, Z["altcorr_bwd_f2"]) <= 1e-6
+    assert float(Z["altcorr_bwd_coords_absmax"]) == 0.0 and not oc.any()
+
+
+# ------------------------------------------------------------------------------------------ kernels (GPU)
+def _t(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["c1", "c1s", "c2", "c2b"])
+def test_kernel_ba_vs_reference_cuda(case):
+    import droid_backends
+    import make_ref_cuda_golden as G
+    p, lm, ep, _ = G.ba_cases()[case]
+    for it, tol in ((1, 1e-4), (2, 3e-4)):
+        poses, disps = _t(p.poses), _t(p.disps)
+        dx, dz = droid_backends.ba(poses, disps, _t(p.intrinsics), _t(p.disps_sens), _t(p.target), _t(p.weight), _t(p.eta),
+                                   _t(p.ii), _t(p.jj), p.t0, p.t1, it, lm, ep, False)
+        assert rel(dx.cpu().numpy(), Z[f"ba_{case}_it{it}_dx"]) <= tol
+        assert rel(dz.cpu().numpy(), Z[f"ba_{case}_it{it}_dz"]) <= tol
+        assert np.abs(poses.cpu().numpy()[:p.t1] - Z[f"ba_{case}_it{it}_poses"]).max() <= 5e-6
+
+
+@pytest.mark.gpu
+def test_kernel_moba_vs_reference_cuda():
+    import droid_backends
+    import make_ref_cuda_golden as G
+    p = G.moba_case()
+    poses, disps = _t(p.poses), _t(p.disps)
+    dx, dz = droid_backends.ba(poses, disps, _t(p.intrinsics), _t(p.disps_sens), _t(p.target), _t(p.weight), _t(p.eta),
+                               _t(p.ii), _t(p.jj), p.t0, p.t1, 1, 1e-4, .1, True)
+    assert dz is None and rel(dx.cpu().numpy(), Z["moba_it1_dx"]) <= 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("beta", [0.3, 0.25])
+def test_kernel_frame_distance_bit_exact_vs_reference_cuda(beta):
+    import droid_backends
+    p, d, ii, jj = _fd_inputs()
+    o = droid_backends.frame_distance(_t(p.poses), _t(d), _t(p.intrinsics), _t(ii), _t(jj), beta).cpu().numpy()
+    np.testing.assert_array_equal(bits(o), bits(Z[f"fd_beta{beta}"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,shape,dt", [("f16", (2, 12, 16, 12, 16), np.float16), ("f32", (2, 12, 16, 12, 16), np.float32),
+                                          ("f16b", (1, 24, 32, 6, 8), np.float16)])
+def test_kernel_lookup_bit_exact_vs_reference_cuda(tag, shape, dt):
+    import droid_backends
+    import make_ref_cuda_golden as G
+    vol, co = G.lookup_inputs(21, shape, dt)
+    o, = droid_backends.corr_index_forward(_t(vol), _t(co), 3)
+    np.testing.assert_array_equal(bits(o.cpu().numpy()), bits(Z[f"lookup_{tag}"]))
+
+
+@pytest.mark.gpu
+def test_kernel_lookup_backward_and_altcorr_vs_reference_cuda():
+    import droid_backends
+    import make_ref_cuda_golden as G
+    vol, co = G.lookup_inputs(22, (2, 12, 16, 12, 16), np.float32)
+    g = np.random.default_rng(23).normal(0, 1, (2, 7, 7, 12, 16)).astype(np.float32)
+    o, = droid_backends.corr_index_backward(_t(vol), _t(co), _t(g), 3)
+    np.testing.assert_array_equal(bits(o.cpu().numpy()), bits(Z["lookup_bwd_f32"]))
+    f1, f2, co, g = G.altcorr_inputs(31)
+    o, = droid_backends.altcorr_forward(_t(f1), _t(f2), _t(co), 3)
+    assert np.abs(o.cpu().numpy() - Z["altcorr_fwd"]).max() <= 1e-4 * np.abs(Z["altcorr_fwd"]).max()
+    g1, g2, gc = droid_backends.altcorr_backward(_t(f1), _t(f2), _t(co), _t(g), 3)
+    assert rel(g1.cpu().numpy(), Z["altcorr_bwd_f1"]) <= 1e-4 and rel(g2.cpu().numpy(), Z["altcorr_bwd_f2"]) <= 1e-4
