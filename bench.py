@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 hot path (dense BA edge-iterations/s; corr lookups/s beside it).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port) on host cores
+
+Workload (BASELINE.json configs[2], the one `north_star` quotes its target on): stereo-EuRoC-shaped global
+backend BA, 512 keyframes, ~6k edges, 48x64 maps, one step = one `droid_backends.ba(..., itrs=2, lm=1e-5,
+ep=1e-2)` call exactly as `FactorGraph.update_lowmem` issues it (droid_slam/factor_graph.py:297-298) from
+the SAME initial state every step.  value = edges * itrs * steps / time  [edge-iterations/s].
+N > 1: edges sharded by source frame over the ranks (one process per GPU), one NCCL all-reduce of the
+reduced pose system per iteration (droid_b200/dist.py) — total work fixed => "scaling": "strong".
+
+Prints ONE JSON line on rank 0 (see the task contract): value (inputs resident in HBM), e2e (host buffers,
+H2D/D2H inside the timed region), roofline of the dominant kernel (measured live with CUDA events recorded
+by the library around it), cpu_baseline (oracle port on a bounded sample), clocks, gpu_launches.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+for _p in (REPO, os.path.join(REPO, "droid-slam_reserch_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "dense BA edge-iterations/s (global backend BA, 512 keyframes / ~6k edges, itrs=2 per call)"
+UNIT = "edge-iters/s"
+ITRS, LM, EP = 2, 1e-5, 1e-2          # factor_graph.py:297-298
+WORKLOAD = dict(workload="c3: stereo-EuRoC global backend BA", keyframes=512, edges_target=6000, ht=48, wd=64,
+                itrs_per_call=ITRS, lm=LM, ep=EP, t0=1)
+STAGES = ["graph", "edge_prep", "accumulate", "solve", "post", "backsub"]
+
+
+def peaks():
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# --------------------------------------------------------------------------------------------- CPU arm
+def cpu_sample_problem():
+    """Bounded sample of the c3 workload for the CPU arm: the same generator at 128 keyframes / ~1500 edges
+    (1/4 of c3; the scalar+OpenMP port needs ~7 s per Gauss-Newton iteration on 8 cores here)."""
+    from droid_b200 import synth
+    return synth.config_c3(n_kf=128, n_edges=1500), "c3 generator at 128 keyframes / ~1500 edges (1/4 of c3), itrs=2"
+
+
+def run_cpu(steps, warmup):
+    from oracle import oracle
+    p, sample = cpu_sample_problem()
+    cores = oracle.num_threads()
+    times = []
+    for s in range(warmup + steps):
+        t = time.perf_counter()
+        oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target, p.weight, p.eta, p.ii, p.jj, p.t0, p.t1, ITRS, LM, EP)
+        if s >= warmup:
+            times.append(time.perf_counter() - t)
+    tot = sum(times)
+    return dict(value=p.n_edges * ITRS * len(times) / tot, unit=UNIT, cores=cores, kind="port", sample=sample,
+                ms_per_step=1e3 * tot / len(times), edges=p.n_edges)
+
+
+def main_reference(args, rank):
+    if rank != 0:
+        return
+    steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+    r = run_cpu(steps, warmup)
+    line = dict(impl="reference", metric=METRIC, value=r["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warmup,
+                ms_per_step=r["ms_per_step"], higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
+                data="synthetic", config=dict(WORKLOAD, sample=r["sample"], edges=r["edges"]),
+                cpu_baseline=dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"]),
+                e2e=dict(value=r["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                note="reference's CPU arm = oracle/oracle.cpp (OpenMP restatement of src/droid_kernels.cu ba_cuda, fp32 kernels + "
+                     "fp64 solve); steps capped at 3 (each ~15 s)")
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- GPU arm
+def lookup_bench(dev, steps, warmup, hbm_peak):
+    """Secondary metric: fused 4-level radius-3 CorrBlock lookup on f16 volumes, 96 edges x 48x64 (c2 window).
+    One lookup = one (edge, pixel) producing all 4x49 outputs; algorithmic bytes 912 B/lookup."""
+    import torch
+    import droid_backends
+    N, ht, wd = 96, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(7)
+    levels = [torch.randn((N, ht, wd, ht >> l, wd >> l), device=dev, dtype=torch.float16, generator=g) for l in range(4)]
+    yy, xx = torch.meshgrid(torch.arange(ht, device=dev, dtype=torch.float32), torch.arange(wd, device=dev, dtype=torch.float32),
+                            indexing="ij")
+    coords = torch.stack([xx, yy], 0)[None].repeat(N, 1, 1, 1) + 6.0 * torch.randn((N, 2, ht, wd), device=dev, generator=g)
+    coords = coords.contiguous()
+    for _ in range(warmup):
+        droid_backends.corr_pyramid_lookup(levels, coords, 3)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(steps):
+        droid_backends.corr_pyramid_lookup(levels, coords, 3)
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1]) / steps
+    lookups = N * ht * wd
+    gbs = lookups * 912 / (ms * 1e-3) / 1e9
+    return dict(metric="corr lookups/s (fused 4-level r=3, f16 volumes, 96 edges x 48x64; volumes 2.4 GB > L2)",
+                value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_launch=ms,
+                roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
+                              algorithmic_bytes_per_launch=lookups * 912))
+
+
+def main_gpu(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    import droid_backends
+    from droid_b200 import _capi, synth
+
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _capi.lib()
+    hbm_peak, peak_src = peaks()
+
+    p = synth.config_c3()
+    N, HW, M, P = p.n_edges, p.disps.shape[1] * p.disps.shape[2], p.eta.shape[0], p.t1 - p.t0
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    poses0, disps0 = t(p.poses), t(p.disps)
+    intr, sens = t(p.intrinsics), t(p.disps_sens)
+
+    if world == 1:
+        target, weight, eta, ii, jj = t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)
+        poses, disps = poses0.clone(), disps0.clone()
+
+        def step():
+            poses.copy_(poses0); disps.copy_(disps0)
+            return droid_backends.ba(poses, disps, intr, sens, target, weight, eta, ii, jj, p.t0, p.t1, ITRS, LM, EP, False)
+        runner = None
+    else:
+        from droid_b200 import dist as bdist
+        runner = bdist.ShardedBA(p.ii, p.jj, p.t0, p.t1, rank, world, dev)
+        sel = runner.local_edges
+        target, weight = t(p.target[sel]), t(p.weight[sel])
+        eta = t(p.eta)
+        poses, disps = poses0.clone(), disps0.clone()
+
+        def step():
+            poses.copy_(poses0); disps.copy_(disps0)
+            return runner.ba(poses, disps, intr, sens, target, weight, eta, ITRS, LM, EP)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- timed region: device-resident inputs
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.db200_profile_enable(1)
+    l0 = lib.db200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = lib.db200_launch_count() - l0
+    st_ms = (C.c_double * len(STAGES))(); st_n = (C.c_int * len(STAGES))()
+    lib.db200_profile_collect(st_ms, st_n)
+    lib.db200_profile_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = N * ITRS * args.steps / (ms_total * 1e-3)
+
+    # ---- e2e: host (pinned) buffers in, results out, every step, through the same public call
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    if world == 1:
+        h_in = [pin(a) for a in (p.target, p.weight, p.eta, p.ii, p.jj, p.poses, p.disps)]
+    else:
+        h_in = [pin(a) for a in (p.target[sel], p.weight[sel], p.eta, p.ii[sel], p.jj[sel], p.poses, p.disps)]
+    h_poses, h_disps = torch.empty_like(h_in[5]), torch.empty_like(h_in[6])
+    h_dx = torch.empty((P, 6), dtype=torch.float32).pin_memory()
+    h2d = sum(a.numel() * a.element_size() for a in h_in)
+    d2h = sum(a.numel() * a.element_size() for a in (h_poses, h_disps, h_dx))
+    d_in = [torch.empty(a.shape, dtype=a.dtype, device=dev) for a in h_in]
+
+    def e2e_step():
+        for d, h in zip(d_in, h_in):
+            d.copy_(h, non_blocking=True)
+        tg, wg, et, i_, j_, po, di = d_in
+        if world == 1:
+            dx, _ = droid_backends.ba(po, di, intr, sens, tg, wg, et, i_, j_, p.t0, p.t1, ITRS, LM, EP, False)
+        else:
+            dx, _ = runner.ba(po, di, intr, sens, tg, wg, et, ITRS, LM, EP)
+        h_poses.copy_(po, non_blocking=True); h_disps.copy_(di, non_blocking=True); h_dx.copy_(dx, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller reads the result every step
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+    if world > 1:
+        tt = torch.tensor([ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_e2e = float(tt.item())
+    e2e_value = N * ITRS * e2e_steps / (ms_e2e * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant HBM-bound kernel (accumulate): algorithmic bytes per launch / measured launch time
+    n_loc = int(target.shape[0])
+    m_loc = M if world == 1 else runner.n_local_frames
+    accum_bytes = 16 * HW * n_loc + 20 * HW * m_loc          # target+weight per edge-pixel; disp,eta,sens in + Q,w out per frame-pixel
+    stage = {STAGES[i]: dict(ms_per_iter=(st_ms[i] / st_n[i]) if st_n[i] else None, intervals=int(st_n[i])) for i in range(len(STAGES))}
+    acc_ms = stage["accumulate"]["ms_per_iter"]
+    achieved = accum_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else None
+    iter_bytes = 20 * HW * N + 16 * HW * M + 56 * P       # SURVEY.md §8d whole-iteration figure (block-sparse system term omitted)
+    iter_ms = ms_step / ITRS
+    roofline = dict(bound="hbm", kernel="ba_frame_kernel (accumulate stage)", achieved=achieved, peak=hbm_peak, unit="GB/s",
+                    frac=(achieved / hbm_peak) if achieved else None, traffic=None, peak_source=peak_src,
+                    algorithmic_bytes_per_launch=accum_bytes, ms_per_launch=acc_ms,
+                    whole_iteration=dict(algorithmic_bytes=iter_bytes, ms=iter_ms,
+                                         achieved=iter_bytes / (iter_ms * 1e-3) / 1e9,
+                                         frac=iter_bytes / (iter_ms * 1e-3) / 1e9 / hbm_peak))
+    traffic_file = os.path.join(REPO, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get("ba_frame_kernel_bytes_per_launch")
+        except Exception:
+            pass
+
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32 (fp64 reduced system + solve)",
+                data="synthetic",
+                config=dict(WORKLOAD, edges=N, depth_maps=M, poses=P, parallelism=f"edge-shard x{world}" if world > 1 else "single",
+                            l2="inputs (295 MB of target/weight per iteration) larger than the 126 MB L2; no explicit flush"),
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, steps=e2e_steps,
+                         ms_per_step=ms_e2e / e2e_steps),
+                gpu_launches=int(launches), roofline=roofline, stages=stage, clocks=clocks)
+    if world == 1:
+        line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
+        if not args.no_cpu:
+            r = run_cpu(1, 0)
+            line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"])
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        return main_reference(args, rank)
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch multi-GPU runs with torch.distributed.run (one process per GPU)")
+    main_gpu(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()

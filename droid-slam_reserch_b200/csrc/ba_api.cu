@@ -1,10 +1,68 @@
 // ba_api.cu — C-ABI of the dense bundle adjustment (see include/droid_b200.h).
 // Mirrors droid_backends.ba (/root/reference/src/droid.cpp:88-117, droid_kernels.cu:1314-1434): in-place
 // update of poses/disps, `iterations` Gauss-Newton steps, returns dx/dz of the last step.
+#include <atomic>
 #include <cstdio>
 #include "ba.cuh"
 
 using namespace db200;
+
+// ---- instrumentation: launch counter + optional per-stage CUDA-event timing (bench.py) ----------------
+static std::atomic<long long> g_launches{0};
+extern "C" void db200_count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+extern "C" long long db200_launch_count(void) { return g_launches.load(); }
+
+namespace {
+constexpr int kStages = DB200_NUM_STAGES;
+constexpr int kProfCap = 2048;                 // (start, stop) pairs per stage between two collects
+struct Prof {
+  bool on = false;
+  cudaEvent_t ev[kStages][kProfCap][2];
+  int used[kStages] = {};
+  int made[kStages] = {};
+} g_prof;
+
+struct StageTimer {                             // records start/stop around one stage when profiling is on
+  int s; cudaStream_t st; bool live;
+  StageTimer(int stage, cudaStream_t stream) : s(stage), st(stream), live(false) {
+    if (!g_prof.on || g_prof.used[s] >= kProfCap) return;
+    const int i = g_prof.used[s];
+    if (i >= g_prof.made[s]) {
+      if (cudaEventCreate(&g_prof.ev[s][i][0]) != cudaSuccess || cudaEventCreate(&g_prof.ev[s][i][1]) != cudaSuccess) return;
+      g_prof.made[s] = i + 1;
+    }
+    cudaEventRecord(g_prof.ev[s][i][0], st);
+    live = true;
+  }
+  ~StageTimer() {
+    if (!live) return;
+    cudaEventRecord(g_prof.ev[s][g_prof.used[s]][1], st);
+    g_prof.used[s]++;
+  }
+};
+}  // namespace
+
+extern "C" void db200_profile_enable(int on) {
+  g_prof.on = on != 0;
+  for (int s = 0; s < kStages; s++) g_prof.used[s] = 0;
+}
+
+extern "C" int db200_profile_collect(double* ms_out, int* count_out) {
+  for (int s = 0; s < kStages; s++) {
+    double tot = 0.0;
+    for (int i = 0; i < g_prof.used[s]; i++) {
+      DB200_CUDA(cudaEventSynchronize(g_prof.ev[s][i][1]));
+      float ms = 0.0f;
+      DB200_CUDA(cudaEventElapsedTime(&ms, g_prof.ev[s][i][0], g_prof.ev[s][i][1]));
+      tot += ms;
+    }
+    if (ms_out) ms_out[s] = tot;
+    if (count_out) count_out[s] = g_prof.used[s];
+    g_prof.used[s] = 0;
+  }
+  return DB200_OK;
+}
+
 
 namespace {
 
@@ -61,9 +119,9 @@ extern "C" int db200_ba_accumulate(float* poses, float* disps, const float* intr
                                  motion_only, eta_rows, workspace, L);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DB200_OK;
-  if (first_iteration) rc = ba_build_graph(p, st);
-  if (rc == DB200_OK) rc = ba_edge_prep(p, st);
-  if (rc == DB200_OK) rc = ba_accumulate_frames(p, st);
+  if (first_iteration) { StageTimer t(DB200_STAGE_GRAPH, st); rc = ba_build_graph(p, st); }
+  if (rc == DB200_OK) { StageTimer t(DB200_STAGE_PREP, st); rc = ba_edge_prep(p, st); }
+  if (rc == DB200_OK) { StageTimer t(DB200_STAGE_ACCUM, st); rc = ba_accumulate_frames(p, st); }
   return rc;
 }
 
@@ -79,9 +137,10 @@ extern "C" int db200_ba_solve_update(float* poses, float* disps, const float* in
   const BAParams p = make_params(poses, disps, intrinsics, nullptr, targets, weights, nullptr, ii, jj, N, B, ht, wd, t0, t1,
                                  motion_only, eta_rows, workspace, L);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc = ba_solve(p, lm, ep, st);
-  if (rc == DB200_OK) rc = ba_post_solve(p, dx_out, st);
-  if (rc == DB200_OK && !motion_only) rc = ba_backsub_frames(p, dz_out, st);
+  int rc;
+  { StageTimer t(DB200_STAGE_SOLVE, st); rc = ba_solve(p, lm, ep, st); }
+  if (rc == DB200_OK) { StageTimer t(DB200_STAGE_POST, st); rc = ba_post_solve(p, dx_out, st); }
+  if (rc == DB200_OK && !motion_only) { StageTimer t(DB200_STAGE_BACKSUB, st); rc = ba_backsub_frames(p, dz_out, st); }
   return rc;
 }
 

@@ -163,12 +163,14 @@ int ba_build_graph(const BAParams& p, cudaStream_t st) {
   if (p.N > 0) graph_degree_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
   graph_offsets_kernel<<<1, 32, 0, st>>>(p);
   if (p.N > 0) graph_fill_kernel<<<p.Mcap, 256, 0, st>>>(p);
+  DB200_COUNT(p.N > 0 ? 5 : 2);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
 
 int ba_edge_prep(const BAParams& p, cudaStream_t st) {
   if (p.N > 0) edge_prep_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
+  else DB200_COUNT(-1);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

@@ -265,6 +265,7 @@ int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   }
   chol_backsub_init_kernel<<<cdiv(ld, 256), 256, 0, st>>>(p);
   for (int i = nt - 1; i >= 0; i--) chol_backsub_step_kernel<<<i + 1, 32, 0, st>>>(p, i);
+  DB200_COUNT(1 + nt + (nt - 1) + nt);   // prepare, panels, updates, (init counted below), back-substitution steps
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
@@ -273,6 +274,7 @@ int ba_post_solve(const BAParams& p, float* dx_out, cudaStream_t st) {
   post_dx_kernel<<<cdiv(p.n, 256), 256, 0, st>>>(p, dx_out);
   if (p.N > 0 && !p.motion_only) post_y_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
   pose_retr_kernel<<<cdiv(p.P, 128), 128, 0, st>>>(p);
+  DB200_COUNT((p.N > 0 && !p.motion_only) ? 2 : 1);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

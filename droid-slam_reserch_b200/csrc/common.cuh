@@ -8,9 +8,14 @@
 // last CUDA error seen by the library (for db200_last_cuda_error()); defined in ba_api.cu
 extern "C" void db200_note_cuda_error(int code, const char* file, int line);
 
+// kernel-launch counter (db200_launch_count(); bench.py's "gpu_launches"); defined in ba_api.cu
+extern "C" void db200_count_launches(int n);
+#define DB200_COUNT(n) db200_count_launches(n)
+
 #define DB200_CHECK_LAUNCH()                                   \
   do {                                                         \
     cudaError_t e__ = cudaGetLastError();                      \
+    DB200_COUNT(1);                                            \
     if (e__ != cudaSuccess) {                                  \
       db200_note_cuda_error(int(e__), __FILE__, __LINE__);     \
       return DB200_ERR_CUDA;                                   \

@@ -165,6 +165,7 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
         pool_fmap_kernel<__half><<<blocks, 256, 0, st>>>(static_cast<const __half*>(src), reinterpret_cast<__half*>(wsp), N * C, h, w);
       else
         pool_fmap_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(src), reinterpret_cast<float*>(wsp), N * C, h, w);
+      DB200_COUNT(1);
       src = wsp;
       wsp += ((cnt * es + 255) / 256) * 256;
       h >>= 1; w >>= 1;
@@ -180,6 +181,7 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
                                                  static_cast<float*>(levels_out[l]), C, M, N2);
     }
   }
+  DB200_COUNT(num_levels - 1);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

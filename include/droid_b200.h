@@ -33,6 +33,22 @@ int db200_version(void);
 const char* db200_status_string(int status);
 const char* db200_last_cuda_error(void); /* text of the last CUDA error the library saw (diagnostics) */
 
+/* ---- instrumentation (no reference counterpart; used by bench.py) ----------------------------
+ * db200_launch_count: kernels launched by this library since load.
+ * db200_profile_enable(1): record CUDA events around the BA stages on the caller's stream;
+ * db200_profile_collect: synchronise those events, return summed milliseconds and number of
+ * recorded intervals per stage (arrays of DB200_NUM_STAGES), and reset. */
+#define DB200_STAGE_GRAPH 0   /* device-side graph build (once per ba call) */
+#define DB200_STAGE_PREP 1    /* per-edge relative poses */
+#define DB200_STAGE_ACCUM 2   /* fused reprojection/Jacobian/Hessian/Schur accumulation (the HBM-bound kernel) */
+#define DB200_STAGE_SOLVE 3   /* damped Cholesky of the reduced pose system */
+#define DB200_STAGE_POST 4    /* dx, pose retraction, per-edge back-substitution vectors */
+#define DB200_STAGE_BACKSUB 5 /* depth back-substitution + disparity update */
+#define DB200_NUM_STAGES 6
+long long db200_launch_count(void);
+void db200_profile_enable(int on);
+int db200_profile_collect(double* ms_out, int* count_out);
+
 /* ---- correlation lookup ------------------------------------------------------------------
  * corr_index_forward  (droid.cpp:170-178, correlation_kernels.cu:20-70,126-155)
  *   volume[N,h1,w1,h2,w2] (dtype), coords[N,2,h1,w1] f32 (x then y) -> corr[N,2r+1,2r+1,h1,w1] (dtype),
