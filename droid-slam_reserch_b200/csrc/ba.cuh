@@ -85,6 +85,7 @@ struct BAParams {
   float* poses; float* disps; const float* intr; const float* sens; const float* target; const float* weight;
   const float* eta; const int64_t* ii; const int64_t* jj;
   int N, B, ht, wd, HW, t0, t1, P, eta_rows, motion_only;
+  int own_lo, own_hi;   // owned source frames [own_lo, own_hi) (edge-sharded multi-GPU runs; 0, B otherwise)
   // workspace views
   BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
   float* Q; float* w; double* Hb; double* Wk; double* Lm; double* xsol; float* dx;

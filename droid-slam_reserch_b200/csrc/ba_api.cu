@@ -108,15 +108,17 @@ extern "C" size_t db200_ba_system_elems(int t0, int t1) {
 extern "C" int db200_ba_accumulate(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
                                    const float* targets, const float* weights, const float* eta, const int64_t* ii,
                                    const int64_t* jj, int N, int B, int ht, int wd, int t0, int t1, int motion_only,
-                                   int eta_rows, int first_iteration, void* workspace, size_t workspace_bytes,
-                                   db200_stream_t stream) {
+                                   int eta_rows, int first_iteration, int own_lo, int own_hi, void* workspace,
+                                   size_t workspace_bytes, db200_stream_t stream) {
   if (!workspace || !args_ok(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
                              motion_only, eta_rows))
     return DB200_ERR_ARG;
   const BALayout L = ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only);
   if (workspace_bytes < L.total) return DB200_ERR_WORKSPACE;
-  const BAParams p = make_params(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
-                                 motion_only, eta_rows, workspace, L);
+  BAParams p = make_params(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
+                           motion_only, eta_rows, workspace, L);
+  if (own_lo < 0 || own_hi > B || own_lo > own_hi) return DB200_ERR_ARG;
+  p.own_lo = own_lo; p.own_hi = own_hi;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = DB200_OK;
   if (first_iteration) { StageTimer t(DB200_STAGE_GRAPH, st); rc = ba_build_graph(p, st); }
@@ -128,14 +130,16 @@ extern "C" int db200_ba_accumulate(float* poses, float* disps, const float* intr
 extern "C" int db200_ba_solve_update(float* poses, float* disps, const float* intrinsics, const float* targets,
                                      const float* weights, const int64_t* ii, const int64_t* jj, int N, int B, int ht,
                                      int wd, int t0, int t1, float lm, float ep, int motion_only, int eta_rows,
-                                     float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes,
-                                     db200_stream_t stream) {
+                                     int own_lo, int own_hi, float* dx_out, float* dz_out, void* workspace,
+                                     size_t workspace_bytes, db200_stream_t stream) {
   if (!workspace || !poses || !disps || !intrinsics || N < 0 || B <= 0 || ht <= 0 || wd <= 0 || t0 < 0 || t1 <= t0 || t1 > B)
     return DB200_ERR_ARG;
   const BALayout L = ba_layout(N, B, ht * wd, t0, t1, eta_rows, motion_only);
   if (workspace_bytes < L.total) return DB200_ERR_WORKSPACE;
-  const BAParams p = make_params(poses, disps, intrinsics, nullptr, targets, weights, nullptr, ii, jj, N, B, ht, wd, t0, t1,
-                                 motion_only, eta_rows, workspace, L);
+  BAParams p = make_params(poses, disps, intrinsics, nullptr, targets, weights, nullptr, ii, jj, N, B, ht, wd, t0, t1,
+                           motion_only, eta_rows, workspace, L);
+  if (own_lo < 0 || own_hi > B || own_lo > own_hi) return DB200_ERR_ARG;
+  p.own_lo = own_lo; p.own_hi = own_hi;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc;
   { StageTimer t(DB200_STAGE_SOLVE, st); rc = ba_solve(p, lm, ep, st); }
@@ -151,11 +155,11 @@ extern "C" int db200_ba(float* poses, float* disps, const float* intrinsics, con
   if (iterations < 0) return DB200_ERR_ARG;
   for (int it = 0; it < iterations; it++) {
     int rc = db200_ba_accumulate(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, N, B, ht, wd, t0, t1,
-                                 motion_only, eta_rows, it == 0, workspace, workspace_bytes, stream);
+                                 motion_only, eta_rows, it == 0, 0, B, workspace, workspace_bytes, stream);
     if (rc != DB200_OK) return rc;
     const bool last = (it == iterations - 1);
     rc = db200_ba_solve_update(poses, disps, intrinsics, targets, weights, ii, jj, N, B, ht, wd, t0, t1, lm, ep, motion_only,
-                               eta_rows, last ? dx_out : nullptr, last ? dz_out : nullptr, workspace, workspace_bytes, stream);
+                               eta_rows, 0, B, last ? dx_out : nullptr, last ? dz_out : nullptr, workspace, workspace_bytes, stream);
     if (rc != DB200_OK) return rc;
   }
   return DB200_OK;

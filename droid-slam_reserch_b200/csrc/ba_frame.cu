@@ -166,6 +166,7 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
   const FrameSmem sm = carve(smem_raw, dcap, MOTION);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int f = p.kx[k];
+  if (f < p.own_lo || f >= p.own_hi) return;       // depth map owned by another rank
   const int q_beg = p.deg_off[k], ne = p.deg_off[k + 1] - q_beg;
   const int HW = p.HW, wd = p.wd;
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
@@ -421,6 +422,7 @@ ba_backsub_kernel(BAParams p, float* __restrict__ dz_out) {
   const int pix = blockIdx.x * kBAThreads + threadIdx.x;
   if (pix >= p.HW) return;
   const int f = p.kx[k];
+  if (f < p.own_lo || f >= p.own_hi) return;
   const int q_beg = p.deg_off[k], ne = p.deg_off[k + 1] - q_beg;
   const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
   const float h = p.disps[size_t(f) * p.HW + pix];

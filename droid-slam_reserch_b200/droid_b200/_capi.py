@@ -36,8 +36,8 @@ _SIGNATURES = {
     "db200_ba_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i, _i, _i]),
     "db200_ba": (_i, [_vp] * 9 + [_i] * 7 + [_f, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "db200_ba_status": (_i, [_vp, _vp]),
-    "db200_ba_accumulate": (_i, [_vp] * 9 + [_i] * 9 + [_vp, _sz, _vp]),
-    "db200_ba_solve_update": (_i, [_vp] * 7 + [_i] * 6 + [_f, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "db200_ba_accumulate": (_i, [_vp] * 9 + [_i] * 11 + [_vp, _sz, _vp]),
+    "db200_ba_solve_update": (_i, [_vp] * 7 + [_i] * 6 + [_f, _f, _i, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "db200_ba_system_ptr": (_vp, [_vp, _i, _i, _i, _i, _i, _i, _i, _i]),
     "db200_ba_system_elems": (_sz, [_i, _i]),
 }

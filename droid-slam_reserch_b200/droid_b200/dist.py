@@ -1,0 +1,162 @@
+"""Edge-sharded multi-GPU dense BA — one process per GPU, `torch.distributed` plumbing.
+
+The factor graph of the global backend (`droid_slam/droid_backend.py:27-41`, `factor_graph.py:246-299`) and of
+this fork's multisession `Euroc_Multisession_Stereo/BackendAllMaps.py` is partitioned by SOURCE frame: rank g
+owns a contiguous range of keyframes `[lo_g, hi_g)` and every edge whose `ii` lies in it, together with those
+frames' `target`/`weight` rows, disparity maps and `eta` rows.  Everything the Schur complement couples (C, w,
+Q, the E rows and dz of one depth map) is then rank-local, so one Gauss-Newton iteration is
+
+    db200_ba_accumulate   (local edges)  ->  partial reduced system [H | b] (fp64)
+    all_reduce(sum)        over NVLink   ->  the full reduced system on every rank          (the ONLY exchange)
+    db200_ba_solve_update (replicated damped Cholesky, pose retraction; dz + disparity update of owned frames)
+
+and after the last iteration the owned disparity rows are assembled on every rank (one more all-reduce of a
+row-masked copy, 12 KB per keyframe) so that `disps` ends up identical everywhere, as the reference's
+single-GPU `droid_backends.ba` leaves it.
+
+`partition_frames` / `shard_edges` / `allreduce_system` are pure host logic and run on CPU tensors with the
+gloo backend (tests/test_dist_cpu.py); `ShardedBA` needs the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def frame_costs(ii, jj, n_frames: int) -> np.ndarray:
+    """Work estimate per source frame for the fused accumulation kernel (csrc/ba_frame.cu): the per-edge pixel
+    pass is linear in the number of edges d of the frame, the in-CTA Schur products grow like d(d+1)/2 pairs."""
+    ii = np.asarray(ii, np.int64); jj = np.asarray(jj, np.int64)
+    deg = np.bincount(ii, minlength=n_frames).astype(np.float64)
+    pose_deg = np.bincount(ii[ii != jj], minlength=n_frames).astype(np.float64)
+    return 1.0 + deg + 0.125 * pose_deg * (pose_deg + 1.0)
+
+
+def partition_frames(ii, jj, n_frames: int, world: int) -> np.ndarray:
+    """Contiguous ownership ranges: bounds[g]..bounds[g+1] are the frames of rank g; prefix-balanced on
+    `frame_costs` so that every rank's accumulation kernel runs about equally long.  Returns int64[world+1]."""
+    cost = frame_costs(ii, jj, n_frames)
+    csum = np.concatenate([[0.0], np.cumsum(cost)])
+    targets = csum[-1] * np.arange(1, world) / world
+    cuts = np.searchsorted(csum, targets, side="left")
+    bounds = np.concatenate([[0], cuts, [n_frames]]).astype(np.int64)
+    return np.maximum.accumulate(np.clip(bounds, 0, n_frames))
+
+
+def shard_edges(ii, bounds: np.ndarray, rank: int) -> np.ndarray:
+    """Indices (ascending, i.e. original edge order preserved) of the edges owned by `rank`."""
+    ii = np.asarray(ii, np.int64)
+    return np.nonzero((ii >= bounds[rank]) & (ii < bounds[rank + 1]))[0]
+
+
+def local_depth_rows(ii_all, ii_local, t0: int, t1: int):
+    """Rows of the GLOBAL depth system kx = unique(cat(arange(t0,t1), ii)) (droid_kernels.cu:1336-1344) that the
+    LOCAL graph's kx contains, in order: eta_local = eta[rows]."""
+    ts = np.arange(t0, t1, dtype=np.int64)
+    kx_all = np.unique(np.concatenate([ts, np.asarray(ii_all, np.int64)]))
+    kx_loc = np.unique(np.concatenate([ts, np.asarray(ii_local, np.int64)]))
+    rows = np.searchsorted(kx_all, kx_loc)
+    return kx_all, kx_loc, rows
+
+
+def allreduce_system(Hb: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum of the per-rank partial reduced systems, in place (fp64 [n*n + n]).  NCCL on GPU tensors
+    (NVLink 5 / NVSwitch, in-switch reduction when available), gloo on CPU tensors."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(Hb, op=dist.ReduceOp.SUM, group=group)
+    return Hb
+
+
+def assemble_rows(x: torch.Tensor, lo: int, hi: int, group=None) -> torch.Tensor:
+    """Every rank contributes rows [lo,hi) of `x`; on return all ranks hold the assembled tensor (in place)."""
+    if not (dist.is_initialized() and dist.get_world_size(group) > 1):
+        return x
+    if lo > 0:
+        x[:lo].zero_()
+    if hi < x.shape[0]:
+        x[hi:].zero_()
+    dist.all_reduce(x, op=dist.ReduceOp.SUM, group=group)
+    return x
+
+
+class ShardedBA:
+    """`droid_backends.ba` for an edge-sharded graph.  Construct once per graph (host-side partition), call `.ba`
+    with this rank's `target`/`weight` rows (`[len(local_edges),2,ht,wd]`) and the replicated small tensors."""
+
+    def __init__(self, ii, jj, t0: int, t1: int, rank: int, world: int, device, n_frames=None, group=None):
+        ii = np.asarray(ii, np.int64); jj = np.asarray(jj, np.int64)
+        self.t0, self.t1, self.rank, self.world, self.device, self.group = int(t0), int(t1), rank, world, device, group
+        self.n_frames = int(n_frames) if n_frames is not None else int(max(ii.max(initial=0), jj.max(initial=0), t1 - 1)) + 1
+        self.bounds = partition_frames(ii, jj, self.n_frames, world)
+        self.own_lo, self.own_hi = int(self.bounds[rank]), int(self.bounds[rank + 1])
+        self.local_edges = shard_edges(ii, self.bounds, rank)
+        self.kx_all, self.kx_loc, self.eta_rows = local_depth_rows(ii, ii[self.local_edges], self.t0, self.t1)
+        self.n_local_frames = int(((self.kx_loc >= self.own_lo) & (self.kx_loc < self.own_hi)).sum())
+        self.ii = torch.from_numpy(np.ascontiguousarray(ii[self.local_edges])).to(device)
+        self.jj = torch.from_numpy(np.ascontiguousarray(jj[self.local_edges])).to(device)
+        self._eta_rows_t = torch.from_numpy(self.eta_rows).to(device)
+        self._same_rows = len(self.kx_loc) == len(self.kx_all)
+        # rows of the local dz that this rank owns, and where they go in the global dz
+        own = (self.kx_loc >= self.own_lo) & (self.kx_loc < self.own_hi)
+        self._dz_src = torch.from_numpy(np.nonzero(own)[0]).to(device)
+        self._dz_dst = torch.from_numpy(self.eta_rows[own]).to(device)
+        self._ws = None
+
+    def ba(self, poses, disps, intrinsics, disps_sens, target, weight, eta, iterations, lm, ep, motion_only=False):
+        """Same contract as droid_backends.ba: poses/disps updated in place (identical on all ranks on return),
+        returns [dx[P,6], dz[M,ht*wd]] of the last iteration (dz assembled from the owners)."""
+        from . import _capi
+        lib = _capi.lib()
+        B, ht, wd = disps.shape
+        HW = ht * wd
+        N = int(self.ii.shape[0])
+        P = self.t1 - self.t0
+        mo = int(bool(motion_only))
+        eta_loc = None
+        if not mo:
+            eta_loc = eta if self._same_rows else eta.index_select(0, self._eta_rows_t)
+            eta_loc = eta_loc.contiguous()
+        M_loc = 0 if mo else int(eta_loc.shape[0])
+        if B < self.n_frames:
+            raise RuntimeError("ShardedBA: disps has fewer frames than the partition was built for")
+        own_hi = B if self.rank == self.world - 1 else self.own_hi
+        wsb = lib.db200_ba_workspace_bytes(N, B, ht, wd, self.t0, self.t1, M_loc, mo)
+        if self._ws is None or self._ws.numel() < wsb:
+            self._ws = torch.empty(int(wsb) + 1024, dtype=torch.uint8, device=self.device)
+        ws = self._ws
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        vp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        sys_ptr = lib.db200_ba_system_ptr(vp(ws), N, B, ht, wd, self.t0, self.t1, M_loc, mo)
+        off = int(sys_ptr) - ws.data_ptr()
+        n_el = int(lib.db200_ba_system_elems(self.t0, self.t1))
+        Hb = ws[off:off + 8 * n_el].view(torch.float64)
+        dx = torch.empty((P, 6), dtype=torch.float32, device=self.device)
+        dz_loc = None if mo else torch.empty((M_loc, HW), dtype=torch.float32, device=self.device)
+        for it in range(int(iterations)):
+            last = it == iterations - 1
+            _capi.check(lib.db200_ba_accumulate(vp(poses), vp(disps), vp(intrinsics), vp(disps_sens), vp(target), vp(weight),
+                                                vp(eta_loc), vp(self.ii), vp(self.jj), N, B, ht, wd, self.t0, self.t1, mo,
+                                                M_loc, int(it == 0), self.own_lo, own_hi, vp(ws), ws.numel(), st),
+                        "ba_accumulate")
+            allreduce_system(Hb, self.group)
+            _capi.check(lib.db200_ba_solve_update(vp(poses), vp(disps), vp(intrinsics), vp(target), vp(weight), vp(self.ii),
+                                                  vp(self.jj), N, B, ht, wd, self.t0, self.t1, float(lm), float(ep), mo, M_loc,
+                                                  self.own_lo, own_hi, vp(dx) if last else C.c_void_p(0),
+                                                  vp(dz_loc) if (last and not mo) else C.c_void_p(0), vp(ws), ws.numel(), st),
+                        "ba_solve_update")
+        if mo:
+            return [dx, None]
+        assemble_rows(disps, self.own_lo, own_hi, self.group)
+        dz = torch.zeros((len(self.kx_all), HW), dtype=torch.float32, device=self.device)
+        dz.index_copy_(0, self._dz_dst, dz_loc.index_select(0, self._dz_src))
+        if self.world > 1:
+            dist.all_reduce(dz, op=dist.ReduceOp.SUM, group=self.group)
+        return [dx, dz]
+
+    def status(self):
+        from . import _capi
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return _capi.lib().db200_ba_status(C.c_void_p(self._ws.data_ptr()), st)

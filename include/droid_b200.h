@@ -116,16 +116,20 @@ int db200_ba_status(const void* workspace, db200_stream_t stream);
  *   <allreduce(sum) of Hb over ranks — NCCL, done by the caller>
  *   db200_ba_solve_update: damped Cholesky solve, pose retraction (all poses), depth back-substitution
  *                          and disparity update for the LOCAL source frames.
- * `Hb` points into the workspace: db200_ba_system_ptr(). */
+ * `Hb` points into the workspace: db200_ba_system_ptr().
+ * [own_lo, own_hi) = the source frames (depth maps) this rank owns: depth work (C, w, Q, dz, the disparity
+ * update) is done for those frames only; every local edge must have its source frame in that range.
+ * Single-GPU callers pass 0, B. */
 int db200_ba_accumulate(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
                         const float* targets, const float* weights, const float* eta, const int64_t* ii,
                         const int64_t* jj, int N, int B, int ht, int wd, int t0, int t1, int motion_only,
-                        int eta_rows, int first_iteration, void* workspace, size_t workspace_bytes,
-                        db200_stream_t stream);
+                        int eta_rows, int first_iteration, int own_lo, int own_hi, void* workspace,
+                        size_t workspace_bytes, db200_stream_t stream);
 int db200_ba_solve_update(float* poses, float* disps, const float* intrinsics, const float* targets,
                           const float* weights, const int64_t* ii, const int64_t* jj, int N, int B, int ht, int wd,
-                          int t0, int t1, float lm, float ep, int motion_only, int eta_rows, float* dx_out,
-                          float* dz_out, void* workspace, size_t workspace_bytes, db200_stream_t stream);
+                          int t0, int t1, float lm, float ep, int motion_only, int eta_rows, int own_lo, int own_hi,
+                          float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes,
+                          db200_stream_t stream);
 double* db200_ba_system_ptr(void* workspace, int N, int B, int ht, int wd, int t0, int t1, int eta_rows,
                             int motion_only);
 size_t db200_ba_system_elems(int t0, int t1);
