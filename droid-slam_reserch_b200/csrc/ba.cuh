@@ -20,6 +20,11 @@ constexpr int kBAThreads = 256;       // threads per CTA of the frame kernels = 
 constexpr int kEStride = kBAThreads + 1;  // padded pixel stride of the E stash (bank-conflict free)
 constexpr int kMaxDeg = 28;           // max pose edges per source frame on the fused path
 constexpr int kRec = 16;              // floats per edge record
+constexpr int kCholTile = 64;         // tile edge of the reduced-system Cholesky (ba_solve.cu)
+
+// dataflow flags of the solver: one per tile of the lower block triangle (+ the rhs block row), one counter per
+// block column, one x-ready flag per block column, a few control words
+__host__ __device__ inline size_t chol_flag_words(int nt) { return size_t(nt) * (nt + 3) / 2 + 2 * size_t(nt) + 16; }
 
 // per-edge record (recomputed every iteration from the current poses), indexed by SORTED position
 struct EdgeRec {
@@ -43,7 +48,7 @@ struct BAHeader {
 };
 
 struct BALayout {
-  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, Lm, xsol, dx, total;
+  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, total;
   int n, nt, ld, Mcap;
 };
 
@@ -54,8 +59,8 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   BALayout L{};
   const int P = t1 - t0;
   L.n = 6 * P;
-  L.nt = (L.n + 31) / 32;
-  L.ld = L.nt * 32;
+  L.nt = (L.n + kCholTile - 1) / kCholTile;     // 64x64 tiles of the solver (ba_solve.cu)
+  L.ld = L.nt * kCholTile;
   L.Mcap = motion_only ? (B < P + N ? B : P + N) : eta_rows;
   if (L.Mcap < 1) L.Mcap = 1;
   size_t o = 0;
@@ -72,9 +77,9 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.Q = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
   L.w = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
   L.Hb = take(sizeof(double) * (size_t(L.n) * L.n + L.n));
-  L.Wk = take(sizeof(double) * size_t(L.ld + 32) * L.ld);
-  L.Lm = take(sizeof(double) * size_t(L.ld + 32) * L.ld);
-  L.xsol = take(sizeof(double) * 2 * size_t(L.ld + 32));   // y | x
+  L.Wk = take(sizeof(double) * size_t(L.ld + kCholTile) * L.ld);   // [A; b^T] -> [L; y^T] in place (lower, row-major)
+  L.cflags = take(sizeof(unsigned) * chol_flag_words(L.nt));
+  L.xsol = take(sizeof(double) * size_t(L.ld));
   L.dx = take(sizeof(float) * size_t(L.n));
   L.total = o;
   return L;
@@ -88,7 +93,7 @@ struct BAParams {
   int own_lo, own_hi;   // owned source frames [own_lo, own_hi) (edge-sharded multi-GPU runs; 0, B otherwise)
   // workspace views
   BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
-  float* Q; float* w; double* Hb; double* Wk; double* Lm; double* xsol; float* dx;
+  float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx;
   int n, nt, ld, Mcap;
 };
 
@@ -108,7 +113,7 @@ inline BAParams ba_params(const BALayout& L, void* ws) {
   p.w = reinterpret_cast<float*>(b + L.w);
   p.Hb = reinterpret_cast<double*>(b + L.Hb);
   p.Wk = reinterpret_cast<double*>(b + L.Wk);
-  p.Lm = reinterpret_cast<double*>(b + L.Lm);
+  p.cflags = reinterpret_cast<unsigned*>(b + L.cflags);
   p.xsol = reinterpret_cast<double*>(b + L.xsol);
   p.dx = reinterpret_cast<float*>(b + L.dx);
   p.n = L.n; p.nt = L.nt; p.ld = L.ld; p.Mcap = L.Mcap;

@@ -2,165 +2,357 @@
 // Replaces SparseBlock::solve (host Eigen::SimplicialLLT in fp64 with D2H/H2D copies every iteration,
 // /root/reference/src/droid_kernels.cu:1192-1213), pose_retr_kernel/retrSE3/expSE3 (:877-931, :110-175).
 //
-// Right-looking blocked Cholesky in fp64 (B200 keeps a full-rate FP64 pipe), NB = 32:
-//   step k:  panel kernel  — every CTA re-factors the 32x32 diagonal tile in shared memory (one warp,
-//                            ~2 us) and solves its own 128 rows of the panel against it (thread = row);
-//            update kernel — 128x128 macro tiles, A_ij -= L_ik L_jk^T, 8x8 register tile per thread.
-// The right-hand side rides along as one extra row of the matrix ([A b; b^T .] -> its factor row is
-// y = L^-1 b), so forward substitution costs nothing; back substitution walks the tile rows upwards.
+// Right-looking tiled Cholesky in fp64 (B200 keeps a full-rate FP64 pipe), 64x64 tiles, in ONE cooperative
+// launch: static tile ownership + release/acquire ready flags (no grid barriers, no per-step launches).  The
+// critical path is the panel chain (update diagonal tile -> factor -> triangular solves), which look-ahead
+// overlaps with the trailing updates of the previous step.  The right-hand side rides along as one extra block
+// row ([A b; b^T .] -> its factor row is y = L^-1 b), so forward substitution costs nothing; the backward
+// substitution runs in the same launch, block column j owned by CTA nt-1-j, consuming x_i as they are published.
 // Damping diag += ep + lm*diag (:1197) is applied while copying into the work matrix.  A pivot <= 0
 // reproduces Eigen's NumericalIssue: the pose update is zero (:1207-1210).
 #include "ba.cuh"
 
 namespace db200 {
 
-constexpr int NB = 32;
+constexpr int T = kCholTile;        // 64
+constexpr int TP = T + 1;           // padded row stride of the shared tiles (doubles)
+constexpr int kCholThreads = 256;
+constexpr unsigned kSpinLimit = 1u << 24;   // bounded waits: a broken dependency raises an error instead of hanging the GPU
 
+// ---- tile bookkeeping ---------------------------------------------------------------------------------
+// Block rows 0..nt (row nt = the appended right-hand side), block columns 0..nt-1, lower triangle only.
+// Linear tile index, column-major: idx(i,j) = colstart(j) + (i - j), colstart(j) = j*(nt+1) - j*(j-1)/2.
+__host__ __device__ inline int colstart(int j, int nt) { return j * (nt + 1) - (j * (j - 1)) / 2; }
+__host__ __device__ inline int num_tiles(int nt) { return colstart(nt, nt); }
+
+struct CholFlags {
+  unsigned* ready;       // [num_tiles]  tile (i,j) holds its final L values
+  unsigned* panel_done;  // [nt]         number of final tiles in block column j
+  unsigned* xready;      // [nt]         x_j of the back-substitution is published
+  unsigned* ctl;         // [0] error
+};
+__host__ __device__ inline CholFlags chol_flags(unsigned* base, int nt) {
+  CholFlags f;
+  f.ready = base;
+  f.panel_done = base + num_tiles(nt);
+  f.xready = f.panel_done + nt;
+  f.ctl = f.xready + nt;
+  return f;
+}
+
+__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// thread 0 polls `flag` until it is >= want (bounded); everybody gets the verdict.  false = abort the kernel.
+__device__ __forceinline__ bool wait_flag(const unsigned* flag, unsigned want, unsigned* err, int* s_ok) {
+  if (threadIdx.x == 0) {
+    int ok = 1;
+    unsigned spins = 0;
+    while (ld_acquire(flag) < want) {
+      if (++spins > kSpinLimit || ld_acquire(err) != 0) { ok = 0; atomicExch(err, 1u); break; }
+    }
+    *s_ok = ok;
+  }
+  __syncthreads();
+  const bool ok = *s_ok != 0;
+  __syncthreads();
+  return ok;
+}
+
+// after all threads stored their part of a tile: publish it
+__device__ __forceinline__ void publish(unsigned* flag, unsigned* counter) {
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    st_release(flag, 1u);
+    if (counter) red_release_add(counter, 1u);
+  }
+}
+
+// ---- A + damping -> work matrix; rhs appended as block row nt; flags cleared ---------------------------
 __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   const int n = p.n, ld = p.ld;
-  const size_t total = size_t(ld + NB) * ld;
+  const size_t total = size_t(ld + T) * ld;
   const double* H = p.Hb;
   const double* b = p.Hb + size_t(n) * n;
-  if (blockIdx.x == 0 && threadIdx.x == 0) p.hdr->chol_fail = 0;
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+  const size_t gtid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, gstride = size_t(gridDim.x) * blockDim.x;
+  if (gtid == 0) p.hdr->chol_fail = 0;
+  const size_t nflags = chol_flag_words(p.nt);
+  for (size_t i = gtid; i < nflags; i += gstride) p.cflags[i] = 0u;
+  for (size_t i = gtid; i < total; i += gstride) {
     const int r = int(i / ld), c = int(i - size_t(r) * ld);
     double v = 0.0;
     if (r < n) {
       if (c <= r) {
         v = H[size_t(r) * n + c];
-        if (c == r) v += double(ep) + double(lm) * v;
+        if (c == r) v += double(ep) + double(lm) * v;        // diag += ep + lm*diag  (droid_kernels.cu:1197)
       }
     } else if (r < ld) {
-      v = (c == r) ? 1.0 : 0.0;
+      v = (c == r) ? 1.0 : 0.0;                             // identity padding up to the tile size
     } else if (r == ld) {
-      v = (c < n) ? b[c] : 0.0;
+      v = (c < n) ? b[c] : 0.0;                             // rhs rides along as an extra row: its factor row is y = L^-1 b
     }
     p.Wk[i] = v;
   }
 }
 
-// grid.x = ceil(rows_below / 128); 128 threads.  rows_below = (ld + NB) - NB*(k+1)
-__global__ void __launch_bounds__(128) chol_panel_kernel(BAParams p, int k) {
-  __shared__ double T[NB][NB + 1];
-  const int ld = p.ld, n = p.n;
-  const int tid = threadIdx.x;
-  const double* Akk = p.Wk + size_t(NB * k) * ld + NB * k;
-  for (int i = tid; i < NB * NB; i += 128) T[i / NB][i % NB] = Akk[size_t(i / NB) * ld + (i % NB)];
-  __syncthreads();
-  if (tid < 32) {                         // one warp factors the diagonal tile; lane = row
-    const int r = tid;
-    for (int c = 0; c < NB; c++) {
-      const double dcc = T[c][c];
-      __syncwarp();
-      if (dcc <= 0.0 && NB * k + c < n && r == c) atomicExch(&p.hdr->chol_fail, 1);   // NaN passes, like Eigen's `d <= 0`
-      const double s = sqrt(dcc);
-      if (r == c) T[c][c] = s;
-      if (r > c) T[r][c] = T[r][c] / s;
-      __syncwarp();
-      if (r > c) {
-        const double lrc = T[r][c];
-        for (int m = c + 1; m <= r; m++) T[r][m] -= lrc * T[m][c];
+// ---- tile primitives (256 threads) -------------------------------------------------------------------
+// global tile (row-major, stride ld) -> shared [T][TP]; L1-bypassing loads: other CTAs wrote these values
+__device__ __forceinline__ void load_tile(double (*S)[TP], const double* g, int ld) {
+  for (int e = threadIdx.x; e < T * T; e += kCholThreads) {
+    const int r = e >> 6, c = e & 63;
+    S[r][c] = __ldcg(g + size_t(r) * ld + c);
+  }
+}
+__device__ __forceinline__ void store_tile(double* g, const double (*S)[TP], int ld) {
+  for (int e = threadIdx.x; e < T * T; e += kCholThreads) {
+    const int r = e >> 6, c = e & 63;
+    __stcg(g + size_t(r) * ld + c, S[r][c]);
+  }
+}
+
+// acc[a][b] = sum_k A[ty+16a][k] * B[tx+16b][k]
+__device__ __forceinline__ void tile_abt(const double (*A)[TP], const double (*B)[TP], double (&acc)[4][4]) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
+#pragma unroll 8
+  for (int k = 0; k < T; k++) {
+    double av[4], bv[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) { av[a] = A[ty + 16 * a][k]; bv[a] = B[tx + 16 * a][k]; }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+  }
+}
+
+// In-place Cholesky of the shared tile S (lower triangle in, L out, strict upper zeroed).
+// Micro-panels of 8 columns: warp 0 factors the panel in registers (lane = rows lane, lane+32; pivots and
+// multipliers travel by shuffle), then all warps apply the rank-8 update to the trailing block.
+// `row0` = global index of the tile's first row (pivots of rows >= n are the identity padding).
+__device__ void factor_tile(double (*S)[TP], int row0, int n, int* chol_fail) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int p = 0; p < 8; p++) {
+    const int c0 = 8 * p;
+    if (warp == 0) {
+      double a0[8], a1[8];
+#pragma unroll
+      for (int q = 0; q < 8; q++) { a0[q] = S[lane][c0 + q]; a1[q] = S[lane + 32][c0 + q]; }
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        const int cc = c0 + c;
+        const double piv = (cc < 32) ? a0[c] : a1[c];
+        const double d = __shfl_sync(0xffffffffu, piv, cc & 31);
+        if (lane == 0 && d <= 0.0 && row0 + cc < n) atomicExch(chol_fail, 1);   // NaN passes, like Eigen's `d <= 0`
+        const double rs = rsqrt(d);
+        const double sq = d * rs;
+        const int r0 = lane, r1 = lane + 32;
+        a0[c] = (r0 > cc) ? a0[c] * rs : (r0 == cc ? sq : 0.0);
+        a1[c] = (r1 > cc) ? a1[c] * rs : (r1 == cc ? sq : 0.0);
+#pragma unroll
+        for (int m = c + 1; m < 8; m++) {
+          const int mm = c0 + m;
+          const double lv = (mm < 32) ? a0[c] : a1[c];
+          const double lm_ = __shfl_sync(0xffffffffu, lv, mm & 31);
+          a0[m] = fma(-a0[c], lm_, a0[m]);
+          a1[m] = fma(-a1[c], lm_, a1[m]);
+        }
       }
-      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < 8; q++) { S[lane][c0 + q] = a0[q]; S[lane + 32][c0 + q] = a1[q]; }
     }
-  }
-  __syncthreads();
-  if (blockIdx.x == 0) {
-    double* Lkk = p.Lm + size_t(NB * k) * ld + NB * k;
-    for (int i = tid; i < NB * NB; i += 128) {
-      const int r = i / NB, c = i % NB;
-      Lkk[size_t(r) * ld + c] = (c <= r) ? T[r][c] : 0.0;
+    __syncthreads();
+    const int base = c0 + 8, nrem = T - base;
+    if (nrem > 0) {
+      for (int e = tid; e < nrem * nrem; e += kCholThreads) {
+        const int rr = e / nrem, c2 = e - rr * nrem;
+        if (c2 <= rr) {
+          double s = S[base + rr][base + c2];
+#pragma unroll
+          for (int q = 0; q < 8; q++) s = fma(-S[base + rr][c0 + q], S[base + c2][c0 + q], s);
+          S[base + rr][base + c2] = s;
+        }
+      }
     }
-  }
-  const int gr = NB * (k + 1) + blockIdx.x * 128 + tid;
-  if (gr >= ld + NB) return;
-  const double* arow = p.Wk + size_t(gr) * ld + NB * k;
-  double x[NB];
-#pragma unroll
-  for (int c = 0; c < NB; c++) x[c] = arow[c];
-#pragma unroll
-  for (int c = 0; c < NB; c++) {          // x L_kk^T = a  ->  forward substitution along the row
-    double s = x[c];
-#pragma unroll
-    for (int m = 0; m < c; m++) s -= x[m] * T[c][m];
-    x[c] = s / T[c][c];
-  }
-  double* lrow = p.Lm + size_t(gr) * ld + NB * k;
-#pragma unroll
-  for (int c = 0; c < NB; c++) lrow[c] = x[c];
-}
-
-// trailing update A_ij -= L_ik L_jk^T on 128x128 macro tiles; block (16,16); dynamic smem 2*128*33 doubles
-__global__ void __launch_bounds__(256) chol_update_kernel(BAParams p, int k) {
-  extern __shared__ __align__(16) double sm_d[];
-  double (*Pr)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(sm_d);
-  double (*Pc)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(sm_d + 128 * (NB + 1));
-  const int ld = p.ld;
-  const int base = NB * (k + 1);
-  const int row0 = base + blockIdx.y * 128, col0 = base + blockIdx.x * 128;
-  if (col0 > row0 + 127) return;          // entirely above the diagonal
-  const int nrows = ld + NB, ncols = ld;
-  const int tid = threadIdx.y * 16 + threadIdx.x;
-  for (int i = tid; i < 128 * NB; i += 256) {
-    const int r = i / NB, c = i % NB;
-    Pr[r][c] = (row0 + r < nrows) ? p.Lm[size_t(row0 + r) * ld + NB * k + c] : 0.0;
-    Pc[r][c] = (col0 + r < ncols) ? p.Lm[size_t(col0 + r) * ld + NB * k + c] : 0.0;
-  }
-  __syncthreads();
-  double acc[8][8];
-#pragma unroll
-  for (int i = 0; i < 8; i++)
-#pragma unroll
-    for (int j = 0; j < 8; j++) acc[i][j] = 0.0;
-#pragma unroll 4
-  for (int kk = 0; kk < NB; kk++) {
-    double a[8], b[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) { a[i] = Pr[threadIdx.y + 16 * i][kk]; b[i] = Pc[threadIdx.x + 16 * i][kk]; }
-#pragma unroll
-    for (int i = 0; i < 8; i++)
-#pragma unroll
-      for (int j = 0; j < 8; j++) acc[i][j] = fma(a[i], b[j], acc[i][j]);
-  }
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const int r = row0 + threadIdx.y + 16 * i;
-    if (r >= nrows) continue;
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      const int c = col0 + threadIdx.x + 16 * j;
-      if (c < ncols && c <= r) p.Wk[size_t(r) * ld + c] -= acc[i][j];
-    }
+    __syncthreads();
   }
 }
 
-__global__ void chol_backsub_init_kernel(BAParams p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < p.ld) p.xsol[i] = p.Lm[size_t(p.ld) * p.ld + i];   // y = factor row of the appended rhs
+// X L^T = C in place (C in shared `X`, L lower in shared `L`, rinv[c] = 1/L[c][c]).  4 threads per row, each
+// owning the columns m = q (mod 4); the freshly solved column is broadcast inside the 4-lane group.
+__device__ void trsm_tile(double (*X)[TP], const double (*L)[TP], const double* rinv) {
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int row = tid >> 2, q = tid & 3;
+  double x[16];
+#pragma unroll
+  for (int t = 0; t < 16; t++) x[t] = X[row][4 * t + q];
+#pragma unroll
+  for (int c = 0; c < T; c++) {
+    const int tc = c >> 2, qc = c & 3;
+    double xc = x[tc] * rinv[c];
+    xc = __shfl_sync(0xffffffffu, xc, (lane & ~3) | qc);
+    if (q == qc) x[tc] = xc;
+#pragma unroll
+    for (int t = tc; t < 16; t++) {
+      const int m = 4 * t + q;
+      if (t > tc || q > qc) x[t] = fma(-xc, L[m][c], x[t]);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 16; t++) X[row][4 * t + q] = x[t];
 }
 
-// step i (descending): grid = i+1 CTAs of one warp.  x_i = L_ii^-T y_i (every CTA, redundantly);
-// CTA kk < i: y_kk -= L_{i,kk}^T x_i;  CTA i stores x_i.
-__global__ void __launch_bounds__(32) chol_backsub_step_kernel(BAParams p, int i) {
-  __shared__ double T[NB][NB + 1];
-  const int ld = p.ld, lane = threadIdx.x, kk = blockIdx.x;
-  double* y = p.xsol;
-  double* x = p.xsol + (ld + NB);
-  const double* Lii = p.Lm + size_t(NB * i) * ld + NB * i;
-  for (int r = 0; r < NB; r++) T[r][lane] = Lii[size_t(r) * ld + lane];
-  __syncwarp();
-  double xv = y[NB * i + lane];           // lane m ends up holding x_i[m]
-  for (int c = NB - 1; c >= 0; c--) {
-    double s = (lane > c) ? T[lane][c] * xv : 0.0;
+// ---- the solver: ONE cooperative launch ------------------------------------------------------------------
+// Static tile ownership (tile idx -> CTA idx mod G) + release/acquire ready flags instead of grid barriers:
+//   step s, for every owned tile (i,j) with j >= s:
+//     s > 0:  wait L(i,s-1), L(j,s-1);  C(i,j) -= L(i,s-1) L(j,s-1)^T
+//     j == s: i == j ? factor the tile : (wait L(s,s); solve X L(s,s)^T = C)   -> publish L(i,s)
+// Tiles of block column s are the first ones in every CTA's list at step s, so the panel of step s is formed
+// while the other CTAs are still applying panel s-1 (look-ahead falls out of the data flow).
+// Then x = L^-T y: CTA j (j < nt) owns x_j = L_jj^-T (y_j - sum_{i>j} L_ij^T x_i), consuming x_i as they appear.
+__global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double (*sA)[TP] = reinterpret_cast<double (*)[TP]>(smem_raw);
+  double (*sB)[TP] = reinterpret_cast<double (*)[TP]>(smem_raw + sizeof(double) * T * TP);
+  double* sv = reinterpret_cast<double*>(smem_raw + 2 * sizeof(double) * T * TP);   // [6*64] scratch vectors
+  __shared__ int s_ok;
+  const int nt = p.nt, ld = p.ld, n = p.n;
+  const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
+  const int ty = tid >> 4, tx = tid & 15;
+  const CholFlags F = chol_flags(p.cflags, nt);
+  unsigned* err = F.ctl;
+  double* W = p.Wk;
+  const int ntiles = num_tiles(nt);
+
+  for (int s = 0; s < nt; s++) {
+    const int cs = colstart(s, nt);
+    int idx = cs + ((cta - cs) % G + G) % G;        // first owned tile index >= colstart(s)
+    bool panel_full = (s == 0);
+    int j = s;
+    for (; idx < ntiles; idx += G) {
+      while (idx >= colstart(j + 1, nt)) j++;
+      const int i = j + (idx - colstart(j, nt));
+      double acc[4][4];
+      double* Cg = W + size_t(i) * T * ld + size_t(j) * T;
+      if (s > 0) {
+        if (!panel_full) {
+          if (tid == 0) s_ok = (ld_acquire(F.panel_done + (s - 1)) >= unsigned(nt + 1 - (s - 1))) ? 1 : 0;
+          __syncthreads();
+          panel_full = s_ok != 0;
+          __syncthreads();
+          if (!panel_full) {
+            if (!wait_flag(F.ready + colstart(s - 1, nt) + (i - (s - 1)), 1u, err, &s_ok)) return;
+            if (i != j && !wait_flag(F.ready + colstart(s - 1, nt) + (j - (s - 1)), 1u, err, &s_ok)) return;
+          }
+        }
+        load_tile(sA, W + size_t(i) * T * ld + size_t(s - 1) * T, ld);
+        if (i != j) load_tile(sB, W + size_t(j) * T * ld + size_t(s - 1) * T, ld);
+        __syncthreads();
+        tile_abt(sA, (i != j) ? sB : sA, acc);
+        __syncthreads();
+      } else {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == c) xv = (xv - s) / T[c][c];
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+          for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
+      }
+      if (j > s) {                                   // bulk tile: C -= acc in global memory
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+          for (int b = 0; b < 4; b++) {
+            double* g = Cg + size_t(ty + 16 * a) * ld + tx + 16 * b;
+            __stcg(g, __ldcg(g) - acc[a][b]);
+          }
+        continue;
+      }
+      // panel tile (j == s): finish it now
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          const int r = ty + 16 * a, c = tx + 16 * b;
+          sA[r][c] = __ldcg(Cg + size_t(r) * ld + c) - acc[a][b];
+        }
+      __syncthreads();
+      if (i == j) {
+        factor_tile(sA, s * T, n, &p.hdr->chol_fail);
+      } else {
+        if (!wait_flag(F.ready + cs, 1u, err, &s_ok)) return;
+        load_tile(sB, W + size_t(s) * T * ld + size_t(s) * T, ld);
+        __syncthreads();
+        if (tid < T) sv[tid] = 1.0 / sB[tid][tid];
+        __syncthreads();
+        trsm_tile(sA, sB, sv);
+      }
+      __syncthreads();
+      store_tile(Cg, sA, ld);
+      publish(F.ready + idx, F.panel_done + s);
+      __syncthreads();
+    }
   }
-  if (kk == i) { x[NB * i + lane] = xv; return; }
-  const double* Lik = p.Lm + size_t(NB * i) * ld + NB * kk;
-  double s = 0.0;
-  for (int m = 0; m < NB; m++) s += Lik[size_t(m) * ld + lane] * __shfl_sync(0xffffffffu, xv, m);
-  y[NB * kk + lane] -= s;
+
+  // ---- back-substitution L^T x = y (y = row ld of the factor) ------------------------------------------
+  for (int j = nt - 1 - cta; j >= 0; j -= G) {
+    // the whole block column j must be final
+    if (!wait_flag(F.panel_done + j, unsigned(nt + 1 - j), err, &s_ok)) return;
+    // inverse of L_jj^T applied by substitution: keep L_jj in sA
+    load_tile(sA, W + size_t(j) * T * ld + size_t(j) * T, ld);
+    __syncthreads();
+    if (tid < T) sv[320 + tid] = 1.0 / sA[tid][tid];
+    // partial sums: thread (c = tid & 63, g = tid >> 6) accumulates sum over rows 16g..16g+15 of L_ij[r][c] x_i[r]
+    const int c = tid & 63, g4 = tid >> 6;
+    double part = 0.0;
+    for (int i = nt - 1; i > j; i--) {
+      const double* Lij = W + size_t(i) * T * ld + size_t(j) * T;
+      double lv[16];
+#pragma unroll
+      for (int r = 0; r < 16; r++) lv[r] = __ldcg(Lij + size_t(16 * g4 + r) * ld + c);   // prefetch before the wait
+      if (!wait_flag(F.xready + i, 1u, err, &s_ok)) return;
+      if (tid < T) sv[tid] = __ldcg(p.xsol + size_t(i) * T + tid);
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < 16; r++) part = fma(lv[r], sv[16 * g4 + r], part);
+      __syncthreads();
+    }
+    sv[64 + tid] = part;
+    __syncthreads();
+    if (tid < T) {
+      const double y = __ldcg(W + size_t(ld) * ld + size_t(j) * T + tid);
+      sv[tid] = y - (sv[64 + tid] + sv[128 + tid] + sv[192 + tid] + sv[256 + tid]);
+    }
+    __syncthreads();
+    // backward substitution with L_jj^T by warp 0: lane holds rows lane, lane+32
+    if (tid < 32) {
+      double v0 = sv[tid], v1 = sv[tid + 32];
+      for (int cc = T - 1; cc >= 0; cc--) {
+        const double piv = (cc < 32) ? v0 : v1;
+        const double xc = __shfl_sync(0xffffffffu, piv, cc & 31) * sv[320 + cc];
+        if (tid == (cc & 31)) { if (cc < 32) v0 = xc; else v1 = xc; }
+        // rows r < cc: y_r -= L[cc][r] * x_cc
+        if (tid < cc) v0 = fma(-sA[cc][tid], xc, v0);
+        if (tid + 32 < cc) v1 = fma(-sA[cc][tid + 32], xc, v1);
+      }
+      __stcg(p.xsol + size_t(j) * T + tid, v0);
+      __stcg(p.xsol + size_t(j) * T + tid + 32, v1);
+    }
+    publish(F.xready + j, nullptr);
+    __syncthreads();
+  }
 }
 
 // dx (fp32) = failed ? 0 : x ;  also the user-visible dx_out
@@ -170,7 +362,7 @@ __global__ void post_dx_kernel(BAParams p, float* __restrict__ dx_out) {
   const bool fail = p.hdr->chol_fail != 0;
   if (i == 0 && fail) { p.hdr->any_fail += 1; if (p.hdr->status == 0) p.hdr->status = 1; }
   if (i < p.n) {
-    const float v = fail ? 0.0f : float(p.xsol[p.ld + NB + i]);
+    const float v = fail ? 0.0f : float(p.xsol[i]);
     p.dx[i] = v;
     if (dx_out) dx_out[i] = v;
   }
@@ -245,27 +437,32 @@ __global__ void pose_retr_kernel(BAParams p) {
   pose[3] = q1[0]; pose[4] = q1[1]; pose[5] = q1[2]; pose[6] = q1[3];
 }
 
+static int chol_grid_size(size_t smem) {
+  static int ctas_per_sm = -1;
+  if (ctas_per_sm < 0) {
+    if (cudaFuncSetAttribute(chol_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)) != cudaSuccess) return -1;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, chol_solve_kernel, kCholThreads, smem) != cudaSuccess || occ < 1)
+      return -1;
+    ctas_per_sm = 1;            // one CTA per SM: the factorisation is latency-bound on the panel chain
+  }
+  int dev = 0, sms = kNumSMs;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms * ctas_per_sm;
+}
+
 int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
-  const int nt = p.nt, ld = p.ld;
   chol_prepare_kernel<<<4 * kNumSMs, 256, 0, st>>>(p, lm, ep);
-  const size_t upd_smem = sizeof(double) * 2 * 128 * (NB + 1);
-  static bool attr_set = false;
-  if (!attr_set) {
-    DB200_CUDA(cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(upd_smem)));
-    attr_set = true;
-  }
-  for (int k = 0; k < nt; k++) {
-    const int rows_below = (ld + NB) - NB * (k + 1);
-    chol_panel_kernel<<<cdiv(rows_below, 128), 128, 0, st>>>(p, k);
-    const int cols_below = ld - NB * (k + 1);
-    if (cols_below > 0) {
-      dim3 grid(cdiv(cols_below, 128), cdiv(rows_below, 128));
-      chol_update_kernel<<<grid, dim3(16, 16), upd_smem, st>>>(p, k);
-    }
-  }
-  chol_backsub_init_kernel<<<cdiv(ld, 256), 256, 0, st>>>(p);
-  for (int i = nt - 1; i >= 0; i--) chol_backsub_step_kernel<<<i + 1, 32, 0, st>>>(p, i);
-  DB200_COUNT(1 + nt + (nt - 1) + nt);   // prepare, panels, updates, (init counted below), back-substitution steps
+  DB200_CHECK_LAUNCH();
+  const size_t smem = 2 * sizeof(double) * T * TP + sizeof(double) * 6 * 64;
+  int grid = chol_grid_size(smem);
+  if (grid < 1) { db200_note_cuda_error(int(cudaGetLastError()), __FILE__, __LINE__); return DB200_ERR_CUDA; }
+  const int ntiles = num_tiles(p.nt);
+  if (grid > ntiles) grid = ntiles;
+  BAParams pp = p;
+  void* args[] = {&pp};
+  // cooperative launch: guarantees that every CTA is resident, which the flag waits rely on
+  DB200_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_solve_kernel), dim3(grid), dim3(kCholThreads), args, smem, st));
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
