@@ -68,11 +68,11 @@ __device__ __forceinline__ bool wait_flag(const unsigned* flag, unsigned want, u
   return ok;
 }
 
-// after all threads stored their part of a tile: publish it
-__device__ __forceinline__ void publish(unsigned* flag, unsigned* counter) {
-  __threadfence();
+// After all threads stored their part of a tile: bar.sync orders those stores before the release performed by
+// thread `sel` (release is cumulative over what the barrier made visible to it — the CUTLASS semaphore pattern).
+__device__ __forceinline__ void publish(unsigned* flag, unsigned* counter, int sel = 0) {
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == sel) {
     st_release(flag, 1u);
     if (counter) red_release_add(counter, 1u);
   }
@@ -108,16 +108,32 @@ __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
 // ---- tile primitives (256 threads) -------------------------------------------------------------------
 // global tile (row-major, stride ld) -> shared [T][TP]; L1-bypassing loads: other CTAs wrote these values
 __device__ __forceinline__ void load_tile(double (*S)[TP], const double* g, int ld) {
-  for (int e = threadIdx.x; e < T * T; e += kCholThreads) {
-    const int r = e >> 6, c = e & 63;
-    S[r][c] = __ldcg(g + size_t(r) * ld + c);
+  double v[16];
+#pragma unroll
+  for (int t = 0; t < 16; t++) {
+    const int e = threadIdx.x + kCholThreads * t;
+    v[t] = __ldcg(g + size_t(e >> 6) * ld + (e & 63));
+  }
+#pragma unroll
+  for (int t = 0; t < 16; t++) {
+    const int e = threadIdx.x + kCholThreads * t;
+    S[e >> 6][e & 63] = v[t];
   }
 }
 __device__ __forceinline__ void store_tile(double* g, const double (*S)[TP], int ld) {
-  for (int e = threadIdx.x; e < T * T; e += kCholThreads) {
-    const int r = e >> 6, c = e & 63;
-    __stcg(g + size_t(r) * ld + c, S[r][c]);
+#pragma unroll
+  for (int t = 0; t < 16; t++) {
+    const int e = threadIdx.x + kCholThreads * t;
+    __stcg(g + size_t(e >> 6) * ld + (e & 63), S[e >> 6][e & 63]);
   }
+}
+// this thread's 4x4 sub-block (rows ty+16a, cols tx+16b) of a global tile
+__device__ __forceinline__ void load_frag(double (&c)[4][4], const double* g, int ld) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) c[a][b] = __ldcg(g + size_t(ty + 16 * a) * ld + tx + 16 * b);
 }
 
 // acc[a][b] = sum_k A[ty+16a][k] * B[tx+16b][k]
@@ -139,190 +155,415 @@ __device__ __forceinline__ void tile_abt(const double (*A)[TP], const double (*B
   }
 }
 
-// In-place Cholesky of the shared tile S (lower triangle in, L out, strict upper zeroed).
-// Micro-panels of 8 columns: warp 0 factors the panel in registers (lane = rows lane, lane+32; pivots and
-// multipliers travel by shuffle), then all warps apply the rank-8 update to the trailing block.
-// `row0` = global index of the tile's first row (pivots of rows >= n are the identity padding).
-__device__ void factor_tile(double (*S)[TP], int row0, int n, int* chol_fail) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// 1/sqrt(d): hardware seed (20 bits, MUFU.RSQ64H) + two Newton steps -> ~1 ulp; negative -> NaN, 0 -> inf
+__device__ __forceinline__ double fast_rsqrt(double d) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  const double h = 0.5 * d;
+  double e = fma(-(h * y), y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-(h * y), y, 0.5);
+  y = fma(y, e, y);
+  return y;
+}
+
+// acc[a][b] for b <= a only (the lower block triangle of A A^T; diagonal tiles are symmetric)
+__device__ __forceinline__ void tile_aat_lower(const double (*A)[TP], double (&acc)[4][4]) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
 #pragma unroll
-  for (int p = 0; p < 8; p++) {
-    const int c0 = 8 * p;
-    if (warp == 0) {
-      double a0[8], a1[8];
+  for (int a = 0; a < 4; a++)
 #pragma unroll
-      for (int q = 0; q < 8; q++) { a0[q] = S[lane][c0 + q]; a1[q] = S[lane + 32][c0 + q]; }
+    for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
+#pragma unroll 8
+  for (int k = 0; k < T; k++) {
+    double av[4], bv[4];
 #pragma unroll
-      for (int c = 0; c < 8; c++) {
-        const int cc = c0 + c;
-        const double piv = (cc < 32) ? a0[c] : a1[c];
-        const double d = __shfl_sync(0xffffffffu, piv, cc & 31);
-        if (lane == 0 && d <= 0.0 && row0 + cc < n) atomicExch(chol_fail, 1);   // NaN passes, like Eigen's `d <= 0`
-        const double rs = rsqrt(d);
-        const double sq = d * rs;
-        const int r0 = lane, r1 = lane + 32;
-        a0[c] = (r0 > cc) ? a0[c] * rs : (r0 == cc ? sq : 0.0);
-        a1[c] = (r1 > cc) ? a1[c] * rs : (r1 == cc ? sq : 0.0);
+    for (int a = 0; a < 4; a++) { av[a] = A[ty + 16 * a][k]; bv[a] = A[tx + 16 * a][k]; }
 #pragma unroll
-        for (int m = c + 1; m < 8; m++) {
-          const int mm = c0 + m;
-          const double lv = (mm < 32) ? a0[c] : a1[c];
-          const double lm_ = __shfl_sync(0xffffffffu, lv, mm & 31);
-          a0[m] = fma(-a0[c], lm_, a0[m]);
-          a1[m] = fma(-a1[c], lm_, a1[m]);
-        }
-      }
+    for (int a = 0; a < 4; a++)
 #pragma unroll
-      for (int q = 0; q < 8; q++) { S[lane][c0 + q] = a0[q]; S[lane + 32][c0 + q] = a1[q]; }
-    }
-    __syncthreads();
-    const int base = c0 + 8, nrem = T - base;
-    if (nrem > 0) {
-      for (int e = tid; e < nrem * nrem; e += kCholThreads) {
-        const int rr = e / nrem, c2 = e - rr * nrem;
-        if (c2 <= rr) {
-          double s = S[base + rr][base + c2];
-#pragma unroll
-          for (int q = 0; q < 8; q++) s = fma(-S[base + rr][c0 + q], S[base + c2][c0 + q], s);
-          S[base + rr][base + c2] = s;
-        }
-      }
-    }
-    __syncthreads();
+      for (int b = 0; b <= a; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
   }
 }
 
-// X L^T = C in place (C in shared `X`, L lower in shared `L`, rinv[c] = 1/L[c][c]).  4 threads per row, each
-// owning the columns m = q (mod 4); the freshly solved column is broadcast inside the 4-lane group.
-__device__ void trsm_tile(double (*X)[TP], const double (*L)[TP], const double* rinv) {
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int row = tid >> 2, q = tid & 3;
-  double x[16];
+// ---- 64x64 tile factorisation / triangular solve with the tile held in REGISTERS -------------------------
+// Thread (ty,tx) owns the 4x4 fragment rows ty+16a, columns tx+16b — the layout tile_abt produces, so the
+// updated tile never takes a detour through memory.  Eight steps of 8 columns:
+//   owners of the 8 columns write them to shared memory  | bar |
+//   threads 0..63-c0 ("panel"): each holds the 8x8 diagonal block in registers, factors it redundantly (no
+//     shuffles; pivots in pairs so that two reciprocal square roots overlap:
+//     1/sqrt(d1) = sqrt(d0)/sqrt(d0*a11 - a10^2)) and solves its own row against it          | bar |
+//   every thread applies the rank-8 update to its register fragment (blocks already final are pruned at
+//     compile time: the step index is a template parameter).
+template <int P>
+__device__ __forceinline__ void cols_to_smem(double (*S)[TP], const double (&c)[4][4], bool lower_only) {
+  constexpr int c0 = 8 * P, bsel = c0 / 16, txlo = c0 % 16;
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  if (tx >= txlo && tx < txlo + 8) {
+    const int col = tx + 16 * bsel;
 #pragma unroll
-  for (int t = 0; t < 16; t++) x[t] = X[row][4 * t + q];
-#pragma unroll
-  for (int c = 0; c < T; c++) {
-    const int tc = c >> 2, qc = c & 3;
-    double xc = x[tc] * rinv[c];
-    xc = __shfl_sync(0xffffffffu, xc, (lane & ~3) | qc);
-    if (q == qc) x[tc] = xc;
-#pragma unroll
-    for (int t = tc; t < 16; t++) {
-      const int m = 4 * t + q;
-      if (t > tc || q > qc) x[t] = fma(-xc, L[m][c], x[t]);
+    for (int a = 0; a < 4; a++) {
+      const int r = ty + 16 * a;
+      S[r][col] = (!lower_only || r >= col) ? c[a][bsel] : 0.0;
     }
   }
+}
+
+template <int P, bool LOWER>
+__device__ __forceinline__ void frag_rank8(double (&c)[4][4], const double (*Pm)[TP], const double (*Qm)[TP]) {
+  constexpr int c0 = 8 * P, base = c0 + 8;
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
 #pragma unroll
-  for (int t = 0; t < 16; t++) X[row][4 * t + q] = x[t];
+  for (int q = 0; q < 8; q++) {
+    double pv[4], qv[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      if (!LOWER || 16 * a + 15 >= base) pv[a] = Pm[ty + 16 * a][c0 + q];
+      if (16 * a + 15 >= base) qv[a] = Qm[tx + 16 * a][c0 + q];
+    }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++)
+        if ((!LOWER || (16 * a + 15 >= base && b <= a)) && 16 * b + 15 >= base) c[a][b] = fma(-pv[a], qv[b], c[a][b]);
+  }
+}
+
+template <int P>
+__device__ __forceinline__ void factor_panel(double (*S)[TP], int row0, int n, int* chol_fail) {
+  constexpr int c0 = 8 * P;
+  const int tid = threadIdx.x;
+  if (tid < T - c0) {
+    const int r = c0 + tid;
+    double D[8][8], x[8];
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) D[a][b] = S[c0 + a][c0 + b];
+#pragma unroll
+    for (int q = 0; q < 8; q++) x[q] = S[r][c0 + q];
+    bool bad = false;
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      const double d0 = D[c][c], a10 = D[c + 1][c], a11 = D[c + 1][c + 1];
+      const double det = fma(a11, d0, -(a10 * a10));
+      bad = bad || (d0 <= 0.0 && row0 + c0 + c < n) || (det <= 0.0 && row0 + c0 + c + 1 < n);
+      const double rs0 = fast_rsqrt(d0), rsd = fast_rsqrt(det);
+      const double sq0 = d0 * rs0;
+      const double rs1 = sq0 * rsd;            // 1/sqrt(d1), d1 = det/d0
+      const double l10 = a10 * rs0;
+      D[c + 1][c] = l10;
+#pragma unroll
+      for (int a = c + 2; a < 8; a++) {
+        D[a][c] *= rs0;
+        D[a][c + 1] = fma(-D[a][c], l10, D[a][c + 1]) * rs1;
+      }
+#pragma unroll
+      for (int a = c + 2; a < 8; a++)
+#pragma unroll
+        for (int b = c + 2; b <= a; b++) D[a][b] = fma(-D[a][c + 1], D[b][c + 1], fma(-D[a][c], D[b][c], D[a][b]));
+      // this thread's own row against the two finished columns (x L8^T = a); for the rows of the diagonal
+      // block itself this reproduces the row of L8 (entries right of the diagonal are masked at the store)
+      double s0 = x[c], s1 = x[c + 1];
+#pragma unroll
+      for (int m = 0; m < c; m++) { s0 = fma(-x[m], D[c][m], s0); s1 = fma(-x[m], D[c + 1][m], s1); }
+      x[c] = s0 * rs0;
+      x[c + 1] = fma(-x[c], l10, s1) * rs1;
+    }
+    if (tid == 0 && bad) atomicExch(chol_fail, 1);      // NaN pivots pass, like Eigen's `d <= 0` test
+#pragma unroll
+    for (int q = 0; q < 8; q++) S[r][c0 + q] = (tid < q) ? 0.0 : x[q];
+  }
+}
+
+__device__ long long* g_chol_fine = nullptr;   // debug: clock64 marks inside one factor_tile call
+__device__ __forceinline__ void fine_mark(int slot) {
+  if (g_chol_fine != nullptr && threadIdx.x == 0) g_chol_fine[slot] = clock64();
+}
+template <int P>
+__device__ __forceinline__ void factor_step(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail) {
+  fine_mark(4 * P);
+  cols_to_smem<P>(S, c, true);
+  __syncthreads();
+  fine_mark(4 * P + 1);
+  factor_panel<P>(S, row0, n, chol_fail);
+  fine_mark(4 * P + 2);
+  __syncthreads();
+  fine_mark(4 * P + 3);
+  if (P < 7) frag_rank8<P, true>(c, S, S);
+}
+
+// In: the tile as register fragments `c` (lower triangle meaningful).  Out: L in shared S (strict upper zero).
+__device__ __forceinline__ void factor_tile(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail) {
+  factor_step<0>(c, S, row0, n, chol_fail); factor_step<1>(c, S, row0, n, chol_fail);
+  factor_step<2>(c, S, row0, n, chol_fail); factor_step<3>(c, S, row0, n, chol_fail);
+  factor_step<4>(c, S, row0, n, chol_fail); factor_step<5>(c, S, row0, n, chol_fail);
+  factor_step<6>(c, S, row0, n, chol_fail); factor_step<7>(c, S, row0, n, chol_fail);
+  __syncthreads();
+}
+
+template <int P>
+__device__ __forceinline__ void trsm_step(double (&c)[4][4], double (*X)[TP], const double (*L)[TP], const double* rinv) {
+  constexpr int c0 = 8 * P;
+  const int tid = threadIdx.x;
+  cols_to_smem<P>(X, c, false);
+  __syncthreads();
+  if (tid < T) {
+    double D[8][8], x[8];
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+      for (int b = 0; b < a; b++) D[a][b] = L[c0 + a][c0 + b];
+#pragma unroll
+    for (int q = 0; q < 8; q++) x[q] = X[tid][c0 + q];
+#pragma unroll
+    for (int cc = 0; cc < 8; cc++) {
+      double sacc = x[cc];
+#pragma unroll
+      for (int m = 0; m < cc; m++) sacc = fma(-x[m], D[cc][m], sacc);
+      x[cc] = sacc * rinv[c0 + cc];
+    }
+#pragma unroll
+    for (int q = 0; q < 8; q++) X[tid][c0 + q] = x[q];
+  }
+  __syncthreads();
+  if (P < 7) frag_rank8<P, false>(c, X, L);
+}
+
+// X L^T = C: C as register fragments `c`, L (lower) in shared `L`, rinv[k] = 1/L[k][k].  Out: X in shared `X`.
+__device__ __forceinline__ void trsm_tile(double (&c)[4][4], double (*X)[TP], const double (*L)[TP], const double* rinv) {
+  trsm_step<0>(c, X, L, rinv); trsm_step<1>(c, X, L, rinv); trsm_step<2>(c, X, L, rinv); trsm_step<3>(c, X, L, rinv);
+  trsm_step<4>(c, X, L, rinv); trsm_step<5>(c, X, L, rinv); trsm_step<6>(c, X, L, rinv); trsm_step<7>(c, X, L, rinv);
+  __syncthreads();
+}
+
+// optional timeline of the panel chain (debug/profiling; db200_debug_chol_trace): trace[8*s + e] = globaltimer ns
+__device__ long long* g_chol_trace = nullptr;
+__device__ __forceinline__ void trace_mark(int s, int e) {
+  if (g_chol_trace != nullptr && threadIdx.x == 0) {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_chol_trace[8 * s + e] = t;
+  }
+}
+
+struct CholCtx {
+  double (*sA)[TP]; double (*sB)[TP]; double (*sC)[TP]; double* sv; int* s_ok;
+  double* W; CholFlags F; int nt, ld, n; bool panel_full;
+};
+
+__device__ __forceinline__ double* tile_ptr(const CholCtx& cx, int i, int j) { return cx.W + size_t(i) * T * cx.ld + size_t(j) * T; }
+
+// acc = L(i,s-1) L(j,s-1)^T (waits until both panel tiles are final).  Uses sA (and sB when i != j).
+__device__ __forceinline__ bool apply_panel(CholCtx& cx, int i, int j, int s, double (&acc)[4][4]) {
+  const int k = s - 1, ck = colstart(k, cx.nt);
+  if (!cx.panel_full) {
+    if (threadIdx.x == 0) *cx.s_ok = (ld_acquire(cx.F.panel_done + k) >= unsigned(cx.nt + 1 - k)) ? 1 : 0;
+    __syncthreads();
+    cx.panel_full = *cx.s_ok != 0;
+    __syncthreads();
+    if (!cx.panel_full) {
+      if (!wait_flag(cx.F.ready + ck + (i - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+      if (i != j && !wait_flag(cx.F.ready + ck + (j - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+    }
+  }
+  load_tile(cx.sA, tile_ptr(cx, i, k), cx.ld);
+  if (i != j) load_tile(cx.sB, tile_ptr(cx, j, k), cx.ld);
+  __syncthreads();
+  if (i != j) tile_abt(cx.sA, cx.sB, acc);
+  else tile_aat_lower(cx.sA, acc);
+  __syncthreads();
+  return true;
+}
+
+// S[r][c] = C(i,j)[r][c] - acc  for this thread's fragment (C prefetched into `c` before the product)
+__device__ __forceinline__ void frag_to_smem(double (*S)[TP], const double (&c)[4][4], const double (&acc)[4][4]) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) S[ty + 16 * a][tx + 16 * b] = c[a][b] - acc[a][b];
+}
+
+// generic tile (i,j), j >= s, at step s: apply panel s-1; if j == s also finish it (triangular solve) and publish
+__device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
+  double cf[4][4], acc[4][4];
+  double* Cg = tile_ptr(cx, i, j);
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  load_frag(cf, Cg, cx.ld);                        // in flight while the panel product runs
+  if (s > 0) {
+    if (!apply_panel(cx, i, j, s, acc)) return false;
+  } else {
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
+  }
+  if (j > s) {
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b < 4; b++) __stcg(Cg + size_t(ty + 16 * a) * cx.ld + tx + 16 * b, cf[a][b] - acc[a][b]);
+    return true;
+  }
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
+  const int cs = colstart(s, cx.nt);
+  if (!wait_flag(cx.F.ready + cs, 1u, cx.F.ctl, cx.s_ok)) return false;
+  load_tile(cx.sB, tile_ptr(cx, s, s), cx.ld);
+  __syncthreads();
+  if (threadIdx.x < T) cx.sv[threadIdx.x] = 1.0 / cx.sB[threadIdx.x][threadIdx.x];
+  __syncthreads();
+  trsm_tile(cf, cx.sA, cx.sB, cx.sv);
+  store_tile(Cg, cx.sA, cx.ld);
+  publish(cx.F.ready + cs + (i - s), cx.F.panel_done + s);
+  __syncthreads();
+  return true;
 }
 
 // ---- the solver: ONE cooperative launch ------------------------------------------------------------------
-// Static tile ownership (tile idx -> CTA idx mod G) + release/acquire ready flags instead of grid barriers:
-//   step s, for every owned tile (i,j) with j >= s:
-//     s > 0:  wait L(i,s-1), L(j,s-1);  C(i,j) -= L(i,s-1) L(j,s-1)^T
-//     j == s: i == j ? factor the tile : (wait L(s,s); solve X L(s,s)^T = C)   -> publish L(i,s)
-// Tiles of block column s are the first ones in every CTA's list at step s, so the panel of step s is formed
-// while the other CTAs are still applying panel s-1 (look-ahead falls out of the data flow).
-// Then x = L^-T y: CTA j (j < nt) owns x_j = L_jj^-T (y_j - sum_{i>j} L_ij^T x_i), consuming x_i as they appear.
+// Static tile ownership + release/acquire ready flags instead of grid barriers or per-step launches.
+//   owner(i,j) = idx(i,j) mod G, except that the sub-diagonal tile (d,d-1) belongs to the owner D(d) of the
+//   diagonal tile (d,d): the panel chain  L(d,d-1) -> update (d,d) -> factor (d,d)  then stays inside one CTA
+//   (operands in shared memory), and only the finished diagonal tile crosses CTAs per step.
+//   step s (panel s-1 is applied to every tile with j >= s, block column s becomes final):
+//     CTA D(s+1): [a] (d,d) -= L(d,s-1)L(d,s-1)^T; [b] tile (d,s): apply panel s-1, wait L(s,s), triangular solve;
+//                 [c] (d,d) -= L(d,s)L(d,s)^T, factor, publish              (d = s+1)
+//     every CTA : its other tiles in index order (block column s first): panel update, and for j == s the
+//                 triangular solve against L(s,s) + publish.
+// The trailing updates of step s overlap the panel chain of step s+1 (look-ahead falls out of the data flow).
+// Then x = L^-T y: CTA nt-1-j owns x_j = L_jj^-T (y_j - sum_{i>j} L_ij^T x_i), consuming x_i as they appear.
 __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double (*sA)[TP] = reinterpret_cast<double (*)[TP]>(smem_raw);
-  double (*sB)[TP] = reinterpret_cast<double (*)[TP]>(smem_raw + sizeof(double) * T * TP);
-  double* sv = reinterpret_cast<double*>(smem_raw + 2 * sizeof(double) * T * TP);   // [6*64] scratch vectors
   __shared__ int s_ok;
+  CholCtx cx;
+  cx.sA = reinterpret_cast<double (*)[TP]>(smem_raw);
+  cx.sB = reinterpret_cast<double (*)[TP]>(smem_raw + sizeof(double) * T * TP);
+  cx.sC = reinterpret_cast<double (*)[TP]>(smem_raw + 2 * sizeof(double) * T * TP);
+  cx.sv = reinterpret_cast<double*>(smem_raw + 3 * sizeof(double) * T * TP);   // [6*64] scratch vectors
+  cx.s_ok = &s_ok;
+  cx.W = p.Wk; cx.nt = p.nt; cx.ld = p.ld; cx.n = p.n;
+  cx.F = chol_flags(p.cflags, p.nt);
   const int nt = p.nt, ld = p.ld, n = p.n;
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
-  const int ty = tid >> 4, tx = tid & 15;
-  const CholFlags F = chol_flags(p.cflags, nt);
-  unsigned* err = F.ctl;
-  double* W = p.Wk;
   const int ntiles = num_tiles(nt);
+  const CholFlags& F = cx.F;
 
   for (int s = 0; s < nt; s++) {
     const int cs = colstart(s, nt);
-    int idx = cs + ((cta - cs) % G + G) % G;        // first owned tile index >= colstart(s)
-    bool panel_full = (s == 0);
-    int j = s;
-    for (; idx < ntiles; idx += G) {
-      while (idx >= colstart(j + 1, nt)) j++;
-      const int i = j + (idx - colstart(j, nt));
-      double acc[4][4];
-      double* Cg = W + size_t(i) * T * ld + size_t(j) * T;
-      if (s > 0) {
-        if (!panel_full) {
-          if (tid == 0) s_ok = (ld_acquire(F.panel_done + (s - 1)) >= unsigned(nt + 1 - (s - 1))) ? 1 : 0;
-          __syncthreads();
-          panel_full = s_ok != 0;
-          __syncthreads();
-          if (!panel_full) {
-            if (!wait_flag(F.ready + colstart(s - 1, nt) + (i - (s - 1)), 1u, err, &s_ok)) return;
-            if (i != j && !wait_flag(F.ready + colstart(s - 1, nt) + (j - (s - 1)), 1u, err, &s_ok)) return;
-          }
-        }
-        load_tile(sA, W + size_t(i) * T * ld + size_t(s - 1) * T, ld);
-        if (i != j) load_tile(sB, W + size_t(j) * T * ld + size_t(s - 1) * T, ld);
-        __syncthreads();
-        tile_abt(sA, (i != j) ? sB : sA, acc);
-        __syncthreads();
-      } else {
+    cx.panel_full = (s == 0);
+    if (s == 0 && cta == 0) {                       // D(0): the first diagonal tile
+      double c0f[4][4];
+      load_frag(c0f, tile_ptr(cx, 0, 0), ld);
+      factor_tile(c0f, cx.sB, 0, n, &p.hdr->chol_fail);
+      store_tile(tile_ptr(cx, 0, 0), cx.sB, ld);
+      publish(F.ready + 0, F.panel_done + 0);
+      trace_mark(0, 3);
+      __syncthreads();
+    }
+    const int d = s + 1;
+    if (d < nt && cta == colstart(d, nt) % G) {     // the panel chain of this step
+      double cf[4][4], acc[4][4];
+      // [a] diagonal tile: panel s-1
+      load_frag(cf, tile_ptr(cx, d, d), ld);
+      if (s > 0) { if (!apply_panel(cx, d, d, s, acc)) return; }
+      else {
 #pragma unroll
         for (int a = 0; a < 4; a++)
 #pragma unroll
           for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
       }
-      if (j > s) {                                   // bulk tile: C -= acc in global memory
-#pragma unroll
-        for (int a = 0; a < 4; a++)
-#pragma unroll
-          for (int b = 0; b < 4; b++) {
-            double* g = Cg + size_t(ty + 16 * a) * ld + tx + 16 * b;
-            __stcg(g, __ldcg(g) - acc[a][b]);
-          }
-        continue;
-      }
-      // panel tile (j == s): finish it now
+      frag_to_smem(cx.sC, cf, acc);
+      // [b] sub-diagonal tile (d,s): panel s-1, then the triangular solve against L(s,s)
+      load_frag(cf, tile_ptr(cx, d, s), ld);
+      if (s > 0) { if (!apply_panel(cx, d, s, s, acc)) return; }
 #pragma unroll
       for (int a = 0; a < 4; a++)
 #pragma unroll
-        for (int b = 0; b < 4; b++) {
-          const int r = ty + 16 * a, c = tx + 16 * b;
-          sA[r][c] = __ldcg(Cg + size_t(r) * ld + c) - acc[a][b];
-        }
+        for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
+      if (!wait_flag(F.ready + cs, 1u, F.ctl, &s_ok)) return;
+      trace_mark(s, 4);
+      load_tile(cx.sB, tile_ptr(cx, s, s), ld);
       __syncthreads();
-      if (i == j) {
-        factor_tile(sA, s * T, n, &p.hdr->chol_fail);
-      } else {
-        if (!wait_flag(F.ready + cs, 1u, err, &s_ok)) return;
-        load_tile(sB, W + size_t(s) * T * ld + size_t(s) * T, ld);
-        __syncthreads();
-        if (tid < T) sv[tid] = 1.0 / sB[tid][tid];
-        __syncthreads();
-        trsm_tile(sA, sB, sv);
+      if (tid < T) cx.sv[tid] = 1.0 / cx.sB[tid][tid];
+      __syncthreads();
+      trsm_tile(cf, cx.sA, cx.sB, cx.sv);
+      trace_mark(s, 5);
+      store_tile(tile_ptr(cx, d, s), cx.sA, ld);
+      // [c] diagonal tile: panel s straight from shared memory, factor from registers
+      tile_aat_lower(cx.sA, acc);
+      {
+        const int ty = tid >> 4, tx = tid & 15;
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+          for (int b = 0; b < 4; b++) cf[a][b] = cx.sC[ty + 16 * a][tx + 16 * b] - acc[a][b];
       }
+      publish(F.ready + cs + 1, F.panel_done + s, kCholThreads - 1);   // L(d,s): released by the last warp
+      trace_mark(d, 1);
+      factor_tile(cf, cx.sB, d * T, n, &p.hdr->chol_fail);
+      trace_mark(d, 2);
+      store_tile(tile_ptr(cx, d, d), cx.sB, ld);
+      publish(F.ready + colstart(d, nt), F.panel_done + d);
+      trace_mark(d, 3);
       __syncthreads();
-      store_tile(Cg, sA, ld);
-      publish(F.ready + idx, F.panel_done + s);
-      __syncthreads();
+    }
+    // generic tiles of this CTA
+    int idx = cs + ((cta - cs) % G + G) % G;        // first owned tile index >= colstart(s)
+    int j = s;
+    for (; idx < ntiles; idx += G) {
+      while (idx >= colstart(j + 1, nt)) j++;
+      const int i = j + (idx - colstart(j, nt));
+      if (i == j + 1 && i < nt) continue;           // sub-diagonal tiles travel with their diagonal tile
+      if (i == j) {
+        if (j <= s + 1) continue;                   // (s,s) is final, (s+1,s+1) was handled by the chain code above
+        if (!process_tile(cx, j, j, s)) return;     // diagonal tile j >= s+2 ...
+        if (!process_tile(cx, j, j - 1, s)) return; // ... and its sub-diagonal companion (j-1 > s: trailing update)
+        continue;
+      }
+      if (!process_tile(cx, i, j, s)) return;
     }
   }
 
   // ---- back-substitution L^T x = y (y = row ld of the factor) ------------------------------------------
+  double* sv = cx.sv;
   for (int j = nt - 1 - cta; j >= 0; j -= G) {
-    // the whole block column j must be final
-    if (!wait_flag(F.panel_done + j, unsigned(nt + 1 - j), err, &s_ok)) return;
-    // inverse of L_jj^T applied by substitution: keep L_jj in sA
-    load_tile(sA, W + size_t(j) * T * ld + size_t(j) * T, ld);
+    if (!wait_flag(F.panel_done + j, unsigned(nt + 1 - j), F.ctl, &s_ok)) return;   // the whole block column is final
+    load_tile(cx.sA, tile_ptr(cx, j, j), ld);
     __syncthreads();
-    if (tid < T) sv[320 + tid] = 1.0 / sA[tid][tid];
+    if (tid < T) sv[320 + tid] = 1.0 / cx.sA[tid][tid];
+    __syncthreads();
+    // M = L_jj^-1 into sB (thread t < 64 = column t, forward substitution; off the critical path for all but the last block)
+    if (tid < T) {
+      const int t = tid;
+      for (int r = 0; r < T; r++) {
+        double v = 0.0;
+        if (r >= t) {
+          double s0 = (r == t) ? 1.0 : 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+          int k = t;
+          for (; k + 3 < r; k += 4) {
+            s0 = fma(-cx.sA[r][k], cx.sB[k][t], s0);
+            s1 = fma(-cx.sA[r][k + 1], cx.sB[k + 1][t], s1);
+            s2 = fma(-cx.sA[r][k + 2], cx.sB[k + 2][t], s2);
+            s3 = fma(-cx.sA[r][k + 3], cx.sB[k + 3][t], s3);
+          }
+          for (; k < r; k++) s0 = fma(-cx.sA[r][k], cx.sB[k][t], s0);
+          v = ((s0 + s1) + (s2 + s3)) * sv[320 + r];
+        }
+        cx.sB[r][t] = v;
+      }
+    }
     // partial sums: thread (c = tid & 63, g = tid >> 6) accumulates sum over rows 16g..16g+15 of L_ij[r][c] x_i[r]
     const int c = tid & 63, g4 = tid >> 6;
     double part = 0.0;
     for (int i = nt - 1; i > j; i--) {
-      const double* Lij = W + size_t(i) * T * ld + size_t(j) * T;
+      const double* Lij = tile_ptr(cx, i, j);
       double lv[16];
 #pragma unroll
-      for (int r = 0; r < 16; r++) lv[r] = __ldcg(Lij + size_t(16 * g4 + r) * ld + c);   // prefetch before the wait
-      if (!wait_flag(F.xready + i, 1u, err, &s_ok)) return;
+      for (int r = 0; r < 16; r++) lv[r] = __ldcg(Lij + size_t(16 * g4 + r) * ld + c);   // in flight during the wait
+      if (!wait_flag(F.xready + i, 1u, F.ctl, &s_ok)) return;
       if (tid < T) sv[tid] = __ldcg(p.xsol + size_t(i) * T + tid);
       __syncthreads();
 #pragma unroll
@@ -332,25 +573,20 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     sv[64 + tid] = part;
     __syncthreads();
     if (tid < T) {
-      const double y = __ldcg(W + size_t(ld) * ld + size_t(j) * T + tid);
-      sv[tid] = y - (sv[64 + tid] + sv[128 + tid] + sv[192 + tid] + sv[256 + tid]);
+      const double y = __ldcg(cx.W + size_t(ld) * ld + size_t(j) * T + tid);
+      sv[tid] = y - ((sv[64 + tid] + sv[128 + tid]) + (sv[192 + tid] + sv[256 + tid]));
     }
     __syncthreads();
-    // backward substitution with L_jj^T by warp 0: lane holds rows lane, lane+32
-    if (tid < 32) {
-      double v0 = sv[tid], v1 = sv[tid + 32];
-      for (int cc = T - 1; cc >= 0; cc--) {
-        const double piv = (cc < 32) ? v0 : v1;
-        const double xc = __shfl_sync(0xffffffffu, piv, cc & 31) * sv[320 + cc];
-        if (tid == (cc & 31)) { if (cc < 32) v0 = xc; else v1 = xc; }
-        // rows r < cc: y_r -= L[cc][r] * x_cc
-        if (tid < cc) v0 = fma(-sA[cc][tid], xc, v0);
-        if (tid + 32 < cc) v1 = fma(-sA[cc][tid + 32], xc, v1);
-      }
-      __stcg(p.xsol + size_t(j) * T + tid, v0);
-      __stcg(p.xsol + size_t(j) * T + tid + 32, v1);
-    }
+    // x_c = sum_{r >= c} M[r][c] * rhs[r]
+    double px = 0.0;
+#pragma unroll
+    for (int r = 0; r < 16; r++) px = fma(cx.sB[16 * g4 + r][c], sv[16 * g4 + r], px);
+    __syncthreads();
+    sv[64 + tid] = px;
+    __syncthreads();
+    if (tid < T) __stcg(p.xsol + size_t(j) * T + tid, (sv[64 + tid] + sv[128 + tid]) + (sv[192 + tid] + sv[256 + tid]));
     publish(F.xready + j, nullptr);
+    trace_mark(nt + j, 0);
     __syncthreads();
   }
 }
@@ -454,7 +690,7 @@ static int chol_grid_size(size_t smem) {
 int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   chol_prepare_kernel<<<4 * kNumSMs, 256, 0, st>>>(p, lm, ep);
   DB200_CHECK_LAUNCH();
-  const size_t smem = 2 * sizeof(double) * T * TP + sizeof(double) * 6 * 64;
+  const size_t smem = 3 * sizeof(double) * T * TP + sizeof(double) * 6 * 64;
   int grid = chol_grid_size(smem);
   if (grid < 1) { db200_note_cuda_error(int(cudaGetLastError()), __FILE__, __LINE__); return DB200_ERR_CUDA; }
   const int ntiles = num_tiles(p.nt);
@@ -466,6 +702,14 @@ int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
+
+}  // namespace db200
+extern "C" int db200_debug_chol_trace(long long* device_buffer) {
+  long long* fine = device_buffer ? device_buffer + 8 * 1024 : nullptr;   // marks inside factor_tile (buffer >= 8*1024+64 int64)
+  if (cudaMemcpyToSymbol(db200::g_chol_fine, &fine, sizeof(fine)) != cudaSuccess) return DB200_ERR_CUDA;
+  return cudaMemcpyToSymbol(db200::g_chol_trace, &device_buffer, sizeof(device_buffer)) == cudaSuccess ? DB200_OK : DB200_ERR_CUDA;
+}
+namespace db200 {
 
 int ba_post_solve(const BAParams& p, float* dx_out, cudaStream_t st) {
   post_dx_kernel<<<cdiv(p.n, 256), 256, 0, st>>>(p, dx_out);

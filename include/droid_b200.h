@@ -48,6 +48,8 @@ const char* db200_last_cuda_error(void); /* text of the last CUDA error the libr
 long long db200_launch_count(void);
 void db200_profile_enable(int on);
 int db200_profile_collect(double* ms_out, int* count_out);
+/* debug timeline of the Cholesky panel chain: device buffer of 8*(2*nt) int64 (globaltimer ns), NULL = off */
+int db200_debug_chol_trace(long long* device_buffer);
 
 /* ---- correlation lookup ------------------------------------------------------------------
  * corr_index_forward  (droid.cpp:170-178, correlation_kernels.cu:20-70,126-155)

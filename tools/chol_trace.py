@@ -1,0 +1,40 @@
+"""Timeline of the Cholesky panel chain on the c3 problem (debug aid; run on the GPU box)."""
+import os, sys
+import ctypes as C
+import numpy as np, torch
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [REPO, os.path.join(REPO, "droid-slam_reserch_b200")]
+import droid_backends
+from droid_b200 import _capi, synth
+p = synth.config_c3()
+dev = torch.device("cuda:0")
+t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+args = [t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)]
+nt = (6 * (p.t1 - p.t0) + 63) // 64
+buf = torch.zeros(8 * 1024 + 64, dtype=torch.int64, device=dev)
+for it in range(3):
+    poses, disps = t(p.poses), t(p.disps)
+    if it == 2:
+        _capi.lib().db200_debug_chol_trace(C.c_void_p(buf.data_ptr()))
+    droid_backends.ba(poses, disps, args[0], args[1], args[2], args[3], args[4], args[5], args[6], p.t0, p.t1, 1, 1e-5, 1e-2, False)
+    torch.cuda.synchronize()
+_capi.lib().db200_debug_chol_trace(C.c_void_p(0))
+tr = buf.cpu().numpy().reshape(-1, 8)[: 2 * nt].astype(np.float64)
+t0 = tr[0, 1]
+print("step: upd_start  upd->fac  factor  publish | trsm: flag_seen-after_pub  trsm  publish | step period")
+prev = None
+for s in range(nt):
+    r = tr[s]
+    per = (r[3] - prev) if prev else 0.0
+    prev = r[3]
+    print(f"{s:3d}: {(r[0]-t0)/1e3:8.1f} {(r[1]-r[0])/1e3:6.1f} {(r[2]-r[1])/1e3:6.1f} {(r[3]-r[2])/1e3:6.1f} | "
+          f"{(r[4]-r[3])/1e3:6.1f} {(r[5]-r[4])/1e3:6.1f} {(r[6]-r[5])/1e3:6.1f} | {per/1e3:6.1f}")
+xs = tr[nt:2 * nt, 0]
+print("factor total us:", (tr[nt - 1, 3] - t0) / 1e3, " backsub us:", (xs[0] - xs[nt - 1]) / 1e3, " backsub per block us:", (xs[0] - xs[nt - 1]) / 1e3 / (nt - 1))
+
+fine = buf.cpu().numpy()[8 * 1024: 8 * 1024 + 33].astype(np.float64)
+print("inside the last factor_tile (cycles): per step  [cols->smem+bar, panel, bar, rank8 update]")
+for P in range(8):
+    a = fine[4 * P: 4 * P + 5]
+    nxt = fine[4 * P + 4] if P < 7 else np.nan
+    print(P, [a[1] - a[0], a[2] - a[1], a[3] - a[2], nxt - a[3]])
