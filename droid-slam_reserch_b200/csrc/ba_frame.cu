@@ -3,15 +3,19 @@
 // disp_retr_kernel and the host-side block assembly of /root/reference/src/droid_kernels.cu
 // (:176-424, :854-874, :1001-1115, :933-946, :1117-1190, :1222-1311).
 //
-// One CTA = (source frame k, pixel split s), 256 threads = 256 pixels per sub-tile.
-//   phase 1 (thread = pixel): loop over the frame's edges; reprojection, residual, J_j, J_z;
-//           C,w summed in registers; E_e[6] written to the shared-memory stash; the 27 per-edge sums
-//           (Hjj lower triangle + vj) reduced with a transposing shuffle butterfly (31 shuffles for 32
-//           values) into per-warp shared accumulators — no global atomics, no HBM round trip for E.
-//   phase 2 (thread = (edge pair, k-group)): G_ef += (E_e Q) E_f^T over the sub-tile from the stash,
-//           36 register accumulators per pair, persistent over the CTA's sub-tiles.
+// ba_schur_kernel (full BA).  One CTA = (source frame k, pixel split s), 256 threads, 64-pixel chunks:
+//   phase 1 (thread = (edge, pixel lane)): every thread owns ONE edge of the frame and walks the chunk's pixels
+//           with a stride: reprojection, residual, J_j, J_z; the 27 per-edge sums (Hjj lower triangle + vj)
+//           accumulate in REGISTERS over all chunks (one cross-lane reduction per CTA, not per pixel);
+//           E_e[6] and the edge's C/w contributions go to shared memory.
+//   phase 1b (thread = pixel): C, w over the frame's edges in edge order -> Q = 1/C, w to HBM; the stash is
+//           scaled by sqrt(Q) and split into TF32 hi/lo parts; one extra row holds sqrt(Q) w.
+//   phase 2 (warp = list of 16x8 output tiles): G = Es Es^T (lower) and g = Es (sqrt(Q) w) on the tensor
+//           cores, mma.sync m16n8k8 TF32 with the 3-product split (hi*hi + hi*lo + lo*hi: fp32-faithful),
+//           accumulators persistent in registers over the CTA's chunks.
 //   epilogue: fp64 6x6 transforms with A_e and scatter of this CTA's contribution into the reduced
 //           system with fp64 red.global.add (the only atomics; they carry ~d^2*36 values per CTA).
+// ba_frame_kernel<.,true> (motion-only BA): thread = pixel, shuffle-butterfly reduction of the 27 sums.
 // HBM traffic per edge-pixel: target 8 B + weight 8 B (+ disp 4 B per keyframe-pixel) — the algorithmic
 // 20*HW*N + 16*HW*M of SURVEY.md §8d; the back-substitution re-reads weight (8 B) to recompute E.
 #include "ba.cuh"
@@ -411,6 +415,387 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// fused Schur accumulation on the tensor cores (non-motion BA)
+constexpr int kChunk = 64;                 // pixels per chunk
+constexpr int kStride = kChunk + 4;        // stash row stride (floats): 4*row + col -> conflict-free MMA fragment loads
+
+__host__ __device__ inline int schur_rows(int d) { return 6 * d + 1; }                    // E rows + the sqrt(Q) w row
+__host__ __device__ inline int schur_rpad(int d) { return (schur_rows(d) + 15) / 16 * 16; }
+__host__ __device__ inline int schur_gn(int d) { return (6 * d + 7) / 8 * 8; }
+constexpr int kSegTiles = 4;               // 16x8 output tiles per segment (one M-row, consecutive N-tiles)
+__host__ __device__ inline int schur_segs(int d) {                                        // segments covering the lower triangle
+  if (d <= 0) return 0;
+  const int nM = (schur_rows(d) + 15) / 16, nN = (6 * d + 7) / 8;
+  int t = 0;
+  for (int i = 0; i < nM; i++) { const int c = 2 * i + 2; t += ((c < nN ? c : nN) + kSegTiles - 1) / kSegTiles; }
+  return t;
+}
+
+struct SchurSmem {
+  double* Ws; double* cs;                  // [dcap][36], [dcap][6]
+  float* shi; float* slo;                  // [rpad][kStride] stash, hi / lo TF32 parts     (aliased by G, red in the epilogue)
+  float* G; float* red;                    // [rpad][gn], [256][27]
+  float* Cw;                               // [necap][2][kChunk]
+  float* px;                               // [7][kChunk]: X0, X1, disp, sqrt(Q), sqrt(Q) w, disps_sens, eta
+  float* Am; float* Hs;                    // [dcap][36], [dcap][27]
+  int* jp; int* slotq; int* eslot;         // [dcap], [dcap], [necap]
+  unsigned char* segs;                     // [nsegs][4]: M-tile, first N-tile, count
+};
+
+__host__ __device__ inline size_t schur_alias_floats(int dcap) {
+  const size_t stash = size_t(2) * schur_rpad(dcap) * kStride;
+  const size_t epi = size_t(schur_rpad(dcap)) * schur_gn(dcap) + size_t(256) * 27;
+  return stash > epi ? stash : epi;
+}
+__host__ __device__ inline size_t schur_smem_bytes(int dcap, int necap) {
+  size_t b = sizeof(double) * size_t(dcap > 0 ? dcap : 1) * 42;
+  b += sizeof(float) * (schur_alias_floats(dcap) + size_t(necap) * 2 * kChunk + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
+  b += sizeof(int) * (size_t(2) * (dcap > 0 ? dcap : 1) + necap);
+  b += 4 * size_t(schur_segs(dcap) + 8);
+  return (b + 15) / 16 * 16;
+}
+__device__ __forceinline__ SchurSmem schur_carve(unsigned char* base, int dcap, int necap) {
+  SchurSmem s;
+  const int dc = dcap > 0 ? dcap : 1;
+  s.Ws = reinterpret_cast<double*>(base);
+  s.cs = s.Ws + size_t(dc) * 36;
+  s.shi = reinterpret_cast<float*>(s.cs + size_t(dc) * 6);
+  s.slo = s.shi + size_t(schur_rpad(dcap)) * kStride;
+  s.G = s.shi;
+  s.red = s.shi + size_t(schur_rpad(dcap)) * schur_gn(dcap);
+  s.Cw = s.shi + schur_alias_floats(dcap);
+  s.px = s.Cw + size_t(necap) * 2 * kChunk;
+  s.Am = s.px + 7 * kChunk;
+  s.Hs = s.Am + size_t(dc) * 36;
+  s.jp = reinterpret_cast<int*>(s.Hs + size_t(dc) * 27);
+  s.slotq = s.jp + dc;
+  s.eslot = s.slotq + dc;
+  s.segs = reinterpret_cast<unsigned char*>(s.eslot + necap);
+  return s;
+}
+
+__device__ __forceinline__ float to_tf32(float x) {
+  unsigned u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+// D += A(16x8, row) * B(8x8, col), TF32 inputs, fp32 accumulate
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const float (&a)[4], const float (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+                 "r"(__float_as_uint(b[0])), "r"(__float_as_uint(b[1])));
+}
+
+__device__ __forceinline__ void ldsm_x4(float (&r)[4], unsigned addr) {
+  unsigned a, b, c, d;
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
+  r[0] = __uint_as_float(a); r[1] = __uint_as_float(b); r[2] = __uint_as_float(c); r[3] = __uint_as_float(d);
+}
+
+// grid = Mcap * S CTAs; CTA (k, s) handles chunks s, s+S, ... of source frame kx[k]; launches are bucketed by
+// degree: only frames with dlo <= nd[k] <= dcap work here (shared memory and NSEG grow with the bucket).
+template <int NSEG>
+__global__ void __launch_bounds__(kBAThreads, (NSEG <= 2 ? 2 : 1))
+ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (p.hdr->status < 0) return;
+  const int k = blockIdx.x / S, split = blockIdx.x - k * S;
+  if (k >= p.hdr->M) return;
+  const int d = p.nd[k];
+  if (d < dlo || d > dcap) return;
+  const int f = p.kx[k];
+  if (f < p.own_lo || f >= p.own_hi) return;       // depth map owned by another rank
+  const int q_beg = p.deg_off[k], ne = p.deg_off[k + 1] - q_beg;
+  if (ne > necap) { if (threadIdx.x == 0) atomicMin(&p.hdr->status, DB200_ERR_ARG); return; }
+  const SchurSmem sm = schur_carve(smem_raw, dcap, necap);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int HW = p.HW, wd = p.wd;
+  const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const int ip = f - p.t0;                          // pose row of the source frame (<0: fixed)
+  const int nchunks = cdiv(HW, kChunk);
+  const float* dsp = p.disps + size_t(f) * HW;
+  const int R = schur_rows(d), nM = (R + 15) / 16, nN = (6 * d + 7) / 8;
+  const int rpad = schur_rpad(dcap), gn = schur_gn(dcap);
+
+  // ---- set-up: segment list, stash cleared (padding rows must read as zero), thread -> (edge, lane) map
+  int nsegs = 0;
+  for (int i = 0; i < nM && d > 0; i++) { const int c = 2 * i + 2; nsegs += ((c < nN ? c : nN) + kSegTiles - 1) / kSegTiles; }
+  if (tid == 0) {
+    int t = 0;
+    for (int i = 0; i < nM && d > 0; i++) {
+      const int c = 2 * i + 2, cnt = c < nN ? c : nN;
+      for (int j0 = 0; j0 < cnt; j0 += kSegTiles) {
+        sm.segs[4 * t] = (unsigned char)i; sm.segs[4 * t + 1] = (unsigned char)j0;
+        sm.segs[4 * t + 2] = (unsigned char)(cnt - j0 < kSegTiles ? cnt - j0 : kSegTiles); sm.segs[4 * t + 3] = 0;
+        t++;
+      }
+    }
+  }
+  for (int i = tid; i < 2 * rpad * kStride; i += kBAThreads) sm.shi[i] = 0.0f;
+  for (int qq = tid; qq < ne; qq += kBAThreads) {
+    const int sl = p.erec[q_beg + qq].slot;
+    sm.eslot[qq] = sl;
+    if (sl >= 0) sm.slotq[sl] = q_beg + qq;
+  }
+  // pixel lanes per edge: minimise (warps touched) x (pixel iterations)
+  int L = 1;
+  if (ne > 0) {
+    int best = 1 << 30;
+    for (int l = 1; l <= kBAThreads / ne && l <= kChunk; l++) {
+      const int cost = cdiv(ne * l, 32) * cdiv(kChunk, l);
+      if (cost <= best) { best = cost; L = l; }
+    }
+  }
+  const int e = tid / L, g = tid - e * L;
+  const bool active = ne > 0 && e < ne;
+  EdgeRec rec{};
+  int sl = -1;
+  if (active) { rec = load_rec(p.erec + q_beg + e); sl = rec.slot; }
+  const float* tg = p.target + size_t(active ? rec.eid : 0) * 2 * HW;
+  const float* wg = p.weight + size_t(active ? rec.eid : 0) * 2 * HW;
+  float hacc[27];
+#pragma unroll
+  for (int i = 0; i < 27; i++) hacc[i] = 0.0f;
+  float accT[NSEG][kSegTiles][4];
+#pragma unroll
+  for (int u = 0; u < NSEG; u++)
+#pragma unroll
+    for (int q = 0; q < kSegTiles; q++) { accT[u][q][0] = 0.0f; accT[u][q][1] = 0.0f; accT[u][q][2] = 0.0f; accT[u][q][3] = 0.0f; }
+  const int gid = lane >> 2, tig = lane & 3;
+  __syncthreads();
+  // this warp's segments u = 0..NSEG-1 -> segment warp + 8u; ldmatrix row addresses of this lane
+  //   A (x4): matrices {rows 0-7,k 0-3}, {rows 8-15,k 0-3}, {rows 0-7,k 4-7}, {rows 8-15,k 4-7}  -> a0..a3
+  //   B (x4): matrices {hi,k 0-3}, {hi,k 4-7}, {lo,k 0-3}, {lo,k 4-7} of the 8 rows of one N-tile   -> b0h,b1h,b0l,b1l
+  const unsigned shi_base = unsigned(__cvta_generic_to_shared(sm.shi));
+  const unsigned lo_off = unsigned(rpad) * kStride * 4u;
+  const int lm = lane >> 3, lr = lane & 7;
+  unsigned a_addr[NSEG], b_addr[NSEG];
+  int seg_cnt[NSEG], seg_i[NSEG], seg_j0[NSEG];
+#pragma unroll
+  for (int u = 0; u < NSEG; u++) {
+    const int sgi = warp + 8 * u;
+    seg_cnt[u] = 0; seg_i[u] = 0; seg_j0[u] = 0;
+    if (sgi < nsegs) { seg_i[u] = sm.segs[4 * sgi]; seg_j0[u] = sm.segs[4 * sgi + 1]; seg_cnt[u] = sm.segs[4 * sgi + 2]; }
+    a_addr[u] = shi_base + 4u * unsigned((16 * seg_i[u] + lr + 8 * (lm & 1)) * kStride + 4 * (lm >> 1));
+    b_addr[u] = shi_base + (lm >> 1) * lo_off + 4u * unsigned((8 * seg_j0[u] + lr) * kStride + 4 * (lm & 1));
+  }
+  // prefetch of the first chunk's per-pixel data
+  float nx_h = 1.0f, nx_s = 0.0f, nx_e = 0.0f;
+  if (tid < kChunk) {
+    const int pix = split * kChunk + tid;
+    if (split < nchunks && pix < HW) { nx_h = dsp[pix]; nx_s = p.sens[size_t(f) * HW + pix]; nx_e = p.eta[size_t(k) * HW + pix]; }
+  }
+  __syncthreads();
+
+  for (int c = split; c < nchunks; c += S) {
+    const int base = c * kChunk;
+    if (tid < kChunk) {
+      const int pix = base + tid;
+      const int pi_ = pix < HW ? pix : 0;
+      sm.px[tid] = (float(pi_ % wd) - cx) / fx;
+      sm.px[kChunk + tid] = (float(pi_ / wd) - cy) / fy;
+      sm.px[2 * kChunk + tid] = nx_h;
+      sm.px[5 * kChunk + tid] = nx_s;
+      sm.px[6 * kChunk + tid] = nx_e;
+      const int npix = pix + S * kChunk;            // next chunk of this CTA: loads in flight during this one
+      nx_h = 1.0f; nx_s = 0.0f; nx_e = 0.0f;
+      if (c + S < nchunks && npix < HW) { nx_h = dsp[npix]; nx_s = p.sens[size_t(f) * HW + npix]; nx_e = p.eta[size_t(k) * HW + npix]; }
+    }
+    __syncthreads();
+    // ---------------- phase 1
+    if (active) {
+      float n_tu = 0.0f, n_tv = 0.0f, n_wu = 0.0f, n_wv = 0.0f;
+      if (base + g < HW && g < kChunk) {
+        n_tu = __ldg(tg + base + g); n_tv = __ldg(tg + HW + base + g); n_wu = __ldg(wg + base + g); n_wv = __ldg(wg + HW + base + g);
+      }
+      for (int pp = g; pp < kChunk; pp += L) {
+        const float tu = n_tu, tv = n_tv, wur = n_wu, wvr = n_wv;
+        {                                              // loads of the next pixel of this lane are issued before the math
+          const int np = pp + L, npix = base + np;
+          n_tu = 0.0f; n_tv = 0.0f; n_wu = 0.0f; n_wv = 0.0f;
+          if (np < kChunk && npix < HW) {
+            n_tu = __ldg(tg + npix); n_tv = __ldg(tg + HW + npix); n_wu = __ldg(wg + npix); n_wv = __ldg(wg + HW + npix);
+          }
+        }
+        PixEdge pe_;
+        pix_edge(rec, sm.px[pp], sm.px[kChunk + pp], sm.px[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
+        sm.Cw[(size_t(e) * 2 + 0) * kChunk + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
+        sm.Cw[(size_t(e) * 2 + 1) * kChunk + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
+        if (sl >= 0) {                                                         // stereo edges: depth terms only
+          const float au = pe_.wu * pe_.Jzu, av = pe_.wv * pe_.Jzv;
+          float* st = sm.shi + size_t(6 * sl) * kStride + pp;
+#pragma unroll
+          for (int n = 0; n < 6; n++) st[n * kStride] = au * pe_.Ju[n] + av * pe_.Jv[n];   // Eij (:339,372), unscaled for now
+          float wJu[6], wJv[6];
+#pragma unroll
+          for (int n = 0; n < 6; n++) { wJu[n] = pe_.wu * pe_.Ju[n]; wJv[n] = pe_.wv * pe_.Jv[n]; }
+          int l = 0;
+#pragma unroll
+          for (int n = 0; n < 6; n++)
+#pragma unroll
+            for (int m = 0; m <= n; m++) {
+              float a = hacc[l];
+              if (n != 1 && m != 1) a = fmaf(wJu[n], pe_.Ju[m], a);
+              if (n != 0 && m != 0) a = fmaf(wJv[n], pe_.Jv[m], a);
+              hacc[l++] = a;
+            }
+#pragma unroll
+          for (int n = 0; n < 6; n++) hacc[21 + n] = fmaf(wJu[n], pe_.ru, fmaf(wJv[n], pe_.rv, hacc[21 + n]));   // vj (:335,368)
+        }
+      }
+    }
+    __syncthreads();
+    // ---------------- phase 1b: depth system of the chunk (:1396-1400), scaling by sqrt(Q), TF32 split
+    if (tid < kChunk) {
+      const int pix = base + tid;
+      float Csum = 0.0f, wsum = 0.0f;
+      for (int q = 0; q < ne; q++) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + tid]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + tid]; }
+      float Q = 0.0f, wv_ = 0.0f;
+      if (pix < HW) {
+        const float h = sm.px[2 * kChunk + tid];
+        const float ds = sm.px[5 * kChunk + tid];
+        const float m = ds > 0.0f ? 1.0f : 0.0f;
+        const float C = Csum + m * 0.05f + (1.0f - m) * sm.px[6 * kChunk + tid];
+        wv_ = wsum - m * 0.05f * (h - ds);
+        Q = 1.0f / C;
+        p.Q[size_t(k) * HW + pix] = Q;
+        p.w[size_t(k) * HW + pix] = wv_;
+      }
+      const float sq = sqrtf(Q);
+      sm.px[3 * kChunk + tid] = sq;
+      const float vq = sq * wv_;
+      const float hi = to_tf32(vq);
+      sm.shi[size_t(6 * d) * kStride + tid] = hi;
+      sm.slo[size_t(6 * d) * kStride + tid] = to_tf32(vq - hi);
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 6 * d * (kChunk / 4); idx += kBAThreads) {   // 4 pixels per thread and step
+      const int m = idx / (kChunk / 4), pp = 4 * (idx - m * (kChunk / 4));
+      float4* ph = reinterpret_cast<float4*>(sm.shi + size_t(m) * kStride + pp);
+      float4* pl = reinterpret_cast<float4*>(sm.slo + size_t(m) * kStride + pp);
+      const float4 sq4 = *reinterpret_cast<const float4*>(sm.px + 3 * kChunk + pp);
+      float4 x = *ph, hi, lo;
+      x.x *= sq4.x; x.y *= sq4.y; x.z *= sq4.z; x.w *= sq4.w;
+      hi.x = to_tf32(x.x); hi.y = to_tf32(x.y); hi.z = to_tf32(x.z); hi.w = to_tf32(x.w);
+      lo.x = to_tf32(x.x - hi.x); lo.y = to_tf32(x.y - hi.y); lo.z = to_tf32(x.z - hi.z); lo.w = to_tf32(x.w - hi.w);
+      *ph = hi; *pl = lo;
+    }
+    __syncthreads();
+    // ---------------- phase 2: G += Es Es^T on the tensor cores (EEt6x6/Ev6x1, :1001-1093)
+#pragma unroll
+    for (int u = 0; u < NSEG; u++) {
+      if (seg_cnt[u] > 0) {
+#pragma unroll 1
+        for (int k0 = 0; k0 < kChunk; k0 += 8) {
+          float ah[4], al[4], bf[kSegTiles][4];
+          ldsm_x4(ah, a_addr[u] + 4u * k0);
+          ldsm_x4(al, a_addr[u] + lo_off + 4u * k0);
+#pragma unroll
+          for (int q = 0; q < kSegTiles; q++)
+            if (q < seg_cnt[u]) ldsm_x4(bf[q], b_addr[u] + 4u * unsigned(8 * q * kStride + k0));
+          // three passes over the segment's tiles: dependent MMAs on one accumulator are kSegTiles apart
+#pragma unroll
+          for (int q = 0; q < kSegTiles; q++)
+            if (q < seg_cnt[u]) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(accT[u][q], al, bh); }
+#pragma unroll
+          for (int q = 0; q < kSegTiles; q++)
+            if (q < seg_cnt[u]) { const float bl[2] = {bf[q][2], bf[q][3]}; mma_tf32(accT[u][q], ah, bl); }
+#pragma unroll
+          for (int q = 0; q < kSegTiles; q++)
+            if (q < seg_cnt[u]) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(accT[u][q], ah, bh); }
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---------------- epilogue: per-edge sums over the pixel lanes, G tiles -> shared, fp64 transforms, scatter
+  if (active && sl >= 0) {
+#pragma unroll
+    for (int i = 0; i < 27; i++) sm.red[size_t(tid) * 27 + i] = hacc[i];
+  }
+#pragma unroll
+  for (int u = 0; u < NSEG; u++)
+#pragma unroll
+    for (int q = 0; q < kSegTiles; q++)
+      if (q < seg_cnt[u]) {
+        float* gp = sm.G + size_t(16 * seg_i[u] + gid) * gn + 8 * (seg_j0[u] + q) + 2 * tig;
+        gp[0] = accT[u][q][0]; gp[1] = accT[u][q][1]; gp[8 * gn] = accT[u][q][2]; gp[8 * gn + 1] = accT[u][q][3];
+      }
+  __syncthreads();
+  for (int i = tid; i < ne * 27; i += kBAThreads) {       // fixed-order sums over the L lanes of each edge
+    const int q = i / 27, l = i - q * 27, s2 = sm.eslot[q];
+    if (s2 >= 0) {
+      float s = 0.0f;
+      for (int gg = 0; gg < L; gg++) s += sm.red[size_t(q * L + gg) * 27 + l];
+      sm.Hs[s2 * 27 + l] = s;
+    }
+  }
+  for (int q = tid; q < d; q += kBAThreads) {
+    const EdgeRec r = load_rec(p.erec + sm.slotq[q]);
+    sm.jp[q] = r.jpose;
+    build_A(r, sm.Am + q * 36);
+  }
+  __syncthreads();
+  // D_ef[r][c] = [e==f] Hjj_e[r][c] - G_ef[r][c];  c_e = vj_e - g_e     (G lower: mirror the rest)
+  auto Dval = [&](int e1, int f2, int r, int c2) -> double {
+    double v = (e1 == f2) ? double(sm.Hs[e1 * 27 + hs_index(r, c2)]) : 0.0;
+    int row = 6 * e1 + r, col = 6 * f2 + c2;
+    if (col > row) { const int t = row; row = col; col = t; }
+    return v - double(sm.G[size_t(row) * gn + col]);
+  };
+  for (int i = tid; i < d * 6; i += kBAThreads) {
+    const int e1 = i / 6, r = i - e1 * 6;
+    sm.cs[i] = double(sm.Hs[e1 * 27 + 21 + r]) - double(sm.G[size_t(6 * d) * gn + i]);
+  }
+  for (int i = tid; i < d * 36; i += kBAThreads) {   // W_f = sum_e A_e D_ef
+    const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c2 = rc - r * 6;
+    double s = 0.0;
+    for (int e1 = 0; e1 < d; e1++)
+      for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e1 * 36 + r * 6 + kk]) * Dval(e1, f2, kk, c2);
+    sm.Ws[i] = s;
+  }
+  __syncthreads();
+  const int n = p.n;
+  double* H = p.Hb;
+  double* bvec = p.Hb + size_t(n) * n;
+  for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
+    const int ef = i / 36, rc = i - ef * 36, e1 = ef / d, f2 = ef - e1 * d, r = rc / 6, c2 = rc - r * 6;
+    const int je = sm.jp[e1], jf = sm.jp[f2];
+    if (je >= 0 && jf >= 0) atomicAdd(&H[size_t(6 * je + r) * n + 6 * jf + c2], Dval(e1, f2, r, c2));
+  }
+  if (ip >= 0) {
+    for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
+      const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c2 = rc - r * 6;
+      const int jf = sm.jp[f2];
+      if (jf >= 0) {
+        const double v = -sm.Ws[i];
+        atomicAdd(&H[size_t(6 * ip + r) * n + 6 * jf + c2], v);
+        atomicAdd(&H[size_t(6 * jf + c2) * n + 6 * ip + r], v);
+      }
+    }
+    if (tid < 36) {                                      // (i, i) += sum_f W_f A_f^T
+      const int r = tid / 6, c2 = tid - r * 6;
+      double s = 0.0;
+      for (int f2 = 0; f2 < d; f2++)
+        for (int kk = 0; kk < 6; kk++) s += sm.Ws[f2 * 36 + r * 6 + kk] * double(sm.Am[f2 * 36 + c2 * 6 + kk]);
+      atomicAdd(&H[size_t(6 * ip + r) * n + 6 * ip + c2], s);
+    } else if (tid >= 64 && tid < 70) {                  // b_i += -sum_e A_e c_e
+      const int r = tid - 64;
+      double s = 0.0;
+      for (int e1 = 0; e1 < d; e1++)
+        for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e1 * 36 + r * 6 + kk]) * sm.cs[e1 * 6 + kk];
+      atomicAdd(&bvec[6 * ip + r], -s);
+    }
+  }
+  for (int i = tid; i < d * 6; i += kBAThreads) {        // b_{j_e} += c_e
+    const int e1 = i / 6;
+    if (sm.jp[e1] >= 0) atomicAdd(&bvec[6 * sm.jp[e1] + (i - e1 * 6)], sm.cs[i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // depth back-substitution + disparity retraction (EvT6x1_kernel, dz = Q (w - sum E^T dx), disp_retr_kernel;
 // droid_kernels.cu:1095-1115, :1408-1428).  E_e is recomputed from the edge records of THIS iteration
 // (old poses, old disparities); y_e = [0<j_e-t0<P] dx_j - [0<i-t0<P] A_e^T dx_i comes from ba_post_solve.
@@ -457,18 +842,35 @@ static int launch_frames(const BAParams& p, int S, int dlo, int dcap, cudaStream
   return DB200_OK;
 }
 
+template <int NSEG>
+static int launch_schur(const BAParams& p, int S, int dlo, int dcap, cudaStream_t st) {
+  const int necap = dcap + 4;
+  const size_t smem = schur_smem_bytes(dcap, necap);
+  auto kern = ba_schur_kernel<NSEG>;
+  if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  kern<<<p.Mcap * S, kBAThreads, smem, st>>>(p, S, dlo, dcap, necap);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
 int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   DB200_CUDA(cudaMemsetAsync(p.Hb, 0, sizeof(double) * (size_t(p.n) * p.n + p.n), st));
-  const int nsub = cdiv(p.HW, kBAThreads);
-  int S = cdiv(4 * kNumSMs, p.Mcap);               // aim at >= ~4 CTAs per SM
-  S = S < 1 ? 1 : (S > nsub ? nsub : S);
-  if (p.motion_only) return launch_frames<1, true>(p, S, 0, 32, st);
-  // degree buckets (shared memory per CTA grows with the bucket's cap); a frame does its work in exactly one
+  if (p.motion_only) {
+    const int nsub = cdiv(p.HW, kBAThreads);
+    int S = cdiv(4 * kNumSMs, p.Mcap);
+    S = S < 1 ? 1 : (S > nsub ? nsub : S);
+    return launch_frames<1, true>(p, S, 0, 32, st);
+  }
+  const int nchunks = cdiv(p.HW, kChunk);
+  int S = cdiv(6 * kNumSMs, p.Mcap);               // aim at >= ~6 CTAs per SM over the launch
+  S = S < 1 ? 1 : (S > nchunks ? nchunks : S);
+  // degree buckets (shared memory and accumulator registers grow with the bucket's cap); a frame works in exactly one.
+  // NSEG = ceil(schur_segs(dcap) / 8): 6, 12, 25, 36 segments of <= 4 tiles for dcap = 8, 14, 22, 28.
   const int dmax_host = p.N < kMaxDeg ? p.N : kMaxDeg;   // the host only knows d <= N
-  int rc = launch_frames<1, false>(p, S, 0, 8, st);
-  if (rc == DB200_OK && dmax_host > 8) rc = launch_frames<1, false>(p, S, 9, 14, st);
-  if (rc == DB200_OK && dmax_host > 14) rc = launch_frames<1, false>(p, S, 15, 22, st);
-  if (rc == DB200_OK && dmax_host > 22) rc = launch_frames<2, false>(p, S, 23, kMaxDeg, st);
+  int rc = launch_schur<1>(p, S, 0, 8, st);
+  if (rc == DB200_OK && dmax_host > 8) rc = launch_schur<2>(p, S, 9, 14, st);
+  if (rc == DB200_OK && dmax_host > 14) rc = launch_schur<4>(p, S, 15, 22, st);
+  if (rc == DB200_OK && dmax_host > 22) rc = launch_schur<5>(p, S, 23, kMaxDeg, st);
   return rc;
 }
 
