@@ -493,6 +493,27 @@ __device__ __forceinline__ void ldsm_x4(float (&r)[4], unsigned addr) {
   r[0] = __uint_as_float(a); r[1] = __uint_as_float(b); r[2] = __uint_as_float(c); r[3] = __uint_as_float(d);
 }
 
+// one segment (CNT consecutive 16x8 tiles of one M-row) over one chunk: straight-line code, no predicates
+template <int CNT>
+__device__ __forceinline__ void schur_segment(float (&acc)[kSegTiles][4], unsigned aA, unsigned aB, unsigned lo_off) {
+#pragma unroll 1
+  for (int k0 = 0; k0 < kChunk; k0 += 8) {
+    float ah[4], al[4], bf[CNT][4];
+    ldsm_x4(ah, aA);
+    ldsm_x4(al, aA + lo_off);
+#pragma unroll
+    for (int q = 0; q < CNT; q++) ldsm_x4(bf[q], aB + 4u * unsigned(8 * q * kStride));
+    // three passes over the segment's tiles: dependent MMAs on one accumulator are CNT apart
+#pragma unroll
+    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(acc[q], al, bh); }
+#pragma unroll
+    for (int q = 0; q < CNT; q++) { const float bl[2] = {bf[q][2], bf[q][3]}; mma_tf32(acc[q], ah, bl); }
+#pragma unroll
+    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(acc[q], ah, bh); }
+    aA += 32u; aB += 32u;
+  }
+}
+
 // grid = Mcap * S CTAs; CTA (k, s) handles chunks s, s+S, ... of source frame kx[k]; launches are bucketed by
 // degree: only frames with dlo <= nd[k] <= dcap work here (shared memory and NSEG grow with the bucket).
 template <int NSEG>
@@ -685,26 +706,12 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     // ---------------- phase 2: G += Es Es^T on the tensor cores (EEt6x6/Ev6x1, :1001-1093)
 #pragma unroll
     for (int u = 0; u < NSEG; u++) {
-      if (seg_cnt[u] > 0) {
-#pragma unroll 1
-        for (int k0 = 0; k0 < kChunk; k0 += 8) {
-          float ah[4], al[4], bf[kSegTiles][4];
-          ldsm_x4(ah, a_addr[u] + 4u * k0);
-          ldsm_x4(al, a_addr[u] + lo_off + 4u * k0);
-#pragma unroll
-          for (int q = 0; q < kSegTiles; q++)
-            if (q < seg_cnt[u]) ldsm_x4(bf[q], b_addr[u] + 4u * unsigned(8 * q * kStride + k0));
-          // three passes over the segment's tiles: dependent MMAs on one accumulator are kSegTiles apart
-#pragma unroll
-          for (int q = 0; q < kSegTiles; q++)
-            if (q < seg_cnt[u]) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(accT[u][q], al, bh); }
-#pragma unroll
-          for (int q = 0; q < kSegTiles; q++)
-            if (q < seg_cnt[u]) { const float bl[2] = {bf[q][2], bf[q][3]}; mma_tf32(accT[u][q], ah, bl); }
-#pragma unroll
-          for (int q = 0; q < kSegTiles; q++)
-            if (q < seg_cnt[u]) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(accT[u][q], ah, bh); }
-        }
+      switch (seg_cnt[u]) {                           // warp-uniform
+        case 4: schur_segment<4>(accT[u], a_addr[u], b_addr[u], lo_off); break;
+        case 3: schur_segment<3>(accT[u], a_addr[u], b_addr[u], lo_off); break;
+        case 2: schur_segment<2>(accT[u], a_addr[u], b_addr[u], lo_off); break;
+        case 1: schur_segment<1>(accT[u], a_addr[u], b_addr[u], lo_off); break;
+        default: break;
       }
     }
     __syncthreads();

@@ -52,9 +52,11 @@ template <> struct Elem<double> {
 };
 template <> struct Elem<__half> {
   static __device__ __forceinline__ __half from_float(float x) { return __float2half_rn(x); }
+  // c10::Half computes Half(float(s) * float(w)) and Half(float(acc) + float(p)).  The float product of two halves
+  // is exact, and the float sum of two halves is either exact (exponent gap <= 13) or the small operand lies below
+  // a quarter ulp of the large one, so rounding once (native HMUL/HADD, no fusion) gives the same bits.
   static __device__ __forceinline__ __half mad(__half s, __half w, __half acc) {
-    const __half p = __float2half_rn(__fmul_rn(__half2float(s), __half2float(w)));
-    return __float2half_rn(__fadd_rn(__half2float(acc), __half2float(p)));
+    return __hadd_rn(acc, __hmul_rn(s, w));
   }
   static __device__ __forceinline__ __half zero() { return __float2half_rn(0.0f); }
 };

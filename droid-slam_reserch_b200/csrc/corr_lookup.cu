@@ -97,6 +97,151 @@ corr_lookup_fwd_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __
   }
 }
 
+// ---- radius-3 fast path (the only radius DROID-SLAM uses: corr.py:23, droid_net.py) ---------------------------
+// CTA = PX consecutive source pixels x all levels, 256 threads, four stages separated by barriers:
+//   0  thread = (level, pixel): window origin (floor(x)-3, floor(y)-3) and bilinear fractions from the coords;
+//   1  warp = (level, pixel) window: the 8x8 samples are fetched with lanes running along the window rows
+//      (16-byte rows of the volume slice; out-of-range samples are zero-filled — adding a +0 product is
+//      bit-identical to the reference's skipped `within_bounds` branch), four windows in flight per warp;
+//   2  thread = (level, pixel): the window comes back from shared memory as eight 16-byte vectors and all
+//      49 outputs are formed in registers in the reference's accumulation order;
+//   3  the [levels*49][PX] output tile leaves as full coalesced lines.
+// Per lookup this is ~130 warp instructions instead of ~1600 (profiles/r1_v1_lookup_ncu.txt), so the kernel
+// is bound by the DRAM sectors the 16-byte window rows touch, not by issue slots.
+constexpr int kWinStride = 72;     // elements per staged window (64 + 8 pad): conflict-free 16-byte reads at 32 lanes
+
+template <typename T> struct WinVec;            // eight window samples (one x offset, y offsets 0..7) as one aligned vector
+template <> struct WinVec<__half> { static constexpr int kLoads = 1; };
+template <> struct WinVec<float> { static constexpr int kLoads = 2; };
+template <> struct WinVec<double> { static constexpr int kLoads = 4; };
+
+template <typename T>
+__device__ __forceinline__ void load_win_col(const T* __restrict__ p, T (&v)[8]) {
+  constexpr int n16 = 8 * sizeof(T) / 16;
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 tmp[n16];
+#pragma unroll
+  for (int i = 0; i < n16; i++) tmp[i] = q[i];
+  const T* t = reinterpret_cast<const T*>(tmp);
+#pragma unroll
+  for (int i = 0; i < 8; i++) v[i] = t[i];
+}
+
+template <typename T, int PX>
+__global__ void __launch_bounds__(256)
+corr_lookup_r3_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __restrict__ out, int N, int h1, int w1,
+                      int h2, int w2, int num_levels) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int kCh = 49;
+  T* win = reinterpret_cast<T*>(smem_raw);                                   // [L*PX][kWinStride]
+  T* sout = win + size_t(num_levels) * PX * kWinStride;                      // [L*49][PX]
+  int* sxb = reinterpret_cast<int*>(sout + size_t(num_levels) * kCh * PX);   // [L*PX]
+  int* syb = sxb + num_levels * PX;
+  float* sdx = reinterpret_cast<float*>(syb + num_levels * PX);
+  float* sdy = sdx + num_levels * PX;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int x_base = blockIdx.x * PX, y = blockIdx.y, n = blockIdx.z;
+  const int npx = min(PX, w1 - x_base);
+  const size_t plane = size_t(h1) * w1;
+  const int nwin = num_levels * PX;
+
+  // ---- stage 0
+  for (int wi = tid; wi < nwin; wi += 256) {
+    const int l = wi / PX, px = wi - l * PX;
+    int xb = 0, yb = 0;
+    float dx = 0.0f, dy = 0.0f;
+    if (px < npx) {
+      const size_t o = size_t(y) * w1 + x_base + px;
+      const float scale = float(1 << l);
+      const float x0 = coords[(size_t(n) * 2 + 0) * plane + o] / scale, y0 = coords[(size_t(n) * 2 + 1) * plane + o] / scale;
+      const float fx = floorf(x0), fy = floorf(y0);
+      dx = x0 - fx; dy = y0 - fy;
+      xb = static_cast<int>(fx) - 3; yb = static_cast<int>(fy) - 3;
+    }
+    sxb[wi] = xb; syb[wi] = yb; sdx[wi] = dx; sdy[wi] = dy;
+  }
+  __syncthreads();
+
+  // ---- stage 1: gather.  lane -> window element (x offset i = lane & 7, y offsets j = lane >> 3 and +4)
+  {
+    const int i = lane & 7, j0 = lane >> 3;
+    for (int wb = warp * 4; wb < nwin; wb += 32) {           // 4 windows per warp and step
+      T v[4][2];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int wi = wb + u;
+        const int l = wi / PX, px = wi - l * PX;
+        v[u][0] = Elem<T>::zero(); v[u][1] = Elem<T>::zero();
+        if (wi < nwin && px < npx) {
+          const int h2l = h2 >> l, w2l = w2 >> l;
+          const T* slice = static_cast<const T*>(levels.p[l]) + ((size_t(n) * h1 + y) * w1 + x_base + px) * size_t(h2l) * w2l;
+          const int x1 = sxb[wi] + i, y1 = syb[wi] + j0;
+          const bool xin = x1 >= 0 && x1 < w2l;
+          if (xin && y1 >= 0 && y1 < h2l) v[u][0] = slice[size_t(y1) * w2l + x1];
+          if (xin && y1 + 4 >= 0 && y1 + 4 < h2l) v[u][1] = slice[size_t(y1 + 4) * w2l + x1];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int wi = wb + u;
+        if (wi < nwin) {
+          win[size_t(wi) * kWinStride + i * 8 + j0] = v[u][0];
+          win[size_t(wi) * kWinStride + i * 8 + j0 + 4] = v[u][1];
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- stage 2: thread = window; outputs in registers, reference order (i,j), (i,j+1), (i+1,j), (i+1,j+1)
+  for (int wi = tid; wi < nwin; wi += 256) {
+    const int l = wi / PX, px = wi - l * PX;
+    if (px >= npx) continue;
+    const float dx = sdx[wi], dy = sdy[wi];
+    const T w00 = Elem<T>::from_float((1.0f - dx) * (1.0f - dy));
+    const T w01 = Elem<T>::from_float((1.0f - dx) * dy);
+    const T w10 = Elem<T>::from_float(dx * (1.0f - dy));
+    const T w11 = Elem<T>::from_float(dx * dy);
+    const T* wp = win + size_t(wi) * kWinStride;
+    T c0[8], c1[8];
+    load_win_col<T>(wp, c0);
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      load_win_col<T>(wp + (i + 1) * 8, c1);
+#pragma unroll
+      for (int j = 0; j < 7; j++) {
+        T acc = Elem<T>::zero();
+        acc = Elem<T>::mad(c0[j], w00, acc);
+        acc = Elem<T>::mad(c0[j + 1], w01, acc);
+        acc = Elem<T>::mad(c1[j], w10, acc);
+        acc = Elem<T>::mad(c1[j + 1], w11, acc);
+        sout[size_t(l * kCh + i * 7 + j) * PX + px] = acc;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) c0[j] = c1[j];
+    }
+  }
+  __syncthreads();
+
+  // ---- stage 3: coalesced store, out[n][L*49][h1][w1]
+  const int nch = num_levels * kCh;
+  T* obase = out + size_t(n) * nch * plane + size_t(y) * w1 + x_base;
+  constexpr int kVec = 16 / sizeof(T);
+  const bool vec_ok = (npx == PX) && (w1 % kVec == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);
+  if (vec_ok) {
+    constexpr int per_row = PX / kVec;
+    for (int idx = tid; idx < nch * per_row; idx += 256) {
+      const int ch = idx / per_row, v = idx - ch * per_row;
+      *reinterpret_cast<uint4*>(obase + size_t(ch) * plane + v * kVec) = *reinterpret_cast<const uint4*>(sout + size_t(ch) * PX + v * kVec);
+    }
+  } else {
+    for (int idx = tid; idx < nch * PX; idx += 256) {
+      const int ch = idx / PX, px = idx - ch * PX;
+      if (px < npx) obase[size_t(ch) * plane + px] = sout[idx];
+    }
+  }
+}
+
 // Backward: one warp per source pixel writes the WHOLE h2*w2 slice of volume_grad (zeros outside the
 // window), so no separate memset pass is needed.  Gradient value per window sample follows
 // correlation_kernels.cu:108-121 (g accumulates the 4 contributions in that order, then 0 + g).
@@ -140,6 +285,16 @@ corr_lookup_bwd_kernel(const float* __restrict__ coords, const T* __restrict__ c
 template <typename T>
 int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h1, int w1, int h2, int w2, int L, int r,
                cudaStream_t st) {
+  if (r == 3) {
+    constexpr int PX = sizeof(T) == 8 ? 32 : 64;
+    const size_t smem = (size_t(L) * PX * kWinStride + size_t(L) * 49 * PX) * sizeof(T) + size_t(L) * PX * 16;
+    auto kern = corr_lookup_r3_kernel<T, PX>;
+    if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    dim3 grid(cdiv(w1, PX), h1, N);
+    kern<<<grid, 256, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L);
+    DB200_CHECK_LAUNCH();
+    return DB200_OK;
+  }
   const int rd = 2 * r + 1, wn = rd + 1;
   const size_t smem = (size_t(L) * rd * rd * kLookupTX + size_t(kLookupWarps) * wn * wn) * sizeof(T);
   if (smem > 200 * 1024) return DB200_ERR_ARG;
