@@ -164,6 +164,43 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
                               algorithmic_bytes_per_launch=lookups * 912))
 
 
+def reference_cuda_leg(p, dev, steps=3):
+    """Extra reported baseline (north_star: "the reference CUDA extension is also reported where it builds for
+    sm_100"): the UNMODIFIED reference extension, built by baseline/build_ref_cuda.sh as `droid_backends_ref`, on the
+    same c3 problem, same call, CUDA-event timed.  Absent .so -> None.  Never on the product path."""
+    import glob
+    import importlib
+    import torch
+    refdir = os.path.join(REPO, "baseline", "_ref")
+    if not glob.glob(os.path.join(refdir, "droid_backends_ref*.so")):
+        return None
+    try:
+        if refdir not in sys.path:
+            sys.path.insert(0, refdir)
+        ref = importlib.import_module("droid_backends_ref")
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        poses0, disps0 = t(p.poses), t(p.disps)
+        intr, sens, target, weight, eta, ii, jj = t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)
+        poses, disps = poses0.clone(), disps0.clone()
+
+        def step():
+            poses.copy_(poses0); disps.copy_(disps0)
+            ref.ba(poses, disps, intr, sens, target, weight, eta, ii, jj, p.t0, p.t1, ITRS, LM, EP, False)
+        step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return dict(value=p.n_edges * ITRS / (ms * 1e-3), unit=UNIT, ms_per_step=ms, steps=steps,
+                    what="unmodified reference src/droid_kernels.cu ba_cuda rebuilt for sm_100a (host Eigen solve inside), same B200")
+    except Exception as ex:  # the reference extension is a reported extra, never a dependency
+        return dict(unavailable=f"{type(ex).__name__}: {ex}"[:200])
+
+
 def main_gpu(args, rank, world):
     import torch
     import torch.distributed as dist
@@ -292,7 +329,7 @@ def main_gpu(args, rank, world):
     achieved = accum_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else None
     iter_bytes = 20 * HW * N + 16 * HW * M + 56 * P       # SURVEY.md §8d whole-iteration figure (block-sparse system term omitted)
     iter_ms = ms_step / ITRS
-    roofline = dict(bound="hbm", kernel="ba_frame_kernel (accumulate stage)", achieved=achieved, peak=hbm_peak, unit="GB/s",
+    roofline = dict(bound="hbm", kernel="ba_schur_kernel (accumulate stage: reprojection/Jacobians + tensor-core Schur products; 4 degree-bucket launches)", achieved=achieved, peak=hbm_peak, unit="GB/s",
                     frac=(achieved / hbm_peak) if achieved else None, traffic=None, peak_source=peak_src,
                     algorithmic_bytes_per_launch=accum_bytes, ms_per_launch=acc_ms,
                     whole_iteration=dict(algorithmic_bytes=iter_bytes, ms=iter_ms,
@@ -301,7 +338,7 @@ def main_gpu(args, rank, world):
     traffic_file = os.path.join(REPO, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
-            roofline["traffic"] = json.load(open(traffic_file)).get("ba_frame_kernel_bytes_per_launch")
+            roofline["traffic"] = json.load(open(traffic_file)).get("ba_schur_kernel_bytes_per_iteration")
         except Exception:
             pass
 
@@ -315,7 +352,15 @@ def main_gpu(args, rank, world):
                 gpu_launches=int(launches), roofline=roofline, stages=stage, clocks=clocks)
     if world == 1:
         line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
+        try:
+            tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
+            line["lookup"]["roofline"]["traffic"] = tr
+        except Exception:
+            pass
         if not args.no_cpu:
+            rc = reference_cuda_leg(p, dev)
+            if rc is not None:
+                line["reference_cuda"] = rc
             r = run_cpu(1, 0)
             line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"])
     print(json.dumps(line), flush=True)

@@ -105,15 +105,12 @@ class ShardedBA:
         self._dz_dst = torch.from_numpy(self.eta_rows[own]).to(device)
         self._ws = None
 
-    def ba(self, poses, disps, intrinsics, disps_sens, target, weight, eta, iterations, lm, ep, motion_only=False):
-        """Same contract as droid_backends.ba: poses/disps updated in place (identical on all ranks on return),
-        returns [dx[P,6], dz[M,ht*wd]] of the last iteration (dz assembled from the owners)."""
+    # ---- one call = begin -> (accumulate -> all-reduce of .system -> solve_update) x iterations -> finish
+    def begin(self, poses, disps, intrinsics, disps_sens, target, weight, eta, lm, ep, motion_only=False):
         from . import _capi
-        lib = _capi.lib()
+        self._lib = _capi.lib()
+        lib = self._lib
         B, ht, wd = disps.shape
-        HW = ht * wd
-        N = int(self.ii.shape[0])
-        P = self.t1 - self.t0
         mo = int(bool(motion_only))
         eta_loc = None
         if not mo:
@@ -122,39 +119,66 @@ class ShardedBA:
         M_loc = 0 if mo else int(eta_loc.shape[0])
         if B < self.n_frames:
             raise RuntimeError("ShardedBA: disps has fewer frames than the partition was built for")
-        own_hi = B if self.rank == self.world - 1 else self.own_hi
+        N = int(self.ii.shape[0])
         wsb = lib.db200_ba_workspace_bytes(N, B, ht, wd, self.t0, self.t1, M_loc, mo)
         if self._ws is None or self._ws.numel() < wsb:
             self._ws = torch.empty(int(wsb) + 1024, dtype=torch.uint8, device=self.device)
         ws = self._ws
-        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         vp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
         sys_ptr = lib.db200_ba_system_ptr(vp(ws), N, B, ht, wd, self.t0, self.t1, M_loc, mo)
         off = int(sys_ptr) - ws.data_ptr()
         n_el = int(lib.db200_ba_system_elems(self.t0, self.t1))
-        Hb = ws[off:off + 8 * n_el].view(torch.float64)
-        dx = torch.empty((P, 6), dtype=torch.float32, device=self.device)
-        dz_loc = None if mo else torch.empty((M_loc, HW), dtype=torch.float32, device=self.device)
+        self.system = ws[off:off + 8 * n_el].view(torch.float64)        # [H (n x n) | b] fp64: the all-reduced buffer
+        P = self.t1 - self.t0
+        self._dx = torch.empty((P, 6), dtype=torch.float32, device=self.device)
+        self._dz_loc = None if mo else torch.empty((M_loc, ht * wd), dtype=torch.float32, device=self.device)
+        self._call = dict(poses=poses, disps=disps, intr=intrinsics, sens=disps_sens, target=target, weight=weight, eta=eta_loc,
+                          N=N, B=B, ht=ht, wd=wd, mo=mo, M=M_loc, lm=float(lm), ep=float(ep),
+                          own_hi=B if self.rank == self.world - 1 else self.own_hi)
+
+    def accumulate(self, first: bool):
+        from . import _capi
+        c, lib, ws = self._call, self._lib, self._ws
+        vp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _capi.check(lib.db200_ba_accumulate(vp(c["poses"]), vp(c["disps"]), vp(c["intr"]), vp(c["sens"]), vp(c["target"]),
+                                            vp(c["weight"]), vp(c["eta"]), vp(self.ii), vp(self.jj), c["N"], c["B"], c["ht"],
+                                            c["wd"], self.t0, self.t1, c["mo"], c["M"], int(first), self.own_lo, c["own_hi"],
+                                            vp(ws), ws.numel(), st), "ba_accumulate")
+
+    def solve_update(self, last: bool):
+        from . import _capi
+        c, lib, ws = self._call, self._lib, self._ws
+        vp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _capi.check(lib.db200_ba_solve_update(vp(c["poses"]), vp(c["disps"]), vp(c["intr"]), vp(c["target"]), vp(c["weight"]),
+                                              vp(self.ii), vp(self.jj), c["N"], c["B"], c["ht"], c["wd"], self.t0, self.t1,
+                                              c["lm"], c["ep"], c["mo"], c["M"], self.own_lo, c["own_hi"],
+                                              vp(self._dx) if last else C.c_void_p(0),
+                                              vp(self._dz_loc) if (last and not c["mo"]) else C.c_void_p(0), vp(ws), ws.numel(), st),
+                    "ba_solve_update")
+
+    def local_dz_rows(self):
+        """(rows of the global dz this rank owns, their values) after the last solve_update."""
+        return self._dz_dst, self._dz_loc.index_select(0, self._dz_src)
+
+    def ba(self, poses, disps, intrinsics, disps_sens, target, weight, eta, iterations, lm, ep, motion_only=False):
+        """Same contract as droid_backends.ba: poses/disps updated in place (identical on all ranks on return),
+        returns [dx[P,6], dz[M,ht*wd]] of the last iteration (dz assembled from the owners)."""
+        self.begin(poses, disps, intrinsics, disps_sens, target, weight, eta, lm, ep, motion_only)
         for it in range(int(iterations)):
-            last = it == iterations - 1
-            _capi.check(lib.db200_ba_accumulate(vp(poses), vp(disps), vp(intrinsics), vp(disps_sens), vp(target), vp(weight),
-                                                vp(eta_loc), vp(self.ii), vp(self.jj), N, B, ht, wd, self.t0, self.t1, mo,
-                                                M_loc, int(it == 0), self.own_lo, own_hi, vp(ws), ws.numel(), st),
-                        "ba_accumulate")
-            allreduce_system(Hb, self.group)
-            _capi.check(lib.db200_ba_solve_update(vp(poses), vp(disps), vp(intrinsics), vp(target), vp(weight), vp(self.ii),
-                                                  vp(self.jj), N, B, ht, wd, self.t0, self.t1, float(lm), float(ep), mo, M_loc,
-                                                  self.own_lo, own_hi, vp(dx) if last else C.c_void_p(0),
-                                                  vp(dz_loc) if (last and not mo) else C.c_void_p(0), vp(ws), ws.numel(), st),
-                        "ba_solve_update")
-        if mo:
-            return [dx, None]
-        assemble_rows(disps, self.own_lo, own_hi, self.group)
-        dz = torch.zeros((len(self.kx_all), HW), dtype=torch.float32, device=self.device)
-        dz.index_copy_(0, self._dz_dst, dz_loc.index_select(0, self._dz_src))
-        if self.world > 1:
+            self.accumulate(it == 0)
+            allreduce_system(self.system, self.group)
+            self.solve_update(it == iterations - 1)
+        if motion_only:
+            return [self._dx, None]
+        assemble_rows(disps, self.own_lo, self._call["own_hi"], self.group)
+        dz = torch.zeros((len(self.kx_all), self._call["ht"] * self._call["wd"]), dtype=torch.float32, device=self.device)
+        dst, val = self.local_dz_rows()
+        dz.index_copy_(0, dst, val)
+        if self.world > 1 and dist.is_initialized():
             dist.all_reduce(dz, op=dist.ReduceOp.SUM, group=self.group)
-        return [dx, dz]
+        return [self._dx, dz]
 
     def status(self):
         from . import _capi

@@ -1,0 +1,116 @@
+"""GPU: edge-sharded BA (droid_b200/dist.py) through the phase-split C-ABI.
+  * one device: two ranks' shards are run back to back in one process (separate workspaces, the all-reduce replaced
+    by an explicit sum) and compared with the single-GPU `droid_backends.ba` — exercises own-range handling, the
+    local depth rows and the fp64 partial systems;
+  * >= 2 devices: the real thing, one process per GPU over NCCL (skipped on a 1-GPU box)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _problem():
+    from droid_b200 import synth
+    return synth.config_c3(n_kf=48, n_edges=420, ht=24, wd=32, seed=5, stereo_frac=0.2, sensor_frac=0.3)
+
+
+def _single(p, iters, lm, ep, dev):
+    import droid_backends
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    poses, disps = t(p.poses), t(p.disps)
+    dx, dz = droid_backends.ba(poses, disps, t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii),
+                               t(p.jj), p.t0, p.t1, iters, lm, ep, False)
+    return poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy(), dz.cpu().numpy()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_equals_single_on_one_device(world):
+    from droid_b200 import dist as bdist
+    dev = torch.device("cuda:0")
+    p = _problem()
+    iters, lm, ep = 2, 1e-5, 1e-2
+    want = _single(p, iters, lm, ep, dev)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    ranks = [bdist.ShardedBA(p.ii, p.jj, p.t0, p.t1, r, world, dev, n_frames=p.disps.shape[0]) for r in range(world)]
+    assert sum(len(r.local_edges) for r in ranks) == p.n_edges
+    state = [dict(poses=t(p.poses), disps=t(p.disps)) for _ in range(world)]
+    intr, sens, eta = t(p.intrinsics), t(p.disps_sens), t(p.eta)
+    for r, s in zip(ranks, state):
+        r.begin(s["poses"], s["disps"], intr, sens, t(p.target[r.local_edges]), t(p.weight[r.local_edges]), eta, lm, ep)
+    for it in range(iters):
+        for r in ranks:
+            r.accumulate(it == 0)
+        total = sum(r.system.clone() for r in ranks)               # what the NCCL all-reduce produces
+        for r in ranks:
+            r.system.copy_(total)
+            r.solve_update(it == iters - 1)
+    torch.cuda.synchronize()
+    for r in ranks:
+        assert r.status() >= 0
+    # poses: replicated and identical; disparities: every rank updated exactly its own frames
+    for s in state:
+        np.testing.assert_array_equal(s["poses"].cpu().numpy(), state[0]["poses"].cpu().numpy())
+    disps = np.array(p.disps, copy=True)
+    dz = np.zeros_like(want[3])
+    for r, s in zip(ranks, state):
+        lo, hi = r.own_lo, r._call["own_hi"]
+        disps[lo:hi] = s["disps"].cpu().numpy()[lo:hi]
+        dst, val = r.local_dz_rows()
+        dz[dst.cpu().numpy()] = val.cpu().numpy()
+    rel = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
+    assert rel(ranks[0]._dx.cpu().numpy(), want[2]) < 2e-5          # summation regrouped per rank: fp32 round-off only
+    assert rel(dz, want[3]) < 2e-5
+    assert np.abs(state[0]["poses"].cpu().numpy() - want[0]).max() < 1e-5
+    assert np.abs(disps - want[1]).max() < 1e-5
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    return port
+
+
+def _nccl_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from droid_b200 import dist as bdist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        p = _problem()
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        r = bdist.ShardedBA(p.ii, p.jj, p.t0, p.t1, rank, world, dev, n_frames=p.disps.shape[0])
+        poses, disps = t(p.poses), t(p.disps)
+        dx, dz = r.ba(poses, disps, t(p.intrinsics), t(p.disps_sens), t(p.target[r.local_edges]), t(p.weight[r.local_edges]),
+                      t(p.eta), 2, 1e-5, 1e-2)
+        torch.cuda.synchronize()
+        q.put((rank, poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy(), dz.cpu().numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_sharded_nccl_two_gpus():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, q)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted([q.get(timeout=500) for _ in range(world)], key=lambda x: x[0])
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    want = _single(_problem(), 2, 1e-5, 1e-2, torch.device("cuda:0"))
+    for k in range(1, 5):
+        np.testing.assert_array_equal(res[0][k], res[1][k])          # identical on all ranks
+    rel = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
+    assert rel(res[0][3], want[2]) < 2e-5 and rel(res[0][4], want[3]) < 2e-5
+    assert np.abs(res[0][1] - want[0]).max() < 1e-5 and np.abs(res[0][2] - want[1]).max() < 1e-5
