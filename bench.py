@@ -201,6 +201,36 @@ def reference_cuda_leg(p, dev, steps=3):
         return dict(unavailable=f"{type(ex).__name__}: {ex}"[:200])
 
 
+def volume_bench(dev, steps, warmup, hbm_peak):
+    """Secondary metric: CorrBlock construction — all-pairs 128-d correlation + 4-level pyramid, f16, 48 edges x 48x64
+    (corr.py:30-38,63-71).  Output-write bound: algorithmic bytes = pyramid written once (25.1 MB/edge) + fmaps read."""
+    import torch
+    import droid_backends
+    N, C_, ht, wd = 48, 128, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(11)
+    f1 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    f2 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    for _ in range(warmup):
+        droid_backends.corr_volume_pyramid(f1, f2, 4)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(steps):
+        droid_backends.corr_volume_pyramid(f1, f2, 4)
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1]) / steps
+    hw = ht * wd
+    out_bytes = N * hw * sum((ht >> l) * (wd >> l) for l in range(4)) * 2
+    in_bytes = 2 * N * C_ * hw * 2
+    flops = 2.0 * N * hw * C_ * sum((ht >> l) * (wd >> l) for l in range(4))
+    gbs = (out_bytes + in_bytes) / (ms * 1e-3) / 1e9
+    return dict(metric="CorrBlock build edges/s (all-pairs 128-d GEMM + 4-level pyramid, f16, 48 edges x 48x64)",
+                value=N / (ms * 1e-3), unit="edges/s", ms_per_call=ms, tflops=flops / (ms * 1e-3) / 1e12,
+                roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
+                              algorithmic_bytes_per_call=out_bytes + in_bytes))
+
+
 def main_gpu(args, rank, world):
     import torch
     import torch.distributed as dist
@@ -352,6 +382,7 @@ def main_gpu(args, rank, world):
                 gpu_launches=int(launches), roofline=roofline, stages=stage, clocks=clocks)
     if world == 1:
         line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
+        line["corr_volume"] = volume_bench(dev, 10, 3, hbm_peak)
         try:
             tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
             line["lookup"]["roofline"]["traffic"] = tr

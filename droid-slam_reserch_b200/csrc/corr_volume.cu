@@ -13,6 +13,7 @@
 // "row-major" KxN, no transposes needed).  The fp32 (training) path uses an SIMT fp32 tile kernel so that
 // values stay within 1e-4 of the fp32 reference.  [tcgen05/TMA version: see DESIGN.md roadmap]
 #include <mma.h>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace db200 {
@@ -126,9 +127,20 @@ corr_gemm_f32_kernel(const float* __restrict__ f1, const float* __restrict__ f2,
     }
 }
 
+// tcgen05/TMA path (corr_volume_tc.cu)
+size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels);
+bool corr_tc_supported(int C, int ht, int wd);
+int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
+                           int num_levels, void* workspace, cudaStream_t st);
+
 }  // namespace db200
 
 using namespace db200;
+
+static bool use_tc_path(int C, int ht, int wd, int dtype) {
+  static const bool off = getenv("DB200_CORR_NO_TCGEN05") != nullptr;     // debugging aid: force the mma.sync path
+  return !off && dtype == DB200_F16 && corr_tc_supported(C, ht, wd);
+}
 
 extern "C" size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd, int num_levels, int dtype) {
   if (N <= 0 || C <= 0 || ht <= 0 || wd <= 0 || num_levels < 1) return 0;
@@ -136,6 +148,7 @@ extern "C" size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd
   size_t tot = 256;
   int h = ht, w = wd;
   for (int l = 1; l < num_levels; l++) { h >>= 1; w >>= 1; tot += ((size_t(N) * C * h * w * es + 255) / 256) * 256; }
+  if (dtype == DB200_F16) { const size_t t2 = corr_tc_workspace_bytes(N, C, ht, wd, num_levels); if (t2 > tot) tot = t2; }
   return tot;
 }
 
@@ -151,6 +164,11 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
     return DB200_ERR_WORKSPACE;
   if (dtype == DB200_F16 && C % 16 != 0) return DB200_ERR_ARG;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (use_tc_path(C, ht, wd, dtype)) {
+    if (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)) return DB200_ERR_WORKSPACE;
+    return corr_volume_pyramid_tc(static_cast<const __half*>(fmap1), static_cast<const __half*>(fmap2), levels_out, N, C, ht, wd,
+                                  num_levels, workspace, st);
+  }
   const size_t es = dtype == DB200_F16 ? 2 : 4;
   const int M = ht * wd;
   const void* src = fmap2;

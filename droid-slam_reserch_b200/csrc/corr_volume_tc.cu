@@ -1,0 +1,280 @@
+// corr_volume_tc.cu — all-pairs 128-d correlation on the 5th-generation tensor cores (fp16 inference path).
+// Replaces CorrBlock.corr's torch.matmul + the three avg_pool2d passes of
+// /root/reference/droid_slam/modules/corr.py:30-38,63-71 for f16 feature maps.
+//
+//   corr_l[n, p1, p2] = (1/16) sum_c f1[n,c,p1] * pool_l(f2)[n,c,p2]          (pooling commutes with the contraction)
+//
+// prep kernel : feature maps [N][C][HW] -> channels-last K-major copies f1T[N*HW][C], f2T_l[N*HW_l][C] (2x2 mean per level)
+// GEMM kernel : one CTA = one 128x128 output tile of one edge, 128 threads.
+//   thread 0      : two TMA loads per operand (cp.async.bulk.tensor.2d, 128B swizzle, box 64 x 128: the whole K = 128
+//                   of the tile is resident) completing on one mbarrier;
+//   thread 32     : 8 x tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128, K=16), fp32 accumulator in TMEM (128 columns),
+//                   tcgen05.commit -> mbarrier;
+//   all 4 warps   : tcgen05.ld 32x32b (warp w owns TMEM lanes 32w..32w+31 = output rows), x 1/16, cvt to f16, 64-byte
+//                   row segments straight to HBM.
+// 3 CTAs are resident per SM (64 KB smem, 128 of 512 TMEM columns each), so the TMA / MMA / store phases of different tiles
+// overlap without an in-kernel pipeline.  The op is output-write bound (25 MB written per edge, 2.4 GFLOP).
+// Every mbarrier wait is bounded: a broken descriptor raises DB200_ERR_CUDA through the status word instead of hanging.
+#include <cuda.h>
+#include "common.cuh"
+
+namespace db200 {
+
+static inline size_t align_up256(size_t x) { return (x + 255) / 256 * 256; }
+
+constexpr int kTM = 128, kTN = 128, kTK = 64;            // tile, and K per TMA box (64 halfs = one 128-byte swizzle row)
+
+// ---- prep: [N][C][hs*ws] -> [N][(hs>>l)*(ws>>l)][C] with 2^l x 2^l mean (l = 0: plain transpose), fp32 mean rounded once per level
+// (level l+1 is pooled from the ROUNDED level l, like F.avg_pool2d applied to an f16 tensor)
+__global__ void __launch_bounds__(256) transpose_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW) {
+  __shared__ __half tile[32][33];
+  const int n = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int c = c0 + r, p = p0 + tx;
+    tile[r][tx] = (c < C && p < HW) ? src[(size_t(n) * C + c) * HW + p] : __float2half(0.0f);
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int p = p0 + r, c = c0 + tx;
+    if (p < HW && c < C) dst[(size_t(n) * HW + p) * C + c] = tile[tx][r];
+  }
+}
+
+// channels-last pooling: dst[n][y][x][c] = mean of the 2x2 block of src (floor mode)
+__global__ void pool_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int N, int hs, int ws, int C) {
+  const int hd = hs >> 1, wd = ws >> 1;
+  const size_t total = size_t(N) * hd * wd * (C / 2);
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const int c2 = int(i % (C / 2));
+    size_t r = i / (C / 2);
+    const int x = int(r % wd); r /= wd;
+    const int y = int(r % hd);
+    const size_t n = r / hd;
+    const __half2* s = reinterpret_cast<const __half2*>(src + ((n * hs + 2 * y) * ws + 2 * x) * size_t(C)) + c2;
+    const float2 a = __half22float2(s[0]), b = __half22float2(s[C / 2]), c = __half22float2(s[size_t(ws) * (C / 2)]),
+                 d = __half22float2(s[size_t(ws) * (C / 2) + C / 2]);
+    reinterpret_cast<__half2*>(dst)[i] = __floats2half2_rn((a.x + b.x + c.x + d.x) * 0.25f, (a.y + b.y + c.y + d.y) * 0.25f);
+  }
+}
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {      // bounded
+  for (uint32_t it = 0; it < (1u << 20); it++) {
+    uint32_t done;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return true;
+  }
+  return false;
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+// K-major operand tile, 128-byte swizzle, rows of 128 bytes: SBO = 8 rows * 128 B, LBO = 1 (ignored), version 1 (sm_100)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return uint64_t((saddr >> 4) & 0x3FFFu) | (uint64_t(1) << 16) | (uint64_t(1024 >> 4) << 32) | (uint64_t(1) << 46) | (uint64_t(2) << 61);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = F16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t kIdescF16 = (1u << 4) | (uint32_t(kTN >> 3) << 17) | (uint32_t(kTM >> 4) << 24);
+
+// grid (ceil(N2/128), ceil(M/128), edges); 128 threads; dynamic smem 64 KB + 1 KB alignment slack
+__global__ void __launch_bounds__(128)
+corr_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, __half* __restrict__ out,
+                    int M, int N2, int* __restrict__ err) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[2];
+  __shared__ uint32_t tmem_base_s;
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;          // 1024-byte aligned: required by the 128B swizzle
+  const uint32_t sA = s0, sB = s0 + 2 * kTM * kTK * 2;                 // A: 2 k-blocks of [128][64] halfs, then B likewise
+  const uint32_t full_bar = smem_u32(&bars[0]), mma_bar = smem_u32(&bars[1]);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n0 = blockIdx.x * kTN, m0 = blockIdx.y * kTM, e = blockIdx.z;
+
+  if (tid == 0) {
+    mbar_init(full_bar, 1);
+    mbar_init(mma_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {                                                     // TMEM: 128 columns x 128 lanes of fp32
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(kTN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (tid == 0) {
+    mbar_expect_tx(full_bar, 2u * (kTM + kTN) * kTK * 2u);
+    tma_load_2d(sA, &tmA, 0, e * M + m0, full_bar);
+    tma_load_2d(sA + kTM * kTK * 2, &tmA, kTK, e * M + m0, full_bar);
+    tma_load_2d(sB, &tmB, 0, e * N2 + n0, full_bar);
+    tma_load_2d(sB + kTN * kTK * 2, &tmB, kTK, e * N2 + n0, full_bar);
+  }
+  if (tid == 32) {
+    if (mbar_wait(full_bar, 0)) {
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+      for (int kb = 0; kb < 2; kb++)
+#pragma unroll
+        for (int k = 0; k < kTK / 16; k++) {
+          const uint64_t ad = umma_desc_sw128(sA + kb * kTM * kTK * 2 + k * 32);
+          const uint64_t bd = umma_desc_sw128(sB + kb * kTN * kTK * 2 + k * 32);
+          umma_f16(tmem_base, ad, bd, kIdescF16, (kb | k) != 0 ? 1u : 0u);
+        }
+    } else {
+      atomicExch(err, 1);
+    }
+    umma_commit(mma_bar);                                             // arrives when the MMAs above have completed
+  }
+  __syncwarp();
+  const bool ok = mbar_wait(mma_bar, 0);
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (!ok && lane == 0) atomicExch(err, 1);
+
+  // ---- epilogue: TMEM lane = output row, 32 columns per load
+  const int row = m0 + 32 * warp + lane;
+  __half* orow = out + (size_t(e) * M + (row < M ? row : 0)) * N2 + n0;
+  const bool vec = (N2 % 8 == 0);
+#pragma unroll 1
+  for (int cb = 0; cb < kTN; cb += 32) {
+    uint32_t v[32];
+    tmem_ld32(tmem_base + (uint32_t(32 * warp) << 16) + uint32_t(cb), v);
+    if (ok && row < M) {
+      if (vec && n0 + cb + 32 <= N2) {
+        uint4 pk[4];
+        uint32_t* pw = reinterpret_cast<uint32_t*>(pk);
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+          const __half2 h = __floats2half2_rn(__uint_as_float(v[2 * i]) * 0.0625f, __uint_as_float(v[2 * i + 1]) * 0.0625f);
+          pw[i] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        uint4* dstp = reinterpret_cast<uint4*>(orow + cb);
+#pragma unroll
+        for (int i = 0; i < 4; i++) dstp[i] = pk[i];
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; i++)
+          if (n0 + cb + i < N2) orow[cb + i] = __float2half_rn(__uint_as_float(v[i]) * 0.0625f);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTN) : "memory");
+}
+
+// ---- host -------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// rows x C f16 matrix, row-major; box = 64 columns x 128 rows, 128-byte swizzle
+static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, int C) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[2] = {cuuint64_t(C), rows};
+  const cuuint64_t gstride[1] = {cuuint64_t(C) * 2};
+  const cuuint32_t box[2] = {cuuint32_t(kTK), cuuint32_t(kTM)};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels) {
+  size_t tot = 256 + 256;                                           // status word
+  tot += align_up256(size_t(N) * C * ht * wd * 2);                  // f1T
+  int h = ht, w = wd;
+  for (int l = 0; l < num_levels; l++) { tot += align_up256(size_t(N) * C * h * w * 2); h >>= 1; w >>= 1; }
+  return tot;
+}
+
+bool corr_tc_supported(int C, int ht, int wd) { return C == 2 * kTK && (ht * wd) % 8 == 0 && encode_fn() != nullptr; }
+
+int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
+                           int num_levels, void* workspace, cudaStream_t st) {
+  char* ws = static_cast<char*>(workspace);
+  int* err = reinterpret_cast<int*>(ws);
+  ws += 256;
+  DB200_CUDA(cudaMemsetAsync(err, 0, sizeof(int), st));
+  const int HW = ht * wd;
+  __half* f1T = reinterpret_cast<__half*>(ws);
+  ws += align_up256(size_t(N) * C * HW * 2);
+  {
+    dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+    transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap1, f1T, C, HW);
+    DB200_CHECK_LAUNCH();
+  }
+  CUtensorMap tmA;
+  if (!make_map(&tmA, f1T, uint64_t(N) * HW, C)) return DB200_ERR_CUDA;
+  const size_t smem = size_t(2) * (kTM + kTN) * kTK * 2 + 1024;
+  static bool attr = false;
+  if (!attr) { DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))); attr = true; }
+  const __half* prev = nullptr;
+  int h = ht, w = wd;
+  for (int l = 0; l < num_levels; l++) {
+    if (h == 0 || w == 0) return DB200_ERR_ARG;
+    __half* f2T = reinterpret_cast<__half*>(ws);
+    ws += align_up256(size_t(N) * C * h * w * 2);
+    if (l == 0) {
+      dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+      transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap2, f2T, C, HW);
+    } else {
+      const size_t cnt = size_t(N) * h * w * (C / 2);
+      const int blocks = int((cnt + 255) / 256 < 2368 ? (cnt + 255) / 256 : 2368);
+      pool_cl_kernel<<<blocks, 256, 0, st>>>(prev, f2T, N, h << 1, w << 1, C);
+    }
+    DB200_CHECK_LAUNCH();
+    const int N2 = h * w;
+    CUtensorMap tmB;
+    if (!make_map(&tmB, f2T, uint64_t(N) * N2, C)) return DB200_ERR_CUDA;
+    dim3 grid(cdiv(N2, kTN), cdiv(HW, kTM), N);
+    corr_gemm_tc_kernel<<<grid, 128, smem, st>>>(tmA, tmB, static_cast<__half*>(levels_out[l]), HW, N2, err);
+    DB200_CHECK_LAUNCH();
+    prev = f2T;
+    h >>= 1; w >>= 1;
+  }
+  return DB200_OK;
+}
+
+}  // namespace db200

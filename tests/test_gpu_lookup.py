@@ -131,3 +131,23 @@ def test_altcorr_equals_lookup_of_volume():
     b, = droid_backends.altcorr_forward((f1 / 4).permute(0, 2, 3, 1).contiguous(), (f2 / 4).permute(0, 2, 3, 1).contiguous(),
                                         co.permute(0, 2, 3, 1).contiguous()[:, None], 3)
     assert float((a.reshape(N, 49, ht, wd) - b[:, 0]).abs().max()) <= 1e-4 * np.sqrt(C) / 16 * 4
+
+
+def test_corr_volume_pyramid_full_size_f16():
+    """48x64 maps (BASELINE configs): the tcgen05/TMA GEMM path against an fp32 torch reference of
+    CorrBlock.corr + avg_pool2d (corr.py:30-38,63-71) computed on the same f16 inputs."""
+    import droid_backends
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    N, C, ht, wd = 3, 128, 48, 64
+    f1 = torch.randn((N, C, ht, wd), device="cuda", dtype=torch.float16, generator=g)
+    f2 = torch.randn((N, C, ht, wd), device="cuda", dtype=torch.float16, generator=g)
+    outs = droid_backends.corr_volume_pyramid(f1, f2, 4)
+    a = (f1.float() / 4).reshape(N, C, ht * wd)
+    b = f2.float() / 4
+    scale = np.sqrt(C) / 16.0
+    for l in range(4):
+        ref = torch.matmul(a.transpose(1, 2), b.reshape(N, C, -1)).reshape(N, ht, wd, ht >> l, wd >> l)
+        assert outs[l].shape == ref.shape and outs[l].dtype == torch.float16
+        err = float((outs[l].float() - ref).abs().max())
+        assert err <= 3e-3 * scale * 4, (l, err)
+        b = torch.nn.functional.avg_pool2d(b, 2, stride=2)
