@@ -434,7 +434,9 @@ __host__ __device__ inline int schur_segs(int d) {                              
 struct SchurSmem {
   double* Ws; double* cs;                  // [dcap][36], [dcap][6]
   float* shi; float* slo;                  // [rpad][kStride] stash, hi / lo TF32 parts     (aliased by G, red in the epilogue)
-  float* G; float* red;                    // [rpad][gn], [256][27]
+  float* G; float* red;                    // [rpad][gn] (aliases the stash), [256][27] (aliases the staging buffers)
+  float* stage;                            // [2][necap][4][kChunk] target/weight of the current and the next chunk (cp.async)
+  int* eid;                                // [necap] original edge index
   float* Cw;                               // [necap][2][kChunk]
   float* px;                               // [7][kChunk]: X0, X1, disp, sqrt(Q), sqrt(Q) w, disps_sens, eta
   float* Am; float* Hs;                    // [dcap][36], [dcap][27]
@@ -444,13 +446,17 @@ struct SchurSmem {
 
 __host__ __device__ inline size_t schur_alias_floats(int dcap) {
   const size_t stash = size_t(2) * schur_rpad(dcap) * kStride;
-  const size_t epi = size_t(schur_rpad(dcap)) * schur_gn(dcap) + size_t(256) * 27;
+  const size_t epi = size_t(schur_rpad(dcap)) * schur_gn(dcap);
   return stash > epi ? stash : epi;
+}
+__host__ __device__ inline size_t schur_stage_floats(int necap) {
+  const size_t st = size_t(2) * necap * 4 * kChunk, red = size_t(256) * 27;
+  return st > red ? st : red;
 }
 __host__ __device__ inline size_t schur_smem_bytes(int dcap, int necap) {
   size_t b = sizeof(double) * size_t(dcap > 0 ? dcap : 1) * 42;
-  b += sizeof(float) * (schur_alias_floats(dcap) + size_t(necap) * 2 * kChunk + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
-  b += sizeof(int) * (size_t(2) * (dcap > 0 ? dcap : 1) + necap);
+  b += sizeof(float) * (schur_alias_floats(dcap) + schur_stage_floats(necap) + size_t(necap) * 2 * kChunk + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
+  b += sizeof(int) * (size_t(2) * (dcap > 0 ? dcap : 1) + 2 * size_t(necap));
   b += 4 * size_t(schur_segs(dcap) + 8);
   return (b + 15) / 16 * 16;
 }
@@ -462,15 +468,17 @@ __device__ __forceinline__ SchurSmem schur_carve(unsigned char* base, int dcap, 
   s.shi = reinterpret_cast<float*>(s.cs + size_t(dc) * 6);
   s.slo = s.shi + size_t(schur_rpad(dcap)) * kStride;
   s.G = s.shi;
-  s.red = s.shi + size_t(schur_rpad(dcap)) * schur_gn(dcap);
-  s.Cw = s.shi + schur_alias_floats(dcap);
+  s.stage = s.shi + schur_alias_floats(dcap);
+  s.red = s.stage;
+  s.Cw = s.stage + schur_stage_floats(necap);
   s.px = s.Cw + size_t(necap) * 2 * kChunk;
   s.Am = s.px + 7 * kChunk;
   s.Hs = s.Am + size_t(dc) * 36;
   s.jp = reinterpret_cast<int*>(s.Hs + size_t(dc) * 27);
   s.slotq = s.jp + dc;
   s.eslot = s.slotq + dc;
-  s.segs = reinterpret_cast<unsigned char*>(s.eslot + necap);
+  s.eid = s.eslot + necap;
+  s.segs = reinterpret_cast<unsigned char*>(s.eid + necap);
   return s;
 }
 
@@ -486,6 +494,16 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const float (&a)[4], con
                : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
                  "r"(__float_as_uint(b[0])), "r"(__float_as_uint(b[1])));
 }
+
+// 16-byte / 4-byte asynchronous global->shared copies; src_bytes = 0 zero-fills (pixels past the end of the map)
+__device__ __forceinline__ void cp_async16(unsigned dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(unsigned dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ void ldsm_x4(float (&r)[4], unsigned addr) {
   unsigned a, b, c, d;
@@ -557,6 +575,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   for (int qq = tid; qq < ne; qq += kBAThreads) {
     const int sl = p.erec[q_beg + qq].slot;
     sm.eslot[qq] = sl;
+    sm.eid[qq] = p.erec[q_beg + qq].eid;
     if (sl >= 0) sm.slotq[sl] = q_beg + qq;
   }
   // pixel lanes per edge: minimise (warps touched) x (pixel iterations)
@@ -573,8 +592,6 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   EdgeRec rec{};
   int sl = -1;
   if (active) { rec = load_rec(p.erec + q_beg + e); sl = rec.slot; }
-  const float* tg = p.target + size_t(active ? rec.eid : 0) * 2 * HW;
-  const float* wg = p.weight + size_t(active ? rec.eid : 0) * 2 * HW;
   float hacc[27];
 #pragma unroll
   for (int i = 0; i < 27; i++) hacc[i] = 0.0f;
@@ -601,6 +618,31 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     a_addr[u] = shi_base + 4u * unsigned((16 * seg_i[u] + lr + 8 * (lm & 1)) * kStride + 4 * (lm >> 1));
     b_addr[u] = shi_base + (lm >> 1) * lo_off + 4u * unsigned((8 * seg_j0[u] + lr) * kStride + 4 * (lm & 1));
   }
+  // target/weight of one chunk -> staging buffer `buf` (row (q, r) = edge q, r in {tu, tv, wu, wv})
+  const unsigned stage_base = unsigned(__cvta_generic_to_shared(sm.stage));
+  const bool vec16 = (HW % 4 == 0) && (((reinterpret_cast<uintptr_t>(p.target) | reinterpret_cast<uintptr_t>(p.weight)) & 15) == 0);
+  auto stage_chunk = [&](int chunk, int buf) {
+    const int cbase = chunk * kChunk;
+    const unsigned dst0 = stage_base + unsigned(buf) * unsigned(necap) * 4u * kChunk * 4u;
+    if (vec16) {
+      for (int i = tid; i < ne * 4 * (kChunk / 4); i += kBAThreads) {
+        const int q = i / (4 * (kChunk / 4)), rem = i - q * (4 * (kChunk / 4)), r = rem / (kChunk / 4), sg = rem - r * (kChunk / 4);
+        const int pix = cbase + 4 * sg;
+        const float* src = (r < 2 ? p.target : p.weight) + size_t(sm.eid[q]) * 2 * HW + size_t(r & 1) * HW + (pix < HW ? pix : 0);
+        cp_async16(dst0 + 4u * unsigned((q * 4 + r) * kChunk + 4 * sg), src, pix < HW ? 16 : 0);
+      }
+    } else {
+      for (int i = tid; i < ne * 4 * kChunk; i += kBAThreads) {
+        const int q = i / (4 * kChunk), rem = i - q * (4 * kChunk), r = rem / kChunk, px = rem - r * kChunk;
+        const int pix = cbase + px;
+        const float* src = (r < 2 ? p.target : p.weight) + size_t(sm.eid[q]) * 2 * HW + size_t(r & 1) * HW + (pix < HW ? pix : 0);
+        cp_async4(dst0 + 4u * unsigned((q * 4 + r) * kChunk + px), src, pix < HW ? 4 : 0);
+      }
+    }
+    cp_async_commit();
+  };
+  if (split < nchunks) stage_chunk(split, 0);
+  int sbuf = 0;
   // prefetch of the first chunk's per-pixel data
   float nx_h = 1.0f, nx_s = 0.0f, nx_e = 0.0f;
   if (tid < kChunk) {
@@ -611,6 +653,10 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
 
   for (int c = split; c < nchunks; c += S) {
     const int base = c * kChunk;
+    cp_async_wait_all();                              // this chunk's target/weight (issued one chunk ago) have landed
+    if (c + S < nchunks) stage_chunk(c + S, sbuf ^ 1);   // next chunk's copies fly during this chunk's work
+    const float* stg = sm.stage + size_t(sbuf) * necap * 4 * kChunk;
+    sbuf ^= 1;
     if (tid < kChunk) {
       const int pix = base + tid;
       const int pi_ = pix < HW ? pix : 0;
@@ -626,19 +672,9 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     __syncthreads();
     // ---------------- phase 1
     if (active) {
-      float n_tu = 0.0f, n_tv = 0.0f, n_wu = 0.0f, n_wv = 0.0f;
-      if (base + g < HW && g < kChunk) {
-        n_tu = __ldg(tg + base + g); n_tv = __ldg(tg + HW + base + g); n_wu = __ldg(wg + base + g); n_wv = __ldg(wg + HW + base + g);
-      }
+      const float* se = stg + size_t(e) * 4 * kChunk;
       for (int pp = g; pp < kChunk; pp += L) {
-        const float tu = n_tu, tv = n_tv, wur = n_wu, wvr = n_wv;
-        {                                              // loads of the next pixel of this lane are issued before the math
-          const int np = pp + L, npix = base + np;
-          n_tu = 0.0f; n_tv = 0.0f; n_wu = 0.0f; n_wv = 0.0f;
-          if (np < kChunk && npix < HW) {
-            n_tu = __ldg(tg + npix); n_tv = __ldg(tg + HW + npix); n_wu = __ldg(wg + npix); n_wv = __ldg(wg + HW + npix);
-          }
-        }
+        const float tu = se[pp], tv = se[kChunk + pp], wur = se[2 * kChunk + pp], wvr = se[3 * kChunk + pp];
         PixEdge pe_;
         pix_edge(rec, sm.px[pp], sm.px[kChunk + pp], sm.px[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
         sm.Cw[(size_t(e) * 2 + 0) * kChunk + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
