@@ -39,8 +39,8 @@ __device__ __forceinline__ void pix_edge(const EdgeRec& r, float X0, float X1, f
   const bool bad = z < 0.25f;                       // MIN_DEPTH (:26, :302)
   const float d = bad ? 0.0f : 1.0f / z;
   const float d2 = d * d;
-  o.wu = bad ? 0.0f : float(0.001 * double(wur));   // `.001 * weight` is a double product in the source (:305)
-  o.wv = bad ? 0.0f : float(0.001 * double(wvr));
+  o.wu = bad ? 0.0f : 0.001f * wur;   // `.001 * weight` (:305) — the source's double product differs by <= 1 ulp
+  o.wv = bad ? 0.0f : 0.001f * wvr;
   o.ru = tu - (fx * d * x + cx);
   o.rv = tv - (fy * d * y + cy);
   o.Ju[0] = fx * (h * d);
@@ -704,27 +704,33 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     }
     __syncthreads();
     // ---------------- phase 1b: depth system of the chunk (:1396-1400), scaling by sqrt(Q), TF32 split
-    if (tid < kChunk) {
-      const int pix = base + tid;
+    {
+      // 4 threads per pixel (lanes 4p..4p+3) sum the edges q = part, part+4, ...; combined in a fixed order by shuffles
+      const int pp = tid >> 2, part = tid & 3;
+      const int pix = base + pp;
       float Csum = 0.0f, wsum = 0.0f;
-      for (int q = 0; q < ne; q++) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + tid]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + tid]; }
-      float Q = 0.0f, wv_ = 0.0f;
-      if (pix < HW) {
-        const float h = sm.px[2 * kChunk + tid];
-        const float ds = sm.px[5 * kChunk + tid];
-        const float m = ds > 0.0f ? 1.0f : 0.0f;
-        const float C = Csum + m * 0.05f + (1.0f - m) * sm.px[6 * kChunk + tid];
-        wv_ = wsum - m * 0.05f * (h - ds);
-        Q = 1.0f / C;
-        p.Q[size_t(k) * HW + pix] = Q;
-        p.w[size_t(k) * HW + pix] = wv_;
+      for (int q = part; q < ne; q += 4) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + pp]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + pp]; }
+      Csum += __shfl_xor_sync(0xffffffffu, Csum, 1); wsum += __shfl_xor_sync(0xffffffffu, wsum, 1);
+      Csum += __shfl_xor_sync(0xffffffffu, Csum, 2); wsum += __shfl_xor_sync(0xffffffffu, wsum, 2);
+      if (part == 0) {
+        float Q = 0.0f, wv_ = 0.0f;
+        if (pix < HW) {
+          const float h = sm.px[2 * kChunk + pp];
+          const float ds = sm.px[5 * kChunk + pp];
+          const float m = ds > 0.0f ? 1.0f : 0.0f;
+          const float C = Csum + m * 0.05f + (1.0f - m) * sm.px[6 * kChunk + pp];
+          wv_ = wsum - m * 0.05f * (h - ds);
+          Q = 1.0f / C;
+          p.Q[size_t(k) * HW + pix] = Q;
+          p.w[size_t(k) * HW + pix] = wv_;
+        }
+        const float sq = sqrtf(Q);
+        sm.px[3 * kChunk + pp] = sq;
+        const float vq = sq * wv_;
+        const float hi = to_tf32(vq);
+        sm.shi[size_t(6 * d) * kStride + pp] = hi;
+        sm.slo[size_t(6 * d) * kStride + pp] = to_tf32(vq - hi);
       }
-      const float sq = sqrtf(Q);
-      sm.px[3 * kChunk + tid] = sq;
-      const float vq = sq * wv_;
-      const float hi = to_tf32(vq);
-      sm.shi[size_t(6 * d) * kStride + tid] = hi;
-      sm.slo[size_t(6 * d) * kStride + tid] = to_tf32(vq - hi);
     }
     __syncthreads();
     for (int idx = tid; idx < 6 * d * (kChunk / 4); idx += kBAThreads) {   // 4 pixels per thread and step
@@ -910,10 +916,31 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   // degree buckets (shared memory and accumulator registers grow with the bucket's cap); a frame works in exactly one.
   // NSEG = ceil(schur_segs(dcap) / 8): 6, 12, 25, 36 segments of <= 4 tiles for dcap = 8, 14, 22, 28.
   const int dmax_host = p.N < kMaxDeg ? p.N : kMaxDeg;   // the host only knows d <= N
-  int rc = launch_schur<1>(p, S, 0, 8, st);
-  if (rc == DB200_OK && dmax_host > 8) rc = launch_schur<2>(p, S, 9, 14, st);
-  if (rc == DB200_OK && dmax_host > 14) rc = launch_schur<4>(p, S, 15, 22, st);
-  if (rc == DB200_OK && dmax_host > 22) rc = launch_schur<5>(p, S, 23, kMaxDeg, st);
+  // The buckets are independent (disjoint frames; the reduced system is updated with atomics), and each one alone
+  // leaves SMs idle in its last wave: fork them onto side streams so that they overlap, join before returning.
+  static cudaStream_t aux[3] = {nullptr, nullptr, nullptr};
+  static cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
+  if (!ev_fork) {
+    DB200_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    for (int i = 0; i < 3; i++) {
+      DB200_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
+      DB200_CUDA(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
+    }
+  }
+  const bool b1 = dmax_host > 8, b2 = dmax_host > 14, b3 = dmax_host > 22;
+  if (!b1) return launch_schur<1>(p, S, 0, 8, st);
+  DB200_CUDA(cudaEventRecord(ev_fork, st));
+  int rc = launch_schur<2>(p, S, 9, 14, st);                       // the bucket that carries most frames of a backend graph
+  auto side = [&](int i, auto fn) -> int {
+    DB200_CUDA(cudaStreamWaitEvent(aux[i], ev_fork, 0));
+    const int r = fn(aux[i]);
+    DB200_CUDA(cudaEventRecord(ev_join[i], aux[i]));
+    DB200_CUDA(cudaStreamWaitEvent(st, ev_join[i], 0));
+    return r;
+  };
+  if (rc == DB200_OK) rc = side(0, [&](cudaStream_t s2) { return launch_schur<1>(p, S, 0, 8, s2); });
+  if (rc == DB200_OK && b2) rc = side(1, [&](cudaStream_t s2) { return launch_schur<4>(p, S, 15, 22, s2); });
+  if (rc == DB200_OK && b3) rc = side(2, [&](cudaStream_t s2) { return launch_schur<5>(p, S, 23, kMaxDeg, s2); });
   return rc;
 }
 
