@@ -18,6 +18,7 @@
 // ba_frame_kernel<.,true> (motion-only BA): thread = pixel, shuffle-butterfly reduction of the 27 sums.
 // HBM traffic per edge-pixel: target 8 B + weight 8 B (+ disp 4 B per keyframe-pixel) — the algorithmic
 // 20*HW*N + 16*HW*M of SURVEY.md §8d; the back-substitution re-reads weight (8 B) to recompute E.
+#include <cstdlib>
 #include "ba.cuh"
 
 namespace db200 {
@@ -912,6 +913,8 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   }
   const int nchunks = cdiv(p.HW, kChunk);
   int S = cdiv(6 * kNumSMs, p.Mcap);               // aim at >= ~6 CTAs per SM over the launch
+  static const int s_env = getenv("DB200_BA_SPLIT") ? atoi(getenv("DB200_BA_SPLIT")) : 0;   // tuning aid
+  if (s_env > 0) S = s_env;
   S = S < 1 ? 1 : (S > nchunks ? nchunks : S);
   // degree buckets (shared memory and accumulator registers grow with the bucket's cap); a frame works in exactly one.
   // NSEG = ceil(schur_segs(dcap) / 8): 6, 12, 25, 36 segments of <= 4 tiles for dcap = 8, 14, 22, 28.
