@@ -10,6 +10,7 @@
 // accumulation order (bit-identical fp16/fp32/fp64), and a CTA covers 64 consecutive x so that each
 // output channel row is written as one full coalesced line.  HBM-bound: algorithmic bytes per lookup
 // = L*(2r+2)^2*s + 8 + L*(2r+1)^2*s.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace db200 {
@@ -242,6 +243,244 @@ corr_lookup_r3_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __r
   }
 }
 
+// ---- pipelined radius-3 path (fp16 / fp32 volumes whose level widths are multiples of a 16-byte chunk) ----------
+// Persistent CTAs (128 threads, tile = 32 consecutive source pixels x all levels = 128 windows) run a two-stage
+// software pipeline so that HBM always has a full tile of window rows in flight per CTA while the previous tile is
+// being interpolated and stored:
+//   issue(k+1)  every 8-sample window row is fetched as the aligned 16-byte chunks that cover it with
+//               cp.async.cg (L2 only); rows/chunks outside the slice are zero-filled by the copy itself (src-size 0),
+//               which reproduces the reference's skipped `within_bounds` samples (+0 products);
+//   coords(k+2) the coordinates of the tile after next are loaded into registers;
+//   compute(k)  thread = window: two 16-byte shared-memory reads per row, a register funnel to the window's element
+//               offset, and (fp16) packed __hmul2_rn/__hadd2_rn in the reference's accumulation order — two
+//               x-offsets per instruction, each half rounded exactly like the scalar c10::Half sequence;
+//   store(k)    the [levels*49][32] tile leaves as 16-byte stores; then the descriptors of tile k+2 are written.
+// Window origin/descriptor arithmetic is the same float sequence as the reference (coords / 2^l, floorf).
+template <typename T> struct PipeCfg;
+template <> struct PipeCfg<__half> { static constexpr int CE = 8, CH = 2, LOG_CE = 3; };
+template <> struct PipeCfg<float> { static constexpr int CE = 4, CH = 3, LOG_CE = 2; };
+constexpr int kPipePX = 32, kPipeThreads = 128, kPipeWin = kMaxLevels * kPipePX;
+template <typename T> __host__ __device__ constexpr int pipe_win_bytes() { return 8 * PipeCfg<T>::CH * 16 + 16; }
+
+struct PipeDesc {                    // one stage of window descriptors
+  long long base[kPipeWin];          // element offset (from the level base) of window row 0, chunk 0; may be out of range
+  unsigned mask[kPipeWin];           // bits 0-7 valid rows, 8.. valid chunks, 16-19 element offset inside chunk 0
+  float dx[kPipeWin], dy[kPipeWin];
+};
+
+template <typename T>
+__host__ __device__ constexpr size_t pipe_smem_bytes() {
+  return 2 * size_t(kPipeWin) * pipe_win_bytes<T>() + size_t(kMaxLevels) * 49 * kPipePX * sizeof(T) + 2 * sizeof(PipeDesc);
+}
+
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
+  const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  const int n = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+
+// Row of a staged window -> for fp16: A[p] = samples (x=2p, 2p+1), S[p] = samples (x=2p+1, 2p+2) as half2 bit patterns.
+__device__ __forceinline__ void pipe_row_half(const unsigned char* rowp, int q, unsigned sel_a, unsigned sel_s,
+                                              unsigned (&A)[4], unsigned (&S)[4]) {
+  const uint4 a = *reinterpret_cast<const uint4*>(rowp), b = *reinterpret_cast<const uint4*>(rowp + 16);
+  const bool s2 = q & 2, s1 = q & 1;
+  const unsigned t0 = s2 ? a.z : a.x, t1 = s2 ? a.w : a.y, t2 = s2 ? b.x : a.z, t3 = s2 ? b.y : a.w, t4 = s2 ? b.z : b.x,
+                 t5 = s2 ? b.w : b.y;
+  const unsigned u0 = s1 ? t1 : t0, u1 = s1 ? t2 : t1, u2 = s1 ? t3 : t2, u3 = s1 ? t4 : t3, u4 = s1 ? t5 : t4;
+  A[0] = __byte_perm(u0, u1, sel_a); A[1] = __byte_perm(u1, u2, sel_a); A[2] = __byte_perm(u2, u3, sel_a); A[3] = __byte_perm(u3, u4, sel_a);
+  S[0] = __byte_perm(u0, u1, sel_s); S[1] = __byte_perm(u1, u2, sel_s); S[2] = __byte_perm(u2, u3, sel_s); S[3] = __byte_perm(u3, u4, sel_s);
+}
+
+__device__ __forceinline__ __half2 as_h2(unsigned u) { return *reinterpret_cast<__half2*>(&u); }
+
+template <typename T>
+__global__ void __launch_bounds__(kPipeThreads)
+corr_lookup_r3_pipe_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __restrict__ out, int N, int h1, int w1,
+                           int h2, int w2, int num_levels, int num_tiles) {
+  using Cfg = PipeCfg<T>;
+  constexpr int CE = Cfg::CE, CH = Cfg::CH, WINB = pipe_win_bytes<T>(), PX = kPipePX, kCh = 49;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned char* win = smem_raw;                                                        // [2][kPipeWin][WINB]
+  T* sout = reinterpret_cast<T*>(smem_raw + 2 * size_t(kPipeWin) * WINB);               // [L*49][PX]
+  PipeDesc* desc = reinterpret_cast<PipeDesc*>(reinterpret_cast<unsigned char*>(sout) + size_t(kMaxLevels) * kCh * PX * sizeof(T));
+  const int tid = threadIdx.x;
+  const int nwin = num_levels * PX;
+  const int tiles_x = (w1 + PX - 1) / PX;
+  const size_t plane = size_t(h1) * w1;
+  const int my_l = tid / PX, my_px = tid - my_l * PX;              // the window this thread describes and interpolates
+
+  // coordinates of (tile, my_px) -> registers
+  auto load_coords = [&](int tile, float& cx, float& cy) {
+    cx = 0.0f; cy = 0.0f;
+    if (tile < num_tiles && tid < nwin) {
+      const int xt = tile % tiles_x, rest = tile / tiles_x, y = rest % h1, n = rest / h1;
+      const int x = xt * PX + my_px;
+      if (x < w1) {
+        const size_t o = size_t(y) * w1 + x;
+        cx = __ldg(coords + (size_t(n) * 2 + 0) * plane + o);
+        cy = __ldg(coords + (size_t(n) * 2 + 1) * plane + o);
+      }
+    }
+  };
+  auto write_desc = [&](int tile, int s, float cx, float cy) {
+    if (tile >= num_tiles || tid >= nwin) return;
+    const int xt = tile % tiles_x, rest = tile / tiles_x, y = rest % h1, n = rest / h1;
+    const int x = xt * PX + my_px;
+    const int h2l = h2 >> my_l, w2l = w2 >> my_l;
+    const float scale = float(1 << my_l);
+    const float x0 = cx / scale, y0 = cy / scale;
+    const float fx = floorf(x0), fy = floorf(y0);
+    constexpr int kFar = 1 << 20;                                  // anything this far out is all zeros either way
+    const int xb = max(-kFar, min(kFar, static_cast<int>(fx))) - 3, yb = max(-kFar, min(kFar, static_cast<int>(fy))) - 3;
+    const int k0 = xb >> Cfg::LOG_CE, o = xb & (CE - 1);
+    unsigned m = 0;
+    if (x < w1) {
+#pragma unroll
+      for (int r = 0; r < 8; r++) m |= (static_cast<unsigned>(yb + r) < static_cast<unsigned>(h2l)) ? (1u << r) : 0u;
+#pragma unroll
+      for (int c = 0; c < CH; c++)
+        m |= (static_cast<unsigned>(k0 + c) < static_cast<unsigned>(w2l >> Cfg::LOG_CE) && c * CE < o + 8) ? (1u << (8 + c)) : 0u;
+      m |= static_cast<unsigned>(o) << 16;
+      m |= 1u << 31;                                               // live pixel
+    }
+    desc[s].base[tid] = ((static_cast<long long>(n) * h1 + y) * w1 + x) * (static_cast<long long>(h2l) * w2l) +
+                        static_cast<long long>(yb) * w2l + static_cast<long long>(k0) * CE;
+    desc[s].mask[tid] = m;
+    desc[s].dx[tid] = x0 - fx;
+    desc[s].dy[tid] = y0 - fy;
+  };
+  auto issue = [&](int tile, int s) {
+    if (tile < num_tiles) {
+      unsigned char* wbase = win + size_t(s) * kPipeWin * WINB;
+#pragma unroll
+      for (int l = 0; l < kMaxLevels; l++) {
+        if (l < num_levels) {
+          const T* lp = static_cast<const T*>(levels.p[l]);
+          const int w2l = w2 >> l;
+#pragma unroll
+          for (int it = 0; it < (PX * 8 * CH) / kPipeThreads; it++) {
+            const int idx = it * kPipeThreads + tid;
+            const int wl = idx / (8 * CH), rc = idx - wl * (8 * CH), row = rc / CH, c = rc - row * CH;
+            const int w = l * PX + wl;
+            const unsigned m = desc[s].mask[w];
+            const bool ok = ((m >> row) & (m >> (8 + c)) & 1u) != 0;
+            const T* src = ok ? lp + (desc[s].base[w] + static_cast<long long>(row) * w2l + c * CE) : lp;
+            cp_async16_zfill(wbase + size_t(w) * WINB + row * (CH * 16) + c * 16, src, ok);
+          }
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+
+  int tile = blockIdx.x;
+  const int stride = gridDim.x;
+  {
+    float cx, cy;
+    load_coords(tile, cx, cy);
+    write_desc(tile, 0, cx, cy);
+    load_coords(tile + stride, cx, cy);
+    write_desc(tile + stride, 1, cx, cy);
+  }
+  __syncthreads();
+  issue(tile, 0);
+
+  for (int k = 0; tile < num_tiles; k++, tile += stride) {
+    const int s = k & 1;
+    issue(tile + stride, s ^ 1);                                   // desc[s^1] was written before the last barrier
+    float ncx, ncy;
+    load_coords(tile + 2 * stride, ncx, ncy);
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    __syncthreads();                                               // tile k's windows are in shared memory
+
+    // ---- compute: thread = window
+    if (tid < nwin && (desc[s].mask[tid] >> 31)) {
+      const unsigned m = desc[s].mask[tid];
+      const int o = (m >> 16) & 15;
+      const float dx = desc[s].dx[tid], dy = desc[s].dy[tid];
+      const unsigned char* wp = win + (size_t(s) * kPipeWin + tid) * WINB;
+      T* so = sout + size_t(my_l) * kCh * PX + my_px;
+      if constexpr (sizeof(T) == 2) {
+        const __half2 w00 = __half2half2(__float2half_rn((1.0f - dx) * (1.0f - dy)));
+        const __half2 w01 = __half2half2(__float2half_rn((1.0f - dx) * dy));
+        const __half2 w10 = __half2half2(__float2half_rn(dx * (1.0f - dy)));
+        const __half2 w11 = __half2half2(__float2half_rn(dx * dy));
+        const __half2 zero = __half2half2(__float2half_rn(0.0f));
+        const int q = o >> 1;
+        const unsigned sel_a = (o & 1) ? 0x5432u : 0x3210u, sel_s = (o & 1) ? 0x7654u : 0x5432u;
+        unsigned A0[4], S0[4], A1[4], S1[4];
+        pipe_row_half(wp, q, sel_a, sel_s, A0, S0);
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+          pipe_row_half(wp + (j + 1) * (CH * 16), q, sel_a, sel_s, A1, S1);
+#pragma unroll
+          for (int p = 0; p < 4; p++) {
+            __half2 acc = __hadd2_rn(zero, __hmul2_rn(as_h2(A0[p]), w00));     // x offsets i = 2p (low), 2p+1 (high)
+            acc = __hadd2_rn(acc, __hmul2_rn(as_h2(A1[p]), w01));
+            acc = __hadd2_rn(acc, __hmul2_rn(as_h2(S0[p]), w10));
+            acc = __hadd2_rn(acc, __hmul2_rn(as_h2(S1[p]), w11));
+            so[size_t((2 * p) * 7 + j) * PX] = __low2half(acc);
+            if (p < 3) so[size_t((2 * p + 1) * 7 + j) * PX] = __high2half(acc);
+          }
+#pragma unroll
+          for (int p = 0; p < 4; p++) { A0[p] = A1[p]; S0[p] = S1[p]; }
+        }
+      } else {
+        const T w00 = Elem<T>::from_float((1.0f - dx) * (1.0f - dy));
+        const T w01 = Elem<T>::from_float((1.0f - dx) * dy);
+        const T w10 = Elem<T>::from_float(dx * (1.0f - dy));
+        const T w11 = Elem<T>::from_float(dx * dy);
+        T r0[8], r1[8];
+        const T* rp = reinterpret_cast<const T*>(wp) + o;
+#pragma unroll
+        for (int i = 0; i < 8; i++) r0[i] = rp[i];
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+          const T* rn = rp + (j + 1) * (CH * 16 / int(sizeof(T)));
+#pragma unroll
+          for (int i = 0; i < 8; i++) r1[i] = rn[i];
+#pragma unroll
+          for (int i = 0; i < 7; i++) {
+            T acc = Elem<T>::zero();
+            acc = Elem<T>::mad(r0[i], w00, acc);
+            acc = Elem<T>::mad(r1[i], w01, acc);
+            acc = Elem<T>::mad(r0[i + 1], w10, acc);
+            acc = Elem<T>::mad(r1[i + 1], w11, acc);
+            so[size_t(i * 7 + j) * PX] = acc;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; i++) r0[i] = r1[i];
+        }
+      }
+    }
+    __syncthreads();                                               // sout complete; win[s], desc[s] free
+
+    // ---- store tile k, then describe tile k+2 into desc[s]
+    {
+      const int xt = tile % tiles_x, rest = tile / tiles_x, y = rest % h1, n = rest / h1;
+      const int x_base = xt * PX, npx = min(PX, w1 - x_base);
+      const int nch = num_levels * kCh;
+      T* obase = out + size_t(n) * nch * plane + size_t(y) * w1 + x_base;
+      constexpr int kVec = 16 / sizeof(T), per_row = PX / kVec;
+      const bool vec_ok = (npx == PX) && (w1 % kVec == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);
+      if (vec_ok) {
+        for (int idx = tid; idx < nch * per_row; idx += kPipeThreads) {
+          const int ch = idx / per_row, v = idx - ch * per_row;
+          *reinterpret_cast<uint4*>(obase + size_t(ch) * plane + v * kVec) = *reinterpret_cast<const uint4*>(sout + size_t(ch) * PX + v * kVec);
+        }
+      } else {
+        for (int idx = tid; idx < nch * PX; idx += kPipeThreads) {
+          const int ch = idx / PX, px = idx - ch * PX;
+          if (px < npx) obase[size_t(ch) * plane + px] = sout[idx];
+        }
+      }
+    }
+    write_desc(tile + 2 * stride, s, ncx, ncy);
+    __syncthreads();
+  }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
 // Backward: one warp per source pixel writes the WHOLE h2*w2 slice of volume_grad (zeros outside the
 // window), so no separate memset pass is needed.  Gradient value per window sample follows
 // correlation_kernels.cu:108-121 (g accumulates the 4 contributions in that order, then 0 + g).
@@ -285,6 +524,25 @@ corr_lookup_bwd_kernel(const float* __restrict__ coords, const T* __restrict__ c
 template <typename T>
 int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h1, int w1, int h2, int w2, int L, int r,
                cudaStream_t st) {
+  if constexpr (sizeof(T) <= 4) {
+    // pipelined path: every level's width must be whole 16-byte chunks and the level bases 16-byte aligned
+    constexpr int CE = 16 / int(sizeof(T));
+    bool ok = (r == 3) && !getenv("DB200_LOOKUP_NO_PIPE");
+    for (int l = 0; l < L && ok; l++)
+      ok = ((w2 >> l) % CE == 0) && ((h2 >> l) > 0) && (reinterpret_cast<uintptr_t>(lv.p[l]) % 16 == 0);
+    if (ok) {
+      const long long tiles = static_cast<long long>(N) * h1 * cdiv(w1, kPipePX);
+      if (tiles > 0x7fffffff) return DB200_ERR_ARG;
+      const size_t smem = pipe_smem_bytes<T>();
+      auto kern = corr_lookup_r3_pipe_kernel<T>;
+      DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      const int per_sm = smem <= 110 * 1024 ? 2 : 1;
+      const int grid = int(tiles < static_cast<long long>(per_sm) * kNumSMs ? tiles : static_cast<long long>(per_sm) * kNumSMs);
+      kern<<<grid, kPipeThreads, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, int(tiles));
+      DB200_CHECK_LAUNCH();
+      return DB200_OK;
+    }
+  }
   if (r == 3) {
     constexpr int PX = sizeof(T) == 8 ? 32 : 64;
     const size_t smem = (size_t(L) * PX * kWinStride + size_t(L) * 49 * PX) * sizeof(T) + size_t(L) * PX * 16;

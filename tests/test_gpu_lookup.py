@@ -56,6 +56,32 @@ def test_corr_pyramid_lookup_matches_per_level():
     np.testing.assert_array_equal(out.cpu().numpy().view(np.uint16), ref.view(np.uint16))
 
 
+@pytest.mark.parametrize("dtype,N,h1,w1,h2,w2,L", [
+    (np.float16, 2, 5, 40, 16, 64, 4),      # pipelined path, ragged last tile (40 = 32 + 8 source pixels per row)
+    (np.float16, 1, 3, 64, 8, 64, 4),       # level 3 is a single row of 8
+    (np.float16, 3, 2, 7, 24, 32, 2),       # fewer levels than the kernel's maximum, one short tile
+    (np.float32, 1, 4, 33, 8, 32, 4),       # fp32 chunks of 4, levels 32/16/8/4
+    (np.float32, 2, 6, 32, 12, 16, 1),
+    (np.float16, 1, 4, 32, 12, 24, 2),      # level 1 width 12 is not whole 16-byte chunks -> staged (non-pipelined) kernel
+])
+def test_corr_pyramid_lookup_pipelined_path_bit_exact(dtype, N, h1, w1, h2, w2, L):
+    """The cp.async-pipelined radius-3 kernel (csrc/corr_lookup.cu) against the oracle's per-level restatement of
+    correlation_kernels.cu:20-70 — every output bit, including windows that straddle or miss the slice."""
+    import droid_backends
+    from oracle import oracle
+    rng = np.random.default_rng(11)
+    levels = [rng.normal(0, 1, (N, h1, w1, h2 >> l, w2 >> l)).astype(dtype) for l in range(L)]
+    co = _coords(N, h1, w1, h2, w2, 12)
+    co[0, :, 1, 0] = [w2 - 4.0, h2 - 4.0]          # window ends exactly at the border
+    co[0, :, 1, 1] = [-4.0 + 1e-3, 2.5]            # one column inside
+    co[0, :, 1, 2] = [7.999, 0.0]                  # fractional part next to 1
+    ref = np.concatenate([oracle.corr_index_forward(levels[l], (co / 2 ** l).astype(np.float32), 3).reshape(N, 49, h1, w1)
+                          for l in range(L)], 1)
+    out = droid_backends.corr_pyramid_lookup([torch.from_numpy(v).cuda() for v in levels], torch.from_numpy(co).cuda(), 3)
+    bits = np.uint16 if dtype == np.float16 else np.uint32
+    np.testing.assert_array_equal(out.cpu().numpy().view(bits), ref.view(bits))
+
+
 @pytest.mark.parametrize("shape", [(2, 12, 16, 12, 16), (1, 7, 9, 5, 6)])
 def test_corr_index_backward_bit_exact(shape):
     import droid_backends
