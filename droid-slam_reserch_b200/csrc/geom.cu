@@ -159,6 +159,101 @@ __global__ void depth_filter_kernel(const float* __restrict__ poses, const float
   counter[size_t(b) * HW + k] = count;
 }
 
+// projmap (droid_kernels.cu:427-516, 1463-1490): coords[num,ht,wd,3] (third channel stays zero, as the reference's
+// torch::zeros leaves it), valid[num,ht,wd,1].  No stereo special case in the reference kernel.
+__global__ void projmap_kernel(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                               const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int n_poses, int B, int ht, int wd,
+                               float* __restrict__ coords, float* __restrict__ valid) {
+  const int e = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int HW = ht * wd;
+  if (k >= HW) return;
+  const int ix = int(ii[e]), jx = int(jj[e]);
+  float* c = coords + (size_t(e) * HW + k) * 3;
+  if (ix < 0 || jx < 0 || ix >= n_poses || jx >= n_poses || ix >= B) {       // reference: undefined behaviour
+    c[0] = c[1] = c[2] = valid[size_t(e) * HW + k] = __int_as_float(0x7fc00000);
+    return;
+  }
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  float tij[3], qij[4], Y[3];
+  rel_se3(poses + 7 * ix, poses + 7 * jx, tij, qij);
+  const int i = k / wd, j = k - i * wd;
+  const float u = float(j), v = float(i);
+  const float d = disps[size_t(ix) * HW + k];
+  const float X[3] = {(u - cx) / fx, (v - cy) / fy, 1.0f};
+  act_so3(qij, X, Y);
+  Y[0] += d * tij[0]; Y[1] += d * tij[1]; Y[2] += d * tij[2];
+  float ou = u, ov = v;
+  if (Y[2] > 0.01f) { ou = fx * (Y[0] / Y[2]) + cx; ov = fy * (Y[1] / Y[2]) + cy; }
+  c[0] = ou; c[1] = ov; c[2] = 0.0f;
+  valid[size_t(e) * HW + k] = (Y[2] > 0.25f) ? 1.0f : 0.0f;
+}
+
+// DepthVideo.reproject (depth_video.py:150-158) = projective_ops.projective_transform without Jacobians
+// (projective_ops.py:96-125), fused with the motion features of FactorGraph.update (factor_graph.py:203-205):
+//   Gij = Gj * Gi^-1 on quaternions normalised first (lietorch's SO3 constructor does, so3.h:31-37), or the fixed stereo
+//   baseline when ii == jj (:105);  X1 = Gij * ((x-cx_i)/fx_i, (y-cy_i)/fy_i, 1, d);  Z <- 1 where Z < 0.5*MIN_DEPTH;
+//   coords = (fx_j X/Z + cx_j, fy_j Y/Z + cy_j);  valid = X1_z > MIN_DEPTH (= 0.2; X0_z = 1 always passes);
+//   motn = clamp(cat(coords - coords0, target - coords), -64, 64) laid out [N,4,ht,wd].
+// One thread per (edge, pixel); everything is read once and written once (HBM-bound: 4 B in, 12 B out per pixel, or
+// 12 B in, 28 B out with the motion features).
+__device__ __forceinline__ void unit_quat(const float* q, float* o) {
+  const float n = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  o[0] = q[0] / n; o[1] = q[1] / n; o[2] = q[2] / n; o[3] = q[3] / n;
+}
+
+__global__ void reproject_kernel(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                                 int intr_stride, const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int n_poses,
+                                 int B, int ht, int wd, float* __restrict__ coords, float* __restrict__ valid,
+                                 const float* __restrict__ target, float* __restrict__ motn) {
+  const int e = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int HW = ht * wd;
+  if (k >= HW) return;
+  const int ix = int(ii[e]), jx = int(jj[e]);
+  const size_t o = size_t(e) * HW + k;
+  if (ix < 0 || jx < 0 || ix >= n_poses || jx >= n_poses || ix >= B) {
+    const float nan = __int_as_float(0x7fc00000);
+    if (coords) { coords[2 * o] = nan; coords[2 * o + 1] = nan; }
+    if (valid) valid[o] = 0.0f;
+    if (motn) for (int c = 0; c < 4; c++) motn[(size_t(e) * 4 + c) * HW + k] = nan;
+    return;
+  }
+  const float* Ki = intr + size_t(ix) * intr_stride;
+  const float* Kj = intr + size_t(jx) * intr_stride;
+  float tij[3], qij[4];
+  if (ix == jx) {
+    tij[0] = -0.1f; tij[1] = 0.0f; tij[2] = 0.0f;
+    qij[0] = 0.0f; qij[1] = 0.0f; qij[2] = 0.0f; qij[3] = 1.0f;
+  } else {
+    float pi[7], pj[7];
+    for (int c = 0; c < 3; c++) { pi[c] = poses[7 * ix + c]; pj[c] = poses[7 * jx + c]; }
+    unit_quat(poses + 7 * ix + 3, pi + 3);
+    unit_quat(poses + 7 * jx + 3, pj + 3);
+    rel_se3(pi, pj, tij, qij);
+  }
+  const int i = k / wd, j = k - i * wd;
+  const float u = float(j), v = float(i);
+  const float d = disps[size_t(ix) * HW + k];
+  const float X[3] = {(u - Ki[2]) / Ki[0], (v - Ki[3]) / Ki[1], 1.0f};
+  float Y[3];
+  act_so3(qij, X, Y);
+  Y[0] += d * tij[0]; Y[1] += d * tij[1]; Y[2] += d * tij[2];
+  const float Z = (Y[2] < 0.1f) ? 1.0f : Y[2];
+  const float iz = 1.0f / Z;
+  const float x1 = Kj[0] * (Y[0] * iz) + Kj[2], y1 = Kj[1] * (Y[1] * iz) + Kj[3];
+  if (coords) { coords[2 * o] = x1; coords[2 * o + 1] = y1; }
+  if (valid) valid[o] = (Y[2] > 0.2f) ? 1.0f : 0.0f;
+  if (motn) {
+    const float tx = target[2 * o], ty = target[2 * o + 1];
+    float* m = motn + size_t(e) * 4 * HW + k;
+    m[0] = fminf(fmaxf(x1 - u, -64.0f), 64.0f);
+    m[HW] = fminf(fmaxf(y1 - v, -64.0f), 64.0f);
+    m[2 * size_t(HW)] = fminf(fmaxf(tx - x1, -64.0f), 64.0f);
+    m[3 * size_t(HW)] = fminf(fmaxf(ty - y1, -64.0f), 64.0f);
+  }
+}
+
 }  // namespace db200
 
 using namespace db200;
@@ -194,6 +289,35 @@ extern "C" int db200_depth_filter(const float* poses, const float* disps, const 
   dim3 grid(cdiv(ht * wd, 256), n_inds);
   depth_filter_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(poses, disps, intrinsics, inds, thresh, num, ht, wd,
                                                                           counter);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+extern "C" int db200_projmap(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                             const int64_t* jj, int num, int n_poses, int B, int ht, int wd, float* coords, float* valid,
+                             db200_stream_t stream) {
+  if (!poses || !disps || !intrinsics || !coords || !valid || num < 0 || ht <= 0 || wd <= 0 || n_poses <= 0 || B <= 0)
+    return DB200_ERR_ARG;
+  if (num == 0) return DB200_OK;
+  if (!ii || !jj) return DB200_ERR_ARG;
+  dim3 grid(cdiv(ht * wd, 256), num);
+  projmap_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(poses, disps, intrinsics, ii, jj, n_poses, B, ht, wd, coords,
+                                                                      valid);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+extern "C" int db200_reproject(const float* poses, const float* disps, const float* intrinsics, int per_frame_intrinsics,
+                               const int64_t* ii, const int64_t* jj, int N, int n_poses, int B, int ht, int wd, float* coords,
+                               float* valid, const float* target, float* motn, db200_stream_t stream) {
+  if (!poses || !disps || !intrinsics || N < 0 || ht <= 0 || wd <= 0 || n_poses <= 0 || B <= 0 || (motn && !target) ||
+      (!coords && !valid && !motn))
+    return DB200_ERR_ARG;
+  if (N == 0) return DB200_OK;
+  if (!ii || !jj) return DB200_ERR_ARG;
+  dim3 grid(cdiv(ht * wd, 256), N);
+  reproject_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(poses, disps, intrinsics, per_frame_intrinsics ? 4 : 0, ii,
+                                                                        jj, n_poses, B, ht, wd, coords, valid, target, motn);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

@@ -32,6 +32,13 @@ _SIGNATURES = {
     "db200_altcorr_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_altcorr_backward": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_frame_distance": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),
+    "db200_proximity_workspace_bytes": (_sz, [_i, _i, _i]),
+    "db200_proximity_max_edges": (_i, [_i, _i, _i, _i, _i]),
+    "db200_proximity_edges": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, C.c_double, _i, _i, _vp, _vp, _i, _vp, _i,
+                                   _vp, _vp, _sz, _vp]),
+    "db200_filter_repeated_edges": (_i, [_vp, _vp, _i, _vp, _vp, _i, _vp, _vp]),
+    "db200_projmap": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "db200_reproject": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "db200_iproj": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "db200_depth_filter": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "db200_ba_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i, _i, _i]),

@@ -149,8 +149,15 @@ def depth_filter(poses, disps, intrinsics, ix, thresh):
 
 
 def projmap(poses, disps, intrinsics, ii, jj):
-    """droid.cpp:139-154.  No caller exists in the reference; not part of the hot path."""
-    raise NotImplementedError("projmap has no caller in the reference and is out of scope (SURVEY.md §8)")
+    """droid.cpp:139-154 -> [coords[num,ht,wd,3], valid[num,ht,wd,1]] (no caller in the reference; kept for the surface)."""
+    _chk(("poses", poses), ("disps", disps), ("intrinsics", intrinsics), ("ii", ii), ("jj", jj))
+    num = ii.shape[0]
+    B, ht, wd = disps.shape
+    coords = torch.empty((num, ht, wd, 3), dtype=torch.float32, device=disps.device)
+    valid = torch.empty((num, ht, wd, 1), dtype=torch.float32, device=disps.device)
+    _capi.check(_capi.lib().db200_projmap(_ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ii), _ptr(jj), num, poses.shape[0], B,
+                                          ht, wd, _ptr(coords), _ptr(valid), _stream()), "projmap")
+    return [coords, valid]
 
 
 # ------------------------------------------------------------------------------------------------ bundle adjustment

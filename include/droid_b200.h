@@ -92,6 +92,43 @@ int db200_frame_distance(const float* poses, const float* disps, const float* in
                          const int64_t* jj, int K, int n_poses, int B, int ht, int wd, float beta, float* dist,
                          db200_stream_t stream);
 
+/* ---- factor-graph edge selection (droid_slam/factor_graph.py:315-379 `add_proximity_factors`, :44-55
+ * `__filter_repeated_edges`) ---------------------------------------------------------------
+ * db200_proximity_edges writes the reference's `es` list, in its order, to es_out[n][2] (int64, device) and the
+ * count to *n_out (device int): first the neighbourhood edges ((i,i) when `stereo`, then (i,j),(j,i) for
+ * j in [max(i-rad-1,0), i), i = t0..t-1), then the greedy distance-ordered picks with (2*nms+1)^2 suppression, both
+ * directions per pick, stopping once more than `max_factors` entries exist.  `t` = video.counter.value;
+ * (ii_old, jj_old) = cat(ii, ii_bad, ii_inac) / cat(jj, ...) of the graph.  Distances are the mean of both
+ * directions of frame_distance with `beta` over meshgrid(arange(t0,t), arange(t1,t)) (depth_video.py:171-181).
+ * Ties in distance (unspecified order in torch.argsort) resolve to the lower flat pair index; NaN distances
+ * (non-finite poses) are never picked.  es_capacity >= db200_proximity_max_edges(...). */
+size_t db200_proximity_workspace_bytes(int t0, int t1, int t);
+int db200_proximity_max_edges(int t0, int t, int rad, int stereo, int max_factors);
+int db200_proximity_edges(const float* poses, const float* disps, const float* intrinsics, int B, int ht, int wd,
+                          int t0, int t1, int t, int rad, int nms, float beta, double thresh, int max_factors,
+                          int stereo, const int64_t* ii_old, const int64_t* jj_old, int n_old, int64_t* es_out,
+                          int es_capacity, int* n_out, void* workspace, size_t workspace_bytes,
+                          db200_stream_t stream);
+/* keep[k] = 1 iff (ii_new[k], jj_new[k]) is not among the old edges (factor_graph.py:44-55; duplicates inside the
+ * new list are kept, as there). */
+int db200_filter_repeated_edges(const int64_t* ii_new, const int64_t* jj_new, int n_new, const int64_t* ii_old,
+                                const int64_t* jj_old, int n_old, unsigned char* keep, db200_stream_t stream);
+
+/* ---- projmap (droid.cpp:139-154, droid_kernels.cu:427-516,1463-1490): coords[num,ht,wd,3] (channel 2 = 0),
+ * valid[num,ht,wd,1] ------------------------------------------------------------------------ */
+int db200_projmap(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                  const int64_t* jj, int num, int n_poses, int B, int ht, int wd, float* coords, float* valid,
+                  db200_stream_t stream);
+
+/* ---- reprojection + motion features: DepthVideo.reproject (depth_video.py:150-158 ->
+ * geom/projective_ops.py:96-125 without Jacobians) fused with FactorGraph.update's `motn` (factor_graph.py:203-205).
+ * intrinsics: [4] shared, or [B,4] per frame when per_frame_intrinsics != 0 (ii's for the back-projection, jj's
+ * for the projection).  Outputs (each may be NULL): coords[N,ht,wd,2], valid[N,ht,wd,1],
+ * motn[N,4,ht,wd] = clamp(cat(coords - grid, target - coords), -64, 64) with target[N,ht,wd,2]. */
+int db200_reproject(const float* poses, const float* disps, const float* intrinsics, int per_frame_intrinsics,
+                    const int64_t* ii, const int64_t* jj, int N, int n_poses, int B, int ht, int wd, float* coords,
+                    float* valid, const float* target, float* motn, db200_stream_t stream);
+
 /* ---- iproj / depth_filter (droid.cpp:157-167,220-234, droid_kernels.cu:661-850) ------------- */
 int db200_iproj(const float* poses, const float* disps, const float* intrinsics, int num, int ht, int wd,
                 float* points, db200_stream_t stream);

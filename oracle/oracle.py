@@ -198,3 +198,76 @@ def ref_eigen_solve(A, b, lm, ep):
     x = np.zeros_like(b)
     st = _REF.ref_eigen_llt_solve(_p(A), _p(b), C.c_int(len(b)), C.c_float(lm), C.c_float(ep), _p(x))
     return x, st
+
+
+# ---- projmap / reproject: elementwise fp32 restatements in numpy (test infrastructure only) ---------------------------
+def _rel_pose_f32(pi, pj):
+    """relSE3 (droid_kernels.cu:97-107): q_ij = q_j (x) conj(q_i), t_ij = t_j - R(q_ij) t_i; quaternion (x,y,z,w)."""
+    f = np.float32
+    ti, qi, tj, qj = pi[:3].astype(f), pi[3:].astype(f), pj[:3].astype(f), pj[3:].astype(f)
+    q = np.array([-qj[3] * qi[0] + qj[0] * qi[3] - qj[1] * qi[2] + qj[2] * qi[1],
+                  -qj[3] * qi[1] + qj[1] * qi[3] - qj[2] * qi[0] + qj[0] * qi[2],
+                  -qj[3] * qi[2] + qj[2] * qi[3] - qj[0] * qi[1] + qj[1] * qi[0],
+                  qj[3] * qi[3] + qj[0] * qi[0] + qj[1] * qi[1] + qj[2] * qi[2]], f)
+    return (tj - _rot_f32(q, ti)).astype(f), q
+
+
+def _rot_f32(q, X):
+    """actSO3 (droid_kernels.cu:58-68) on X[...,3]."""
+    f = np.float32
+    qv = q[:3].astype(f)
+    uv = f(2.0) * np.cross(np.broadcast_to(qv, X.shape), X).astype(f)
+    return (X + q[3] * uv + np.cross(np.broadcast_to(qv, X.shape), uv)).astype(f)
+
+
+def projmap(poses, disps, intrinsics, ii, jj):
+    """projmap_kernel (droid_kernels.cu:427-516): coords[num,ht,wd,3] (channel 2 zero), valid[num,ht,wd,1]."""
+    f = np.float32
+    poses, disps = np.asarray(poses, f), np.asarray(disps, f)
+    fx, fy, cx, cy = [f(v) for v in intrinsics]
+    _, ht, wd = disps.shape
+    v, u = np.meshgrid(np.arange(ht, dtype=f), np.arange(wd, dtype=f), indexing="ij")
+    coords = np.zeros((len(ii), ht, wd, 3), f); valid = np.zeros((len(ii), ht, wd, 1), f)
+    for e, (i, j) in enumerate(zip(ii, jj)):
+        t, q = _rel_pose_f32(poses[i], poses[j])
+        X = np.stack([(u - cx) / fx, (v - cy) / fy, np.ones_like(u)], -1).astype(f)
+        Y = _rot_f32(q, X) + disps[i][..., None] * t
+        ok = Y[..., 2] > f(0.01)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            coords[e, ..., 0] = np.where(ok, fx * (Y[..., 0] / Y[..., 2]) + cx, u)
+            coords[e, ..., 1] = np.where(ok, fy * (Y[..., 1] / Y[..., 2]) + cy, v)
+        valid[e, ..., 0] = (Y[..., 2] > f(0.25)).astype(f)
+    return coords, valid
+
+
+def reproject(poses, disps, intrinsics, ii, jj, target=None):
+    """projective_transform without Jacobians (geom/projective_ops.py:96-125, via depth_video.py:150-158) and the
+    motion features of factor_graph.py:203-205.  intrinsics [4] or [B,4].  Returns coords[N,ht,wd,2],
+    valid[N,ht,wd,1] (and motn[N,4,ht,wd] when target[N,ht,wd,2] is given)."""
+    f = np.float32
+    poses, disps = np.asarray(poses, f), np.asarray(disps, f)
+    K = np.asarray(intrinsics, f)
+    _, ht, wd = disps.shape
+    v, u = np.meshgrid(np.arange(ht, dtype=f), np.arange(wd, dtype=f), indexing="ij")
+    N = len(ii)
+    coords = np.zeros((N, ht, wd, 2), f); valid = np.zeros((N, ht, wd, 1), f)
+    for e, (i, j) in enumerate(zip(ii, jj)):
+        Ki, Kj = (K, K) if K.ndim == 1 else (K[i], K[j])
+        if i == j:
+            t, q = np.array([-0.1, 0, 0], f), np.array([0, 0, 0, 1], f)
+        else:
+            pi, pj = poses[i].copy(), poses[j].copy()
+            pi[3:] /= np.sqrt((pi[3:] ** 2).sum(dtype=f)); pj[3:] /= np.sqrt((pj[3:] ** 2).sum(dtype=f))
+            t, q = _rel_pose_f32(pi, pj)
+        X = np.stack([(u - Ki[2]) / Ki[0], (v - Ki[3]) / Ki[1], np.ones_like(u)], -1).astype(f)
+        Y = _rot_f32(q, X) + disps[i][..., None] * t
+        Z = np.where(Y[..., 2] < f(0.1), f(1.0), Y[..., 2])
+        d = f(1.0) / Z
+        coords[e, ..., 0] = Kj[0] * (Y[..., 0] * d) + Kj[2]
+        coords[e, ..., 1] = Kj[1] * (Y[..., 1] * d) + Kj[3]
+        valid[e, ..., 0] = (Y[..., 2] > f(0.2)).astype(f)
+    if target is None:
+        return coords, valid
+    grid = np.stack([u, v], -1)
+    motn = np.concatenate([coords - grid, np.asarray(target, f) - coords], -1).transpose(0, 3, 1, 2)
+    return coords, valid, np.clip(motn, -64.0, 64.0).astype(f)

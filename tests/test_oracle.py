@@ -194,3 +194,63 @@ def test_droid_backends_surface_and_no_cpu_fallback():
         droid_backends.corr_index_forward(torch.zeros(1, 2, 2, 2, 2), torch.zeros(1, 2, 2, 2), 3)
     with pytest.raises(RuntimeError):                                     # CHECK_CONTIGUOUS (droid.cpp:84-85)
         droid_backends.corr_index_forward(torch.zeros(1, 2, 2, 2, 4)[..., ::2], torch.zeros(1, 2, 2, 2), 3)
+
+
+# ------------------------------------------------------------------------------------------ edge selection (§8f-2)
+def test_proximity_edges_oracle_hand_worked_case():
+    """6 frames, rad=1, nms=1: 18 neighbourhood edges, then picks (5,0), (4,1), (3,0), (5,2) — (4,0), (5,1) fall to the
+    suppression of earlier picks (factor_graph.py:355-378 worked by hand)."""
+    from oracle import graph_edges as g
+    t = 6
+    ii, jj = np.meshgrid(np.arange(t), np.arange(t), indexing="ij")
+    ii, jj = ii.reshape(-1), jj.reshape(-1)
+    d = np.full(t * t, 5.0, np.float32); d[5 * 6 + 0] = 1.0; d[4 * 6 + 1] = 2.0
+    es = g.add_proximity_factors_edges(ii, jj, d, 0, 0, t, 1, 1, 16.0, 100, False, [], [])
+    nb = [(1, 0), (0, 1), (2, 0), (0, 2), (2, 1), (1, 2), (3, 1), (1, 3), (3, 2), (2, 3), (4, 2), (2, 4), (4, 3), (3, 4),
+          (5, 3), (3, 5), (5, 4), (4, 5)]
+    assert es == nb + [(5, 0), (0, 5), (4, 1), (1, 4), (3, 0), (0, 3), (5, 2), (2, 5)]
+    # max_factors: the check precedes each pick (len(es) > max_factors): 18 <= 19 lets one pick in, 20 > 19 stops
+    es = g.add_proximity_factors_edges(ii, jj, d, 0, 0, t, 1, 1, 16.0, 19, False, [], [])
+    assert es == nb + [(5, 0), (0, 5)]
+    es = g.add_proximity_factors_edges(ii, jj, d, 0, 0, t, 1, 1, 16.0, 17, False, [], [])
+    assert es == nb
+    # threshold and existing edges: (5,0) too far; an existing (4,1) suppresses itself, (3,1), (5,1), (4,0), (4,2)
+    d2 = d.copy(); d2[5 * 6 + 0] = 17.0
+    es = g.add_proximity_factors_edges(ii, jj, d2, 0, 0, t, 1, 1, 16.0, 100, False, [4], [1])
+    assert es == nb + [(3, 0), (0, 3), (5, 2), (2, 5)]
+    # stereo: (i,i) first for every frame
+    es = g.add_proximity_factors_edges(ii, jj, d, 0, 0, t, 1, 1, 0.5, 100, True, [], [])
+    assert es[:3] == [(0, 0), (1, 1), (1, 0)] and len(es) == 18 + 6
+
+
+def test_filter_repeated_and_neighborhood_edges_oracle():
+    from oracle import graph_edges as g
+    ii, jj = g.add_neighborhood_factors_edges(0, 8, 3)
+    assert len(ii) == 36 and np.all(np.abs(ii - jj) <= 3) and np.all(ii != jj)        # BASELINE config 1: 36 edges
+    ii, jj = g.add_neighborhood_factors_edges(0, 8, 3, stereo=True)
+    assert len(ii) == 22                                                               # SURVEY §8: stereo variant
+    a, b = g.filter_repeated_edges([1, 2, 2, 3], [0, 1, 1, 5], [2, 9], [1, 9])
+    assert a.tolist() == [1, 3] and b.tolist() == [0, 5]
+
+
+def test_reproject_oracle_matches_reference_projective_transform():
+    """oracle.reproject (fp32) vs the reference's own projective_ops.projective_transform run in fp64 under the
+    lietorch shim (tests/golden/make_pyref_reproject_golden.py): stereo edges, near points, a non-unit quaternion."""
+    import importlib.util
+    from oracle import oracle
+    spec = importlib.util.spec_from_file_location("mk", os.path.join(REPO, "tests", "golden", "make_pyref_reproject_golden.py"))
+    g = np.load(os.path.join(REPO, "tests", "golden", "pyref_reproject.npz"))
+    src = open(spec.origin).read()
+    ns = {}
+    exec(src[src.index("def problem():"):src.index("def main():")], {"np": np}, ns)      # the seeded problem only
+    p = ns["problem"]()
+    coords, valid = oracle.reproject(p.poses, p.disps, p.intrinsics, p.ii, p.jj)
+    assert 0.5 < g["valid"].mean() < 1.0                                                  # the case has invalid points
+    far = np.abs(g["coords"]).max(-1) > 1e4                                               # |Z| ~ 0: ill-conditioned pixels
+    np.testing.assert_allclose(coords[~far], g["coords"][~far], rtol=1e-4, atol=2e-3)
+    assert (valid != g["valid"]).mean() < 1e-3                                            # depth exactly at the 0.2 threshold
+    K = np.tile(p.intrinsics, (p.poses.shape[0], 1)); K[3] *= 1.25
+    c2, _, motn = oracle.reproject(p.poses, p.disps, K, p.ii, p.jj, target=g["coords"])
+    sel = p.ii != 3
+    np.testing.assert_array_equal(c2[sel & (p.jj != 3)], coords[sel & (p.jj != 3)])
+    assert motn.shape == (len(p.ii), 4, 24, 32) and np.abs(motn).max() <= 64.0

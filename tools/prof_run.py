@@ -1,0 +1,41 @@
+"""One pass over the hot kernels at benchmark sizes, for `ncu` (profiles/README.md gives the command lines).
+c3 global-backend BA (one call, 2 iterations), the fused 4-level lookup (96 edges) and the CorrBlock build (48 edges)."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(REPO, "droid-slam_reserch_b200"))
+sys.path.insert(0, REPO)
+import droid_backends  # noqa: E402
+from droid_b200 import synth  # noqa: E402
+
+dev = torch.device("cuda", 0)
+what = sys.argv[1:] or ["ba", "lookup", "volume"]
+if "ba" in what:
+    p = synth.config_c3()
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    args = [t(p.poses), t(p.disps), t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)]
+    droid_backends.ba(*args, p.t0, p.t1, 2, 1e-5, 1e-2, False)
+    torch.cuda.synchronize()
+if "lookup" in what:
+    N, ht, wd = 96, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(7)
+    levels = [torch.randn((N, ht, wd, ht >> l, wd >> l), device=dev, dtype=torch.float16, generator=g) for l in range(4)]
+    yy, xx = torch.meshgrid(torch.arange(ht, device=dev, dtype=torch.float32), torch.arange(wd, device=dev, dtype=torch.float32), indexing="ij")
+    coords = (torch.stack([xx, yy], 0)[None].repeat(N, 1, 1, 1) + 6.0 * torch.randn((N, 2, ht, wd), device=dev, generator=g)).contiguous()
+    for _ in range(2):
+        droid_backends.corr_pyramid_lookup(levels, coords, 3)
+    torch.cuda.synchronize()
+    del levels
+if "volume" in what:
+    N, C_, ht, wd = 48, 128, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(11)
+    f1 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    f2 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    for _ in range(2):
+        droid_backends.corr_volume_pyramid(f1, f2, 4)
+    torch.cuda.synchronize()
+print("prof_run ok", what)
