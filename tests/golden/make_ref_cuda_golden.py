@@ -72,7 +72,38 @@ def moba_case():
     return synth.make_ba_problem(ii, jj, n_kf + n_new, seed=9, t0=n_kf, t1=n_kf + n_new)
 
 
+def extra_problem():
+    """Problem of make_pyref_reproject_golden.py (stereo edges dropped: projmap has no stereo case)."""
+    src = open(os.path.join(HERE, "make_pyref_reproject_golden.py")).read()
+    ns = {}
+    exec(src[src.index("def problem():"):src.index("def main():")], {"np": np}, ns)
+    return ns["problem"]()
+
+
+def main_extra():
+    """Second fixture (ref_cuda_golden2.npz): the entry points the first one did not cover — projmap, iproj,
+    depth_filter — on the reprojection problem.      gpurun -- python tests/golden/make_ref_cuda_golden.py extra"""
+    ref = load_ref()
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    p = extra_problem()
+    sel = p.ii != p.jj
+    out = {}
+    coords, valid = ref.projmap(t(p.poses), t(p.disps), t(p.intrinsics), t(p.ii[sel]), t(p.jj[sel]))
+    out["projmap_coords"], out["projmap_valid"] = coords.cpu().numpy(), valid.cpu().numpy()
+    n = p.poses.shape[0]
+    out["iproj"] = ref.iproj(t(p.poses), t(p.disps), t(p.intrinsics)).cpu().numpy()
+    inds = np.arange(n, dtype=np.int64)
+    thresh = np.full(n, 0.05, np.float32)
+    out["depth_filter"] = ref.depth_filter(t(p.poses), t(p.disps), t(p.intrinsics), t(inds), t(thresh)).cpu().numpy()
+    path = os.path.join(REPO, "gpurun_out", "ref_cuda_golden2.npz")
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes;", {k: v.shape for k, v in out.items()})
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "extra":
+        return main_extra()
     ref = load_ref()
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
     out = {}

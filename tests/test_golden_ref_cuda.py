@@ -156,3 +156,42 @@ def test_kernel_lookup_backward_and_altcorr_vs_reference_cuda():
     assert np.abs(o.cpu().numpy() - Z["altcorr_fwd"]).max() <= 1e-4 * np.abs(Z["altcorr_fwd"]).max()
     g1, g2, gc = droid_backends.altcorr_backward(_t(f1), _t(f2), _t(co), _t(g), 3)
     assert rel(g1.cpu().numpy(), Z["altcorr_bwd_f1"]) <= 1e-4 and rel(g2.cpu().numpy(), Z["altcorr_bwd_f2"]) <= 1e-4
+
+
+# ---------------------------------------------------------------- second fixture: projmap, iproj, depth_filter
+Z2 = np.load(os.path.join(HERE, "golden", "ref_cuda_golden2.npz"))
+
+
+def _extra():
+    import make_ref_cuda_golden as G
+    p = G.extra_problem()
+    sel = p.ii != p.jj
+    return p, p.ii[sel], p.jj[sel]
+
+
+def test_oracle_projmap_iproj_depth_filter_vs_reference_cuda():
+    from oracle import oracle
+    p, ii, jj = _extra()
+    c, v = oracle.projmap(p.poses, p.disps, p.intrinsics, ii, jj)
+    np.testing.assert_allclose(c, Z2["projmap_coords"], rtol=1e-4, atol=1e-2)      # coordinates reach ~1e3 px near Z = 0.01
+    np.testing.assert_array_equal(v, Z2["projmap_valid"])
+    np.testing.assert_allclose(oracle.iproj(p.poses, p.disps, p.intrinsics), Z2["iproj"], rtol=1e-4, atol=1e-5)
+    n = p.poses.shape[0]
+    df = oracle.depth_filter(p.poses, p.disps, p.intrinsics, np.arange(n), np.full(n, 0.05, np.float32))
+    np.testing.assert_array_equal(df, Z2["depth_filter"])                           # integer counts
+
+
+@pytest.mark.gpu
+def test_kernel_projmap_iproj_depth_filter_vs_reference_cuda():
+    import droid_backends
+    p, ii, jj = _extra()
+    c, v = droid_backends.projmap(_t(p.poses), _t(p.disps), _t(p.intrinsics), _t(ii), _t(jj))
+    np.testing.assert_allclose(c.cpu().numpy(), Z2["projmap_coords"], rtol=1e-4, atol=1e-2)
+    np.testing.assert_array_equal(v.cpu().numpy(), Z2["projmap_valid"])
+    pts = droid_backends.iproj(_t(p.poses), _t(p.disps), _t(p.intrinsics))
+    np.testing.assert_allclose(pts.cpu().numpy(), Z2["iproj"], rtol=1e-4, atol=1e-5)
+    n = p.poses.shape[0]
+    import torch
+    df = droid_backends.depth_filter(_t(p.poses), _t(p.disps), _t(p.intrinsics), torch.arange(n).cuda(),
+                                     torch.full((n,), 0.05).cuda())
+    np.testing.assert_array_equal(df.cpu().numpy(), Z2["depth_filter"])
