@@ -164,6 +164,36 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
                               algorithmic_bytes_per_launch=lookups * 912))
 
 
+def graph_bench(p, dev, steps=5):
+    """Secondary metrics on the c3 keyframe buffer: `frame_distance` over all 512^2 ordered pairs (one direction;
+    DepthVideo.distance calls it twice) and the whole GPU edge selection of add_proximity_factors (both directions of
+    frame_distance + masking + NMS + sort + greedy pick, factor_graph.py:315-379)."""
+    import torch
+    import droid_backends
+    from droid_b200 import graph
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    poses, disps, intr = t(p.poses), t(p.disps), t(p.intrinsics)
+    n = p.t1
+    ii, jj = torch.meshgrid(torch.arange(n), torch.arange(n), indexing="ij")
+    ii, jj = ii.reshape(-1).to(dev), jj.reshape(-1).to(dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    droid_backends.frame_distance(poses, disps, intr, ii, jj, 0.25)
+    graph.proximity_edges(poses, disps, intr, n, 0, 0, 2, 2, 0.25, 16.0, 16 * n, False)
+    torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(steps):
+        droid_backends.frame_distance(poses, disps, intr, ii, jj, 0.25)
+    ev[1].record()
+    for _ in range(steps):
+        gi, _ = graph.proximity_edges(poses, disps, intr, n, 0, 0, 2, 2, 0.25, 16.0, 16 * n, False)
+    ev[2].record()
+    torch.cuda.synchronize()
+    fd_ms, px_ms = ev[0].elapsed_time(ev[1]) / steps, ev[1].elapsed_time(ev[2]) / steps
+    return dict(frame_distance=dict(pairs=int(ii.numel()), ms_per_call=fd_ms, value=ii.numel() / (fd_ms * 1e-3), unit="pairs/s"),
+                proximity_edges=dict(keyframes=int(n), ms_per_call=px_ms, edges_selected=int(gi.numel()),
+                                     what="add_proximity_factors edge list on the GPU (rad=2, nms=2, beta=0.25, thresh=16)"))
+
+
 def reference_cuda_leg(p, dev, steps=3):
     """Extra reported baseline (north_star: "the reference CUDA extension is also reported where it builds for
     sm_100"): the UNMODIFIED reference extension, built by baseline/build_ref_cuda.sh as `droid_backends_ref`, on the
@@ -371,6 +401,15 @@ def main_gpu(args, rank, world):
                     whole_iteration=dict(algorithmic_bytes=iter_bytes, ms=iter_ms,
                                          achieved=iter_bytes / (iter_ms * 1e-3) / 1e9,
                                          frac=iter_bytes / (iter_ms * 1e-3) / 1e9 / hbm_peak))
+    # the solve is FP64-pipe / latency bound, not HBM bound: reported against the measured DFMA issue rate of this part
+    # (1.33 warp-instructions/clk/SM x 148 SMs x 1.965 GHz x 64 flop = 24.8 TFLOP/s)
+    sol_ms = stage["solve"]["ms_per_iter"]
+    n_sys = 6 * P
+    sol_flops = n_sys ** 3 / 3.0 + 2.0 * n_sys ** 2
+    roofline["solver"] = dict(kernel="chol_solve_kernel (cooperative tiled fp64 Cholesky + both substitutions)", bound="fp64 pipe / panel-chain latency",
+                              gflops=(sol_flops / (sol_ms * 1e-3) / 1e9) if sol_ms else None, peak_gflops=24800.0,
+                              frac=(sol_flops / (sol_ms * 1e-3) / 1e9 / 24800.0) if sol_ms else None, ms_per_launch=sol_ms,
+                              share_of_iteration=(sol_ms / iter_ms) if sol_ms else None)
     traffic_file = os.path.join(REPO, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
@@ -391,9 +430,14 @@ def main_gpu(args, rank, world):
     if world == 1:
         line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
         line["corr_volume"] = volume_bench(dev, 10, 3, hbm_peak)
+        line["graph"] = graph_bench(p, dev)
         try:
             tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
             line["lookup"]["roofline"]["traffic"] = tr
+            # what the kernel actually moves (ncu dram bytes) over the live launch time: the 16-byte window rows cost
+            # whole 64-byte DRAM bursts, so the DRAM interface is far busier than the algorithmic figure says
+            line["lookup"]["roofline"]["dram_gbs_actual_traffic"] = tr / (line["lookup"]["ms_per_launch"] * 1e-3) / 1e9
+            line["lookup"]["roofline"]["dram_frac_actual_traffic"] = line["lookup"]["roofline"]["dram_gbs_actual_traffic"] / hbm_peak
         except Exception:
             pass
         if not args.no_cpu:
