@@ -121,6 +121,9 @@ def run_cpu(steps, warmup):
 def main_reference(args, rank):
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is the CPU path "with all the host threads it
+    # can use", and only rank 0 runs it — restore the full core count before the OpenMP runtime of the oracle starts
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     steps, warmup = min(args.steps, 3), min(args.warmup, 1)
     r = run_cpu(steps, warmup)
     line = dict(impl="reference", metric=METRIC, value=r["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warmup,
