@@ -16,6 +16,7 @@
 // overlap without an in-kernel pipeline.  The op is output-write bound (25 MB written per edge, 2.4 GFLOP).
 // Every mbarrier wait is bounded: a broken descriptor raises DB200_ERR_CUDA through the status word instead of hanging.
 #include <cuda.h>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace db200 {
@@ -192,6 +193,178 @@ corr_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTN) : "memory");
 }
 
+// ---- persistent, warp-specialised pipeline ---------------------------------------------------------------------
+// One CTA per SM walks the tiles (n-tile fastest, so consecutive tiles share the A operand in L2):
+//   warp 0 (one lane) : TMA producer — two shared-memory stages of [A 128x128 | B 128x128] halfs (64 KB each);
+//   warp 1 (one lane) : issues the 16 tcgen05.mma of a tile into one of TWO 128-column TMEM accumulators, commits the
+//                       stage back to the producer and the accumulator to the epilogue;
+//   warps 2..5        : epilogue — tcgen05.ld of their TMEM lane quarter, x 1/16, f16, row segments to HBM, then hand
+//                       the accumulator back.  The stores of tile k overlap the MMAs of tile k+1 and the loads of k+2.
+// mbarrier phases: stage s = k & 1 is in its (k >> 1)-th use; "empty"-type barriers are waited with the inverted
+// parity so that the first use passes.  Every wait is bounded (status word instead of a hang).
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+constexpr int kPipeThreadsTC = 192;
+// two operand stages (64 KB each) + two output staging tiles (32 KB each) + alignment slack
+constexpr size_t kPipeSmemTC = 2 * (2 * (kTM + kTN) * kTK * 2) + 2 * (kTM * kTN * 2) + 1024;
+
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }   // the four epilogue warps
+
+// TMA_STORE: the f16 tile is staged in shared memory in the 128-byte-swizzled box layout (bank-conflict free for
+// thread = row) and leaves as two asynchronous bulk tensor stores (full lines, clipped per edge by the 3-D tensor map);
+// otherwise every thread writes its row segments directly (any N2).
+template <bool TMA_STORE>
+__global__ void __launch_bounds__(kPipeThreadsTC, 1)
+corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmO, __half* __restrict__ out, int M, int N2, int E,
+                         int* __restrict__ err) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[8];          // full[2], empty[2], tfull[2], tempty[2]
+  __shared__ uint32_t tmem_base_s;
+  constexpr uint32_t kStageBytes = 2u * (kTM + kTN) * kTK * 2u;        // 64 KB
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int MT = (M + kTM - 1) / kTM, NT = (N2 + kTN - 1) / kTN;
+  const long long tiles = static_cast<long long>(E) * MT * NT;
+  auto bar = [&](int i) { return smem_u32(&bars[i]); };
+
+  if (tid == 0) {
+    for (int i = 0; i < 6; i++) mbar_init(bar(i), 1);
+    mbar_init(bar(6), 4); mbar_init(bar(7), 4);                        // four epilogue warps release an accumulator
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * kTN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int k = 0;
+      for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+        const int s = k & 1, use = k >> 1;
+        const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
+        if (!mbar_wait(bar(2 + s), (use & 1) ^ 1)) { atomicExch(err, 1); break; }
+        const uint32_t sA = s0 + s * kStageBytes, sB = sA + 2 * kTM * kTK * 2;
+        mbar_expect_tx(bar(s), kStageBytes);
+        tma_load_2d(sA, &tmA, 0, e * M + mt * kTM, bar(s));
+        tma_load_2d(sA + kTM * kTK * 2, &tmA, kTK, e * M + mt * kTM, bar(s));
+        tma_load_2d(sB, &tmB, 0, e * N2 + nt * kTN, bar(s));
+        tma_load_2d(sB + kTN * kTK * 2, &tmB, kTK, e * N2 + nt * kTN, bar(s));
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int k = 0;
+      for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+        const int s = k & 1, use = k >> 1;
+        if (!mbar_wait(bar(6 + s), (use & 1) ^ 1)) { atomicExch(err, 1); break; }     // accumulator s drained
+        if (!mbar_wait(bar(s), use & 1)) { atomicExch(err, 1); break; }               // operands landed
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t sA = s0 + s * kStageBytes, sB = sA + 2 * kTM * kTK * 2;
+#pragma unroll
+        for (int kb = 0; kb < 2; kb++)
+#pragma unroll
+          for (int kk = 0; kk < kTK / 16; kk++) {
+            const uint64_t ad = umma_desc_sw128(sA + kb * kTM * kTK * 2 + kk * 32);
+            const uint64_t bd = umma_desc_sw128(sB + kb * kTN * kTK * 2 + kk * 32);
+            umma_f16(tmem_base + uint32_t(s * kTN), ad, bd, kIdescF16, (kb | kk) != 0 ? 1u : 0u);
+          }
+        umma_commit(bar(2 + s));                                       // stage free once these MMAs have read it
+        umma_commit(bar(4 + s));                                       // accumulator ready for the epilogue
+      }
+    }
+  } else {
+    const int quarter = warp & 3;                                      // TMEM lane quarter this warp may read
+    const bool vec = (N2 % 8 == 0);
+    int k = 0;
+    for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+      const int s = k & 1, use = k >> 1;
+      const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
+      const bool ok = mbar_wait(bar(4 + s), use & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (!ok) { if (lane == 0) atomicExch(err, 1); break; }
+      const int n0 = nt * kTN, row = mt * kTM + 32 * quarter + lane;
+      if constexpr (TMA_STORE) {
+        const int trow = 32 * quarter + lane;                          // row inside the tile
+        const uint32_t stg = s0 + 2 * kStageBytes + uint32_t(s) * (kTM * kTN * 2);
+        if (tid == 64) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read this buffer
+        epi_bar();
+#pragma unroll 1
+        for (int cb = 0; cb < kTN; cb += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + (uint32_t(32 * quarter) << 16) + uint32_t(s * kTN + cb), v);
+          const uint32_t box = stg + uint32_t(cb >> 6) * (kTM * 128) + uint32_t(trow) * 128;
+          const int ch0 = (cb & 63) >> 3;
+#pragma unroll
+          for (int c4 = 0; c4 < 4; c4++) {
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+              const __half2 h = __floats2half2_rn(__uint_as_float(v[8 * c4 + 2 * i]) * 0.0625f, __uint_as_float(v[8 * c4 + 2 * i + 1]) * 0.0625f);
+              w[i] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            const uint32_t a = box + uint32_t(((ch0 + c4) ^ (trow & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(6 + s));                        // accumulator drained: the next MMAs may start
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the TMA
+        epi_bar();
+        if (tid == 64) {
+          tma_store_3d(&tmO, stg, n0, mt * kTM, e);
+          if (n0 + 64 < N2) tma_store_3d(&tmO, stg + kTM * 128, n0 + 64, mt * kTM, e);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        continue;
+      }
+      __half* orow = out + (size_t(e) * M + (row < M ? row : 0)) * N2 + n0;
+#pragma unroll 1
+      for (int cb = 0; cb < kTN; cb += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + (uint32_t(32 * quarter) << 16) + uint32_t(s * kTN + cb), v);
+        if (row < M) {
+          if (vec && n0 + cb + 32 <= N2) {
+            uint4 pk[4];
+            uint32_t* pw = reinterpret_cast<uint32_t*>(pk);
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+              const __half2 h = __floats2half2_rn(__uint_as_float(v[2 * i]) * 0.0625f, __uint_as_float(v[2 * i + 1]) * 0.0625f);
+              pw[i] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            uint4* dstp = reinterpret_cast<uint4*>(orow + cb);
+#pragma unroll
+            for (int i = 0; i < 4; i++) dstp[i] = pk[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++)
+              if (n0 + cb + i < N2) orow[cb + i] = __float2half_rn(__uint_as_float(v[i]) * 0.0625f);
+          }
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(6 + s));
+    }
+    if (TMA_STORE && tid == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * kTN) : "memory");
+}
+
 // ---- host -------------------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -219,6 +392,18 @@ static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, int C) {
   const cuuint32_t estr[2] = {1, 1};
   return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// output level [E][M][N2] f16 as a 3-D tensor: box = 64 columns x 128 rows x 1 edge, 128-byte swizzle
+static bool make_out_map(CUtensorMap* m, void* base, int N2, int M, int E) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[3] = {cuuint64_t(N2), cuuint64_t(M), cuuint64_t(E)};
+  const cuuint64_t gstride[2] = {cuuint64_t(N2) * 2, cuuint64_t(M) * N2 * 2};
+  const cuuint32_t box[3] = {64, cuuint32_t(kTM), 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels) {
@@ -249,7 +434,12 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
   if (!make_map(&tmA, f1T, uint64_t(N) * HW, C)) return DB200_ERR_CUDA;
   const size_t smem = size_t(2) * (kTM + kTN) * kTK * 2 + 1024;
   static bool attr = false;
-  if (!attr) { DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))); attr = true; }
+  if (!attr) {
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
+    attr = true;
+  }
   const __half* prev = nullptr;
   int h = ht, w = wd;
   for (int l = 0; l < num_levels; l++) {
@@ -268,8 +458,22 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
     const int N2 = h * w;
     CUtensorMap tmB;
     if (!make_map(&tmB, f2T, uint64_t(N) * N2, C)) return DB200_ERR_CUDA;
-    dim3 grid(cdiv(N2, kTN), cdiv(HW, kTM), N);
-    corr_gemm_tc_kernel<<<grid, 128, smem, st>>>(tmA, tmB, static_cast<__half*>(levels_out[l]), HW, N2, err);
+    static const bool one_shot = getenv("DB200_CORR_TC_ONESHOT") != nullptr;       // previous kernel: one tile per CTA
+    if (one_shot) {
+      dim3 grid(cdiv(N2, kTN), cdiv(HW, kTM), N);
+      corr_gemm_tc_kernel<<<grid, 128, smem, st>>>(tmA, tmB, static_cast<__half*>(levels_out[l]), HW, N2, err);
+    } else {
+      const long long tiles = static_cast<long long>(N) * cdiv(HW, kTM) * cdiv(N2, kTN);
+      const int grid = int(tiles < kNumSMs ? tiles : kNumSMs);
+      static const bool no_tma_store = getenv("DB200_CORR_TC_NO_TMA_STORE") != nullptr;
+      CUtensorMap tmO = tmB;                                           // placeholder when the direct-store epilogue is used
+      const bool tma_store = !no_tma_store && N2 % 64 == 0 && (reinterpret_cast<uintptr_t>(levels_out[l]) % 16 == 0) &&
+                             make_out_map(&tmO, levels_out[l], N2, HW, N);
+      if (tma_store)
+        corr_gemm_tc_pipe_kernel<true><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err);
+      else
+        corr_gemm_tc_pipe_kernel<false><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err);
+    }
     DB200_CHECK_LAUNCH();
     prev = f2T;
     h >>= 1; w >>= 1;
