@@ -24,6 +24,8 @@ constexpr int kCholTile = 64;         // tile edge of the reduced-system Cholesk
 
 // dataflow flags of the solver: one per tile of the lower block triangle (+ the rhs block row), one counter per
 // block column, one x-ready flag per block column, a few control words
+// per diagonal tile: the 64x64 factor, streamed out panel by panel, + the 64 reciprocal pivots
+__host__ __device__ inline size_t chol_stage_doubles() { return size_t(kCholTile) * kCholTile + kCholTile; }
 __host__ __device__ inline size_t chol_flag_words(int nt) { return size_t(nt) * (nt + 3) / 2 + 2 * size_t(nt) + 16; }
 
 // per-edge record (recomputed every iteration from the current poses), indexed by SORTED position
@@ -48,7 +50,7 @@ struct BAHeader {
 };
 
 struct BALayout {
-  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, total;
+  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, Lstage, total;
   int n, nt, ld, Mcap;
 };
 
@@ -81,6 +83,7 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.cflags = take(sizeof(unsigned) * chol_flag_words(L.nt));
   L.xsol = take(sizeof(double) * size_t(L.ld));
   L.dx = take(sizeof(float) * size_t(L.n));
+  L.Lstage = take(sizeof(double) * size_t(L.nt) * chol_stage_doubles());   // streamed diagonal factors (ba_solve.cu)
   L.total = o;
   return L;
 }
@@ -93,7 +96,7 @@ struct BAParams {
   int own_lo, own_hi;   // owned source frames [own_lo, own_hi) (edge-sharded multi-GPU runs; 0, B otherwise)
   // workspace views
   BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
-  float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx;
+  float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx; double* Lstage;
   int n, nt, ld, Mcap;
 };
 
@@ -116,6 +119,7 @@ inline BAParams ba_params(const BALayout& L, void* ws) {
   p.cflags = reinterpret_cast<unsigned*>(b + L.cflags);
   p.xsol = reinterpret_cast<double*>(b + L.xsol);
   p.dx = reinterpret_cast<float*>(b + L.dx);
+  p.Lstage = reinterpret_cast<double*>(b + L.Lstage);
   p.n = L.n; p.nt = L.nt; p.ld = L.ld; p.Mcap = L.Mcap;
   return p;
 }

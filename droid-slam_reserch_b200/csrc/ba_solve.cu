@@ -52,6 +52,18 @@ __device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Streamed diagonal factors: words that have not been produced yet hold this quiet-NaN payload (arithmetic NaNs carry
+// the canonical payload, never this one), so every 8-byte word validates itself — no fence, no flag on the chain.
+constexpr unsigned long long kStageEmpty = 0x7ff8dead0000beefULL;
+__device__ __forceinline__ void st_relaxed_f64(double* p, double v) {
+  asm volatile("st.relaxed.gpu.global.f64 [%0], %1;" ::"l"(p), "d"(v));   // the value is an operand: no memory clobber needed
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const double* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+
 // thread 0 polls `flag` until it is >= want (bounded); everybody gets the verdict.  false = abort the kernel.
 __device__ __forceinline__ bool wait_flag(const unsigned* flag, unsigned want, unsigned* err, int* s_ok) {
   if (threadIdx.x == 0) {
@@ -88,6 +100,9 @@ __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   if (gtid == 0) p.hdr->chol_fail = 0;
   const size_t nflags = chol_flag_words(p.nt);
   for (size_t i = gtid; i < nflags; i += gstride) p.cflags[i] = 0u;
+  unsigned long long* stage = reinterpret_cast<unsigned long long*>(p.Lstage);
+  const size_t nstage = size_t(p.nt) * chol_stage_doubles();
+  for (size_t i = gtid; i < nstage; i += gstride) stage[i] = kStageEmpty;
   for (size_t i = gtid; i < total; i += gstride) {
     const int r = int(i / ld), c = int(i - size_t(r) * ld);
     double v = 0.0;
@@ -229,9 +244,9 @@ __device__ __forceinline__ void frag_rank8(double (&c)[4][4], const double (*Pm)
   }
 }
 
-template <int P>
-__device__ __forceinline__ void factor_panel(double (*S)[TP], int row0, int n, int* chol_fail) {
-  constexpr int c0 = 8 * P;
+// One copy of this code serves all eight steps (c0 is a run-time value: it only enters shared-memory addresses): the
+// solver's instruction footprint otherwise exceeds the SM's instruction cache and the single-warp phases stall on fetch.
+__device__ __forceinline__ void factor_panel(double (*S)[TP], int c0, int row0, int n, int* chol_fail) {
   const int tid = threadIdx.x;
   if (tid < T - c0) {
     const int r = c0 + tid;
@@ -280,34 +295,59 @@ __device__ long long* g_chol_fine = nullptr;   // debug: clock64 marks inside on
 __device__ __forceinline__ void fine_mark(int slot) {
   if (g_chol_fine != nullptr && threadIdx.x == 0) g_chol_fine[slot] = clock64();
 }
-template <int P>
-__device__ __forceinline__ void factor_step(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail) {
-  fine_mark(4 * P);
-  cols_to_smem<P>(S, c, true);
-  __syncthreads();
-  fine_mark(4 * P + 1);
-  factor_panel<P>(S, row0, n, chol_fail);
-  fine_mark(4 * P + 2);
-  __syncthreads();
-  fine_mark(4 * P + 3);
-  if (P < 7) frag_rank8<P, true>(c, S, S);
+// The fragment-dependent parts need the step index at compile time (register arrays); everything else takes it at run
+// time, so that each routine exists ONCE in the instruction stream: unrolled eight-fold, the solver's code exceeded the
+// SM's instruction cache and the single-warp phases of the chain stalled on instruction fetch.
+// (dispatch by a branch tree of uniform compares: a `switch` becomes an indirect BRX jump, which costs hundreds of cycles)
+__device__ __forceinline__ void cols_to_smem_sw(int P, double (*S)[TP], const double (&c)[4][4], bool lower_only) {
+  if (P < 4) {
+    if (P < 2) { if (P == 0) cols_to_smem<0>(S, c, lower_only); else cols_to_smem<1>(S, c, lower_only); }
+    else { if (P == 2) cols_to_smem<2>(S, c, lower_only); else cols_to_smem<3>(S, c, lower_only); }
+  } else {
+    if (P < 6) { if (P == 4) cols_to_smem<4>(S, c, lower_only); else cols_to_smem<5>(S, c, lower_only); }
+    else { if (P == 6) cols_to_smem<6>(S, c, lower_only); else cols_to_smem<7>(S, c, lower_only); }
+  }
+}
+template <bool LOWER>
+__device__ __forceinline__ void frag_rank8_sw(int P, double (&c)[4][4], const double (*Pm)[TP], const double (*Qm)[TP]) {
+  if (P < 4) {
+    if (P < 2) { if (P == 0) frag_rank8<0, LOWER>(c, Pm, Qm); else frag_rank8<1, LOWER>(c, Pm, Qm); }
+    else { if (P == 2) frag_rank8<2, LOWER>(c, Pm, Qm); else frag_rank8<3, LOWER>(c, Pm, Qm); }
+  } else {
+    if (P < 6) { if (P == 4) frag_rank8<4, LOWER>(c, Pm, Qm); else frag_rank8<5, LOWER>(c, Pm, Qm); }
+    else if (P == 6) frag_rank8<6, LOWER>(c, Pm, Qm);
+  }
 }
 
-// In: the tile as register fragments `c` (lower triangle meaningful).  Out: L in shared S (strict upper zero).
-__device__ __forceinline__ void factor_tile(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail) {
-  factor_step<0>(c, S, row0, n, chol_fail); factor_step<1>(c, S, row0, n, chol_fail);
-  factor_step<2>(c, S, row0, n, chol_fail); factor_step<3>(c, S, row0, n, chol_fail);
-  factor_step<4>(c, S, row0, n, chol_fail); factor_step<5>(c, S, row0, n, chol_fail);
-  factor_step<6>(c, S, row0, n, chol_fail); factor_step<7>(c, S, row0, n, chol_fail);
+// In: the tile as register fragments `c` (lower triangle meaningful).  Out: L in shared S (strict upper zero); every
+// finished 64x8 panel is also streamed to `stage` (global, may be null) for the CTAs that solve against this tile.
+__device__ __forceinline__ void factor_tile(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail, double* stage) {
+#pragma unroll 1
+  for (int P = 0; P < 8; P++) {
+    const int c0 = 8 * P;
+    fine_mark(4 * P);
+    cols_to_smem_sw(P, S, c, true);
+    __syncthreads();
+    fine_mark(4 * P + 1);
+    factor_panel(S, c0, row0, n, chol_fail);
+    fine_mark(4 * P + 2);
+    __syncthreads();
+    fine_mark(4 * P + 3);
+    if (stage != nullptr) {
+#pragma unroll
+      for (int t = 0; t < 2; t++) {
+        const int e = threadIdx.x + kCholThreads * t, r = e >> 3, q = e & 7;
+        st_relaxed_f64(stage + r * T + c0 + q, S[r][c0 + q]);
+      }
+    }
+    frag_rank8_sw<true>(P, c, S, S);
+  }
   __syncthreads();
 }
 
-template <int P>
-__device__ __forceinline__ void trsm_step(double (&c)[4][4], double (*X)[TP], const double (*L)[TP], const double* rinv) {
-  constexpr int c0 = 8 * P;
+// rows of X against the 8x8 diagonal block of panel c0 (threads 0..63 = rows)
+__device__ __forceinline__ void trsm_solve(double (*X)[TP], const double (*L)[TP], const double* rinv, int c0) {
   const int tid = threadIdx.x;
-  cols_to_smem<P>(X, c, false);
-  __syncthreads();
   if (tid < T) {
     double D[8][8], x[8];
 #pragma unroll
@@ -326,15 +366,90 @@ __device__ __forceinline__ void trsm_step(double (&c)[4][4], double (*X)[TP], co
 #pragma unroll
     for (int q = 0; q < 8; q++) X[tid][c0 + q] = x[q];
   }
-  __syncthreads();
-  if (P < 7) frag_rank8<P, false>(c, X, L);
 }
 
-// X L^T = C: C as register fragments `c`, L (lower) in shared `L`, rinv[k] = 1/L[k][k].  Out: X in shared `X`.
-__device__ __forceinline__ void trsm_tile(double (&c)[4][4], double (*X)[TP], const double (*L)[TP], const double* rinv) {
-  trsm_step<0>(c, X, L, rinv); trsm_step<1>(c, X, L, rinv); trsm_step<2>(c, X, L, rinv); trsm_step<3>(c, X, L, rinv);
-  trsm_step<4>(c, X, L, rinv); trsm_step<5>(c, X, L, rinv); trsm_step<6>(c, X, L, rinv); trsm_step<7>(c, X, L, rinv);
+// ---- streamed hand-over of a diagonal factor ---------------------------------------------------------------------
+struct StreamRegs { unsigned long long v[2]; };      // this thread's two words of a 64x8 panel
+
+__device__ __forceinline__ const double* stream_addr(const double* stage, int c0, int t) {
+  const int e = threadIdx.x + kCholThreads * t;
+  return stage + (e >> 3) * T + c0 + (e & 7);
+}
+// first look at the panel starting at column c0 (no waiting): issued one step ahead so that the L2 round trip hides
+// behind the previous step's arithmetic
+__device__ __forceinline__ void stream_issue(StreamRegs& sr, const double* stage, int c0) {
+#pragma unroll
+  for (int t = 0; t < 2; t++) sr.v[t] = ld_relaxed_u64(stream_addr(stage, c0, t));
+}
+// words that were not there yet are polled (bounded); the panel lands in L[.][c0..c0+7], its pivots' reciprocals in
+// rinv[c0..].  Returns 1 to give up (spin limit, or another CTA raised an error); the caller's barrier shares the verdict.
+__device__ __forceinline__ int stream_commit(StreamRegs& sr, double (*L)[TP], double* rinv, const double* stage, int c0,
+                                             unsigned* err) {
+  int fail = 0;
+#pragma unroll
+  for (int t = 0; t < 2; t++) {
+    const double* src = stream_addr(stage, c0, t);
+    unsigned long long v = sr.v[t];
+    unsigned spins = 0;
+    while (v == kStageEmpty) {
+      if (++spins > kSpinLimit || ((spins & 1023u) == 0 && ld_acquire(err) != 0)) { fail = 1; break; }
+      v = ld_relaxed_u64(src);
+    }
+    const int e = threadIdx.x + kCholThreads * t, r = e >> 3, q = e & 7;
+    const double val = __longlong_as_double(static_cast<long long>(v));
+    L[r][c0 + q] = val;
+    if (r == c0 + q) {                              // a pivot: 1/L[k][k] by hardware seed + two Newton steps (~1 ulp)
+      double y;
+      asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(val));
+      y = fma(y, fma(-val, y, 1.0), y);
+      y = fma(y, fma(-val, y, 1.0), y);
+      rinv[r] = y;
+    }
+  }
+  return fail;
+}
+
+// cd -= X[:, c0..c0+7] X[:, c0..c0+7]^T on the block-lower fragments (the rank-8 slice of tile_aat_lower)
+__device__ __forceinline__ void frag_syrk8(double (&cd)[4][4], const double (*X)[TP], int c0) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+  for (int q = 0; q < 8; q++) {
+    double pv[4], qv[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) { pv[a] = X[ty + 16 * a][c0 + q]; qv[a] = X[tx + 16 * a][c0 + q]; }
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) cd[a][b] = fma(-pv[a], qv[b], cd[a][b]);
+  }
+}
+
+// X L(s,s)^T = C with L(s,s) arriving panel by panel from the CTA that is factoring it (staging area `stage`, write
+// once, any number of readers).  C as register fragments `cf`; X ends up in shared `X`.  With SYRK, the diagonal tile
+// `cd` of the chain takes its rank-8 update X_P X_P^T right behind every solved panel, so that when the last panel of
+// L(s,s) appears only one panel's worth of work separates it from the next factorisation.
+template <bool SYRK>
+__device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][4], double (*X)[TP], double (*L)[TP], double* rinv,
+                                            const double* stage, unsigned* err) {
+  StreamRegs sr;
+  stream_issue(sr, stage, 0);
+#pragma unroll 1
+  for (int P = 0; P < 8; P++) {
+    const int c0 = 8 * P;
+    const int fail = stream_commit(sr, L, rinv, stage, c0, err);
+    if (P < 7) stream_issue(sr, stage, c0 + 8);
+    cols_to_smem_sw(P, X, cf, false);
+    if (__syncthreads_or(fail)) {                  // one barrier: L panel, pivots and the X columns are all in place
+      if (threadIdx.x == 0) atomicExch(err, 1u);
+      return false;
+    }
+    trsm_solve(X, L, rinv, c0);
+    __syncthreads();
+    frag_rank8_sw<false>(P, cf, X, L);
+    if (SYRK) frag_syrk8(cd, X, c0);
+  }
   __syncthreads();
+  return true;
 }
 
 // optional timeline of the panel chain (debug/profiling; db200_debug_chol_trace): trace[8*s + e] = globaltimer ns
@@ -349,7 +464,7 @@ __device__ __forceinline__ void trace_mark(int s, int e) {
 
 struct CholCtx {
   double (*sA)[TP]; double (*sB)[TP]; double (*sC)[TP]; double* sv; int* s_ok;
-  double* W; CholFlags F; int nt, ld, n; bool panel_full;
+  double* W; const double* stage; CholFlags F; int nt, ld, n; bool panel_full;
 };
 
 __device__ __forceinline__ double* tile_ptr(const CholCtx& cx, int i, int j) { return cx.W + size_t(i) * T * cx.ld + size_t(j) * T; }
@@ -411,12 +526,10 @@ __device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
 #pragma unroll
     for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
   const int cs = colstart(s, cx.nt);
-  if (!wait_flag(cx.F.ready + cs, 1u, cx.F.ctl, cx.s_ok)) return false;
-  load_tile(cx.sB, tile_ptr(cx, s, s), cx.ld);
-  __syncthreads();
-  if (threadIdx.x < T) cx.sv[threadIdx.x] = 1.0 / cx.sB[threadIdx.x][threadIdx.x];
-  __syncthreads();
-  trsm_tile(cf, cx.sA, cx.sB, cx.sv);
+  // the triangular solve follows the factorisation of L(s,s) panel by panel (its staging area is write-once, any
+  // number of CTAs may read it) and ends one panel after it, instead of starting when the whole tile is published
+  const double* stage = cx.stage + size_t(s) * chol_stage_doubles();
+  if (!stream_trsm<false>(cf, cf, cx.sA, cx.sB, cx.sv, stage, cx.F.ctl)) return false;
   store_tile(Cg, cx.sA, cx.ld);
   publish(cx.F.ready + cs + (i - s), cx.F.panel_done + s);
   __syncthreads();
@@ -429,10 +542,18 @@ __device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
 //   diagonal tile (d,d): the panel chain  L(d,d-1) -> update (d,d) -> factor (d,d)  then stays inside one CTA
 //   (operands in shared memory), and only the finished diagonal tile crosses CTAs per step.
 //   step s (panel s-1 is applied to every tile with j >= s, block column s becomes final):
-//     CTA D(s+1): [a] (d,d) -= L(d,s-1)L(d,s-1)^T; [b] tile (d,s): apply panel s-1, wait L(s,s), triangular solve;
-//                 [c] (d,d) -= L(d,s)L(d,s)^T, factor, publish              (d = s+1)
-//     every CTA : its other tiles in index order (block column s first): panel update, and for j == s the
-//                 triangular solve against L(s,s) + publish.
+//     CTA D(s+1): [a]+[b] tiles (d,d) and (d,s) take panel s-1 (L(d,s-1) loaded once for both);
+//                 [c] STREAMED solve: L(s,s) arrives 64x8 panel by panel from the CTA that is factoring it (write-once
+//                     staging words pre-filled with a quiet-NaN payload: every word validates itself, no fence and no
+//                     flag on the chain); each solved panel X_P of (d,s) is followed by the rank-8 update
+//                     (d,d) -= X_P X_P^T, so no 64^3 product stands between the solve and the factorisation;
+//                 [d] factor (d,d) — streaming ITS panels out — store, publish            (d = s+1)
+//     every CTA : its other tiles in index order (block column s first): panel update, and for j == s the same
+//                 streamed triangular solve against L(s,s) + publish.
+// Instruction footprint: the 8-column steps are run-time loops (factor_panel / trsm_solve / streaming exist once; only
+// the register-fragment parts are dispatched per step by a compare tree), 11.8k SASS instructions instead of 18.7k —
+// the single-warp panel factor takes ~900 cycles when its code stays in the instruction cache, 1400+ as one of eight
+// unrolled copies.
 // The trailing updates of step s overlap the panel chain of step s+1 (look-ahead falls out of the data flow).
 // Then x = L^-T y: CTA nt-1-j owns x_j = L_jj^-T (y_j - sum_{i>j} L_ij^T x_i), consuming x_i as they appear.
 __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p) {
@@ -444,7 +565,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   cx.sC = reinterpret_cast<double (*)[TP]>(smem_raw + 2 * sizeof(double) * T * TP);
   cx.sv = reinterpret_cast<double*>(smem_raw + 3 * sizeof(double) * T * TP);   // [6*64] scratch vectors
   cx.s_ok = &s_ok;
-  cx.W = p.Wk; cx.nt = p.nt; cx.ld = p.ld; cx.n = p.n;
+  cx.W = p.Wk; cx.stage = p.Lstage; cx.nt = p.nt; cx.ld = p.ld; cx.n = p.n;
   cx.F = chol_flags(p.cflags, p.nt);
   const int nt = p.nt, ld = p.ld, n = p.n;
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
@@ -457,7 +578,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     if (s == 0 && cta == 0) {                       // D(0): the first diagonal tile
       double c0f[4][4];
       load_frag(c0f, tile_ptr(cx, 0, 0), ld);
-      factor_tile(c0f, cx.sB, 0, n, &p.hdr->chol_fail);
+      factor_tile(c0f, cx.sB, 0, n, &p.hdr->chol_fail, p.Lstage);
       store_tile(tile_ptr(cx, 0, 0), cx.sB, ld);
       publish(F.ready + 0, F.panel_done + 0);
       trace_mark(0, 3);
@@ -465,45 +586,44 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     }
     const int d = s + 1;
     if (d < nt && cta == colstart(d, nt) % G) {     // the panel chain of this step
-      double cf[4][4], acc[4][4];
-      // [a] diagonal tile: panel s-1
-      load_frag(cf, tile_ptr(cx, d, d), ld);
-      if (s > 0) { if (!apply_panel(cx, d, d, s, acc)) return; }
-      else {
+      double cf[4][4], cd[4][4];
+      // [a]+[b] diagonal tile (d,d) and sub-diagonal tile (d,s): panel s-1, with L(d,s-1) loaded once for both
+      load_frag(cd, tile_ptr(cx, d, d), ld);
+      load_frag(cf, tile_ptr(cx, d, s), ld);
+      if (s > 0) {
+        const int k = s - 1, ck = colstart(k, nt);
+        if (!wait_flag(F.ready + ck + (d - k), 1u, F.ctl, &s_ok)) return;
+        if (!wait_flag(F.ready + ck + (s - k), 1u, F.ctl, &s_ok)) return;
+        load_tile(cx.sA, tile_ptr(cx, d, k), ld);
+        load_tile(cx.sB, tile_ptr(cx, s, k), ld);
+        __syncthreads();
+        double acc[4][4];
+        tile_aat_lower(cx.sA, acc);
 #pragma unroll
         for (int a = 0; a < 4; a++)
 #pragma unroll
-          for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
+          for (int b = 0; b < 4; b++) cd[a][b] -= acc[a][b];
+        tile_abt(cx.sA, cx.sB, acc);
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+          for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
+        __syncthreads();
       }
-      frag_to_smem(cx.sC, cf, acc);
-      // [b] sub-diagonal tile (d,s): panel s-1, then the triangular solve against L(s,s)
-      load_frag(cf, tile_ptr(cx, d, s), ld);
-      if (s > 0) { if (!apply_panel(cx, d, s, s, acc)) return; }
+      trace_mark(s, 6);
+      // L(s,s) arrives panel by panel from the CTA that is factoring it; the triangular solve and the update of
+      // (d,d) keep pace one panel behind, so only the last panel's work is left when that factorisation ends
+      const double* stage = p.Lstage + size_t(s) * chol_stage_doubles();
+      if (!stream_trsm<true>(cf, cd, cx.sA, cx.sB, cx.sv, stage, F.ctl)) return;
+      trace_mark(s, 5);
+      store_tile(tile_ptr(cx, d, s), cx.sA, ld);
 #pragma unroll
       for (int a = 0; a < 4; a++)
 #pragma unroll
-        for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
-      if (!wait_flag(F.ready + cs, 1u, F.ctl, &s_ok)) return;
-      trace_mark(s, 4);
-      load_tile(cx.sB, tile_ptr(cx, s, s), ld);
-      __syncthreads();
-      if (tid < T) cx.sv[tid] = 1.0 / cx.sB[tid][tid];
-      __syncthreads();
-      trsm_tile(cf, cx.sA, cx.sB, cx.sv);
-      trace_mark(s, 5);
-      store_tile(tile_ptr(cx, d, s), cx.sA, ld);
-      // [c] diagonal tile: panel s straight from shared memory, factor from registers
-      tile_aat_lower(cx.sA, acc);
-      {
-        const int ty = tid >> 4, tx = tid & 15;
-#pragma unroll
-        for (int a = 0; a < 4; a++)
-#pragma unroll
-          for (int b = 0; b < 4; b++) cf[a][b] = cx.sC[ty + 16 * a][tx + 16 * b] - acc[a][b];
-      }
+        for (int b = 0; b < 4; b++) cf[a][b] = cd[a][b];
       publish(F.ready + cs + 1, F.panel_done + s, kCholThreads - 1);   // L(d,s): released by the last warp
       trace_mark(d, 1);
-      factor_tile(cf, cx.sB, d * T, n, &p.hdr->chol_fail);
+      factor_tile(cf, cx.sB, d * T, n, &p.hdr->chol_fail, p.Lstage + size_t(d) * chol_stage_doubles());
       trace_mark(d, 2);
       store_tile(tile_ptr(cx, d, d), cx.sB, ld);
       publish(F.ready + colstart(d, nt), F.panel_done + d);

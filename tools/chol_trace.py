@@ -20,15 +20,15 @@ for it in range(3):
     torch.cuda.synchronize()
 _capi.lib().db200_debug_chol_trace(C.c_void_p(0))
 tr = buf.cpu().numpy().reshape(-1, 8)[: 2 * nt].astype(np.float64)
-t0 = tr[0, 1]
-print("step: upd_start  upd->fac  factor  publish | trsm: flag_seen-after_pub  trsm  publish | step period")
+t0 = tr[1, 1]
+print("tile s: factor_start(us)  factor(us) | consumer of L(s,s): pre-work done after factor start, streamed solve done after factor end | next factor start after that | period")
 prev = None
 for s in range(nt):
     r = tr[s]
-    per = (r[3] - prev) if prev else 0.0
-    prev = r[3]
-    print(f"{s:3d}: {(r[0]-t0)/1e3:8.1f} {(r[1]-r[0])/1e3:6.1f} {(r[2]-r[1])/1e3:6.1f} {(r[3]-r[2])/1e3:6.1f} | "
-          f"{(r[4]-r[3])/1e3:6.1f} {(r[5]-r[4])/1e3:6.1f} {(r[6]-r[5])/1e3:6.1f} | {per/1e3:6.1f}")
+    nxt = tr[s + 1][1] if s + 1 < nt else np.nan
+    per = (r[2] - prev) if prev else 0.0
+    prev = r[2]
+    print(f"{s:3d}: {(r[1]-t0)/1e3:8.1f} {(r[2]-r[1])/1e3:6.1f} | prework done {(r[6]-r[1])/1e3:6.1f} stream done {(r[5]-r[2])/1e3:6.1f} | {(nxt-r[5])/1e3:6.1f} | {per/1e3:6.1f}")
 xs = tr[nt:2 * nt, 0]
 print("factor total us:", (tr[nt - 1, 3] - t0) / 1e3, " backsub us:", (xs[0] - xs[nt - 1]) / 1e3, " backsub per block us:", (xs[0] - xs[nt - 1]) / 1e3 / (nt - 1))
 
@@ -38,3 +38,4 @@ for P in range(8):
     a = fine[4 * P: 4 * P + 5]
     nxt = fine[4 * P + 4] if P < 7 else np.nan
     print(P, [a[1] - a[0], a[2] - a[1], a[3] - a[2], nxt - a[3]])
+
