@@ -167,6 +167,83 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
                               algorithmic_bytes_per_launch=lookups * 912))
 
 
+def training_bench(dev, steps=10, warmup=3):
+    """Secondary timings at the TartanAir training shape (BASELINE config 5: 4 clips x 22 edges = 88 edges, fp32,
+    48x64 maps): CorrBlock path = volume pyramid + 4-level lookup + lookup backward per level; AltCorrBlock path =
+    altcorr forward/backward per level on channels-last pyramids (corr.py:91-139)."""
+    import torch
+    import droid_backends
+    N, C_, ht, wd = 88, 128, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(21)
+    f1 = torch.randn((N, C_, ht, wd), device=dev, generator=g)
+    f2 = torch.randn((N, C_, ht, wd), device=dev, generator=g)
+    yy, xx = torch.meshgrid(torch.arange(ht, device=dev, dtype=torch.float32), torch.arange(wd, device=dev, dtype=torch.float32), indexing="ij")
+    coords = (torch.stack([xx, yy], 0)[None].repeat(N, 1, 1, 1) + 4.0 * torch.randn((N, 2, ht, wd), device=dev, generator=g)).contiguous()
+
+    def timed(fn):
+        for _ in range(warmup):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    out = {}
+    out["corr_volume_f32_ms"] = timed(lambda: droid_backends.corr_volume_pyramid(f1, f2, 4))
+    levels = droid_backends.corr_volume_pyramid(f1, f2, 4)
+    out["lookup_f32_ms"] = timed(lambda: droid_backends.corr_pyramid_lookup(levels, coords, 3))
+    grads = [torch.randn((N, 7, 7, ht, wd), device=dev, generator=g) for _ in range(4)]
+    cl = [(coords / 2 ** l).contiguous() for l in range(4)]
+    out["lookup_backward_f32_4levels_ms"] = timed(lambda: [droid_backends.corr_index_backward(levels[l], cl[l], grads[l], 3) for l in range(4)])
+    del levels
+    # AltCorrBlock: channels-last pyramid of fmap2, fmap1 at full resolution
+    f1c = f1.permute(0, 2, 3, 1).contiguous()
+    pyr = [f2]
+    for _ in range(3):
+        pyr.append(torch.nn.functional.avg_pool2d(pyr[-1], 2, stride=2))
+    pyr = [q.permute(0, 2, 3, 1).contiguous() for q in pyr]
+    ca = [(coords / 2 ** l).permute(0, 2, 3, 1)[:, None].contiguous() for l in range(4)]       # [B,S=1,H,W,2]
+    out["altcorr_forward_4levels_ms"] = timed(lambda: [droid_backends.altcorr_forward(f1c, pyr[l], ca[l], 3) for l in range(4)])
+    ga = [torch.randn((N, 1, 49, ht, wd), device=dev, generator=g) for _ in range(4)]
+    out["altcorr_backward_4levels_ms"] = timed(lambda: [droid_backends.altcorr_backward(f1c, pyr[l], ca[l], ga[l], 3) for l in range(4)])
+    out["shape"] = "88 edges x 48x64, 128 channels, fp32 (BASELINE config 5)"
+    # the unmodified reference CUDA extension on the same tensors (absent .so -> skipped); never on the product path
+    try:
+        import glob
+        import importlib
+        refdir = os.path.join(REPO, "baseline", "_ref")
+        if glob.glob(os.path.join(refdir, "droid_backends_ref*.so")):
+            if refdir not in sys.path:
+                sys.path.insert(0, refdir)
+            ref = importlib.import_module("droid_backends_ref")
+            levels = droid_backends.corr_volume_pyramid(f1, f2, 4)
+            r = {}
+            r["lookup_f32_ms"] = timed(lambda: [ref.corr_index_forward(levels[l], cl[l], 3) for l in range(4)])
+            r["lookup_backward_f32_4levels_ms"] = timed(lambda: [ref.corr_index_backward(levels[l], cl[l], grads[l], 3) for l in range(4)])
+            del levels
+            r["altcorr_forward_4levels_ms"] = timed(lambda: [ref.altcorr_forward(f1c, pyr[l], ca[l], 3) for l in range(4)])
+            r["altcorr_backward_4levels_ms"] = timed(lambda: [ref.altcorr_backward(f1c, pyr[l], ca[l], ga[l], 3) for l in range(4)])
+            fm1, fm2 = f1.reshape(1, N, C_, ht * wd), f2.reshape(1, N, C_, ht * wd)
+
+            def ref_volume():                                      # CorrBlock.corr + pyramid as the reference does it (corr.py:30-38,63-71)
+                c = torch.matmul(fm1.transpose(2, 3), fm2).view(N, ht, wd, ht, wd) / 4.0
+                lv = [c]
+                x = c.reshape(N * ht * wd, 1, ht, wd)
+                for _ in range(3):
+                    x = torch.nn.functional.avg_pool2d(x, 2, stride=2)
+                    lv.append(x)
+                return lv
+            r["corr_volume_f32_ms"] = timed(ref_volume)
+            out["reference_cuda_same_shapes"] = r
+    except Exception as ex:
+        out["reference_cuda_same_shapes"] = dict(unavailable=f"{type(ex).__name__}: {ex}"[:200])
+    return out
+
+
 def graph_bench(p, dev, steps=5):
     """Secondary metrics on the c3 keyframe buffer: `frame_distance` over all 512^2 ordered pairs (one direction;
     DepthVideo.distance calls it twice) and the whole GPU edge selection of add_proximity_factors (both directions of
@@ -434,6 +511,9 @@ def main_gpu(args, rank, world):
         line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
         line["corr_volume"] = volume_bench(dev, 10, 3, hbm_peak)
         line["graph"] = graph_bench(p, dev)
+        del target, weight
+        torch.cuda.empty_cache()
+        line["training_shapes"] = training_bench(dev)
         try:
             tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
             line["lookup"]["roofline"]["traffic"] = tr

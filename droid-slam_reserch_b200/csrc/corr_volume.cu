@@ -133,6 +133,11 @@ bool corr_tc_supported(int C, int ht, int wd);
 int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
                            int num_levels, void* workspace, cudaStream_t st);
 
+size_t corr_tc_f32_workspace_bytes(int N, int C, int ht, int wd, int num_levels);
+bool corr_tc_f32_supported(int C, int ht, int wd, int num_levels);
+int corr_volume_pyramid_tc_f32(const float* fmap1, const float* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
+                               int num_levels, void* workspace, cudaStream_t st);
+
 }  // namespace db200
 
 using namespace db200;
@@ -142,6 +147,11 @@ static bool use_tc_path(int C, int ht, int wd, int dtype) {
   return !off && dtype == DB200_F16 && corr_tc_supported(C, ht, wd);
 }
 
+static bool use_tc_f32_path(int C, int ht, int wd, int num_levels) {
+  static const bool off = getenv("DB200_CORR_NO_TCGEN05") != nullptr;
+  return !off && corr_tc_f32_supported(C, ht, wd, num_levels);
+}
+
 extern "C" size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd, int num_levels, int dtype) {
   if (N <= 0 || C <= 0 || ht <= 0 || wd <= 0 || num_levels < 1) return 0;
   const size_t es = dtype == DB200_F16 ? 2 : 4;
@@ -149,6 +159,10 @@ extern "C" size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd
   int h = ht, w = wd;
   for (int l = 1; l < num_levels; l++) { h >>= 1; w >>= 1; tot += ((size_t(N) * C * h * w * es + 255) / 256) * 256; }
   if (dtype == DB200_F16) { const size_t t2 = corr_tc_workspace_bytes(N, C, ht, wd, num_levels); if (t2 > tot) tot = t2; }
+  if (dtype == DB200_F32 && use_tc_f32_path(C, ht, wd, num_levels)) {
+    const size_t t2 = corr_tc_f32_workspace_bytes(N, C, ht, wd, num_levels);
+    if (t2 > tot) tot = t2;
+  }
   return tot;
 }
 
@@ -168,6 +182,11 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
     if (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)) return DB200_ERR_WORKSPACE;
     return corr_volume_pyramid_tc(static_cast<const __half*>(fmap1), static_cast<const __half*>(fmap2), levels_out, N, C, ht, wd,
                                   num_levels, workspace, st);
+  }
+  if (dtype == DB200_F32 && use_tc_f32_path(C, ht, wd, num_levels)) {
+    if (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)) return DB200_ERR_WORKSPACE;
+    return corr_volume_pyramid_tc_f32(static_cast<const float*>(fmap1), static_cast<const float*>(fmap2), levels_out, N, C, ht, wd,
+                                      num_levels, workspace, st);
   }
   const size_t es = dtype == DB200_F16 ? 2 : 4;
   const int M = ht * wd;

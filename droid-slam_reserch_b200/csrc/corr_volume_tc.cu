@@ -365,6 +365,179 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * kTN) : "memory");
 }
 
+// ---- fp32 volumes (training path) on the tensor cores: 3xTF32 ----------------------------------------------------
+// a = a_hi + a_lo with a_hi = tf32(a), a_lo = tf32(a - a_hi):  a.b ~= a_hi.b_hi + a_hi.b_lo + a_lo.b_hi (the dropped
+// lo.lo term is ~2^-22 relative), accumulated in fp32 in TMEM — fp32-faithful (|err| ~ 1e-6 of the fp32 SGEMM the
+// reference calls), at tensor-core rate.  Operands: channels-last fp32 copies split by the prep kernels; the GEMM is
+// a K = 3 x 128 chain streamed in 12 blocks of 32 (one 128-byte swizzle row) through a 4-stage TMA ring.
+__global__ void __launch_bounds__(256) transpose_cl_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int c = c0 + r, p = p0 + tx;
+    tile[r][tx] = (c < C && p < HW) ? src[(size_t(n) * C + c) * HW + p] : 0.0f;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int p = p0 + r, c = c0 + tx;
+    if (p < HW && c < C) dst[(size_t(n) * HW + p) * C + c] = tile[tx][r];
+  }
+}
+__global__ void pool_cl_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int hs, int ws, int C) {
+  const int hd = hs >> 1, wd = ws >> 1;
+  const size_t total = size_t(N) * hd * wd * C;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const int c = int(i % C);
+    size_t r = i / C;
+    const int x = int(r % wd); r /= wd;
+    const int y = int(r % hd);
+    const size_t n = r / hd;
+    const float* s = src + ((n * hs + 2 * y) * ws + 2 * x) * size_t(C) + c;
+    dst[i] = (s[0] + s[C] + s[size_t(ws) * C] + s[size_t(ws) * C + C]) * 0.25f;
+  }
+}
+__global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    uint32_t h, l;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
+    const float r = v - __uint_as_float(h);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
+    hi[i] = __uint_as_float(h);
+    lo[i] = __uint_as_float(l);
+  }
+}
+
+constexpr int kTKf = 32;                                 // fp32 elements per 128-byte swizzle row = K per TMA box
+constexpr int kStagesF = 4;
+constexpr uint32_t kStageBytesF = (kTM + kTN) * kTKf * 4;           // 32 KB: one K-block of A and of B
+constexpr size_t kSmemTF32 = kStagesF * kStageBytesF + size_t(kTM) * kTN * 4 + 1024;   // + one fp32 output staging tile
+// instruction descriptor: D = F32, A = B = TF32 (format 2), both K-major
+constexpr uint32_t kIdescTF32 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kTN >> 3) << 17) | (uint32_t(kTM >> 4) << 24);
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__global__ void __launch_bounds__(kPipeThreadsTC, 1)
+corr_gemm_tc_tf32_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
+                         const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo,
+                         const __grid_constant__ CUtensorMap tmO, int M, int N2, int E, int* __restrict__ err) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[2 * kStagesF + 4];   // full[4], empty[4], tfull[2], tempty[2]
+  __shared__ uint32_t tmem_base_s;
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+  const uint32_t stg = s0 + kStagesF * kStageBytesF;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int MT = (M + kTM - 1) / kTM, NT = (N2 + kTN - 1) / kTN;
+  const long long tiles = static_cast<long long>(E) * MT * NT;
+  constexpr int kKB = 12;                                   // 3 products x (128 / 32) K-blocks
+  auto full = [&](int i) { return smem_u32(&bars[i]); };
+  auto empty = [&](int i) { return smem_u32(&bars[kStagesF + i]); };
+  auto tfull = [&](int i) { return smem_u32(&bars[2 * kStagesF + i]); };
+  auto tempty = [&](int i) { return smem_u32(&bars[2 * kStagesF + 2 + i]); };
+
+  if (tid == 0) {
+    for (int i = 0; i < 2 * kStagesF + 2; i++) mbar_init(smem_u32(&bars[i]), 1);
+    mbar_init(tempty(0), 4); mbar_init(tempty(1), 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(2 * kTN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      long long it = 0;
+      bool dead = false;
+      for (long long t = blockIdx.x; t < tiles && !dead; t += gridDim.x) {
+        const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
+        for (int kb = 0; kb < kKB; kb++, it++) {
+          const int s = int(it % kStagesF);
+          const uint32_t use = uint32_t(it / kStagesF);
+          if (!mbar_wait(empty(s), (use & 1) ^ 1)) { atomicExch(err, 1); dead = true; break; }
+          const uint32_t sA = s0 + s * kStageBytesF, sB = sA + kTM * kTKf * 4;
+          const int prod = kb >> 2, koff = (kb & 3) * kTKf;      // 0: hi.hi  1: hi.lo  2: lo.hi
+          mbar_expect_tx(full(s), kStageBytesF);
+          tma_load_2d(sA, prod == 2 ? &tmAlo : &tmAhi, koff, e * M + mt * kTM, full(s));
+          tma_load_2d(sB, prod == 1 ? &tmBlo : &tmBhi, koff, e * N2 + nt * kTN, full(s));
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      long long it = 0;
+      int k = 0;
+      bool dead = false;
+      for (long long t = blockIdx.x; t < tiles && !dead; t += gridDim.x, k++) {
+        const int acc = k & 1;
+        if (!mbar_wait(tempty(acc), ((k >> 1) & 1) ^ 1)) { atomicExch(err, 1); break; }
+        for (int kb = 0; kb < kKB; kb++, it++) {
+          const int s = int(it % kStagesF);
+          const uint32_t use = uint32_t(it / kStagesF);
+          if (!mbar_wait(full(s), use & 1)) { atomicExch(err, 1); dead = true; break; }
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sA = s0 + s * kStageBytesF, sB = sA + kTM * kTKf * 4;
+#pragma unroll
+          for (int kk = 0; kk < kTKf / 8; kk++)
+            umma_tf32(tmem_base + uint32_t(acc * kTN), umma_desc_sw128(sA + kk * 32), umma_desc_sw128(sB + kk * 32), kIdescTF32,
+                      (kb | kk) != 0 ? 1u : 0u);
+          umma_commit(empty(s));
+        }
+        if (!dead) umma_commit(tfull(acc));
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    int k = 0;
+    for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+      const int acc = k & 1;
+      const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
+      const bool ok = mbar_wait(tfull(acc), (k >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (!ok) { if (lane == 0) atomicExch(err, 1); break; }
+      const int n0 = nt * kTN, trow = 32 * quarter + lane;
+      if (tid == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // the single staging tile is free again
+      epi_bar();
+#pragma unroll 1
+      for (int cb = 0; cb < kTN; cb += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + (uint32_t(32 * quarter) << 16) + uint32_t(acc * kTN + cb), v);
+        const uint32_t box = stg + uint32_t(cb >> 5) * (kTM * 128) + uint32_t(trow) * 128;
+#pragma unroll
+        for (int c4 = 0; c4 < 8; c4++) {
+          const uint32_t a = box + uint32_t((c4 ^ (trow & 7)) << 4);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(__uint_as_float(v[4 * c4]) * 0.0625f),
+                       "f"(__uint_as_float(v[4 * c4 + 1]) * 0.0625f), "f"(__uint_as_float(v[4 * c4 + 2]) * 0.0625f),
+                       "f"(__uint_as_float(v[4 * c4 + 3]) * 0.0625f) : "memory");
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty(acc));
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      epi_bar();
+      if (tid == 64) {
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+          if (n0 + 32 * b < N2) tma_store_3d(&tmO, stg + b * (kTM * 128), n0 + 32 * b, mt * kTM, e);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (tid == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * kTN) : "memory");
+}
+
 // ---- host -------------------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -476,6 +649,100 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
     }
     DB200_CHECK_LAUNCH();
     prev = f2T;
+    h >>= 1; w >>= 1;
+  }
+  return DB200_OK;
+}
+
+// ---- fp32 host path ---------------------------------------------------------------------------------------------------
+static bool make_map_f32(CUtensorMap* m, const void* base, uint64_t rows, int C) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[2] = {cuuint64_t(C), rows};
+  const cuuint64_t gstride[1] = {cuuint64_t(C) * 4};
+  const cuuint32_t box[2] = {cuuint32_t(kTKf), cuuint32_t(kTM)};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+static bool make_out_map_f32(CUtensorMap* m, void* base, int N2, int M, int E) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[3] = {cuuint64_t(N2), cuuint64_t(M), cuuint64_t(E)};
+  const cuuint64_t gstride[2] = {cuuint64_t(N2) * 4, cuuint64_t(M) * N2 * 4};
+  const cuuint32_t box[3] = {32, cuuint32_t(kTM), 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// every level needs N2 >= 32 and N2 % 4 == 0 (TMA store box / 16-byte global strides)
+bool corr_tc_f32_supported(int C, int ht, int wd, int num_levels) {
+  if (C != 128 || encode_fn() == nullptr) return false;
+  int h = ht, w = wd;
+  for (int l = 0; l < num_levels; l++) {
+    const int n2 = h * w;
+    if (n2 < 32 || n2 % 4 != 0) return false;
+    h >>= 1; w >>= 1;
+  }
+  return true;
+}
+
+size_t corr_tc_f32_workspace_bytes(int N, int C, int ht, int wd, int num_levels) {
+  size_t tot = 512;
+  tot += 2 * align_up256(size_t(N) * C * ht * wd * 4);               // f1 hi, lo (the full copy reuses f2's level-0 slot order)
+  tot += align_up256(size_t(N) * C * ht * wd * 4);                   // f1 full (transposed) before the split
+  int h = ht, w = wd;
+  for (int l = 0; l < num_levels; l++) { tot += 3 * align_up256(size_t(N) * C * h * w * 4); h >>= 1; w >>= 1; }   // f2 full, hi, lo
+  return tot;
+}
+
+int corr_volume_pyramid_tc_f32(const float* fmap1, const float* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
+                               int num_levels, void* workspace, cudaStream_t st) {
+  char* ws = static_cast<char*>(workspace);
+  int* err = reinterpret_cast<int*>(ws);
+  ws += 256;
+  DB200_CUDA(cudaMemsetAsync(err, 0, sizeof(int), st));
+  const int HW = ht * wd;
+  auto take = [&ws](size_t bytes) { char* p = ws; ws += align_up256(bytes); return reinterpret_cast<float*>(p); };
+  const size_t n1 = size_t(N) * C * HW;
+  float* f1full = take(n1 * 4); float* f1hi = take(n1 * 4); float* f1lo = take(n1 * 4);
+  {
+    dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+    transpose_cl_f32_kernel<<<grid, 256, 0, st>>>(fmap1, f1full, C, HW);
+    DB200_CHECK_LAUNCH();
+    split_tf32_kernel<<<kNumSMs * 8, 256, 0, st>>>(f1full, f1hi, f1lo, n1);
+    DB200_CHECK_LAUNCH();
+  }
+  CUtensorMap tmAhi, tmAlo;
+  if (!make_map_f32(&tmAhi, f1hi, uint64_t(N) * HW, C) || !make_map_f32(&tmAlo, f1lo, uint64_t(N) * HW, C)) return DB200_ERR_CUDA;
+  static bool attr = false;
+  if (!attr) { DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemTF32))); attr = true; }
+  const float* prev = nullptr;
+  int h = ht, w = wd;
+  for (int l = 0; l < num_levels; l++) {
+    const size_t n2e = size_t(N) * C * h * w;
+    float* full = take(n2e * 4); float* hi = take(n2e * 4); float* lo = take(n2e * 4);
+    if (l == 0) {
+      dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+      transpose_cl_f32_kernel<<<grid, 256, 0, st>>>(fmap2, full, C, HW);
+    } else {
+      const int blocks = int((n2e + 255) / 256 < 2368 ? (n2e + 255) / 256 : 2368);
+      pool_cl_f32_kernel<<<blocks, 256, 0, st>>>(prev, full, N, h << 1, w << 1, C);
+    }
+    DB200_CHECK_LAUNCH();
+    split_tf32_kernel<<<kNumSMs * 8, 256, 0, st>>>(full, hi, lo, n2e);
+    DB200_CHECK_LAUNCH();
+    const int N2 = h * w;
+    CUtensorMap tmBhi, tmBlo, tmO;
+    if (!make_map_f32(&tmBhi, hi, uint64_t(N) * N2, C) || !make_map_f32(&tmBlo, lo, uint64_t(N) * N2, C) ||
+        !make_out_map_f32(&tmO, levels_out[l], N2, HW, N))
+      return DB200_ERR_CUDA;
+    const long long tiles = static_cast<long long>(N) * cdiv(HW, kTM) * cdiv(N2, kTN);
+    const int grid = int(tiles < kNumSMs ? tiles : kNumSMs);
+    corr_gemm_tc_tf32_kernel<<<grid, kPipeThreadsTC, kSmemTF32, st>>>(tmAhi, tmAlo, tmBhi, tmBlo, tmO, HW, N2, N, err);
+    DB200_CHECK_LAUNCH();
+    prev = full;
     h >>= 1; w >>= 1;
   }
   return DB200_OK;

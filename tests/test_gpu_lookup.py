@@ -177,3 +177,24 @@ def test_corr_volume_pyramid_full_size_f16():
         err = float((outs[l].float() - ref).abs().max())
         assert err <= 3e-3 * scale * 4, (l, err)
         b = torch.nn.functional.avg_pool2d(b, 2, stride=2)
+
+
+def test_corr_volume_pyramid_full_size_f32():
+    """fp32 volumes (training path) through the 3xTF32 tcgen05 pipeline against torch's fp32 matmul + avg_pool2d
+    (corr.py:30-38,63-71): within 1e-4 relative of the value scale, i.e. fp32-faithful, not TF32-grade (1e-3)."""
+    import droid_backends
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    N, C, ht, wd = 3, 128, 48, 64
+    f1 = torch.randn((N, C, ht, wd), device="cuda", generator=g)
+    f2 = torch.randn((N, C, ht, wd), device="cuda", generator=g)
+    outs = droid_backends.corr_volume_pyramid(f1, f2, 4)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    a = (f1.double() / 4).reshape(N, C, ht * wd)
+    corr = torch.matmul(a.transpose(1, 2), (f2.double() / 4).reshape(N, C, -1)).reshape(N * ht * wd, 1, ht, wd)
+    scale = np.sqrt(C) / 16.0
+    for l in range(4):
+        ref = corr.reshape(N, ht, wd, ht >> l, wd >> l)
+        assert outs[l].shape == ref.shape and outs[l].dtype == torch.float32
+        err = float((outs[l].double() - ref).abs().max())
+        assert err <= 1e-4 * scale, (l, err)                 # measured ~2e-6: the dropped lo*lo terms and fp32 accumulation
+        corr = torch.nn.functional.avg_pool2d(corr, 2, stride=2)
