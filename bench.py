@@ -137,6 +137,21 @@ def main_reference(args, rank):
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
+def _load_ref_ext():
+    """The unmodified reference CUDA extension (baseline/_ref, built by baseline/build_ref_cuda.sh) or None."""
+    import glob
+    import importlib
+    refdir = os.path.join(REPO, "baseline", "_ref")
+    if not glob.glob(os.path.join(refdir, "droid_backends_ref*.so")):
+        return None
+    try:
+        if refdir not in sys.path:
+            sys.path.insert(0, refdir)
+        return importlib.import_module("droid_backends_ref")
+    except Exception:
+        return None
+
+
 def lookup_bench(dev, steps, warmup, hbm_peak):
     """Secondary metric: fused 4-level radius-3 CorrBlock lookup on f16 volumes, 96 edges x 48x64 (c2 window).
     One lookup = one (edge, pixel) producing all 4x49 outputs; algorithmic bytes 912 B/lookup."""
@@ -161,8 +176,22 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
     ms = ev[0].elapsed_time(ev[1]) / steps
     lookups = N * ht * wd
     gbs = lookups * 912 / (ms * 1e-3) / 1e9
+    ref_ms = None
+    ref = _load_ref_ext()
+    if ref is not None:                      # CorrBlock.__call__ as the reference runs it: 4 launches + cat (corr.py:40-50)
+        try:
+            cl = [(coords / 2 ** l).contiguous() for l in range(4)]
+            fn = lambda: torch.cat([ref.corr_index_forward(levels[l], cl[l], 3)[0].view(N, -1, ht, wd) for l in range(4)], 1)
+            fn(); torch.cuda.synchronize()
+            ev[0].record()
+            for _ in range(5):
+                fn()
+            ev[1].record(); torch.cuda.synchronize()
+            ref_ms = ev[0].elapsed_time(ev[1]) / 5
+        except Exception:
+            ref_ms = None
     return dict(metric="corr lookups/s (fused 4-level r=3, f16 volumes, 96 edges x 48x64; volumes 2.4 GB > L2)",
-                value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_launch=ms,
+                value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_launch=ms, reference_cuda_ms=ref_ms,
                 roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
                               algorithmic_bytes_per_launch=lookups * 912))
 
@@ -269,7 +298,20 @@ def graph_bench(p, dev, steps=5):
     ev[2].record()
     torch.cuda.synchronize()
     fd_ms, px_ms = ev[0].elapsed_time(ev[1]) / steps, ev[1].elapsed_time(ev[2]) / steps
-    return dict(frame_distance=dict(pairs=int(ii.numel()), ms_per_call=fd_ms, value=ii.numel() / (fd_ms * 1e-3), unit="pairs/s"),
+    ref_ms = None
+    ref = _load_ref_ext()
+    if ref is not None:
+        try:
+            ref.frame_distance(poses, disps, intr, ii, jj, 0.25); torch.cuda.synchronize()
+            ev[0].record()
+            for _ in range(steps):
+                ref.frame_distance(poses, disps, intr, ii, jj, 0.25)
+            ev[1].record(); torch.cuda.synchronize()
+            ref_ms = ev[0].elapsed_time(ev[1]) / steps
+        except Exception:
+            ref_ms = None
+    return dict(frame_distance=dict(pairs=int(ii.numel()), ms_per_call=fd_ms, value=ii.numel() / (fd_ms * 1e-3), unit="pairs/s",
+                                    reference_cuda_ms=ref_ms),
                 proximity_edges=dict(keyframes=int(n), ms_per_call=px_ms, edges_selected=int(gi.numel()),
                                      what="add_proximity_factors edge list on the GPU (rad=2, nms=2, beta=0.25, thresh=16)"))
 
@@ -335,8 +377,28 @@ def volume_bench(dev, steps, warmup, hbm_peak):
     in_bytes = 2 * N * C_ * hw * 2
     flops = 2.0 * N * hw * C_ * sum((ht >> l) * (wd >> l) for l in range(4))
     gbs = (out_bytes + in_bytes) / (ms * 1e-3) / 1e9
+
+    def ref_build():                         # CorrBlock.__init__ of the reference in f16 (corr.py:23-38,63-71): cuBLAS + 3 avg_pool2d
+        a = (f1.reshape(N, C_, hw) / 4.0).transpose(1, 2)
+        c = torch.matmul(a, f2.reshape(N, C_, hw) / 4.0).reshape(N * hw, 1, ht, wd)
+        lv = [c]
+        for _ in range(3):
+            c = torch.nn.functional.avg_pool2d(c, 2, stride=2)
+            lv.append(c)
+        return lv
+    ref_ms = None
+    try:
+        ref_build(); torch.cuda.synchronize()
+        ev[0].record()
+        for _ in range(5):
+            ref_build()
+        ev[1].record(); torch.cuda.synchronize()
+        ref_ms = ev[0].elapsed_time(ev[1]) / 5
+    except Exception:
+        pass
     return dict(metric="CorrBlock build edges/s (all-pairs 128-d GEMM + 4-level pyramid, f16, 48 edges x 48x64)",
                 value=N / (ms * 1e-3), unit="edges/s", ms_per_call=ms, tflops=flops / (ms * 1e-3) / 1e12,
+                reference_torch_ms=ref_ms,
                 roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
                               algorithmic_bytes_per_call=out_bytes + in_bytes))
 

@@ -8,6 +8,7 @@
 // documented in oracle/oracle.cpp, read from the reference's SASS).  Intrinsics (__fmaf_rn/__fmul_rn/
 // __fadd_rn) pin the contraction so that nvcc cannot re-associate.  One CTA per pair, 256 threads; the
 // disparity map of frame i (12 KB) is L1/L2 resident across the up-to-t pairs that share it.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace db200 {
@@ -101,6 +102,99 @@ frame_distance_kernel(const float* __restrict__ poses, const float* __restrict__
   const float tt = fd_block_reduce(total, sred);
   const float vv = fd_block_reduce(valid, sred);
   if (threadIdx.x == 0) dist[b] = (double(vv) / (double(tt) + 1e-8) < 0.75) ? 1000.0f : __fdiv_rn(a, vv);
+}
+
+// Batched variant for maps of at most NPIX*256 pixels: one CTA walks kFdBatch consecutive pairs.  Everything that does
+// not depend on the pair is hoisted out of the pair loop — the two IEEE divisions of the back-projection per pixel, the
+// pixel coordinates, the `total` sum and its reduction (it is the same constant for every pair), and the disparity
+// map while consecutive pairs share their source frame (meshgrid order) — and `accum`/`valid` go through ONE pass of the
+// reference's reduction tree instead of three.  Every value is produced by the same operations in the same order as in
+// frame_distance_kernel above, so the results are bit-identical.
+constexpr int kFdBatch = 8;
+
+template <int NPIX>
+__global__ void __launch_bounds__(256, 3)
+frame_distance_batch_kernel(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+                            const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int K, int n_poses, int B, int ht,
+                            int wd, float beta, float* __restrict__ dist) {
+  __shared__ float sa[256], sv[256];
+  const int t = threadIdx.x;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const float omb = fa(1.0f, -beta);
+  const int HW = ht * wd;
+  float X0[NPIX], X1[NPIX], U[NPIX], V[NPIX], D[NPIX];
+  float total = 0.0f;
+#pragma unroll
+  for (int m = 0; m < NPIX; m++) {
+    const int k = t + 256 * m;
+    const int i = k / wd, j = k - i * wd;
+    U[m] = float(j); V[m] = float(i);
+    X0[m] = __fdiv_rn(fa(U[m], -cx), fx);
+    X1[m] = __fdiv_rn(fa(V[m], -cy), fy);
+    D[m] = 0.0f;
+    if (k < HW) { total = fa(total, beta); total = fa(total, omb); }
+  }
+  const float tt = fd_block_reduce(total, sa);          // thread 0 holds the reference's `total` (pair independent)
+  int cur_ix = -1;
+  const int b0 = blockIdx.x * kFdBatch;
+  for (int g = 0; g < kFdBatch; g++) {
+    const int b = b0 + g;
+    if (b >= K) break;
+    const int ix = int(ii[b]), jx = int(jj[b]);
+    if (ix < 0 || jx < 0 || ix >= n_poses || jx >= n_poses || ix >= B) {
+      if (t == 0) dist[b] = __int_as_float(0x7fc00000);
+      continue;
+    }
+    if (ix != cur_ix) {
+      const float* dsp = disps + size_t(ix) * HW;
+#pragma unroll
+      for (int m = 0; m < NPIX; m++) { const int k = t + 256 * m; D[m] = (k < HW) ? dsp[k] : 0.0f; }
+      cur_ix = ix;
+    }
+    float tij[3], q[4];
+    fd_rel(poses + 7 * ix, poses + 7 * ix + 3, poses + 7 * jx, poses + 7 * jx + 3, tij, q);
+    float accum = 0.0f, valid = 0.0f;
+#pragma unroll
+    for (int m = 0; m < NPIX; m++) {
+      if (t + 256 * m < HW) {
+        const float x0 = X0[m], x1 = X1[m], u = U[m], v = V[m], d = D[m];
+        float uv0 = ff(-q[2], x1, q[1]); uv0 = fa(uv0, uv0);
+        float uv1 = ff(q[2], x0, -q[0]); uv1 = fa(uv1, uv1);
+        float uv2 = ff(q[0], x1, -fm(q[1], x0)); uv2 = fa(uv2, uv2);
+        float Y0 = fa(ff(q[3], uv0, x0), ff(q[1], uv2, -fm(q[2], uv1)));
+        float Y1 = fa(ff(q[3], uv1, x1), ff(q[2], uv0, -fm(q[0], uv2)));
+        float Y2 = fa(ff(q[3], uv2, 1.0f), ff(q[0], uv1, -fm(q[1], uv0)));
+        const float p0 = fm(tij[0], d), p1 = fm(tij[1], d), p2 = fm(tij[2], d);
+        Y0 = fa(Y0, p0); Y1 = fa(Y1, p1); Y2 = fa(Y2, p2);
+        float du = fa(ff(fx, __fdiv_rn(Y0, Y2), cx), -u);
+        float dv = fa(ff(fy, __fdiv_rn(Y1, Y2), cy), -v);
+        float dd = __fsqrt_rn(ff(du, du, fm(dv, dv)));
+        if (Y2 > 0.25f) { accum = ff(dd, beta, accum); valid = fa(valid, beta); }
+        const float Z0 = fa(p0, x0), Z1 = fa(p1, x1), Z2 = fa(p2, 1.0f);
+        du = fa(ff(fx, __fdiv_rn(Z0, Z2), cx), -u);
+        dv = fa(ff(fy, __fdiv_rn(Z1, Z2), cy), -v);
+        dd = __fsqrt_rn(ff(du, du, fm(dv, dv)));
+        if (Z2 > 0.25f) { accum = ff(omb, dd, accum); valid = fa(valid, omb); }
+      }
+    }
+    // both quantities through the reference's tree (256 -> 128 -> 64 -> 32 -> shuffles) in one pass
+    sa[t] = accum; sv[t] = valid;
+    __syncthreads();
+    if (t < 128) { sa[t] = fa(sa[t], sa[t + 128]); sv[t] = fa(sv[t], sv[t + 128]); }
+    __syncthreads();
+    if (t < 64) { sa[t] = fa(sa[t], sa[t + 64]); sv[t] = fa(sv[t], sv[t + 64]); }
+    __syncthreads();
+    if (t < 32) {
+      float a = fa(sa[t], sa[t + 32]), vv = fa(sv[t], sv[t + 32]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        a = fa(a, __shfl_down_sync(0xffffffffu, a, o));
+        vv = fa(vv, __shfl_down_sync(0xffffffffu, vv, o));
+      }
+      if (t == 0) dist[b] = (double(vv) / (double(tt) + 1e-8) < 0.75) ? 1000.0f : __fdiv_rn(a, vv);
+    }
+    __syncthreads();
+  }
 }
 
 // points[n,i,j,:] = (G_n X)_{xyz} / X_w   (droid_kernels.cu:779-850)
@@ -264,8 +358,16 @@ extern "C" int db200_frame_distance(const float* poses, const float* disps, cons
   if (!poses || !disps || !intrinsics || !dist || K < 0 || ht <= 0 || wd <= 0 || n_poses <= 0 || B <= 0) return DB200_ERR_ARG;
   if (K == 0) return DB200_OK;
   if (!ii || !jj) return DB200_ERR_ARG;
-  frame_distance_kernel<<<K, 256, 0, static_cast<cudaStream_t>(stream)>>>(poses, disps, intrinsics, ii, jj, K, n_poses, B, ht,
-                                                                         wd, beta, dist);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  static const bool no_batch = getenv("DB200_FD_NO_BATCH") != nullptr;
+  const int npix = cdiv(ht * wd, 256);
+  const int nb = cdiv(K, kFdBatch);
+  if (!no_batch && npix <= 12 && K >= 4 * kFdBatch * kNumSMs) {       // enough pairs to fill the GPU with batched CTAs
+    if (npix <= 10) frame_distance_batch_kernel<10><<<nb, 256, 0, st>>>(poses, disps, intrinsics, ii, jj, K, n_poses, B, ht, wd, beta, dist);
+    else frame_distance_batch_kernel<12><<<nb, 256, 0, st>>>(poses, disps, intrinsics, ii, jj, K, n_poses, B, ht, wd, beta, dist);
+  } else {
+    frame_distance_kernel<<<K, 256, 0, st>>>(poses, disps, intrinsics, ii, jj, K, n_poses, B, ht, wd, beta, dist);
+  }
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

@@ -194,6 +194,34 @@ def test_frame_distance_bit_exact(beta):
     np.testing.assert_array_equal(np.argsort(out, kind="stable"), np.argsort(ref, kind="stable"))
 
 
+@pytest.mark.parametrize("ht,wd", [(48, 64), (40, 64), (24, 32)])
+def test_frame_distance_batched_kernel_bit_exact(ht, wd):
+    """Enough pairs (>= 4736) to take the batched kernel (8 pairs per CTA, pair-independent work hoisted): still every
+    bit of the oracle, for the 48x64 and the fork's 40x64 map sizes, ragged pair count, pairs that change their source
+    frame inside a batch, an invalid index and the 1000.0 branch."""
+    import droid_backends
+    from oracle import oracle
+    from droid_b200 import synth
+    n = 72
+    ii0, jj0 = synth.neighborhood_edges(0, n, 2)
+    p = synth.make_ba_problem(ii0, jj0, n, ht=ht, wd=wd, seed=31)
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    ii, jj = ii.reshape(-1).astype(np.int64), jj.reshape(-1).astype(np.int64)
+    rng = np.random.default_rng(2)
+    perm = rng.permutation(len(ii))[:1003]                       # + a ragged tail of pairs in random order
+    ii, jj = np.concatenate([ii, ii[perm]]), np.concatenate([jj, jj[perm]])
+    assert len(ii) >= 4736 and len(ii) % 8 != 0
+    disps = p.disps.copy(); disps[5] = 1e3
+    ref = oracle.frame_distance(p.poses, disps, p.intrinsics, ii, jj, 0.25)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    out = droid_backends.frame_distance(t(p.poses), t(disps), t(p.intrinsics), t(ii), t(jj), 0.25).cpu().numpy()
+    assert (ref == 1000.0).any() and (ref != 1000.0).any()
+    np.testing.assert_array_equal(out.view(np.uint32), ref.view(np.uint32))
+    ii[17] = n + 3                                               # out of range: NaN for that pair only
+    out2 = droid_backends.frame_distance(t(p.poses), t(disps), t(p.intrinsics), t(ii), t(jj), 0.25).cpu().numpy()
+    assert np.isnan(out2[17]) and np.array_equal(np.delete(out2, 17).view(np.uint32), np.delete(ref, 17).view(np.uint32))
+
+
 def test_iproj_depth_filter():
     import droid_backends
     from oracle import oracle
