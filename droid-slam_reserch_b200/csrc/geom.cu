@@ -119,6 +119,20 @@ frame_distance_batch_kernel(const float* __restrict__ poses, const float* __rest
                             int wd, float beta, float* __restrict__ dist) {
   __shared__ float sa[256], sv[256];
   const int t = threadIdx.x;
+  {                                                      // a batch without a single valid pair (callers mark pairs whose
+    bool any = false;                                    // result they will discard with a negative index) costs nothing
+    for (int g = 0; g < kFdBatch; g++) {
+      const int b = blockIdx.x * kFdBatch + g;
+      if (b < K) {
+        const long long ix = ii[b], jx = jj[b];
+        any |= !(ix < 0 || jx < 0 || ix >= n_poses || jx >= n_poses || ix >= B);
+      }
+    }
+    if (!any) {
+      if (t < kFdBatch && blockIdx.x * kFdBatch + t < K) dist[blockIdx.x * kFdBatch + t] = __int_as_float(0x7fc00000);
+      return;
+    }
+  }
   const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
   const float omb = fa(1.0f, -beta);
   const int HW = ht * wd;

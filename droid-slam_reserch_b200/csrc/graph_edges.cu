@@ -34,8 +34,12 @@ __device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); 
 __global__ void prox_pairs_kernel(ProxParams p, int64_t* __restrict__ ii, int64_t* __restrict__ jj) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= p.K) return;
-  ii[k] = p.t0 + k / p.cols;
-  jj[k] = p.t1 + k % p.cols;
+  const int i = p.t0 + k / p.cols, j = p.t1 + k % p.cols;
+  // cells that factor_graph.py:328 overwrites with inf (ii - rad < jj) are never looked at: mark them invalid so that
+  // frame_distance skips them (it returns NaN there; prox_mask_kernel writes the inf)
+  const bool masked = (i - p.rad < j);
+  ii[k] = masked ? -1 : i;
+  jj[k] = masked ? -1 : j;
 }
 
 // steps 1 (average) + 2 + cell index values for the sort
