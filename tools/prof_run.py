@@ -13,7 +13,7 @@ import droid_backends  # noqa: E402
 from droid_b200 import synth  # noqa: E402
 
 dev = torch.device("cuda", 0)
-what = sys.argv[1:] or ["ba", "lookup", "volume"]
+what = sys.argv[1:] or ["ba", "lookup", "volume", "volume32", "fd"]
 if "ba" in what:
     p = synth.config_c3()
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
@@ -37,5 +37,21 @@ if "volume" in what:
     f2 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
     for _ in range(2):
         droid_backends.corr_volume_pyramid(f1, f2, 4)
+    torch.cuda.synchronize()
+if "volume32" in what:
+    N, C_, ht, wd = 24, 128, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(12)
+    f1 = torch.randn((N, C_, ht, wd), device=dev, generator=g)
+    f2 = torch.randn((N, C_, ht, wd), device=dev, generator=g)
+    for _ in range(2):
+        droid_backends.corr_volume_pyramid(f1, f2, 4)
+    torch.cuda.synchronize()
+if "fd" in what:
+    p = synth.config_c3(n_edges=2000)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    n = p.t1
+    ii, jj = torch.meshgrid(torch.arange(n), torch.arange(n), indexing="ij")
+    for _ in range(2):
+        droid_backends.frame_distance(t(p.poses), t(p.disps), t(p.intrinsics), ii.reshape(-1).to(dev), jj.reshape(-1).to(dev), 0.25)
     torch.cuda.synchronize()
 print("prof_run ok", what)
