@@ -50,7 +50,7 @@ struct BAHeader {
 };
 
 struct BALayout {
-  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, Lstage, total;
+  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, Lstage, Xstage, total;
   int n, nt, ld, Mcap;
 };
 
@@ -84,6 +84,7 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.xsol = take(sizeof(double) * size_t(L.ld));
   L.dx = take(sizeof(float) * size_t(L.n));
   L.Lstage = take(sizeof(double) * size_t(L.nt) * chol_stage_doubles());   // streamed diagonal factors (ba_solve.cu)
+  L.Xstage = take(sizeof(double) * size_t(L.nt) * kCholTile * kCholTile);   // streamed sub-diagonal tiles of the chain
   L.total = o;
   return L;
 }
@@ -96,7 +97,7 @@ struct BAParams {
   int own_lo, own_hi;   // owned source frames [own_lo, own_hi) (edge-sharded multi-GPU runs; 0, B otherwise)
   // workspace views
   BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
-  float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx; double* Lstage;
+  float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx; double* Lstage; double* Xstage;
   int n, nt, ld, Mcap;
 };
 
@@ -120,6 +121,7 @@ inline BAParams ba_params(const BALayout& L, void* ws) {
   p.xsol = reinterpret_cast<double*>(b + L.xsol);
   p.dx = reinterpret_cast<float*>(b + L.dx);
   p.Lstage = reinterpret_cast<double*>(b + L.Lstage);
+  p.Xstage = reinterpret_cast<double*>(b + L.Xstage);
   p.n = L.n; p.nt = L.nt; p.ld = L.ld; p.Mcap = L.Mcap;
   return p;
 }

@@ -16,6 +16,9 @@ namespace db200 {
 
 constexpr int T = kCholTile;        // 64
 constexpr int TP = T + 1;           // padded row stride of the shared tiles (doubles)
+constexpr int TQ = T + 4;           // row stride of the cp.async-staged operand tiles: rows 16-byte aligned, and the DMMA
+                                    // fragment loads (8 rows x 4 consecutive doubles per warp; bank shift 8 words per row)
+                                    // are conflict-free per half warp
 constexpr int kCholThreads = 256;
 constexpr unsigned kSpinLimit = 1u << 24;   // bounded waits: a broken dependency raises an error instead of hanging the GPU
 
@@ -103,6 +106,9 @@ __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   unsigned long long* stage = reinterpret_cast<unsigned long long*>(p.Lstage);
   const size_t nstage = size_t(p.nt) * chol_stage_doubles();
   for (size_t i = gtid; i < nstage; i += gstride) stage[i] = kStageEmpty;
+  unsigned long long* xstage = reinterpret_cast<unsigned long long*>(p.Xstage);
+  const size_t nxstage = size_t(p.nt) * T * T;
+  for (size_t i = gtid; i < nxstage; i += gstride) xstage[i] = kStageEmpty;
   for (size_t i = gtid; i < total; i += gstride) {
     const int r = int(i / ld), c = int(i - size_t(r) * ld);
     double v = 0.0;
@@ -199,6 +205,78 @@ __device__ __forceinline__ void tile_aat_lower(const double (*A)[TP], double (&a
 #pragma unroll
       for (int b = 0; b <= a; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
   }
+}
+
+// ---- cp.async-staged operand tiles of the trailing updates (double-buffered: the next tile's operands travel while
+// the current product runs; the update is otherwise half memory phase, half FP64 phase) ---------------------------
+__device__ __forceinline__ void cp_async16_cg(unsigned dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// global tile (row-major, stride ld) -> shared [T][TQ], 8 x 16 bytes per thread, L1-bypassing
+__device__ __forceinline__ void cp_async_tile(double (*S)[TQ], const double* g, int ld) {
+  const unsigned s0 = static_cast<unsigned>(__cvta_generic_to_shared(&S[0][0]));
+#pragma unroll
+  for (int t = 0; t < 8; t++) {
+    const int c = threadIdx.x + kCholThreads * t, r = c >> 5, q = c & 31;
+    cp_async16_cg(s0 + unsigned(r * TQ + 2 * q) * 8u, g + size_t(r) * ld + 2 * q);
+  }
+}
+// ---- the trailing-update product on the FP64 tensor-core path (DMMA) ----------------------------------------------
+// mma.sync.m8n8k4.f64 runs at the full FP64 rate of the SM (measured: 64 FMA/clk/SM, tools/mb_tile.cu) with 1/8 of the
+// instructions of the DFMA formulation, which leaves issue slots for the shared/global traffic around it: the DFMA
+// product reaches 62 % of that rate with 8 warps per SM, and every memory instruction beside it costs extra time.
+// Warp w = (wr = w >> 2, wc = w & 3) owns rows 32 wr .. +31, columns 16 wc .. +15 of the 64x64 result as 4 x 2 tiles of
+// 8x8; lane = 4 g + t holds acc[mi][ni][0..1] = C[32 wr + 8 mi + g][16 wc + 8 ni + 2 t + {0,1}].
+struct MmaPos {
+  int wr, wc, g, t;
+  __device__ __forceinline__ MmaPos() {
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    wr = w >> 2; wc = w & 3; g = lane >> 2; t = lane & 3;
+  }
+  __device__ __forceinline__ int row(int mi) const { return 32 * wr + 8 * mi + g; }
+  __device__ __forceinline__ int col(int ni) const { return 16 * wc + 8 * ni + 2 * t; }
+  // on a diagonal tile only the block-lower part is needed: warps that lie entirely above the diagonal rest
+  __device__ __forceinline__ bool active(bool diag) const { return !diag || 16 * wc <= 32 * wr + 31; }
+};
+__device__ __forceinline__ void dmma884(double (&d)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
+}
+// acc = A B^T (A, B: [T][TQ] shared tiles, k along the rows' columns)
+__device__ __forceinline__ void tile_abt_mma(const double (*A)[TQ], const double (*B)[TQ], double (&acc)[4][2][2], const MmaPos& mp,
+                                             bool diag) {
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+    for (int ni = 0; ni < 2; ni++) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+  if (!mp.active(diag)) return;
+  const double* pa = &A[32 * mp.wr + mp.g][mp.t];
+  const double* pb = &B[16 * mp.wc + mp.g][mp.t];
+#pragma unroll 4
+  for (int k0 = 0; k0 < T; k0 += 4) {
+    double a[4], b[2];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++) a[mi] = pa[mi * 8 * TQ + k0];
+#pragma unroll
+    for (int ni = 0; ni < 2; ni++) b[ni] = pb[ni * 8 * TQ + k0];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 2; ni++) dmma884(acc[mi][ni], a[mi], b[ni]);
+  }
+}
+// this thread's part of a global tile in the DMMA accumulator layout (16-byte accesses, L1-bypassing)
+__device__ __forceinline__ void load_frag_mma(double (&c)[4][2][2], const double* g, int ld, const MmaPos& mp) {
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+    for (int ni = 0; ni < 2; ni++) {
+      const double2 v = __ldcg(reinterpret_cast<const double2*>(g + size_t(mp.row(mi)) * ld + mp.col(ni)));
+      c[mi][ni][0] = v.x; c[mi][ni][1] = v.y;
+    }
 }
 
 // ---- 64x64 tile factorisation / triangular solve with the tile held in REGISTERS -------------------------
@@ -428,9 +506,11 @@ __device__ __forceinline__ void frag_syrk8(double (&cd)[4][4], const double (*X)
 // once, any number of readers).  C as register fragments `cf`; X ends up in shared `X`.  With SYRK, the diagonal tile
 // `cd` of the chain takes its rank-8 update X_P X_P^T right behind every solved panel, so that when the last panel of
 // L(s,s) appears only one panel's worth of work separates it from the next factorisation.
+// The chain (SYRK) additionally streams every solved panel X_P of L(d,d-1) to `xout` (write-once words like `stage`): the
+// NEXT chain CTA applies it to its sub-diagonal tile panel by panel (stream_gemm) instead of waiting for the whole tile.
 template <bool SYRK>
 __device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][4], double (*X)[TP], double (*L)[TP], double* rinv,
-                                            const double* stage, unsigned* err) {
+                                            const double* stage, unsigned* err, double* xout = nullptr) {
   StreamRegs sr;
   stream_issue(sr, stage, 0);
 #pragma unroll 1
@@ -445,8 +525,58 @@ __device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][
     }
     trsm_solve(X, L, rinv, c0);
     __syncthreads();
+    if (SYRK && xout != nullptr) {
+#pragma unroll
+      for (int t = 0; t < 2; t++) {
+        const int e = threadIdx.x + kCholThreads * t, r = e >> 3, q = e & 7;
+        st_relaxed_f64(xout + r * T + c0 + q, X[r][c0 + q]);
+      }
+    }
     frag_rank8_sw<false>(P, cf, X, L);
     if (SYRK) frag_syrk8(cd, X, c0);
+  }
+  __syncthreads();
+  return true;
+}
+
+// cf -= A B^T with B (= L(s,s-1), solved by the previous chain CTA) arriving 64x8 panel by panel through `xstage`;
+// A (= L(d,s-1)) complete in shared memory, B lands in `Bm`.  One barrier per panel (panels occupy disjoint columns).
+__device__ __forceinline__ bool stream_gemm(double (&cf)[4][4], const double (*A)[TP], double (*Bm)[TP], const double* xstage,
+                                            unsigned* err) {
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  StreamRegs sr;
+  stream_issue(sr, xstage, 0);
+#pragma unroll 1
+  for (int P = 0; P < 8; P++) {
+    const int c0 = 8 * P;
+    int fail = 0;
+#pragma unroll
+    for (int t = 0; t < 2; t++) {
+      const double* src = stream_addr(xstage, c0, t);
+      unsigned long long v = sr.v[t];
+      unsigned spins = 0;
+      while (v == kStageEmpty) {
+        if (++spins > kSpinLimit || ((spins & 1023u) == 0 && ld_acquire(err) != 0)) { fail = 1; break; }
+        v = ld_relaxed_u64(src);
+      }
+      const int e = threadIdx.x + kCholThreads * t;
+      Bm[e >> 3][c0 + (e & 7)] = __longlong_as_double(static_cast<long long>(v));
+    }
+    if (P < 7) stream_issue(sr, xstage, c0 + 8);
+    if (__syncthreads_or(fail)) {
+      if (threadIdx.x == 0) atomicExch(err, 1u);
+      return false;
+    }
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      double pv[4], qv[4];
+#pragma unroll
+      for (int a = 0; a < 4; a++) { pv[a] = A[ty + 16 * a][c0 + q]; qv[a] = Bm[tx + 16 * a][c0 + q]; }
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) cf[a][b] = fma(-pv[a], qv[b], cf[a][b]);
+    }
   }
   __syncthreads();
   return true;
@@ -463,7 +593,10 @@ __device__ __forceinline__ void trace_mark(int s, int e) {
 }
 
 struct CholCtx {
-  double (*sA)[TP]; double (*sB)[TP]; double (*sC)[TP]; double* sv; int* s_ok;
+  double (*sA)[TP]; double (*sB)[TP]; double* sv; int* s_ok;
+  unsigned char* q0;                             // cp.async stages of the trailing updates ([2] x {A,B} x [T][TQ]); sA/sB alias stage 0
+  __device__ __forceinline__ double (*qA(int buf) const)[TQ] { return reinterpret_cast<double (*)[TQ]>(q0 + size_t(2 * buf) * sizeof(double) * T * TQ); }
+  __device__ __forceinline__ double (*qB(int buf) const)[TQ] { return reinterpret_cast<double (*)[TQ]>(q0 + size_t(2 * buf + 1) * sizeof(double) * T * TQ); }
   double* W; const double* stage; CholFlags F; int nt, ld, n; bool panel_full;
 };
 
@@ -536,6 +669,124 @@ __device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
   return true;
 }
 
+// The tiles a CTA owns at step s, in index order; a diagonal tile j >= s+2 is followed by its sub-diagonal companion.
+struct TileWalk {
+  int idx, j, second, s, G, nt, ntiles;
+  __device__ __forceinline__ void start(int s_, int cta, int G_, int nt_) {
+    s = s_; G = G_; nt = nt_; ntiles = num_tiles(nt_);
+    const int cs = colstart(s_, nt_);
+    idx = cs + ((cta - cs) % G_ + G_) % G_;
+    j = s_; second = -1;
+  }
+  __device__ __forceinline__ bool next(int& ti, int& tj) {
+    if (second >= 0) { ti = second; tj = second - 1; second = -1; return true; }
+    for (; idx < ntiles; idx += G) {
+      while (idx >= colstart(j + 1, nt)) j++;
+      const int i = j + (idx - colstart(j, nt));
+      if (i == j + 1 && i < nt) continue;           // sub-diagonal tiles travel with their diagonal tile
+      if (i == j) {
+        if (j <= s + 1) continue;                   // (s,s) is final, (s+1,s+1) belongs to the chain
+        ti = j; tj = j; second = j; idx += G;
+        return true;
+      }
+      ti = i; tj = j; idx += G;
+      return true;
+    }
+    return false;
+  }
+};
+
+__device__ __forceinline__ bool poll_panel_full(CholCtx& cx, int k) {
+  if (threadIdx.x == 0) *cx.s_ok = (ld_acquire(cx.F.panel_done + k) >= unsigned(cx.nt + 1 - k)) ? 1 : 0;
+  __syncthreads();
+  const bool full = *cx.s_ok != 0;
+  __syncthreads();
+  return full;
+}
+__device__ __forceinline__ void stage_operands(CholCtx& cx, int i, int j, int k, int buf) {
+  cp_async_tile(cx.qA(buf), tile_ptr(cx, i, k), cx.ld);
+  if (i != j) cp_async_tile(cx.qB(buf), tile_ptr(cx, j, k), cx.ld);
+  cp_async_commit_group();
+}
+
+// Step s > 0 for the generic tiles of one CTA: panel s-1 is applied to every owned tile with j >= s; tiles of block column
+// s are then solved against L(s,s) (streamed) and published.  Operands of tile t+1 are staged while tile t is computed
+// (once block column s-1 is known to be complete — before that, per-tile ready flags are awaited as before).
+__device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G) {
+  const int k = s - 1, ck = colstart(k, cx.nt), cs = colstart(s, cx.nt);
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  TileWalk w;
+  w.start(s, cta, G, cx.nt);
+  int ci, cj, ni = 0, nj = 0;
+  if (!w.next(ci, cj)) return true;
+  bool full = poll_panel_full(cx, k);
+  bool cur_staged = false;
+  int buf = 0;
+  if (full) { stage_operands(cx, ci, cj, k, 0); cur_staged = true; }
+  bool have = true;
+  const MmaPos mp;
+  while (have) {
+    double cm[4][2][2], acc[4][2][2];
+    double* Cg = tile_ptr(cx, ci, cj);
+    const bool diag = ci == cj;
+    if (mp.active(diag)) load_frag_mma(cm, Cg, cx.ld, mp);       // in flight while the product runs
+    if (!cur_staged) {
+      if (!full) {
+        if (!wait_flag(cx.F.ready + ck + (ci - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+        if (!diag && !wait_flag(cx.F.ready + ck + (cj - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+      }
+      stage_operands(cx, ci, cj, k, buf);
+    }
+    const bool have_next = w.next(ni, nj);
+    bool next_staged = false;
+    if (have_next) {
+      if (!full) full = poll_panel_full(cx, k);
+      if (full) { stage_operands(cx, ni, nj, k, buf ^ 1); next_staged = true; }
+    }
+    if (next_staged) cp_async_wait_group<1>(); else cp_async_wait_group<0>();
+    __syncthreads();
+    tile_abt_mma(cx.qA(buf), diag ? cx.qA(buf) : cx.qB(buf), acc, mp, diag);
+    if (cj > s) {
+      if (mp.active(diag)) {
+#pragma unroll
+        for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+          for (int ni2 = 0; ni2 < 2; ni2++)
+            __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * cx.ld + mp.col(ni2)),
+                   make_double2(cm[mi][ni2][0] - acc[mi][ni2][0], cm[mi][ni2][1] - acc[mi][ni2][1]));
+      }
+      __syncthreads();                             // stage `buf` is free again (it is refilled two tiles later)
+    } else {
+      // a tile of block column s: into the solver's fragment layout through shared memory (stage `buf` is dead after the
+      // product), then the triangular solve follows the factorisation of L(s,s) panel by panel (stream_trsm)
+      __syncthreads();
+      double (*X)[TP] = reinterpret_cast<double (*)[TP]>(cx.qA(buf));
+      double (*L)[TP] = reinterpret_cast<double (*)[TP]>(cx.qB(buf));
+#pragma unroll
+      for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+        for (int ni2 = 0; ni2 < 2; ni2++) {
+          X[mp.row(mi)][mp.col(ni2)] = cm[mi][ni2][0] - acc[mi][ni2][0];
+          X[mp.row(mi)][mp.col(ni2) + 1] = cm[mi][ni2][1] - acc[mi][ni2][1];
+        }
+      __syncthreads();
+      double cf[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) cf[a][b] = X[ty + 16 * a][tx + 16 * b];
+      __syncthreads();
+      const double* stage = cx.stage + size_t(s) * chol_stage_doubles();
+      if (!stream_trsm<false>(cf, cf, X, L, cx.sv, stage, cx.F.ctl)) return false;
+      store_tile(Cg, X, cx.ld);
+      publish(cx.F.ready + cs + (ci - s), cx.F.panel_done + s);
+      __syncthreads();
+    }
+    have = have_next; ci = ni; cj = nj; cur_staged = next_staged; buf ^= 1;
+  }
+  return true;
+}
+
 // ---- the solver: ONE cooperative launch ------------------------------------------------------------------
 // Static tile ownership + release/acquire ready flags instead of grid barriers or per-step launches.
 //   owner(i,j) = idx(i,j) mod G, except that the sub-diagonal tile (d,d-1) belongs to the owner D(d) of the
@@ -560,10 +811,11 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_ok;
   CholCtx cx;
-  cx.sA = reinterpret_cast<double (*)[TP]>(smem_raw);
-  cx.sB = reinterpret_cast<double (*)[TP]>(smem_raw + sizeof(double) * T * TP);
-  cx.sC = reinterpret_cast<double (*)[TP]>(smem_raw + 2 * sizeof(double) * T * TP);
-  cx.sv = reinterpret_cast<double*>(smem_raw + 3 * sizeof(double) * T * TP);   // [6*64] scratch vectors
+  constexpr size_t kStageBytes = sizeof(double) * T * TQ;
+  cx.q0 = smem_raw;
+  cx.sA = reinterpret_cast<double (*)[TP]>(smem_raw);                  // [T][TP] views of stage 0 (chain, back-substitution)
+  cx.sB = reinterpret_cast<double (*)[TP]>(smem_raw + kStageBytes);
+  cx.sv = reinterpret_cast<double*>(smem_raw + 4 * kStageBytes);       // [6*64] scratch vectors
   cx.s_ok = &s_ok;
   cx.W = p.Wk; cx.stage = p.Lstage; cx.nt = p.nt; cx.ld = p.ld; cx.n = p.n;
   cx.F = chol_flags(p.cflags, p.nt);
@@ -593,9 +845,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
       if (s > 0) {
         const int k = s - 1, ck = colstart(k, nt);
         if (!wait_flag(F.ready + ck + (d - k), 1u, F.ctl, &s_ok)) return;
-        if (!wait_flag(F.ready + ck + (s - k), 1u, F.ctl, &s_ok)) return;
         load_tile(cx.sA, tile_ptr(cx, d, k), ld);
-        load_tile(cx.sB, tile_ptr(cx, s, k), ld);
         __syncthreads();
         double acc[4][4];
         tile_aat_lower(cx.sA, acc);
@@ -603,18 +853,15 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
         for (int a = 0; a < 4; a++)
 #pragma unroll
           for (int b = 0; b < 4; b++) cd[a][b] -= acc[a][b];
-        tile_abt(cx.sA, cx.sB, acc);
-#pragma unroll
-        for (int a = 0; a < 4; a++)
-#pragma unroll
-          for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
-        __syncthreads();
+        trace_mark(s, 7);
+        // (d,s) -= L(d,s-1) L(s,s-1)^T with L(s,s-1) streamed from the previous chain CTA while it is being solved
+        if (!stream_gemm(cf, cx.sA, cx.sB, p.Xstage + size_t(s) * T * T, F.ctl)) return;
       }
       trace_mark(s, 6);
       // L(s,s) arrives panel by panel from the CTA that is factoring it; the triangular solve and the update of
       // (d,d) keep pace one panel behind, so only the last panel's work is left when that factorisation ends
       const double* stage = p.Lstage + size_t(s) * chol_stage_doubles();
-      if (!stream_trsm<true>(cf, cd, cx.sA, cx.sB, cx.sv, stage, F.ctl)) return;
+      if (!stream_trsm<true>(cf, cd, cx.sA, cx.sB, cx.sv, stage, F.ctl, p.Xstage + size_t(d) * T * T)) return;
       trace_mark(s, 5);
       store_tile(tile_ptr(cx, d, s), cx.sA, ld);
 #pragma unroll
@@ -631,19 +878,14 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
       __syncthreads();
     }
     // generic tiles of this CTA
-    int idx = cs + ((cta - cs) % G + G) % G;        // first owned tile index >= colstart(s)
-    int j = s;
-    for (; idx < ntiles; idx += G) {
-      while (idx >= colstart(j + 1, nt)) j++;
-      const int i = j + (idx - colstart(j, nt));
-      if (i == j + 1 && i < nt) continue;           // sub-diagonal tiles travel with their diagonal tile
-      if (i == j) {
-        if (j <= s + 1) continue;                   // (s,s) is final, (s+1,s+1) was handled by the chain code above
-        if (!process_tile(cx, j, j, s)) return;     // diagonal tile j >= s+2 ...
-        if (!process_tile(cx, j, j - 1, s)) return; // ... and its sub-diagonal companion (j-1 > s: trailing update)
-        continue;
-      }
-      if (!process_tile(cx, i, j, s)) return;
+    if (s > 0) {
+      if (!generic_step(cx, s, cta, G)) return;
+    } else {
+      TileWalk w;
+      w.start(0, cta, G, nt);
+      int i, j;
+      while (w.next(i, j))
+        if (!process_tile(cx, i, j, 0)) return;
     }
   }
 
@@ -810,7 +1052,7 @@ static int chol_grid_size(size_t smem) {
 int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   chol_prepare_kernel<<<4 * kNumSMs, 256, 0, st>>>(p, lm, ep);
   DB200_CHECK_LAUNCH();
-  const size_t smem = 3 * sizeof(double) * T * TP + sizeof(double) * 6 * 64;
+  const size_t smem = 4 * sizeof(double) * T * TQ + sizeof(double) * 6 * 64;
   int grid = chol_grid_size(smem);
   if (grid < 1) { db200_note_cuda_error(int(cudaGetLastError()), __FILE__, __LINE__); return DB200_ERR_CUDA; }
   const int ntiles = num_tiles(p.nt);
