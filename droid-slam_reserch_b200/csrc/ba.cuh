@@ -79,7 +79,8 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.Q = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
   L.w = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
   L.Hb = take(sizeof(double) * (size_t(L.n) * L.n + L.n));
-  L.Wk = take(sizeof(double) * size_t(L.ld + kCholTile) * L.ld);   // [A; b^T] -> [L; y^T] in place (lower, row-major)
+  // [A; b^T] -> [L; y^T] in place: lower block triangle + the rhs block row, tile-major, tiles of [64][64+4] (ba_solve.cu)
+  L.Wk = take(sizeof(double) * (size_t(L.nt) * (L.nt + 3) / 2) * kCholTile * (kCholTile + 4));
   L.cflags = take(sizeof(unsigned) * chol_flag_words(L.nt));
   L.xsol = take(sizeof(double) * size_t(L.ld));
   L.dx = take(sizeof(float) * size_t(L.n));

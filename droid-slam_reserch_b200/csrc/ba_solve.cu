@@ -96,7 +96,6 @@ __device__ __forceinline__ void publish(unsigned* flag, unsigned* counter, int s
 // ---- A + damping -> work matrix; rhs appended as block row nt; flags cleared ---------------------------
 __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   const int n = p.n, ld = p.ld;
-  const size_t total = size_t(ld + T) * ld;
   const double* H = p.Hb;
   const double* b = p.Hb + size_t(n) * n;
   const size_t gtid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, gstride = size_t(gridDim.x) * blockDim.x;
@@ -109,20 +108,31 @@ __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   unsigned long long* xstage = reinterpret_cast<unsigned long long*>(p.Xstage);
   const size_t nxstage = size_t(p.nt) * T * T;
   for (size_t i = gtid; i < nxstage; i += gstride) xstage[i] = kStageEmpty;
-  for (size_t i = gtid; i < total; i += gstride) {
-    const int r = int(i / ld), c = int(i - size_t(r) * ld);
-    double v = 0.0;
-    if (r < n) {
-      if (c <= r) {
-        v = H[size_t(r) * n + c];
-        if (c == r) v += double(ep) + double(lm) * v;        // diag += ep + lm*diag  (droid_kernels.cu:1197)
+  // tile-major work matrix: tile (i,j), j <= i <= nt, is one contiguous [T][TQ] block (the shared-memory image of the
+  // staged operand tiles, so that ONE bulk copy moves a tile); pad columns are never read by the arithmetic
+  const int nt = p.nt;
+  const int ntl = num_tiles(nt);
+  for (int tl = blockIdx.x; tl < ntl; tl += gridDim.x) {
+    int j = 0;
+    while (tl >= colstart(j + 1, nt)) j++;
+    const int i = j + (tl - colstart(j, nt));
+    double* dst = p.Wk + size_t(tl) * (T * TQ);
+    for (int e = threadIdx.x; e < T * T; e += blockDim.x) {
+      const int rr = e >> 6, cc = e & 63;
+      const int r = i * T + rr, c = j * T + cc;
+      double v = 0.0;
+      if (r < n) {
+        if (c <= r) {
+          v = H[size_t(r) * n + c];
+          if (c == r) v += double(ep) + double(lm) * v;      // diag += ep + lm*diag  (droid_kernels.cu:1197)
+        }
+      } else if (r < ld) {
+        v = (c == r) ? 1.0 : 0.0;                           // identity padding up to the tile size
+      } else if (r == ld) {
+        v = (c < n) ? b[c] : 0.0;                           // rhs rides along as an extra row: its factor row is y = L^-1 b
       }
-    } else if (r < ld) {
-      v = (c == r) ? 1.0 : 0.0;                             // identity padding up to the tile size
-    } else if (r == ld) {
-      v = (c < n) ? b[c] : 0.0;                             // rhs rides along as an extra row: its factor row is y = L^-1 b
+      dst[rr * TQ + cc] = v;
     }
-    p.Wk[i] = v;
   }
 }
 
@@ -207,24 +217,41 @@ __device__ __forceinline__ void tile_aat_lower(const double (*A)[TP], double (&a
   }
 }
 
-// ---- cp.async-staged operand tiles of the trailing updates (double-buffered: the next tile's operands travel while
-// the current product runs; the update is otherwise half memory phase, half FP64 phase) ---------------------------
-__device__ __forceinline__ void cp_async16_cg(unsigned dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+// ---- operand tiles of the trailing updates, staged by the bulk-copy engine (TMA, 1D rows) -------------------------------
+// Two stages: while the tensor-core product of tile t runs, warp 0's copies for tiles t+1 / t+2 are in flight (64 rows of
+// 512 B per tile, two rows per lane, completion on one mbarrier per stage).  No thread spends issue slots on the copies
+// beyond those few instructions — with 8 warps per SM every memory instruction beside the product costs time.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+  unsigned ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void bulk_copy_row(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
-// global tile (row-major, stride ld) -> shared [T][TQ], 8 x 16 bytes per thread, L1-bypassing
-__device__ __forceinline__ void cp_async_tile(double (*S)[TQ], const double* g, int ld) {
-  const unsigned s0 = static_cast<unsigned>(__cvta_generic_to_shared(&S[0][0]));
-#pragma unroll
-  for (int t = 0; t < 8; t++) {
-    const int c = threadIdx.x + kCholThreads * t, r = c >> 5, q = c & 31;
-    cp_async16_cg(s0 + unsigned(r * TQ + 2 * q) * 8u, g + size_t(r) * ld + 2 * q);
+// thread 0: global tile(s) -> shared stage.  A tile is the same contiguous [T][TQ] image in both places (tile-major work
+// matrix), so one bulk copy moves it; B == nullptr for a diagonal tile (A A^T)
+constexpr unsigned kTileBytes = unsigned(sizeof(double) * T * TQ);
+__device__ __forceinline__ void bulk_stage_tiles(double (*SA)[TQ], double (*SB)[TQ], const double* A, const double* B, unsigned bar) {
+  if (threadIdx.x == 0) {
+    fence_proxy_async();            // the tiles were written through the generic proxy (by other CTAs; acquired via flags)
+    mbar_arrive_expect_tx(bar, (B != nullptr ? 2u : 1u) * kTileBytes);
+    bulk_copy_row(smem_u32(&SA[0][0]), A, kTileBytes, bar);
+    if (B != nullptr) bulk_copy_row(smem_u32(&SB[0][0]), B, kTileBytes, bar);
   }
 }
+
 // ---- the trailing-update product on the FP64 tensor-core path (DMMA) ----------------------------------------------
 // mma.sync.m8n8k4.f64 runs at the full FP64 rate of the SM (measured: 64 FMA/clk/SM, tools/mb_tile.cu) with 1/8 of the
 // instructions of the DFMA formulation, which leaves issue slots for the shared/global traffic around it: the DFMA
@@ -594,13 +621,14 @@ __device__ __forceinline__ void trace_mark(int s, int e) {
 
 struct CholCtx {
   double (*sA)[TP]; double (*sB)[TP]; double* sv; int* s_ok;
+  unsigned bar0;                                 // shared address of the two stage mbarriers (8 bytes apart)
   unsigned char* q0;                             // cp.async stages of the trailing updates ([2] x {A,B} x [T][TQ]); sA/sB alias stage 0
   __device__ __forceinline__ double (*qA(int buf) const)[TQ] { return reinterpret_cast<double (*)[TQ]>(q0 + size_t(2 * buf) * sizeof(double) * T * TQ); }
   __device__ __forceinline__ double (*qB(int buf) const)[TQ] { return reinterpret_cast<double (*)[TQ]>(q0 + size_t(2 * buf + 1) * sizeof(double) * T * TQ); }
   double* W; const double* stage; CholFlags F; int nt, ld, n; bool panel_full;
 };
 
-__device__ __forceinline__ double* tile_ptr(const CholCtx& cx, int i, int j) { return cx.W + size_t(i) * T * cx.ld + size_t(j) * T; }
+__device__ __forceinline__ double* tile_ptr(const CholCtx& cx, int i, int j) { return cx.W + size_t(colstart(j, cx.nt) + (i - j)) * (T * TQ); }
 
 // acc = L(i,s-1) L(j,s-1)^T (waits until both panel tiles are final).  Uses sA (and sB when i != j).
 __device__ __forceinline__ bool apply_panel(CholCtx& cx, int i, int j, int s, double (&acc)[4][4]) {
@@ -704,49 +732,68 @@ __device__ __forceinline__ bool poll_panel_full(CholCtx& cx, int k) {
   return full;
 }
 __device__ __forceinline__ void stage_operands(CholCtx& cx, int i, int j, int k, int buf) {
-  cp_async_tile(cx.qA(buf), tile_ptr(cx, i, k), cx.ld);
-  if (i != j) cp_async_tile(cx.qB(buf), tile_ptr(cx, j, k), cx.ld);
-  cp_async_commit_group();
+  bulk_stage_tiles(cx.qA(buf), cx.qB(buf), tile_ptr(cx, i, k), i != j ? tile_ptr(cx, j, k) : nullptr, cx.bar0 + 8u * unsigned(buf));
+}
+// all threads: wait until stage `buf` has landed (bounded).  false = give up (the error word is raised)
+__device__ __forceinline__ bool stage_wait(CholCtx& cx, int buf, unsigned parity) {
+  const unsigned bar = cx.bar0 + 8u * unsigned(buf);
+  unsigned spins = 0;
+  int fail = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > kSpinLimit) { fail = 1; break; }
+  }
+  if (__syncthreads_or(fail)) {
+    if (threadIdx.x == 0) atomicExch(cx.F.ctl, 1u);
+    return false;
+  }
+  return true;
 }
 
 // Step s > 0 for the generic tiles of one CTA: panel s-1 is applied to every owned tile with j >= s; tiles of block column
-// s are then solved against L(s,s) (streamed) and published.  Operands of tile t+1 are staged while tile t is computed
-// (once block column s-1 is known to be complete — before that, per-tile ready flags are awaited as before).
-__device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G) {
+// s are then solved against L(s,s) (streamed) and published.  The operands of the next two tiles travel while a product runs
+// (once block column s-1 is known to be complete — before that, per-tile ready flags are awaited tile by tile).
+// `ph` = the phase parities of the two stage mbarriers (bit b = stage b), carried across steps.
+__device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G, unsigned& ph) {
   const int k = s - 1, ck = colstart(k, cx.nt), cs = colstart(s, cx.nt);
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
   TileWalk w;
   w.start(s, cta, G, cx.nt);
-  int ci, cj, ni = 0, nj = 0;
-  if (!w.next(ci, cj)) return true;
+  int ai, aj, bi = 0, bj = 0, ci = 0, cj = 0;
+  if (!w.next(ai, aj)) return true;
+  bool have_a = true, have_b = w.next(bi, bj);
   bool full = poll_panel_full(cx, k);
-  bool cur_staged = false;
+  fence_proxy_async();                             // the chain used stage 0 through the generic proxy
+  __syncthreads();
+  bool a_iss = false, b_iss = false;
   int buf = 0;
-  if (full) { stage_operands(cx, ci, cj, k, 0); cur_staged = true; }
-  bool have = true;
+  if (full) {
+    stage_operands(cx, ai, aj, k, 0); a_iss = true;
+    if (have_b) { stage_operands(cx, bi, bj, k, 1); b_iss = true; }
+  }
   const MmaPos mp;
-  while (have) {
+  while (have_a) {
     double cm[4][2][2], acc[4][2][2];
-    double* Cg = tile_ptr(cx, ci, cj);
-    const bool diag = ci == cj;
+    double* Cg = tile_ptr(cx, ai, aj);
+    const bool diag = ai == aj;
     if (mp.active(diag)) load_frag_mma(cm, Cg, cx.ld, mp);       // in flight while the product runs
-    if (!cur_staged) {
+    if (!a_iss) {
       if (!full) {
-        if (!wait_flag(cx.F.ready + ck + (ci - k), 1u, cx.F.ctl, cx.s_ok)) return false;
-        if (!diag && !wait_flag(cx.F.ready + ck + (cj - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+        if (!wait_flag(cx.F.ready + ck + (ai - k), 1u, cx.F.ctl, cx.s_ok)) return false;
+        if (!diag && !wait_flag(cx.F.ready + ck + (aj - k), 1u, cx.F.ctl, cx.s_ok)) return false;
       }
-      stage_operands(cx, ci, cj, k, buf);
+      stage_operands(cx, ai, aj, k, buf);
     }
-    const bool have_next = w.next(ni, nj);
-    bool next_staged = false;
-    if (have_next) {
-      if (!full) full = poll_panel_full(cx, k);
-      if (full) { stage_operands(cx, ni, nj, k, buf ^ 1); next_staged = true; }
-    }
-    if (next_staged) cp_async_wait_group<1>(); else cp_async_wait_group<0>();
-    __syncthreads();
+    if (!stage_wait(cx, buf, (ph >> buf) & 1u)) return false;
+    ph ^= 1u << buf;
     tile_abt_mma(cx.qA(buf), diag ? cx.qA(buf) : cx.qB(buf), acc, mp, diag);
-    if (cj > s) {
+    const bool have_c = have_b && w.next(ci, cj);
+    bool c_iss = false;
+    if (aj > s) {
+      __syncthreads();                             // stage `buf` is free again: send the tile after next into it
+      if (have_c) {
+        if (!full) full = poll_panel_full(cx, k);
+        if (full) { stage_operands(cx, ci, cj, k, buf); c_iss = true; }
+      }
       if (mp.active(diag)) {
 #pragma unroll
         for (int mi = 0; mi < 4; mi++)
@@ -755,7 +802,6 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G)
             __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * cx.ld + mp.col(ni2)),
                    make_double2(cm[mi][ni2][0] - acc[mi][ni2][0], cm[mi][ni2][1] - acc[mi][ni2][1]));
       }
-      __syncthreads();                             // stage `buf` is free again (it is refilled two tiles later)
     } else {
       // a tile of block column s: into the solver's fragment layout through shared memory (stage `buf` is dead after the
       // product), then the triangular solve follows the factorisation of L(s,s) panel by panel (stream_trsm)
@@ -779,10 +825,17 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G)
       const double* stage = cx.stage + size_t(s) * chol_stage_doubles();
       if (!stream_trsm<false>(cf, cf, X, L, cx.sv, stage, cx.F.ctl)) return false;
       store_tile(Cg, X, cx.ld);
-      publish(cx.F.ready + cs + (ci - s), cx.F.panel_done + s);
+      publish(cx.F.ready + cs + (ai - s), cx.F.panel_done + s);
+      fence_proxy_async();                         // generic-proxy writes to the stage before the copy engine refills it
       __syncthreads();
+      if (have_c) {
+        if (!full) full = poll_panel_full(cx, k);
+        if (full) { stage_operands(cx, ci, cj, k, buf); c_iss = true; }
+      }
     }
-    have = have_next; ci = ni; cj = nj; cur_staged = next_staged; buf ^= 1;
+    have_a = have_b; ai = bi; aj = bj; a_iss = b_iss;
+    have_b = have_c; bi = ci; bj = cj; b_iss = c_iss;
+    buf ^= 1;
   }
   return true;
 }
@@ -810,16 +863,25 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G)
 __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_ok;
+  __shared__ __align__(8) unsigned long long s_bar[2];
   CholCtx cx;
   constexpr size_t kStageBytes = sizeof(double) * T * TQ;
   cx.q0 = smem_raw;
+  cx.bar0 = smem_u32(&s_bar[0]);
+  if (threadIdx.x == 0) {
+    mbar_init(cx.bar0, 1u);
+    mbar_init(cx.bar0 + 8u, 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  unsigned stage_phase = 0u;
   cx.sA = reinterpret_cast<double (*)[TP]>(smem_raw);                  // [T][TP] views of stage 0 (chain, back-substitution)
   cx.sB = reinterpret_cast<double (*)[TP]>(smem_raw + kStageBytes);
   cx.sv = reinterpret_cast<double*>(smem_raw + 4 * kStageBytes);       // [6*64] scratch vectors
   cx.s_ok = &s_ok;
-  cx.W = p.Wk; cx.stage = p.Lstage; cx.nt = p.nt; cx.ld = p.ld; cx.n = p.n;
+  cx.W = p.Wk; cx.stage = p.Lstage; cx.nt = p.nt; cx.ld = TQ; cx.n = p.n;      // ld = row stride inside a tile
   cx.F = chol_flags(p.cflags, p.nt);
-  const int nt = p.nt, ld = p.ld, n = p.n;
+  const int nt = p.nt, ld = TQ, n = p.n;
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
   const int ntiles = num_tiles(nt);
   const CholFlags& F = cx.F;
@@ -879,7 +941,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     }
     // generic tiles of this CTA
     if (s > 0) {
-      if (!generic_step(cx, s, cta, G)) return;
+      if (!generic_step(cx, s, cta, G, stage_phase)) return;
     } else {
       TileWalk w;
       w.start(0, cta, G, nt);
@@ -935,7 +997,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     sv[64 + tid] = part;
     __syncthreads();
     if (tid < T) {
-      const double y = __ldcg(cx.W + size_t(ld) * ld + size_t(j) * T + tid);
+      const double y = __ldcg(tile_ptr(cx, nt, j) + tid);
       sv[tid] = y - ((sv[64 + tid] + sv[128 + tid]) + (sv[192 + tid] + sv[256 + tid]));
     }
     __syncthreads();

@@ -2,6 +2,7 @@
 // self-check of the DMMA fragment layout against the DFMA product.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 --expt-relaxed-constexpr -o tools/mb_tile tools/mb_tile.cu
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 #include <cmath>
 #include "../droid-slam_reserch_b200/csrc/ba_solve.cu"
@@ -19,52 +20,59 @@ __global__ void __launch_bounds__(256, 1) mb_kernel(long long* out, double* W, d
   auto qB = [&](int b) { return reinterpret_cast<double (*)[TQ]>(smem_raw + size_t(2 * b + 1) * kStageBytes); };
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
   const MmaPos mp;
-  auto tile = [&](int r, int which) { return W + size_t((blockIdx.x * 131 + r * 17 + which * 7919) % ntile) * 4096; };
+  __shared__ __align__(8) unsigned long long s_bar[2];
+  const unsigned bar0 = smem_u32(&s_bar[0]);
+  if (threadIdx.x == 0) { mbar_init(bar0, 1u); mbar_init(bar0 + 8u, 1u); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  unsigned ph = 0;
+  auto issue = [&](int b, const double* A, const double* B) { bulk_stage_tiles(qA(b), qB(b), A, B, bar0 + 8u * b); };
+  auto wait = [&](int b) { while (!mbar_try_wait(bar0 + 8u * b, (ph >> b) & 1u)) {} ph ^= 1u << b; };
+  auto tile = [&](int r, int which) { return W + size_t((blockIdx.x * 131 + r * 17 + which * 7919) % ntile) * (T * TQ); };
   __syncthreads();
   long long t0 = clock64();
   double acc[4][4], cf[4][4], am[4][2][2], cm[4][2][2];
   double sink = 0.0;
   if (mode == 0) {            // DFMA product only
-    load_tile(sA, tile(0, 0), 64); load_tile(sB, tile(0, 1), 64); __syncthreads();
+    load_tile(sA, tile(0, 0), TQ); load_tile(sB, tile(0, 1), TQ); __syncthreads();
     t0 = clock64();
     for (int r = 0; r < reps; r++) { tile_abt(sA, sB, acc); for (int a = 0; a < 4; a++) for (int b = 0; b < 4; b++) sink += acc[a][b]; __syncthreads(); }
   } else if (mode == 1) {     // DMMA product only
-    cp_async_tile(qA(0), tile(0, 0), 64); cp_async_tile(qB(0), tile(0, 1), 64); cp_async_commit_group(); cp_async_wait_group<0>(); __syncthreads();
+    issue(0, tile(0, 0), tile(0, 1)); wait(0); __syncthreads();
     t0 = clock64();
     for (int r = 0; r < reps; r++) { tile_abt_mma(qA(0), qB(0), am, mp, false); for (int a = 0; a < 4; a++) for (int b = 0; b < 2; b++) sink += am[a][b][0] + am[a][b][1]; __syncthreads(); }
   } else if (mode == 2) {     // the old generic update: loads, DFMA product, store — serial
     for (int r = 0; r < reps; r++) {
       double* Cg = tile(r, 2);
-      load_frag(cf, Cg, 64);
-      load_tile(sA, tile(r, 0), 64); load_tile(sB, tile(r, 1), 64); __syncthreads();
+      load_frag(cf, Cg, TQ);
+      load_tile(sA, tile(r, 0), TQ); load_tile(sB, tile(r, 1), TQ); __syncthreads();
       tile_abt(sA, sB, acc); __syncthreads();
-      for (int a = 0; a < 4; a++) for (int b = 0; b < 4; b++) __stcg(Cg + size_t(ty + 16 * a) * 64 + tx + 16 * b, cf[a][b] - 1e-9 * acc[a][b]);
+      for (int a = 0; a < 4; a++) for (int b = 0; b < 4; b++) __stcg(Cg + size_t(ty + 16 * a) * TQ + tx + 16 * b, cf[a][b] - 1e-9 * acc[a][b]);
     }
-  } else if (mode == 3) {     // double-buffered cp.async + DMMA (generic_step)
+  } else if (mode == 3) {     // bulk-copy staged (two tiles ahead) + DMMA (generic_step)
     int buf = 0;
-    cp_async_tile(qA(0), tile(0, 0), 64); cp_async_tile(qB(0), tile(0, 1), 64); cp_async_commit_group();
+    issue(0, tile(0, 0), tile(0, 1));
+    if (reps > 1) issue(1, tile(1, 0), tile(1, 1));
     for (int r = 0; r < reps; r++) {
       double* Cg = tile(r, 2);
-      load_frag_mma(cm, Cg, 64, mp);
-      if (r + 1 < reps) { cp_async_tile(qA(buf ^ 1), tile(r + 1, 0), 64); cp_async_tile(qB(buf ^ 1), tile(r + 1, 1), 64); cp_async_commit_group(); cp_async_wait_group<1>(); }
-      else cp_async_wait_group<0>();
-      __syncthreads();
+      load_frag_mma(cm, Cg, TQ, mp);
+      wait(buf);
       tile_abt_mma(qA(buf), qB(buf), am, mp, false);
-      for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++)
-        __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * 64 + mp.col(ni)), make_double2(cm[mi][ni][0] - 1e-9 * am[mi][ni][0], cm[mi][ni][1] - 1e-9 * am[mi][ni][1]));
       __syncthreads();
+      if (r + 2 < reps) issue(buf, tile(r + 2, 0), tile(r + 2, 1));
+      for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++)
+        __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * TQ + mp.col(ni)), make_double2(cm[mi][ni][0] - 1e-9 * am[mi][ni][0], cm[mi][ni][1] - 1e-9 * am[mi][ni][1]));
       buf ^= 1;
     }
   } else if (mode == 4) {     // self-check: chk[0] = A B^T by DFMA, chk[1] = by DMMA (CTA 0 only)
     if (blockIdx.x == 0) {
-      load_tile(sA, W, 64); load_tile(sB, W + 4096, 64); __syncthreads();
+      load_tile(sA, W, TQ); load_tile(sB, W + T * TQ, TQ); __syncthreads();
       tile_abt(sA, sB, acc); __syncthreads();
       for (int a = 0; a < 4; a++) for (int b = 0; b < 4; b++) chk[(ty + 16 * a) * 64 + tx + 16 * b] = acc[a][b];
-      cp_async_tile(qA(0), W, 64); cp_async_tile(qB(0), W + 4096, 64); cp_async_commit_group(); cp_async_wait_group<0>(); __syncthreads();
+      issue(0, W, W + T * TQ); wait(0); __syncthreads();
       tile_abt_mma(qA(0), qB(0), am, mp, false);
       for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++) {
-        chk[4096 + mp.row(mi) * 64 + mp.col(ni)] = am[mi][ni][0];
-        chk[4096 + mp.row(mi) * 64 + mp.col(ni) + 1] = am[mi][ni][1];
+        chk[4096 + mp.row(mi) * TQ + mp.col(ni)] = am[mi][ni][0];
+        chk[4096 + mp.row(mi) * TQ + mp.col(ni) + 1] = am[mi][ni][1];
       }
     }
   }
@@ -74,31 +82,32 @@ __global__ void __launch_bounds__(256, 1) mb_kernel(long long* out, double* W, d
   if (sink == 1.2345) out[1000] = 1;
 }
 
-int main() {
+int main(int argc, char** argv) {
+  const int grid = argc > 1 ? atoi(argv[1]) : 148;
   const int ntile = 1200, reps = 40;
   double *W, *chk; long long* out;
-  cudaMalloc(&W, sizeof(double) * 4096 * ntile);
+  cudaMalloc(&W, sizeof(double) * T * TQ * ntile);
   cudaMalloc(&chk, sizeof(double) * 8192);
   cudaMalloc(&out, sizeof(long long) * 2048);
-  std::vector<double> h(size_t(4096) * ntile);
+  std::vector<double> h(size_t(T * TQ) * ntile);
   for (size_t i = 0; i < h.size(); i++) h[i] = 1e-3 * double((i * 2654435761u) % 1000) - 0.4;
   cudaMemcpy(W, h.data(), h.size() * 8, cudaMemcpyHostToDevice);
   const size_t smem = 4 * sizeof(double) * T * TQ + 1024;
   cudaFuncSetAttribute(mb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-  const char* names[] = {"DFMA product", "DMMA product", "serial update, DFMA (round-1 solver)", "cp.async double-buffered DMMA update", "self-check"};
+  const char* names[] = {"DFMA product", "DMMA product", "serial update, DFMA (round-1 solver)", "bulk-copy staged (2 ahead) DMMA update", "self-check"};
   for (int mode = 0; mode < 5; mode++) {
     for (int it = 0; it < 3; it++) {
       cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
       cudaEventRecord(e0);
-      mb_kernel<<<148, 256, smem>>>(out, W, chk, ntile, reps, mode);
+      mb_kernel<<<grid, 256, smem>>>(out, W, chk, ntile, reps, mode);
       cudaEventRecord(e1);
       cudaError_t err = cudaDeviceSynchronize();
       if (err != cudaSuccess) { printf("error %s\n", cudaGetErrorString(err)); return 1; }
       float ms; cudaEventElapsedTime(&ms, e0, e1);
-      std::vector<long long> c(148);
-      cudaMemcpy(c.data(), out, 148 * 8, cudaMemcpyDeviceToHost);
+      std::vector<long long> c(grid);
+      cudaMemcpy(c.data(), out, grid * 8, cudaMemcpyDeviceToHost);
       double mean = 0; long long mx = 0; for (auto v : c) { mean += double(v); if (v > mx) mx = v; }
-      mean /= 148;
+      mean /= grid;
       if (it == 2 && mode < 4) printf("%-40s: %8.0f cycles/tile (max CTA %8.0f), kernel %.3f ms -> %.2f us/tile\n", names[mode], mean / reps, double(mx) / reps, ms, 1e3 * ms / reps);
     }
   }
