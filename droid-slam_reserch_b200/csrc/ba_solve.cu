@@ -697,27 +697,52 @@ __device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
   return true;
 }
 
+// Tile ownership (static: a tile is only ever updated by its owner, so the trailing updates need no flags).
+//   nd "diagonal" CTAs own every diagonal tile (d,d) together with its sub-diagonal companion (d,d-1): CTA d % nd runs the
+//   panel chain of step d-1 and the trailing updates of its pairs.  The chain costs its CTA ~28 us per step; spread over
+//   CTAs that own no other tiles it does not turn one CTA per step into a straggler whose column tile everybody else
+//   waits for (round 1: owner = idx mod G for all tiles, chain CTA = owner of (d,d); step period 30 us where the FP64
+//   work needs 20).  The other G - nd CTAs own the remaining tiles, tile idx -> CTA nd + idx mod (G - nd).
+//   nd = 0 (small grids): the old scheme.
+__host__ __device__ inline int chol_num_diag_ctas(int G, int nt) {
+  if (G < 64 || nt < 8) return 0;
+  int nd = (4 * G + nt / 2) / nt;                  // balances 2 (nt-s)/nd pair updates against (nt-s)^2 / (2 (G-nd)) tiles
+  return nd < 2 ? 2 : (nd > 16 ? 16 : nd);
+}
+__device__ __forceinline__ int chain_owner(int d, int G, int nt, int nd) { return nd > 0 ? d % nd : colstart(d, nt) % G; }
+
 // The tiles a CTA owns at step s, in index order; a diagonal tile j >= s+2 is followed by its sub-diagonal companion.
 struct TileWalk {
-  int idx, j, second, s, G, nt, ntiles;
-  __device__ __forceinline__ void start(int s_, int cta, int G_, int nt_) {
-    s = s_; G = G_; nt = nt_; ntiles = num_tiles(nt_);
-    const int cs = colstart(s_, nt_);
-    idx = cs + ((cta - cs) % G_ + G_) % G_;
-    j = s_; second = -1;
+  int idx, j, second, s, stride, nt, ntiles, nd, dnext;
+  __device__ __forceinline__ void start(int s_, int cta, int G, int nt_, int nd_) {
+    s = s_; nt = nt_; nd = nd_; ntiles = num_tiles(nt_); second = -1; j = s_;
+    dnext = -1;
+    if (nd_ > 0 && cta < nd_) {                     // a diagonal CTA: pairs d = cta (mod nd), d >= s+2
+      dnext = s_ + 2 + ((cta - (s_ + 2)) % nd_ + nd_) % nd_;
+      idx = ntiles; stride = 1;
+      return;
+    }
+    stride = G - nd_;
+    const int cs = colstart(s_, nt_), r = cta - nd_;
+    idx = cs + ((r - cs) % stride + stride) % stride;
   }
   __device__ __forceinline__ bool next(int& ti, int& tj) {
     if (second >= 0) { ti = second; tj = second - 1; second = -1; return true; }
-    for (; idx < ntiles; idx += G) {
+    if (dnext >= 0) {
+      if (dnext >= nt) return false;
+      ti = dnext; tj = dnext; second = dnext; dnext += nd;
+      return true;
+    }
+    for (; idx < ntiles; idx += stride) {
       while (idx >= colstart(j + 1, nt)) j++;
       const int i = j + (idx - colstart(j, nt));
       if (i == j + 1 && i < nt) continue;           // sub-diagonal tiles travel with their diagonal tile
       if (i == j) {
-        if (j <= s + 1) continue;                   // (s,s) is final, (s+1,s+1) belongs to the chain
-        ti = j; tj = j; second = j; idx += G;
+        if (nd > 0 || j <= s + 1) continue;         // diagonal CTAs' tiles; (s,s) is final, (s+1,s+1) belongs to the chain
+        ti = j; tj = j; second = j; idx += stride;
         return true;
       }
-      ti = i; tj = j; idx += G;
+      ti = i; tj = j; idx += stride;
       return true;
     }
     return false;
@@ -753,11 +778,11 @@ __device__ __forceinline__ bool stage_wait(CholCtx& cx, int buf, unsigned parity
 // s are then solved against L(s,s) (streamed) and published.  The operands of the next two tiles travel while a product runs
 // (once block column s-1 is known to be complete — before that, per-tile ready flags are awaited tile by tile).
 // `ph` = the phase parities of the two stage mbarriers (bit b = stage b), carried across steps.
-__device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G, unsigned& ph) {
+__device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G, int nd, unsigned& ph) {
   const int k = s - 1, ck = colstart(k, cx.nt), cs = colstart(s, cx.nt);
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
   TileWalk w;
-  w.start(s, cta, G, cx.nt);
+  w.start(s, cta, G, cx.nt, nd);
   int ai, aj, bi = 0, bj = 0, ci = 0, cj = 0;
   if (!w.next(ai, aj)) return true;
   bool have_a = true, have_b = w.next(bi, bj);
@@ -883,7 +908,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   cx.F = chol_flags(p.cflags, p.nt);
   const int nt = p.nt, ld = TQ, n = p.n;
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
-  const int ntiles = num_tiles(nt);
+  const int nd = chol_num_diag_ctas(G, nt);
   const CholFlags& F = cx.F;
 
   for (int s = 0; s < nt; s++) {
@@ -899,7 +924,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
       __syncthreads();
     }
     const int d = s + 1;
-    if (d < nt && cta == colstart(d, nt) % G) {     // the panel chain of this step
+    if (d < nt && cta == chain_owner(d, G, nt, nd)) {     // the panel chain of this step
       double cf[4][4], cd[4][4];
       // [a]+[b] diagonal tile (d,d) and sub-diagonal tile (d,s): panel s-1, with L(d,s-1) loaded once for both
       load_frag(cd, tile_ptr(cx, d, d), ld);
@@ -941,10 +966,10 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     }
     // generic tiles of this CTA
     if (s > 0) {
-      if (!generic_step(cx, s, cta, G, stage_phase)) return;
+      if (!generic_step(cx, s, cta, G, nd, stage_phase)) return;
     } else {
       TileWalk w;
-      w.start(0, cta, G, nt);
+      w.start(0, cta, G, nt, nd);
       int i, j;
       while (w.next(i, j))
         if (!process_tile(cx, i, j, 0)) return;
