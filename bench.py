@@ -543,14 +543,14 @@ def main_gpu(args, rank, world):
                     whole_iteration=dict(algorithmic_bytes=iter_bytes, ms=iter_ms,
                                          achieved=iter_bytes / (iter_ms * 1e-3) / 1e9,
                                          frac=iter_bytes / (iter_ms * 1e-3) / 1e9 / hbm_peak))
-    # the solve is FP64-pipe / latency bound, not HBM bound: reported against the measured DFMA issue rate of this part
-    # (1.33 warp-instructions/clk/SM x 148 SMs x 1.965 GHz x 64 flop = 24.8 TFLOP/s)
+    # the solve is FP64-pipe / latency bound, not HBM bound: reported against the measured FP64 rate of this part
+    # (DMMA m8n8k4 and register-only DFMA both reach 64 FMA/clk/SM, tools/mb_tile.cu: x 148 SMs x 1.965 GHz x 2 = 37.2 TFLOP/s)
     sol_ms = stage["solve"]["ms_per_iter"]
     n_sys = 6 * P
     sol_flops = n_sys ** 3 / 3.0 + 2.0 * n_sys ** 2
-    roofline["solver"] = dict(kernel="chol_solve_kernel (cooperative tiled fp64 Cholesky + both substitutions)", bound="fp64 pipe / panel-chain latency",
-                              gflops=(sol_flops / (sol_ms * 1e-3) / 1e9) if sol_ms else None, peak_gflops=24800.0,
-                              frac=(sol_flops / (sol_ms * 1e-3) / 1e9 / 24800.0) if sol_ms else None, ms_per_launch=sol_ms,
+    roofline["solver"] = dict(kernel="chol_solve_kernel (cooperative tiled fp64 Cholesky, trailing updates on DMMA + both substitutions)", bound="fp64 pipe / panel-chain latency",
+                              gflops=(sol_flops / (sol_ms * 1e-3) / 1e9) if sol_ms else None, peak_gflops=37200.0,
+                              frac=(sol_flops / (sol_ms * 1e-3) / 1e9 / 37200.0) if sol_ms else None, ms_per_launch=sol_ms,
                               share_of_iteration=(sol_ms / iter_ms) if sol_ms else None)
     traffic_file = os.path.join(REPO, "profiles", "traffic.json")
     if os.path.exists(traffic_file):

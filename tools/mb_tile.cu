@@ -63,6 +63,37 @@ __global__ void __launch_bounds__(256, 1) mb_kernel(long long* out, double* W, d
         __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * TQ + mp.col(ni)), make_double2(cm[mi][ni][0] - 1e-9 * am[mi][ni][0], cm[mi][ni][1] - 1e-9 * am[mi][ni][1]));
       buf ^= 1;
     }
+  } else if (mode == 5) {     // as mode 3 without the C traffic
+    int buf = 0;
+    issue(0, tile(0, 0), tile(0, 1));
+    if (reps > 1) issue(1, tile(1, 0), tile(1, 1));
+    for (int r = 0; r < reps; r++) {
+      wait(buf);
+      tile_abt_mma(qA(buf), qB(buf), am, mp, false);
+      __syncthreads();
+      if (r + 2 < reps) issue(buf, tile(r + 2, 0), tile(r + 2, 1));
+      for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++) sink += am[mi][ni][0] + am[mi][ni][1];
+      buf ^= 1;
+    }
+  } else if (mode == 6) {     // as mode 3 with resident operands (C traffic only)
+    issue(0, tile(0, 0), tile(0, 1)); wait(0); __syncthreads();
+    for (int r = 0; r < reps; r++) {
+      double* Cg = tile(r, 2);
+      load_frag_mma(cm, Cg, TQ, mp);
+      tile_abt_mma(qA(0), qB(0), am, mp, false);
+      __syncthreads();
+      for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++)
+        __stcg(reinterpret_cast<double2*>(Cg + size_t(mp.row(mi)) * TQ + mp.col(ni)), make_double2(cm[mi][ni][0] - 1e-9 * am[mi][ni][0], cm[mi][ni][1] - 1e-9 * am[mi][ni][1]));
+    }
+  } else if (mode == 7) {     // as mode 6, C load only
+    issue(0, tile(0, 0), tile(0, 1)); wait(0); __syncthreads();
+    for (int r = 0; r < reps; r++) {
+      double* Cg = tile(r, 2);
+      load_frag_mma(cm, Cg, TQ, mp);
+      tile_abt_mma(qA(0), qB(0), am, mp, false);
+      __syncthreads();
+      for (int mi = 0; mi < 4; mi++) for (int ni = 0; ni < 2; ni++) sink += cm[mi][ni][0] - 1e-9 * am[mi][ni][0] + cm[mi][ni][1] - 1e-9 * am[mi][ni][1];
+    }
   } else if (mode == 4) {     // self-check: chk[0] = A B^T by DFMA, chk[1] = by DMMA (CTA 0 only)
     if (blockIdx.x == 0) {
       load_tile(sA, W, TQ); load_tile(sB, W + T * TQ, TQ); __syncthreads();
@@ -94,8 +125,8 @@ int main(int argc, char** argv) {
   cudaMemcpy(W, h.data(), h.size() * 8, cudaMemcpyHostToDevice);
   const size_t smem = 4 * sizeof(double) * T * TQ + 1024;
   cudaFuncSetAttribute(mb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-  const char* names[] = {"DFMA product", "DMMA product", "serial update, DFMA (round-1 solver)", "bulk-copy staged (2 ahead) DMMA update", "self-check"};
-  for (int mode = 0; mode < 5; mode++) {
+  const char* names[] = {"DFMA product", "DMMA product", "serial update, DFMA (round-1 solver)", "bulk-copy staged (2 ahead) DMMA update", "self-check", "  staged DMMA, no C traffic", "  resident operands, C load + store", "  resident operands, C load only"};
+  for (int mode = 0; mode < 8; mode++) {
     for (int it = 0; it < 3; it++) {
       cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
       cudaEventRecord(e0);
@@ -108,7 +139,7 @@ int main(int argc, char** argv) {
       cudaMemcpy(c.data(), out, grid * 8, cudaMemcpyDeviceToHost);
       double mean = 0; long long mx = 0; for (auto v : c) { mean += double(v); if (v > mx) mx = v; }
       mean /= grid;
-      if (it == 2 && mode < 4) printf("%-40s: %8.0f cycles/tile (max CTA %8.0f), kernel %.3f ms -> %.2f us/tile\n", names[mode], mean / reps, double(mx) / reps, ms, 1e3 * ms / reps);
+      if (it == 2 && mode != 4) printf("%-40s: %8.0f cycles/tile (max CTA %8.0f), kernel %.3f ms -> %.2f us/tile\n", names[mode], mean / reps, double(mx) / reps, ms, 1e3 * ms / reps);
     }
   }
   std::vector<double> c(8192);
