@@ -862,6 +862,9 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G,
     have_b = have_c; bi = ci; bj = cj; b_iss = c_iss;
     buf ^= 1;
   }
+  // The tensor-core accumulator layout differs from the fragment layout of the chain (load_frag): a tile stored above is
+  // read back by OTHER threads of this CTA when it turns into chain work — order those accesses.
+  __syncthreads();
   return true;
 }
 

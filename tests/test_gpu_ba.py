@@ -174,6 +174,21 @@ def test_ba_c3_properties_full_size():
     assert rel(dx2, dx) < 1e-6 and rel(dz2, dz) < 1e-6
 
 
+def test_ba_c3_repeatable():
+    """Race detector for the solver's dataflow (static tile ownership, flags, streamed hand-overs, staged operands): the
+    same call repeated must give the same update.  The only run-to-run freedom is the order of the fp64 atomics of the
+    Schur scatter (~1e-13 on dx at this size); a tile read before it is final shows up as 1e-4 .. 1e-1."""
+    from droid_b200 import synth
+    p = synth.config_c3()
+    first = None
+    for _ in range(12):
+        _, _, dx, _ = run_gpu(p, 2, 1e-5, 1e-2)
+        if first is None:
+            first = dx
+        else:
+            assert rel(dx, first) < 1e-10
+
+
 @pytest.mark.timeout(600)
 def test_ba_c4_multisession_size():
     """BASELINE config 4 (3 fused maps, 1536 keyframes, ~20k edges incl. stereo and cross-map edges) on ONE GPU:
