@@ -100,6 +100,7 @@ struct BAParams {
   BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
   float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx; double* Lstage; double* Xstage;
   int n, nt, ld, Mcap;
+  int chol_nd;          // solver: number of diagonal CTAs, -1 = automatic (ba_solve.cu)
 };
 
 inline BAParams ba_params(const BALayout& L, void* ws) {
@@ -123,7 +124,7 @@ inline BAParams ba_params(const BALayout& L, void* ws) {
   p.dx = reinterpret_cast<float*>(b + L.dx);
   p.Lstage = reinterpret_cast<double*>(b + L.Lstage);
   p.Xstage = reinterpret_cast<double*>(b + L.Xstage);
-  p.n = L.n; p.nt = L.nt; p.ld = L.ld; p.Mcap = L.Mcap;
+  p.n = L.n; p.nt = L.nt; p.ld = L.ld; p.Mcap = L.Mcap; p.chol_nd = -1;
   return p;
 }
 

@@ -10,6 +10,7 @@
 // substitution runs in the same launch, block column j owned by CTA nt-1-j, consuming x_i as they are published.
 // Damping diag += ep + lm*diag (:1197) is applied while copying into the work matrix.  A pivot <= 0
 // reproduces Eigen's NumericalIssue: the pose update is zero (:1207-1210).
+#include <cstdlib>
 #include "ba.cuh"
 
 namespace db200 {
@@ -706,8 +707,10 @@ __device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
 //   nd = 0 (small grids): the old scheme.
 __host__ __device__ inline int chol_num_diag_ctas(int G, int nt) {
   if (G < 64 || nt < 8) return 0;
-  int nd = (4 * G + nt / 2) / nt;                  // balances 2 (nt-s)/nd pair updates against (nt-s)^2 / (2 (G-nd)) tiles
-  return nd < 2 ? 2 : (nd > 16 ? 16 : nd);
+  // pair updates 2 (nt-s)/nd per diagonal CTA against (nt-s)^2 / (2 (G-nd)) tiles per other CTA balance at one s only;
+  // nd = 8 G / nt balances them half-way through the factorisation (measured: 16 of 148 at nt = 48, 8 at nt = 144)
+  int nd = (8 * G + nt / 2) / nt;
+  return nd < 8 ? 8 : (nd > 16 ? 16 : nd);
 }
 __device__ __forceinline__ int chain_owner(int d, int G, int nt, int nd) { return nd > 0 ? d % nd : colstart(d, nt) % G; }
 
@@ -911,7 +914,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   cx.F = chol_flags(p.cflags, p.nt);
   const int nt = p.nt, ld = TQ, n = p.n;
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
-  const int nd = chol_num_diag_ctas(G, nt);
+  const int nd = p.chol_nd >= 0 ? p.chol_nd : chol_num_diag_ctas(G, nt);
   const CholFlags& F = cx.F;
 
   for (int s = 0; s < nt; s++) {
@@ -1148,6 +1151,11 @@ int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   const int ntiles = num_tiles(p.nt);
   if (grid > ntiles) grid = ntiles;
   BAParams pp = p;
+  pp.chol_nd = -1;
+  if (const char* e = getenv("DB200_CHOL_ND")) {   // tuning override: number of diagonal CTAs (0 = round-1 ownership)
+    const int v = atoi(e);
+    if (v >= 0 && v <= grid / 2) pp.chol_nd = v;
+  }
   void* args[] = {&pp};
   // cooperative launch: guarantees that every CTA is resident, which the flag waits rely on
   DB200_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_solve_kernel), dim3(grid), dim3(kCholThreads), args, smem, st));

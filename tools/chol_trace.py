@@ -6,7 +6,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [REPO, os.path.join(REPO, "droid-slam_reserch_b200")]
 import droid_backends
 from droid_b200 import _capi, synth
-p = synth.config_c3()
+p = synth.config_c4() if (len(sys.argv) > 1 and sys.argv[1] == 'c4') else synth.config_c3()
 dev = torch.device("cuda:0")
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 args = [t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)]
@@ -28,7 +28,8 @@ for s in range(nt):
     nxt = tr[s + 1][1] if s + 1 < nt else np.nan
     per = (r[2] - prev) if prev else 0.0
     prev = r[2]
-    print(f"{s:3d}: {(r[1]-t0)/1e3:8.1f} {(r[2]-r[1])/1e3:6.1f} | prework done {(r[6]-r[1])/1e3:6.1f} stream done {(r[5]-r[2])/1e3:6.1f} | {(nxt-r[5])/1e3:6.1f} | {per/1e3:6.1f}")
+    ntr = (nt - s) * (nt - s + 1) / 2 / 148.0          # trailing tile products per CTA in the step that follows
+    print(f"{s:3d}: {(r[1]-t0)/1e3:8.1f} {(r[2]-r[1])/1e3:6.1f} | prework done {(r[6]-r[1])/1e3:6.1f} stream done {(r[5]-r[2])/1e3:6.1f} | {(nxt-r[5])/1e3:6.1f} | {per/1e3:6.1f} | {ntr:5.1f} products/CTA -> {per/1e3/max(ntr,1e-9):5.2f} us each")
 xs = tr[nt:2 * nt, 0]
 print("factor total us:", (tr[nt - 1, 3] - t0) / 1e3, " backsub us:", (xs[0] - xs[nt - 1]) / 1e3, " backsub per block us:", (xs[0] - xs[nt - 1]) / 1e3 / (nt - 1))
 
