@@ -133,7 +133,7 @@ def main_reference(args, rank):
                 e2e=dict(value=r["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 note="reference's CPU arm = oracle/oracle.cpp (OpenMP restatement of src/droid_kernels.cu ba_cuda, fp32 kernels + "
                      "fp64 solve); steps capped at 3 (each ~15 s)")
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
@@ -591,12 +591,34 @@ def main_gpu(args, rank, world):
                 line["reference_cuda"] = rc
             r = run_cpu(1, 0)
             line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"])
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to stdout when
+    NCCL_DEBUG=VERSION is exported on the box): keep a private copy of the real stdout for the result line and point
+    fd 1 at stderr for everything else."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    text = json.dumps(line) + "\n"
+    if _RESULT_FD is None:
+        sys.stdout.write(text); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, text.encode())
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
