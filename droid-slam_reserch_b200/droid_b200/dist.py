@@ -14,7 +14,10 @@ and after the last iteration the owned disparity rows are assembled on every ran
 row-masked copy, 12 KB per keyframe) so that `disps` ends up identical everywhere, as the reference's
 single-GPU `droid_backends.ba` leaves it.
 
-`partition_frames` / `shard_edges` / `allreduce_system` are pure host logic and run on CPU tensors with the
+`frame_distance` (and the lookups) are pair-/edge-parallel: `frame_distance_sharded` splits the pair list evenly and
+all-gathers `dist[K]`.
+
+`partition_frames` / `shard_edges` / `allreduce_system` / `sharded_pair_op` are pure host logic and run on CPU tensors with the
 gloo backend (tests/test_dist_cpu.py); `ShardedBA` needs the CUDA library.
 """
 from __future__ import annotations
@@ -80,6 +83,37 @@ def assemble_rows(x: torch.Tensor, lo: int, hi: int, group=None) -> torch.Tensor
         x[hi:].zero_()
     dist.all_reduce(x, op=dist.ReduceOp.SUM, group=group)
     return x
+
+
+def pair_range(n_pairs: int, rank: int, world: int):
+    """Even split of a pair list (`frame_distance` is pair-parallel): rank r gets
+    [r*chunk, min((r+1)*chunk, K)) with chunk = ceil(K / world), so that one all-gather of equal chunks rebuilds the list."""
+    chunk = -(-int(n_pairs) // max(int(world), 1)) if n_pairs > 0 else 0
+    lo = min(rank * chunk, n_pairs)
+    return lo, min(lo + chunk, n_pairs), chunk
+
+
+def sharded_pair_op(fn, ii: torch.Tensor, jj: torch.Tensor, group=None) -> torch.Tensor:
+    """`fn(ii_slice, jj_slice) -> f32[len]` evaluated on this rank's slice of the pair list, results all-gathered in pair
+    order (K floats in total, <= 1 MB for the 512^2 meshgrid of `DepthVideo.distance`, depth_video.py:171-185).
+    Every rank returns the full `dist[K]`, bit-identical to the unsharded call (pairs are independent)."""
+    K = int(ii.numel())
+    if not (dist.is_initialized() and dist.get_world_size(group) > 1):
+        return fn(ii, jj)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    lo, hi, chunk = pair_range(K, rank, world)
+    mine = torch.zeros(chunk, dtype=torch.float32, device=ii.device)
+    if hi > lo:
+        mine[:hi - lo] = fn(ii[lo:hi].contiguous(), jj[lo:hi].contiguous())
+    out = torch.empty(chunk * world, dtype=torch.float32, device=ii.device)
+    dist.all_gather_into_tensor(out, mine, group=group)
+    return out[:K]
+
+
+def frame_distance_sharded(poses, disps, intrinsics, ii, jj, beta: float, group=None) -> torch.Tensor:
+    """`droid_backends.frame_distance` (droid.cpp:120-136) with the pair list split over the ranks; no other collective."""
+    import droid_backends
+    return sharded_pair_op(lambda a, b: droid_backends.frame_distance(poses, disps, intrinsics, a, b, beta), ii, jj, group)
 
 
 class ShardedBA:

@@ -102,3 +102,47 @@ def test_gloo_world2_partial_systems_sum_to_the_full_system():
     # every rank solved with its PARTIAL system above (oracle.ba is one self-contained call), so only the
     # assembly mechanics are checked here: row r of the assembled map comes from r's owner
     assert res[0][2].shape == full["disps"].shape
+
+
+def _fd_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import oracle
+        p = synth.config_c3(n_kf=12, n_edges=60, ht=16, wd=24, seed=5)
+        n = p.t1
+        ii, jj = torch.meshgrid(torch.arange(n), torch.arange(n), indexing="ij")
+        ii, jj = ii.reshape(-1)[:-5], jj.reshape(-1)[:-5]            # 139 pairs: not a multiple of the world size
+        calls = []
+
+        def fn(a, b):
+            calls.append(len(a))
+            return torch.from_numpy(oracle.frame_distance(p.poses, p.disps, p.intrinsics, a.numpy(), b.numpy(), 0.3))
+        d = bdist.sharded_pair_op(fn, ii, jj)
+        q.put((rank, d.numpy().copy(), calls))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_gloo_world2_frame_distance_pairs_are_split_and_gathered():
+    from oracle import oracle
+    assert bdist.pair_range(139, 0, 2) == (0, 70, 70) and bdist.pair_range(139, 1, 2) == (70, 139, 70)
+    assert bdist.pair_range(3, 7, 8) == (3, 3, 1) and bdist.pair_range(0, 0, 2) == (0, 0, 0)
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_fd_worker, args=(r, world, port, q)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted([q.get(timeout=240) for _ in range(world)], key=lambda t: t[0])
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    p = synth.config_c3(n_kf=12, n_edges=60, ht=16, wd=24, seed=5)
+    n = p.t1
+    ii, jj = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    want = oracle.frame_distance(p.poses, p.disps, p.intrinsics, ii.reshape(-1)[:-5], jj.reshape(-1)[:-5], 0.3)
+    for rank, d, calls in res:
+        np.testing.assert_array_equal(d.view(np.uint32), want.view(np.uint32))      # bit-exact, in pair order, on every rank
+    assert res[0][2] == [70] and res[1][2] == [69]

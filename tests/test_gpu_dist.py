@@ -88,7 +88,13 @@ def _nccl_worker(rank, world, port, q):
         dx, dz = r.ba(poses, disps, t(p.intrinsics), t(p.disps_sens), t(p.target[r.local_edges]), t(p.weight[r.local_edges]),
                       t(p.eta), 2, 1e-5, 1e-2)
         torch.cuda.synchronize()
-        q.put((rank, poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy(), dz.cpu().numpy()))
+        # pair-sharded frame_distance on the initial state: the full dist[K] on every rank
+        n = p.t1
+        mi, mj = torch.meshgrid(torch.arange(n), torch.arange(n), indexing="ij")
+        mi, mj = mi.reshape(-1)[:-3].to(dev), mj.reshape(-1)[:-3].to(dev)
+        fd = bdist.frame_distance_sharded(t(p.poses), t(p.disps), t(p.intrinsics), mi, mj, 0.3)
+        torch.cuda.synchronize()
+        q.put((rank, poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy(), dz.cpu().numpy(), fd.cpu().numpy()))
     finally:
         dist.destroy_process_group()
 
@@ -109,8 +115,18 @@ def test_sharded_nccl_two_gpus():
         pr.join(timeout=60)
         assert pr.exitcode == 0
     want = _single(_problem(), 2, 1e-5, 1e-2, torch.device("cuda:0"))
-    for k in range(1, 5):
+    for k in range(1, 6):
         np.testing.assert_array_equal(res[0][k], res[1][k])          # identical on all ranks
     rel = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
     assert rel(res[0][3], want[2]) < 2e-5 and rel(res[0][4], want[3]) < 2e-5
     assert np.abs(res[0][1] - want[0]).max() < 1e-5 and np.abs(res[0][2] - want[1]).max() < 1e-5
+    # frame_distance split over the ranks == the single-GPU call, bit for bit, on every rank
+    import droid_backends
+    p = _problem()
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    n = p.t1
+    mi, mj = torch.meshgrid(torch.arange(n), torch.arange(n), indexing="ij")
+    one = droid_backends.frame_distance(t(p.poses), t(p.disps), t(p.intrinsics), mi.reshape(-1)[:-3].to(dev), mj.reshape(-1)[:-3].to(dev), 0.3)
+    for r in res:
+        np.testing.assert_array_equal(r[5].view(np.uint32), one.cpu().numpy().view(np.uint32))
