@@ -159,6 +159,7 @@ __device__ __forceinline__ void store_tile(double* g, const double (*S)[TP], int
     __stcg(g + size_t(e >> 6) * ld + (e & 63), S[e >> 6][e & 63]);
   }
 }
+// (round-1 DFMA fragment layout; kept as the reference of tools/mb_tile.cu)
 // this thread's 4x4 sub-block (rows ty+16a, cols tx+16b) of a global tile
 __device__ __forceinline__ void load_frag(double (&c)[4][4], const double* g, int ld) {
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
@@ -197,25 +198,6 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
   e = fma(-(h * y), y, 0.5);
   y = fma(y, e, y);
   return y;
-}
-
-// acc[a][b] for b <= a only (the lower block triangle of A A^T; diagonal tiles are symmetric)
-__device__ __forceinline__ void tile_aat_lower(const double (*A)[TP], double (&acc)[4][4]) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-#pragma unroll
-  for (int a = 0; a < 4; a++)
-#pragma unroll
-    for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
-#pragma unroll 8
-  for (int k = 0; k < T; k++) {
-    double av[4], bv[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) { av[a] = A[ty + 16 * a][k]; bv[a] = A[tx + 16 * a][k]; }
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b <= a; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
-  }
 }
 
 // ---- operand tiles of the trailing updates, staged by the bulk-copy engine (TMA, 1D rows) -------------------------------
@@ -308,45 +290,67 @@ __device__ __forceinline__ void load_frag_mma(double (&c)[4][2][2], const double
 }
 
 // ---- 64x64 tile factorisation / triangular solve with the tile held in REGISTERS -------------------------
-// Thread (ty,tx) owns the 4x4 fragment rows ty+16a, columns tx+16b — the layout tile_abt produces, so the
-// updated tile never takes a detour through memory.  Eight steps of 8 columns:
+// The tile lives in the tensor-core accumulator layout (MmaPos): c[mi][ni][e] = C[32 wr + 8 mi + g][16 wc + 8 ni + 2 t + e],
+// the layout the trailing-update product leaves it in, so an updated tile never takes a detour through memory and every
+// rank-8 update below is two DMMAs per 8x8 tile (k = 0..3, 4..7).  Eight steps of 8 columns:
 //   owners of the 8 columns write them to shared memory  | bar |
 //   threads 0..63-c0 ("panel"): each holds the 8x8 diagonal block in registers, factors it redundantly (no
 //     shuffles; pivots in pairs so that two reciprocal square roots overlap:
 //     1/sqrt(d1) = sqrt(d0)/sqrt(d0*a11 - a10^2)) and solves its own row against it          | bar |
-//   every thread applies the rank-8 update to its register fragment (blocks already final are pruned at
-//     compile time: the step index is a template parameter).
-template <int P>
-__device__ __forceinline__ void cols_to_smem(double (*S)[TP], const double (&c)[4][4], bool lower_only) {
-  constexpr int c0 = 8 * P, bsel = c0 / 16, txlo = c0 % 16;
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  if (tx >= txlo && tx < txlo + 8) {
-    const int col = tx + 16 * bsel;
+//   every warp applies the rank-8 update to the 8x8 tiles of its fragment that are still open (warp-uniform tests).
+// Round 1 kept the fragments in a 4x4-per-thread DFMA layout: its rank-8 updates ran at ~1.1 DFMA warp-instructions per
+// clock and made up half of every 8-column step of the chain.
+__device__ __forceinline__ void cols_to_smem_mma(int P, double (*S)[TP], const double (&c)[4][2][2], const MmaPos& mp, bool lower_only) {
+  if (mp.wc == (P >> 1)) {
+    const bool hi = (P & 1) != 0;
+    const int col = 8 * P + 2 * mp.t;
 #pragma unroll
-    for (int a = 0; a < 4; a++) {
-      const int r = ty + 16 * a;
-      S[r][col] = (!lower_only || r >= col) ? c[a][bsel] : 0.0;
+    for (int mi = 0; mi < 4; mi++) {
+      const int r = mp.row(mi);
+      const double v0 = hi ? c[mi][1][0] : c[mi][0][0];
+      const double v1 = hi ? c[mi][1][1] : c[mi][0][1];
+      S[r][col] = (!lower_only || r >= col) ? v0 : 0.0;
+      S[r][col + 1] = (!lower_only || r >= col + 1) ? v1 : 0.0;
     }
   }
 }
 
-template <int P, bool LOWER>
-__device__ __forceinline__ void frag_rank8(double (&c)[4][4], const double (*Pm)[TP], const double (*Qm)[TP]) {
-  constexpr int c0 = 8 * P, base = c0 + 8;
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+// c[tile] -= Pm[tile rows][c0..c0+7] * Qm[tile cols][c0..c0+7]^T for the 8x8 tiles of the fragment selected by MODE:
+enum { kUpdTrsm = 0,      // every row, columns right of the panel            (X L^T = C: the columns still to be solved)
+       kUpdFactor = 1,    // block-lower part right of the panel              (trailing part of the tile being factored)
+       kUpdSyrk = 2,      // block-lower part, every column                   (C -= X_P X_P^T)
+       kUpdGemm = 3 };    // everything                                       (C -= A_P B_P^T)
+template <int MODE>
+__device__ __forceinline__ void frag_rank8_mma(double (&c)[4][2][2], const double (*Pm)[TP], const double (*Qm)[TP], int c0,
+                                               const MmaPos& mp) {
+  const int base = c0 + 8;
+  double b[2][2];
+  bool nb[2];
 #pragma unroll
-  for (int q = 0; q < 8; q++) {
-    double pv[4], qv[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) {
-      if (!LOWER || 16 * a + 15 >= base) pv[a] = Pm[ty + 16 * a][c0 + q];
-      if (16 * a + 15 >= base) qv[a] = Qm[tx + 16 * a][c0 + q];
+  for (int ni = 0; ni < 2; ni++) {
+    const int cb = 16 * mp.wc + 8 * ni;
+    nb[ni] = (MODE == kUpdTrsm || MODE == kUpdFactor) ? (cb >= base) : true;
+    if (nb[ni]) {
+      b[ni][0] = Qm[cb + mp.g][c0 + mp.t];
+      b[ni][1] = Qm[cb + mp.g][c0 + 4 + mp.t];
     }
+  }
+  // the two DMMAs of a tile (k = 0..3, 4..7) depend on each other: all first halves, then all second halves, so that
+  // dependent instructions are as many tiles apart as the warp has open (operands re-read per half: no extra registers)
 #pragma unroll
-    for (int a = 0; a < 4; a++)
+  for (int kh = 0; kh < 2; kh++) {
 #pragma unroll
-      for (int b = 0; b < 4; b++)
-        if ((!LOWER || (16 * a + 15 >= base && b <= a)) && 16 * b + 15 >= base) c[a][b] = fma(-pv[a], qv[b], c[a][b]);
+    for (int mi = 0; mi < 4; mi++) {
+      const int rb = 32 * mp.wr + 8 * mi;
+      const bool lower = (MODE == kUpdFactor || MODE == kUpdSyrk);
+      const bool n0 = nb[0] && (!lower || rb + 7 >= 16 * mp.wc);
+      const bool n1 = nb[1] && (!lower || rb + 7 >= 16 * mp.wc + 8);
+      if (n0 || n1) {
+        const double a = -Pm[rb + mp.g][c0 + 4 * kh + mp.t];
+        if (n0) dmma884(c[mi][0], a, b[0][kh]);
+        if (n1) dmma884(c[mi][1], a, b[1][kh]);
+      }
+    }
   }
 }
 
@@ -401,38 +405,17 @@ __device__ long long* g_chol_fine = nullptr;   // debug: clock64 marks inside on
 __device__ __forceinline__ void fine_mark(int slot) {
   if (g_chol_fine != nullptr && threadIdx.x == 0) g_chol_fine[slot] = clock64();
 }
-// The fragment-dependent parts need the step index at compile time (register arrays); everything else takes it at run
-// time, so that each routine exists ONCE in the instruction stream: unrolled eight-fold, the solver's code exceeded the
-// SM's instruction cache and the single-warp phases of the chain stalled on instruction fetch.
-// (dispatch by a branch tree of uniform compares: a `switch` becomes an indirect BRX jump, which costs hundreds of cycles)
-__device__ __forceinline__ void cols_to_smem_sw(int P, double (*S)[TP], const double (&c)[4][4], bool lower_only) {
-  if (P < 4) {
-    if (P < 2) { if (P == 0) cols_to_smem<0>(S, c, lower_only); else cols_to_smem<1>(S, c, lower_only); }
-    else { if (P == 2) cols_to_smem<2>(S, c, lower_only); else cols_to_smem<3>(S, c, lower_only); }
-  } else {
-    if (P < 6) { if (P == 4) cols_to_smem<4>(S, c, lower_only); else cols_to_smem<5>(S, c, lower_only); }
-    else { if (P == 6) cols_to_smem<6>(S, c, lower_only); else cols_to_smem<7>(S, c, lower_only); }
-  }
-}
-template <bool LOWER>
-__device__ __forceinline__ void frag_rank8_sw(int P, double (&c)[4][4], const double (*Pm)[TP], const double (*Qm)[TP]) {
-  if (P < 4) {
-    if (P < 2) { if (P == 0) frag_rank8<0, LOWER>(c, Pm, Qm); else frag_rank8<1, LOWER>(c, Pm, Qm); }
-    else { if (P == 2) frag_rank8<2, LOWER>(c, Pm, Qm); else frag_rank8<3, LOWER>(c, Pm, Qm); }
-  } else {
-    if (P < 6) { if (P == 4) frag_rank8<4, LOWER>(c, Pm, Qm); else frag_rank8<5, LOWER>(c, Pm, Qm); }
-    else if (P == 6) frag_rank8<6, LOWER>(c, Pm, Qm);
-  }
-}
-
-// In: the tile as register fragments `c` (lower triangle meaningful).  Out: L in shared S (strict upper zero); every
+// In: the tile as a register fragment `c` (lower triangle meaningful).  Out: L in shared S (strict upper zero); every
 // finished 64x8 panel is also streamed to `stage` (global, may be null) for the CTAs that solve against this tile.
-__device__ __forceinline__ void factor_tile(double (&c)[4][4], double (*S)[TP], int row0, int n, int* chol_fail, double* stage) {
+// The 8-column steps are a run-time loop: unrolled, the solver's code exceeded the SM's instruction cache and the
+// single-warp phases of the chain stalled on instruction fetch.
+__device__ __forceinline__ void factor_tile(double (&c)[4][2][2], double (*S)[TP], int row0, int n, int* chol_fail, double* stage,
+                                            const MmaPos& mp) {
 #pragma unroll 1
   for (int P = 0; P < 8; P++) {
     const int c0 = 8 * P;
     fine_mark(4 * P);
-    cols_to_smem_sw(P, S, c, true);
+    cols_to_smem_mma(P, S, c, mp, true);
     __syncthreads();
     fine_mark(4 * P + 1);
     factor_panel(S, c0, row0, n, chol_fail);
@@ -446,7 +429,7 @@ __device__ __forceinline__ void factor_tile(double (&c)[4][4], double (*S)[TP], 
         st_relaxed_f64(stage + r * T + c0 + q, S[r][c0 + q]);
       }
     }
-    frag_rank8_sw<true>(P, c, S, S);
+    if (P < 7) frag_rank8_mma<kUpdFactor>(c, S, S, c0, mp);
   }
   __syncthreads();
 }
@@ -515,30 +498,15 @@ __device__ __forceinline__ int stream_commit(StreamRegs& sr, double (*L)[TP], do
   return fail;
 }
 
-// cd -= X[:, c0..c0+7] X[:, c0..c0+7]^T on the block-lower fragments (the rank-8 slice of tile_aat_lower)
-__device__ __forceinline__ void frag_syrk8(double (&cd)[4][4], const double (*X)[TP], int c0) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-#pragma unroll
-  for (int q = 0; q < 8; q++) {
-    double pv[4], qv[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) { pv[a] = X[ty + 16 * a][c0 + q]; qv[a] = X[tx + 16 * a][c0 + q]; }
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b <= a; b++) cd[a][b] = fma(-pv[a], qv[b], cd[a][b]);
-  }
-}
-
 // X L(s,s)^T = C with L(s,s) arriving panel by panel from the CTA that is factoring it (staging area `stage`, write
-// once, any number of readers).  C as register fragments `cf`; X ends up in shared `X`.  With SYRK, the diagonal tile
+// once, any number of readers).  C as register fragment `cf`; X ends up in shared `X`.  With SYRK, the diagonal tile
 // `cd` of the chain takes its rank-8 update X_P X_P^T right behind every solved panel, so that when the last panel of
 // L(s,s) appears only one panel's worth of work separates it from the next factorisation.
 // The chain (SYRK) additionally streams every solved panel X_P of L(d,d-1) to `xout` (write-once words like `stage`): the
 // NEXT chain CTA applies it to its sub-diagonal tile panel by panel (stream_gemm) instead of waiting for the whole tile.
 template <bool SYRK>
-__device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][4], double (*X)[TP], double (*L)[TP], double* rinv,
-                                            const double* stage, unsigned* err, double* xout = nullptr) {
+__device__ __forceinline__ bool stream_trsm(double (&cf)[4][2][2], double (&cd)[4][2][2], double (*X)[TP], double (*L)[TP], double* rinv,
+                                            const double* stage, unsigned* err, const MmaPos& mp, double* xout = nullptr) {
   StreamRegs sr;
   stream_issue(sr, stage, 0);
 #pragma unroll 1
@@ -546,7 +514,7 @@ __device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][
     const int c0 = 8 * P;
     const int fail = stream_commit(sr, L, rinv, stage, c0, err);
     if (P < 7) stream_issue(sr, stage, c0 + 8);
-    cols_to_smem_sw(P, X, cf, false);
+    cols_to_smem_mma(P, X, cf, mp, false);
     if (__syncthreads_or(fail)) {                  // one barrier: L panel, pivots and the X columns are all in place
       if (threadIdx.x == 0) atomicExch(err, 1u);
       return false;
@@ -560,8 +528,8 @@ __device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][
         st_relaxed_f64(xout + r * T + c0 + q, X[r][c0 + q]);
       }
     }
-    frag_rank8_sw<false>(P, cf, X, L);
-    if (SYRK) frag_syrk8(cd, X, c0);
+    if (P < 7) frag_rank8_mma<kUpdTrsm>(cf, X, L, c0, mp);
+    if (SYRK) frag_rank8_mma<kUpdSyrk>(cd, X, X, c0, mp);
   }
   __syncthreads();
   return true;
@@ -569,9 +537,8 @@ __device__ __forceinline__ bool stream_trsm(double (&cf)[4][4], double (&cd)[4][
 
 // cf -= A B^T with B (= L(s,s-1), solved by the previous chain CTA) arriving 64x8 panel by panel through `xstage`;
 // A (= L(d,s-1)) complete in shared memory, B lands in `Bm`.  One barrier per panel (panels occupy disjoint columns).
-__device__ __forceinline__ bool stream_gemm(double (&cf)[4][4], const double (*A)[TP], double (*Bm)[TP], const double* xstage,
-                                            unsigned* err) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+__device__ __forceinline__ bool stream_gemm(double (&cf)[4][2][2], const double (*A)[TP], double (*Bm)[TP], const double* xstage,
+                                            unsigned* err, const MmaPos& mp) {
   StreamRegs sr;
   stream_issue(sr, xstage, 0);
 #pragma unroll 1
@@ -595,16 +562,7 @@ __device__ __forceinline__ bool stream_gemm(double (&cf)[4][4], const double (*A
       if (threadIdx.x == 0) atomicExch(err, 1u);
       return false;
     }
-#pragma unroll
-    for (int q = 0; q < 8; q++) {
-      double pv[4], qv[4];
-#pragma unroll
-      for (int a = 0; a < 4; a++) { pv[a] = A[ty + 16 * a][c0 + q]; qv[a] = Bm[tx + 16 * a][c0 + q]; }
-#pragma unroll
-      for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) cf[a][b] = fma(-pv[a], qv[b], cf[a][b]);
-    }
+    frag_rank8_mma<kUpdGemm>(cf, A, Bm, c0, mp);
   }
   __syncthreads();
   return true;
@@ -631,69 +589,14 @@ struct CholCtx {
 
 __device__ __forceinline__ double* tile_ptr(const CholCtx& cx, int i, int j) { return cx.W + size_t(colstart(j, cx.nt) + (i - j)) * (T * TQ); }
 
-// acc = L(i,s-1) L(j,s-1)^T (waits until both panel tiles are final).  Uses sA (and sB when i != j).
-__device__ __forceinline__ bool apply_panel(CholCtx& cx, int i, int j, int s, double (&acc)[4][4]) {
-  const int k = s - 1, ck = colstart(k, cx.nt);
-  if (!cx.panel_full) {
-    if (threadIdx.x == 0) *cx.s_ok = (ld_acquire(cx.F.panel_done + k) >= unsigned(cx.nt + 1 - k)) ? 1 : 0;
-    __syncthreads();
-    cx.panel_full = *cx.s_ok != 0;
-    __syncthreads();
-    if (!cx.panel_full) {
-      if (!wait_flag(cx.F.ready + ck + (i - k), 1u, cx.F.ctl, cx.s_ok)) return false;
-      if (i != j && !wait_flag(cx.F.ready + ck + (j - k), 1u, cx.F.ctl, cx.s_ok)) return false;
-    }
-  }
-  load_tile(cx.sA, tile_ptr(cx, i, k), cx.ld);
-  if (i != j) load_tile(cx.sB, tile_ptr(cx, j, k), cx.ld);
-  __syncthreads();
-  if (i != j) tile_abt(cx.sA, cx.sB, acc);
-  else tile_aat_lower(cx.sA, acc);
-  __syncthreads();
-  return true;
-}
-
-// S[r][c] = C(i,j)[r][c] - acc  for this thread's fragment (C prefetched into `c` before the product)
-__device__ __forceinline__ void frag_to_smem(double (*S)[TP], const double (&c)[4][4], const double (&acc)[4][4]) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-#pragma unroll
-  for (int a = 0; a < 4; a++)
-#pragma unroll
-    for (int b = 0; b < 4; b++) S[ty + 16 * a][tx + 16 * b] = c[a][b] - acc[a][b];
-}
-
-// generic tile (i,j), j >= s, at step s: apply panel s-1; if j == s also finish it (triangular solve) and publish
-__device__ __forceinline__ bool process_tile(CholCtx& cx, int i, int j, int s) {
-  double cf[4][4], acc[4][4];
-  double* Cg = tile_ptr(cx, i, j);
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  load_frag(cf, Cg, cx.ld);                        // in flight while the panel product runs
-  if (s > 0) {
-    if (!apply_panel(cx, i, j, s, acc)) return false;
-  } else {
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
-  }
-  if (j > s) {
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b < 4; b++) __stcg(Cg + size_t(ty + 16 * a) * cx.ld + tx + 16 * b, cf[a][b] - acc[a][b]);
-    return true;
-  }
-#pragma unroll
-  for (int a = 0; a < 4; a++)
-#pragma unroll
-    for (int b = 0; b < 4; b++) cf[a][b] -= acc[a][b];
-  const int cs = colstart(s, cx.nt);
-  // the triangular solve follows the factorisation of L(s,s) panel by panel (its staging area is write-once, any
-  // number of CTAs may read it) and ends one panel after it, instead of starting when the whole tile is published
-  const double* stage = cx.stage + size_t(s) * chol_stage_doubles();
-  if (!stream_trsm<false>(cf, cf, cx.sA, cx.sB, cx.sv, stage, cx.F.ctl)) return false;
+// step 0: a tile (i,0) of the first block column has no panel to take — streamed triangular solve against L(0,0), publish
+__device__ __forceinline__ bool first_column_tile(CholCtx& cx, int i, const MmaPos& mp) {
+  double cf[4][2][2];
+  double* Cg = tile_ptr(cx, i, 0);
+  load_frag_mma(cf, Cg, cx.ld, mp);
+  if (!stream_trsm<false>(cf, cf, cx.sA, cx.sB, cx.sv, cx.stage, cx.F.ctl, mp)) return false;
   store_tile(Cg, cx.sA, cx.ld);
-  publish(cx.F.ready + cs + (i - s), cx.F.panel_done + s);
+  publish(cx.F.ready + i, cx.F.panel_done + 0);
   __syncthreads();
   return true;
 }
@@ -783,7 +686,6 @@ __device__ __forceinline__ bool stage_wait(CholCtx& cx, int buf, unsigned parity
 // `ph` = the phase parities of the two stage mbarriers (bit b = stage b), carried across steps.
 __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G, int nd, unsigned& ph) {
   const int k = s - 1, ck = colstart(k, cx.nt), cs = colstart(s, cx.nt);
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
   TileWalk w;
   w.start(s, cta, G, cx.nt, nd);
   int ai, aj, bi = 0, bj = 0, ci = 0, cj = 0;
@@ -831,8 +733,8 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G,
                    make_double2(cm[mi][ni2][0] - acc[mi][ni2][0], cm[mi][ni2][1] - acc[mi][ni2][1]));
       }
     } else {
-      // a tile of block column s: into the solver's fragment layout through shared memory (stage `buf` is dead after the
-      // product), then the triangular solve follows the factorisation of L(s,s) panel by panel (stream_trsm)
+      // a tile of block column s (stage `buf` is dead after the product and serves as scratch): the triangular solve
+      // follows the factorisation of L(s,s) panel by panel (stream_trsm) on the fragment the product left in registers
       __syncthreads();
       double (*X)[TP] = reinterpret_cast<double (*)[TP]>(cx.qA(buf));
       double (*L)[TP] = reinterpret_cast<double (*)[TP]>(cx.qB(buf));
@@ -840,18 +742,11 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G,
       for (int mi = 0; mi < 4; mi++)
 #pragma unroll
         for (int ni2 = 0; ni2 < 2; ni2++) {
-          X[mp.row(mi)][mp.col(ni2)] = cm[mi][ni2][0] - acc[mi][ni2][0];
-          X[mp.row(mi)][mp.col(ni2) + 1] = cm[mi][ni2][1] - acc[mi][ni2][1];
+          cm[mi][ni2][0] -= acc[mi][ni2][0];
+          cm[mi][ni2][1] -= acc[mi][ni2][1];
         }
-      __syncthreads();
-      double cf[4][4];
-#pragma unroll
-      for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) cf[a][b] = X[ty + 16 * a][tx + 16 * b];
-      __syncthreads();
       const double* stage = cx.stage + size_t(s) * chol_stage_doubles();
-      if (!stream_trsm<false>(cf, cf, X, L, cx.sv, stage, cx.F.ctl)) return false;
+      if (!stream_trsm<false>(cm, cm, X, L, cx.sv, stage, cx.F.ctl, mp)) return false;
       store_tile(Cg, X, cx.ld);
       publish(cx.F.ready + cs + (ai - s), cx.F.panel_done + s);
       fence_proxy_async();                         // generic-proxy writes to the stage before the copy engine refills it
@@ -872,23 +767,21 @@ __device__ __forceinline__ bool generic_step(CholCtx& cx, int s, int cta, int G,
 }
 
 // ---- the solver: ONE cooperative launch ------------------------------------------------------------------
-// Static tile ownership + release/acquire ready flags instead of grid barriers or per-step launches.
-//   owner(i,j) = idx(i,j) mod G, except that the sub-diagonal tile (d,d-1) belongs to the owner D(d) of the
-//   diagonal tile (d,d): the panel chain  L(d,d-1) -> update (d,d) -> factor (d,d)  then stays inside one CTA
-//   (operands in shared memory), and only the finished diagonal tile crosses CTAs per step.
-//   step s (panel s-1 is applied to every tile with j >= s, block column s becomes final):
-//     CTA D(s+1): [a]+[b] tiles (d,d) and (d,s) take panel s-1 (L(d,s-1) loaded once for both);
+// Static tile ownership (chol_num_diag_ctas / TileWalk) + release/acquire ready flags instead of grid barriers or per-step
+// launches.  Step s (panel s-1 is applied to every tile with j >= s, block column s becomes final):
+//     chain CTA D(s+1) (a diagonal CTA):
+//                 [a] (d,d) -= L(d,s-1) L(d,s-1)^T as soon as L(d,s-1) is published;
+//                 [b] (d,s) -= L(d,s-1) L(s,s-1)^T with L(s,s-1) STREAMED from the previous chain CTA (Xstage);
 //                 [c] STREAMED solve: L(s,s) arrives 64x8 panel by panel from the CTA that is factoring it (write-once
 //                     staging words pre-filled with a quiet-NaN payload: every word validates itself, no fence and no
 //                     flag on the chain); each solved panel X_P of (d,s) is followed by the rank-8 update
 //                     (d,d) -= X_P X_P^T, so no 64^3 product stands between the solve and the factorisation;
 //                 [d] factor (d,d) — streaming ITS panels out — store, publish            (d = s+1)
-//     every CTA : its other tiles in index order (block column s first): panel update, and for j == s the same
-//                 streamed triangular solve against L(s,s) + publish.
-// Instruction footprint: the 8-column steps are run-time loops (factor_panel / trsm_solve / streaming exist once; only
-// the register-fragment parts are dispatched per step by a compare tree), 11.8k SASS instructions instead of 18.7k —
-// the single-warp panel factor takes ~900 cycles when its code stays in the instruction cache, 1400+ as one of eight
-// unrolled copies.
+//     every CTA : its other tiles in index order (block column s first): tensor-core panel update from bulk-copy staged
+//                 operands, and for j == s the same streamed triangular solve against L(s,s) + publish.
+// All register fragments (trailing updates, chain, column tiles) share the DMMA accumulator layout; every update is a
+// DMMA.  The 8-column steps are run-time loops: 6k SASS instructions (round 1: 18.7k unrolled, then 11.8k) — the
+// single-warp panel factor stalls on instruction fetch when the code does not fit the instruction cache.
 // The trailing updates of step s overlap the panel chain of step s+1 (look-ahead falls out of the data flow).
 // Then x = L^-T y: CTA nt-1-j owns x_j = L_jj^-T (y_j - sum_{i>j} L_ij^T x_i), consuming x_i as they appear.
 __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p) {
@@ -916,14 +809,15 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   const int G = gridDim.x, cta = blockIdx.x, tid = threadIdx.x;
   const int nd = p.chol_nd >= 0 ? p.chol_nd : chol_num_diag_ctas(G, nt);
   const CholFlags& F = cx.F;
+  const MmaPos mp;
 
   for (int s = 0; s < nt; s++) {
     const int cs = colstart(s, nt);
     cx.panel_full = (s == 0);
     if (s == 0 && cta == 0) {                       // D(0): the first diagonal tile
-      double c0f[4][4];
-      load_frag(c0f, tile_ptr(cx, 0, 0), ld);
-      factor_tile(c0f, cx.sB, 0, n, &p.hdr->chol_fail, p.Lstage);
+      double c0f[4][2][2];
+      load_frag_mma(c0f, tile_ptr(cx, 0, 0), ld, mp);
+      factor_tile(c0f, cx.sB, 0, n, &p.hdr->chol_fail, p.Lstage, mp);
       store_tile(tile_ptr(cx, 0, 0), cx.sB, ld);
       publish(F.ready + 0, F.panel_done + 0);
       trace_mark(0, 3);
@@ -931,39 +825,31 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
     }
     const int d = s + 1;
     if (d < nt && cta == chain_owner(d, G, nt, nd)) {     // the panel chain of this step
-      double cf[4][4], cd[4][4];
+      double cf[4][2][2], cd[4][2][2];
       // [a]+[b] diagonal tile (d,d) and sub-diagonal tile (d,s): panel s-1, with L(d,s-1) loaded once for both
-      load_frag(cd, tile_ptr(cx, d, d), ld);
-      load_frag(cf, tile_ptr(cx, d, s), ld);
+      load_frag_mma(cd, tile_ptr(cx, d, d), ld, mp);
+      load_frag_mma(cf, tile_ptr(cx, d, s), ld, mp);
       if (s > 0) {
         const int k = s - 1, ck = colstart(k, nt);
         if (!wait_flag(F.ready + ck + (d - k), 1u, F.ctl, &s_ok)) return;
         load_tile(cx.sA, tile_ptr(cx, d, k), ld);
         __syncthreads();
-        double acc[4][4];
-        tile_aat_lower(cx.sA, acc);
-#pragma unroll
-        for (int a = 0; a < 4; a++)
-#pragma unroll
-          for (int b = 0; b < 4; b++) cd[a][b] -= acc[a][b];
+#pragma unroll 1
+        for (int P = 0; P < 8; P++) frag_rank8_mma<kUpdSyrk>(cd, cx.sA, cx.sA, 8 * P, mp);   // (d,d) -= L(d,s-1) L(d,s-1)^T
         trace_mark(s, 7);
         // (d,s) -= L(d,s-1) L(s,s-1)^T with L(s,s-1) streamed from the previous chain CTA while it is being solved
-        if (!stream_gemm(cf, cx.sA, cx.sB, p.Xstage + size_t(s) * T * T, F.ctl)) return;
+        if (!stream_gemm(cf, cx.sA, cx.sB, p.Xstage + size_t(s) * T * T, F.ctl, mp)) return;
       }
       trace_mark(s, 6);
       // L(s,s) arrives panel by panel from the CTA that is factoring it; the triangular solve and the update of
       // (d,d) keep pace one panel behind, so only the last panel's work is left when that factorisation ends
       const double* stage = p.Lstage + size_t(s) * chol_stage_doubles();
-      if (!stream_trsm<true>(cf, cd, cx.sA, cx.sB, cx.sv, stage, F.ctl, p.Xstage + size_t(d) * T * T)) return;
+      if (!stream_trsm<true>(cf, cd, cx.sA, cx.sB, cx.sv, stage, F.ctl, mp, p.Xstage + size_t(d) * T * T)) return;
       trace_mark(s, 5);
       store_tile(tile_ptr(cx, d, s), cx.sA, ld);
-#pragma unroll
-      for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) cf[a][b] = cd[a][b];
       publish(F.ready + cs + 1, F.panel_done + s, kCholThreads - 1);   // L(d,s): released by the last warp
       trace_mark(d, 1);
-      factor_tile(cf, cx.sB, d * T, n, &p.hdr->chol_fail, p.Lstage + size_t(d) * chol_stage_doubles());
+      factor_tile(cd, cx.sB, d * T, n, &p.hdr->chol_fail, p.Lstage + size_t(d) * chol_stage_doubles(), mp);
       trace_mark(d, 2);
       store_tile(tile_ptr(cx, d, d), cx.sB, ld);
       publish(F.ready + colstart(d, nt), F.panel_done + d);
@@ -978,7 +864,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
       w.start(0, cta, G, nt, nd);
       int i, j;
       while (w.next(i, j))
-        if (!process_tile(cx, i, j, 0)) return;
+        if (j == 0 && !first_column_tile(cx, i, mp)) return;     // tiles with j > 0 have nothing to take at step 0
     }
   }
 
