@@ -54,6 +54,13 @@ struct BALayout {
   int n, nt, ld, Mcap;
 };
 
+// Reduced system Hb = [H | b] in fp64: H is symmetric and only its lower triangle is ever read (ba_solve.cu), so only
+// that is stored — packed row by row, element (r, c <= r) at r (r+1)/2 + c.  Half the bytes for the all-reduce of the
+// edge-sharded multi-GPU runs (the only exchange of an iteration) and half the atomics of the scatter.
+__host__ __device__ inline size_t sys_index(int r, int c) { return size_t(r) * size_t(r + 1) / 2 + size_t(c); }
+__host__ __device__ inline size_t sys_h_elems(int n) { return size_t(n) * size_t(n + 1) / 2; }
+__host__ __device__ inline size_t sys_elems(int n) { return sys_h_elems(n) + size_t(n); }
+
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 // Host-side layout of the caller-provided workspace.
@@ -78,7 +85,7 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.yvec = take(sizeof(float) * 6 * size_t(N > 0 ? N : 1));
   L.Q = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
   L.w = take(motion_only ? 16 : sizeof(float) * size_t(L.Mcap) * HW);
-  L.Hb = take(sizeof(double) * (size_t(L.n) * L.n + L.n));
+  L.Hb = take(sizeof(double) * sys_elems(L.n));
   // [A; b^T] -> [L; y^T] in place: lower block triangle + the rhs block row, tile-major, tiles of [64][64+4] (ba_solve.cu)
   L.Wk = take(sizeof(double) * (size_t(L.nt) * (L.nt + 3) / 2) * kCholTile * (kCholTile + 4));
   L.cflags = take(sizeof(unsigned) * chol_flag_words(L.nt));

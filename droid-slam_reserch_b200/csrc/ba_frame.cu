@@ -378,11 +378,11 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
     __syncthreads();
     const int n = p.n;
     double* H = p.Hb;
-    double* bvec = p.Hb + size_t(n) * n;
+    double* bvec = p.Hb + sys_h_elems(n);
     for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
       const int ef = i / 36, rc = i - ef * 36, e = ef / d, f2 = ef - e * d, r = rc / 6, c = rc - r * 6;
       const int je = sm.jp[e], jf = sm.jp[f2];
-      if (je >= 0 && jf >= 0) atomicAdd(&H[size_t(6 * je + r) * n + 6 * jf + c], Dval(e, f2, r, c));
+      if (je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c)], Dval(e, f2, r, c));
     }
     if (ip >= 0) {
       for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
@@ -390,8 +390,8 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
         const int jf = sm.jp[f2];
         if (jf >= 0) {
           const double v = -sm.Ws[i];
-          atomicAdd(&H[size_t(6 * ip + r) * n + 6 * jf + c], v);
-          atomicAdd(&H[size_t(6 * jf + c) * n + 6 * ip + r], v);
+          const int ra = 6 * ip + r, ca = 6 * jf + c;      // the element and its mirror: one of them is in the lower triangle
+          atomicAdd(&H[ra >= ca ? sys_index(ra, ca) : sys_index(ca, ra)], v);
         }
       }
       if (tid < 36) {                                      // (i, i) += sum_f W_f A_f^T
@@ -399,7 +399,7 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
         double s = 0.0;
         for (int f2 = 0; f2 < d; f2++)
           for (int kk = 0; kk < 6; kk++) s += sm.Ws[f2 * 36 + r * 6 + kk] * double(sm.Am[f2 * 36 + c * 6 + kk]);
-        atomicAdd(&H[size_t(6 * ip + r) * n + 6 * ip + c], s);
+        if (r >= c) atomicAdd(&H[sys_index(6 * ip + r, 6 * ip + c)], s);
       } else if (tid >= 64 && tid < 70) {                  // b_i += -sum_e A_e c_e
         const int r = tid - 64;
         double s = 0.0;
@@ -809,11 +809,11 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   __syncthreads();
   const int n = p.n;
   double* H = p.Hb;
-  double* bvec = p.Hb + size_t(n) * n;
+  double* bvec = p.Hb + sys_h_elems(n);
   for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
     const int ef = i / 36, rc = i - ef * 36, e1 = ef / d, f2 = ef - e1 * d, r = rc / 6, c2 = rc - r * 6;
     const int je = sm.jp[e1], jf = sm.jp[f2];
-    if (je >= 0 && jf >= 0) atomicAdd(&H[size_t(6 * je + r) * n + 6 * jf + c2], Dval(e1, f2, r, c2));
+    if (je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c2) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c2)], Dval(e1, f2, r, c2));
   }
   if (ip >= 0) {
     for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
@@ -821,8 +821,8 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
       const int jf = sm.jp[f2];
       if (jf >= 0) {
         const double v = -sm.Ws[i];
-        atomicAdd(&H[size_t(6 * ip + r) * n + 6 * jf + c2], v);
-        atomicAdd(&H[size_t(6 * jf + c2) * n + 6 * ip + r], v);
+        const int ra = 6 * ip + r, ca = 6 * jf + c2;     // the element and its mirror: one of them is in the lower triangle
+        atomicAdd(&H[ra >= ca ? sys_index(ra, ca) : sys_index(ca, ra)], v);
       }
     }
     if (tid < 36) {                                      // (i, i) += sum_f W_f A_f^T
@@ -830,7 +830,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
       double s = 0.0;
       for (int f2 = 0; f2 < d; f2++)
         for (int kk = 0; kk < 6; kk++) s += sm.Ws[f2 * 36 + r * 6 + kk] * double(sm.Am[f2 * 36 + c2 * 6 + kk]);
-      atomicAdd(&H[size_t(6 * ip + r) * n + 6 * ip + c2], s);
+      if (r >= c2) atomicAdd(&H[sys_index(6 * ip + r, 6 * ip + c2)], s);
     } else if (tid >= 64 && tid < 70) {                  // b_i += -sum_e A_e c_e
       const int r = tid - 64;
       double s = 0.0;
@@ -904,7 +904,7 @@ static int launch_schur(const BAParams& p, int S, int dlo, int dcap, cudaStream_
 }
 
 int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
-  DB200_CUDA(cudaMemsetAsync(p.Hb, 0, sizeof(double) * (size_t(p.n) * p.n + p.n), st));
+  DB200_CUDA(cudaMemsetAsync(p.Hb, 0, sizeof(double) * sys_elems(p.n), st));
   if (p.motion_only) {
     const int nsub = cdiv(p.HW, kBAThreads);
     int S = cdiv(4 * kNumSMs, p.Mcap);

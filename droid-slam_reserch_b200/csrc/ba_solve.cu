@@ -98,7 +98,7 @@ __device__ __forceinline__ void publish(unsigned* flag, unsigned* counter, int s
 __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
   const int n = p.n, ld = p.ld;
   const double* H = p.Hb;
-  const double* b = p.Hb + size_t(n) * n;
+  const double* b = p.Hb + sys_h_elems(n);
   const size_t gtid = size_t(blockIdx.x) * blockDim.x + threadIdx.x, gstride = size_t(gridDim.x) * blockDim.x;
   if (gtid == 0) p.hdr->chol_fail = 0;
   const size_t nflags = chol_flag_words(p.nt);
@@ -124,7 +124,7 @@ __global__ void chol_prepare_kernel(BAParams p, float lm, float ep) {
       double v = 0.0;
       if (r < n) {
         if (c <= r) {
-          v = H[size_t(r) * n + c];
+          v = H[sys_index(r, c)];
           if (c == r) v += double(ep) + double(lm) * v;      // diag += ep + lm*diag  (droid_kernels.cu:1197)
         }
       } else if (r < ld) {

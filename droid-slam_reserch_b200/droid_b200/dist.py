@@ -66,7 +66,7 @@ def local_depth_rows(ii_all, ii_local, t0: int, t1: int):
 
 
 def allreduce_system(Hb: torch.Tensor, group=None) -> torch.Tensor:
-    """Sum of the per-rank partial reduced systems, in place (fp64 [n*n + n]).  NCCL on GPU tensors
+    """Sum of the per-rank partial reduced systems, in place (fp64, lower triangle of H packed + b: n(n+1)/2 + n values).  NCCL on GPU tensors
     (NVLink 5 / NVSwitch, in-switch reduction when available), gloo on CPU tensors."""
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(Hb, op=dist.ReduceOp.SUM, group=group)
@@ -162,7 +162,7 @@ class ShardedBA:
         sys_ptr = lib.db200_ba_system_ptr(vp(ws), N, B, ht, wd, self.t0, self.t1, M_loc, mo)
         off = int(sys_ptr) - ws.data_ptr()
         n_el = int(lib.db200_ba_system_elems(self.t0, self.t1))
-        self.system = ws[off:off + 8 * n_el].view(torch.float64)        # [H (n x n) | b] fp64: the all-reduced buffer
+        self.system = ws[off:off + 8 * n_el].view(torch.float64)        # [H (packed lower triangle) | b] fp64: the all-reduced buffer
         P = self.t1 - self.t0
         self._dx = torch.empty((P, 6), dtype=torch.float32, device=self.device)
         self._dz_loc = None if mo else torch.empty((M_loc, ht * wd), dtype=torch.float32, device=self.device)

@@ -150,8 +150,9 @@ int db200_ba(float* poses, float* disps, const float* intrinsics, const float* d
 int db200_ba_status(const void* workspace, db200_stream_t stream);
 
 /* Phase-split BA for edge-sharded multi-GPU runs.  One iteration =
- *   db200_ba_accumulate  : local edges -> this rank's partial reduced system Hb = [H (n x n, row-major,
- *                          lower+upper), b (n)] in fp64, n = 6*(t1-t0);   (first call builds the graph)
+ *   db200_ba_accumulate  : local edges -> this rank's partial reduced system Hb = [H (lower triangle packed row by
+ *                          row: element (r, c <= r) at r(r+1)/2 + c), b (n)] in fp64, n = 6*(t1-t0);
+ *                          db200_ba_system_elems() = n(n+1)/2 + n doubles;   (first call builds the graph)
  *   <allreduce(sum) of Hb over ranks — NCCL, done by the caller>
  *   db200_ba_solve_update: damped Cholesky solve, pose retraction (all poses), depth back-substitution
  *                          and disparity update for the LOCAL source frames.
