@@ -932,6 +932,212 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
   }
 }
 
+// ---- small systems (frontend windows): ONE CTA, the whole matrix in shared memory ---------------------------------------
+// The local BA of the frontend (factor_graph.py:199-244: ~25 keyframes, ~100 edges, n = 6 P ~ 130) is latency, not
+// throughput: the tiled solver above needs ~35 us per 64 columns of chain (flags, streaming, 9 CTAs) — 107 us at n = 132.
+// Here the damped lower triangle + the right-hand side as one more row live in shared memory ([np+8][np+1] fp64, np = n
+// rounded up to 8), and one CTA runs a blocked right-looking factorisation: 8 columns per step = the redundant 8x8 block
+// factorisation of factor_panel (one thread per row below the block, paired pivots), then the rank-8 update of the
+// trailing 8x8 tiles by DMMA (tile list from a table built once; eight tiles per warp in flight, the two k-halves in
+// separate accumulators); the rhs row turns into y = L^-1 b on the way.  L^T x = y follows blocked by 8 with the 8x8
+// diagonal blocks inverted up front.  No prepare kernel, no flags: 47 us at n = 132 (c2), 17 us at n = 42 (c1).
+// Measured (tools/small_trace.py, n = 132): load 8k cycles, 17 steps of [panel 1.25k + update 5.7k -> 0.3k], back-
+// substitution 12k.  The update is bound by shared-memory wavefronts (8 accesses of a 2..3-way conflicting fragment
+// pattern per tile and two DMMAs), not by the FP64 pipe; next: trailing tiles resident in registers (as in the tiled
+// solver), panel columns staged in a conflict-free side buffer.
+constexpr int kSmallMaxN = 160;          // [168][161] doubles + vectors = 223 KB of the 227 KB a CTA can have
+constexpr int kSmallThreads = 512;
+
+__device__ __forceinline__ void small_panel(double* A, int ld, int c0, int nrows, int n, int* chol_fail) {
+  const int tid = threadIdx.x;
+  if (tid < nrows) {
+    const int r = c0 + tid;
+    double D[8][8], x[8];
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+      for (int b = 0; b <= a; b++) D[a][b] = A[(c0 + a) * ld + c0 + b];
+#pragma unroll
+    for (int q = 0; q < 8; q++) x[q] = A[r * ld + c0 + q];
+    bool bad = false;
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      const double d0 = D[c][c], a10 = D[c + 1][c], a11 = D[c + 1][c + 1];
+      const double det = fma(a11, d0, -(a10 * a10));
+      bad = bad || (d0 <= 0.0 && c0 + c < n) || (det <= 0.0 && c0 + c + 1 < n);
+      const double rs0 = fast_rsqrt(d0), rsd = fast_rsqrt(det);
+      const double sq0 = d0 * rs0;
+      const double rs1 = sq0 * rsd;            // 1/sqrt(d1), d1 = det/d0
+      const double l10 = a10 * rs0;
+      D[c + 1][c] = l10;
+#pragma unroll
+      for (int a = c + 2; a < 8; a++) {
+        D[a][c] *= rs0;
+        D[a][c + 1] = fma(-D[a][c], l10, D[a][c + 1]) * rs1;
+      }
+#pragma unroll
+      for (int a = c + 2; a < 8; a++)
+#pragma unroll
+        for (int b = c + 2; b <= a; b++) D[a][b] = fma(-D[a][c + 1], D[b][c + 1], fma(-D[a][c], D[b][c], D[a][b]));
+      double s0 = x[c], s1 = x[c + 1];
+#pragma unroll
+      for (int m = 0; m < c; m++) { s0 = fma(-x[m], D[c][m], s0); s1 = fma(-x[m], D[c + 1][m], s1); }
+      x[c] = s0 * rs0;
+      x[c + 1] = fma(-x[c], l10, s1) * rs1;
+    }
+    if (tid == 0 && bad) atomicExch(chol_fail, 1);      // NaN pivots pass, like Eigen's `d <= 0` test
+#pragma unroll
+    for (int q = 0; q < 8; q++) A[r * ld + c0 + q] = (tid < q) ? 0.0 : x[q];
+  }
+}
+
+__global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p, float lm, float ep) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int n = p.n, np = (n + 7) / 8 * 8, ld = np + 1, tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  double* A = reinterpret_cast<double*>(smem_raw);          // [np+8][ld]; row np = right-hand side, rows np+1.. zero
+  double* xs = A + size_t(np + 8) * ld;                     // [np] solution
+  double* Li = xs + np;                                     // [np/8][8][8] inverses of the 8x8 diagonal blocks of L
+  __shared__ unsigned short s_tile[(kSmallMaxN / 8) * (kSmallMaxN / 8 + 1) / 2];   // b -> (ti << 8) | tj of the lower triangle, row by row
+  const double* H = p.Hb;
+  const double* bsrc = p.Hb + sys_h_elems(n);
+  if (tid == 0) p.hdr->chol_fail = 0;
+  for (int b = tid; b < (np / 8) * (np / 8 + 1) / 2; b += kSmallThreads) {   // once: the trailing updates index it every step
+    int ti = int((sqrtf(8.0f * float(b) + 1.0f) - 1.0f) * 0.5f);
+    while ((ti + 1) * (ti + 2) / 2 <= b) ti++;
+    while (ti * (ti + 1) / 2 > b) ti--;
+    s_tile[b] = (unsigned short)((ti << 8) | (b - ti * (ti + 1) / 2));
+  }
+  fine_mark(0);
+  // load: zero fill, then the packed lower triangle row by row (coalesced), identity padding and the rhs row
+  for (int e = tid; e < (np + 8) * ld; e += kSmallThreads) A[e] = 0.0;
+  __syncthreads();
+  // row r of the packed triangle = r+1 contiguous doubles at r(r+1)/2: one warp per row, four rows in flight
+  constexpr int kWarps = kSmallThreads / 32;
+#pragma unroll 1
+  for (int r0 = warp; r0 < n; r0 += 4 * kWarps) {
+    double v[4][5];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int r = r0 + u * kWarps;
+      const double* src = H + sys_index(r < n ? r : 0, 0);
+#pragma unroll
+      for (int k = 0; k < 5; k++) { const int c = lane + 32 * k; v[u][k] = (r < n && c <= r) ? src[c] : 0.0; }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int r = r0 + u * kWarps;
+#pragma unroll
+      for (int k = 0; k < 5; k++) {
+        const int c = lane + 32 * k;
+        if (r < n && c <= r) {
+          double w = v[u][k];
+          if (c == r) w += double(ep) + double(lm) * w;      // diag += ep + lm*diag  (droid_kernels.cu:1197)
+          A[r * ld + c] = w;
+        }
+      }
+    }
+  }
+  for (int j = tid; j < np; j += kSmallThreads) {
+    if (j >= n) A[j * ld + j] = 1.0;                         // identity padding
+    A[np * ld + j] = (j < n) ? bsrc[j] : 0.0;                // right-hand side as one more row
+  }
+  __syncthreads();
+  fine_mark(1);
+  for (int c0 = 0; c0 < np; c0 += 8) {
+    small_panel(A, ld, c0, np + 1 - c0, n, &p.hdr->chol_fail);
+    __syncthreads();
+    if (c0 < 64) fine_mark(2 + c0 / 4);
+    // trailing update on the FP64 tensor-core path: 8x8 tiles (ti, tj <= ti) of the block-lower part from row/column
+    // o = c0 + 8, plus the tile row that holds the rhs (row np, padded with zero rows); one tile = two DMMAs (k = 0..3, 4..7)
+    const int o = c0 + 8, mt = (np - o) / 8;                 // mt column tiles, mt + 1 row tiles
+    const int ntri = mt * (mt + 1) / 2, ntile = ntri + mt;
+    // A DMMA's result takes a few hundred cycles to come back: eight tiles per warp in flight, and the two k-halves of a
+    // tile go to separate accumulators (summed afterwards) so that no DMMA waits for another
+    constexpr int kInFlight = 8;
+#pragma unroll 1
+    for (int b0 = warp; b0 < ntile; b0 += kInFlight * kWarps) {
+      double d1[kInFlight][2], d2[kInFlight][2];
+      double* cc[kInFlight];
+#pragma unroll
+      for (int u = 0; u < kInFlight; u++) {
+        const int b = b0 + u * kWarps;
+        cc[u] = nullptr;
+        if (b < ntile) {                                     // warp-uniform
+          int ti, tj;
+          if (b < ntri) { const int e = s_tile[b]; ti = e >> 8; tj = e & 255; }
+          else { ti = mt; tj = b - ntri; }
+          const double* pr = A + (o + 8 * ti + g) * ld + c0 + t;
+          const double* pc = A + (o + 8 * tj + g) * ld + c0 + t;
+          cc[u] = A + (o + 8 * ti + g) * ld + o + 8 * tj + 2 * t;
+          d1[u][0] = cc[u][0]; d1[u][1] = cc[u][1];
+          d2[u][0] = 0.0; d2[u][1] = 0.0;
+          dmma884(d1[u], -pr[0], pc[0]);
+          dmma884(d2[u], -pr[4], pc[4]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kInFlight; u++)
+        if (cc[u] != nullptr) { cc[u][0] = d1[u][0] + d2[u][0]; cc[u][1] = d1[u][1] + d2[u][1]; }
+    }
+    __syncthreads();
+    if (c0 < 64) fine_mark(3 + c0 / 4);
+  }
+  fine_mark(20);
+  // ---- L^T x = y, y = row np.  The 8x8 diagonal blocks of L are inverted up front (one thread per block, all at once);
+  // then, blocked by 8 from the end: x_blk = Linv^T y_blk by 8 threads, and every thread j < c0 takes
+  // y_j -= sum_q L[c0+q][j] x_q
+  for (int j = tid; j < np; j += kSmallThreads) xs[j] = A[np * ld + j];
+  if (tid < np / 8) {
+    const int c0 = 8 * tid;
+    double Lb[8][8], M[8][8];
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+      for (int c = 0; c <= a; c++) Lb[a][c] = A[(c0 + a) * ld + c0 + c];
+    double ri[8];
+#pragma unroll
+    for (int a = 0; a < 8; a++) ri[a] = 1.0 / Lb[a][a];
+#pragma unroll
+    for (int c = 0; c < 8; c++) {                            // column c of M = Lb^-1 by forward substitution
+#pragma unroll
+      for (int a = 0; a < 8; a++) {
+        if (a < c) { M[a][c] = 0.0; continue; }
+        double sacc = (a == c) ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (k >= c && k < a) sacc = fma(-Lb[a][k], M[k][c], sacc);
+        M[a][c] = sacc * ri[a];
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 8; a++)
+#pragma unroll
+      for (int c = 0; c < 8; c++) Li[tid * 64 + a * 8 + c] = M[a][c];
+  }
+  __syncthreads();
+  for (int c0 = np - 8; c0 >= 0; c0 -= 8) {
+    if (tid < 8) {                                           // x_q = sum_{a >= q} M[a][q] y_a
+      const double* M = Li + (c0 / 8) * 64;
+      double x = 0.0;
+#pragma unroll
+      for (int a = 0; a < 8; a++) x = fma(M[a * 8 + tid], xs[c0 + a], x);
+      __syncwarp(0xffu);
+      xs[c0 + tid] = x;
+    }
+    __syncthreads();
+    for (int j = tid; j < c0; j += kSmallThreads) {
+      double y = xs[j];
+#pragma unroll
+      for (int q = 0; q < 8; q++) y = fma(-A[(c0 + q) * ld + j], xs[c0 + q], y);
+      xs[j] = y;
+    }
+    __syncthreads();
+  }
+  fine_mark(21);
+  for (int j = tid; j < n; j += kSmallThreads) p.xsol[j] = xs[j];
+}
+
 // dx (fp32) = failed ? 0 : x ;  also the user-visible dx_out
 __global__ void post_dx_kernel(BAParams p, float* __restrict__ dx_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1029,6 +1235,19 @@ static int chol_grid_size(size_t smem) {
 }
 
 int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
+  if (p.n <= kSmallMaxN && getenv("DB200_CHOL_NO_SMALL") == nullptr) {           // frontend-size systems: one CTA, no flags
+    const int np = (p.n + 7) / 8 * 8;
+    const size_t smem_small = sizeof(double) * (size_t(np + 8) * (np + 1) + 9 * size_t(np));
+    static bool attr_set = false;
+    if (!attr_set) {
+      const size_t mx = sizeof(double) * (size_t(kSmallMaxN + 8) * (kSmallMaxN + 1) + 9 * size_t(kSmallMaxN));
+      DB200_CUDA(cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx)));
+      attr_set = true;
+    }
+    chol_small_kernel<<<1, kSmallThreads, smem_small, st>>>(p, lm, ep);
+    DB200_CHECK_LAUNCH();
+    return DB200_OK;
+  }
   chol_prepare_kernel<<<4 * kNumSMs, 256, 0, st>>>(p, lm, ep);
   DB200_CHECK_LAUNCH();
   const size_t smem = 4 * sizeof(double) * T * TQ + sizeof(double) * 6 * 64;

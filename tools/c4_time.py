@@ -6,12 +6,14 @@ sys.path[:0] = [REPO, os.path.join(REPO, "droid-slam_reserch_b200")]
 import droid_backends
 from droid_b200 import _capi, synth
 STAGES = ["graph", "edge_prep", "accumulate", "solve", "post", "backsub"]
-p = synth.config_c4() if (len(sys.argv) < 2 or sys.argv[1] == "c4") else synth.config_c3()
+cfg = sys.argv[1] if len(sys.argv) > 1 else "c4"
+p = {"c4": synth.config_c4, "c3": synth.config_c3, "c2": synth.config_c2, "c1": synth.config_c1}[cfg]()
 dev = torch.device("cuda:0")
 t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 args = [t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)]
 lib = _capi.lib()
-for it in range(3):
+reps = 3 if cfg in ("c3", "c4") else 30
+for it in range(reps):
     poses, disps = t(p.poses), t(p.disps)
     torch.cuda.synchronize()
     if it == 1:
@@ -21,7 +23,8 @@ for it in range(3):
     droid_backends.ba(poses, disps, *args, p.t0, p.t1, 2, 1e-5, 1e-2, False)
     e1.record()
     torch.cuda.synchronize()
-    print(f"call {it}: {e0.elapsed_time(e1):.2f} ms for 2 iterations")
+    if it < 2 or it == reps - 1:
+        print(f"call {it}: {e0.elapsed_time(e1):.3f} ms for 2 iterations")
 st_ms = (C.c_double * len(STAGES))(); st_n = (C.c_int * len(STAGES))()
 lib.db200_profile_collect(st_ms, st_n)
 lib.db200_profile_enable(0)
