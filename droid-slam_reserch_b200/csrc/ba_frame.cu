@@ -912,7 +912,12 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
     return launch_frames<1, true>(p, S, 0, 32, st);
   }
   const int nchunks = cdiv(p.HW, kChunk);
-  int S = cdiv(6 * kNumSMs, p.Mcap);               // aim at >= ~6 CTAs per SM over the launch
+  // CTAs per launch: ~6 per SM for backend graphs (hundreds of frames), but a frontend window (8..25 frames) is fastest
+  // with ~1.3 per SM — its CTAs have few chunks each and the per-CTA set-up dominates (measured: 25 frames best at 8
+  // splits, 8 frames at 24, 512 frames at 2)
+  int ctas = 2 * p.Mcap;
+  ctas = ctas < 192 ? 192 : (ctas > 6 * kNumSMs ? 6 * kNumSMs : ctas);
+  int S = cdiv(ctas, p.Mcap);
   static const int s_env = getenv("DB200_BA_SPLIT") ? atoi(getenv("DB200_BA_SPLIT")) : 0;   // tuning aid
   if (s_env > 0) S = s_env;
   S = S < 1 ? 1 : (S > nchunks ? nchunks : S);

@@ -1138,86 +1138,91 @@ __global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p
   for (int j = tid; j < n; j += kSmallThreads) p.xsol[j] = xs[j];
 }
 
-// dx (fp32) = failed ? 0 : x ;  also the user-visible dx_out
-__global__ void post_dx_kernel(BAParams p, float* __restrict__ dx_out) {
+// ---- after the solve: ONE kernel (three launches in the first version; at frontend sizes launches are the cost) ----------
+//   dx (fp32) = failed ? 0 : x, also the user-visible dx_out;
+//   y_e = [0 < j_e-t0 < P] dx_j - [0 < i-t0 < P] A_e^T dx_i   (EvT6x1_kernel's `idx <= 0` quirk, :1105) for the
+//         depth back-substitution;
+//   poses[k] <- Exp(dx[k-t0]) * poses[k]   (retrSE3/expSE3/expSO3, :110-175, :877-895).
+// Every role reads the solution x directly (all three only depend on it), so no role waits for another.
+__device__ __forceinline__ float solved_dx(const BAParams& p, bool fail, int i) { return fail ? 0.0f : float(p.xsol[i]); }
+
+__global__ void post_solve_kernel(BAParams p, float* __restrict__ dx_out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (p.hdr->status < 0) return;
   const bool fail = p.hdr->chol_fail != 0;
+  // (the header is only written by thread 0 below, after every thread of ITS block has read it; other blocks may still
+  // read status afterwards, which only ever changes from 0 to 1 here — never to an error code)
+  __syncthreads();
   if (i == 0 && fail) { p.hdr->any_fail += 1; if (p.hdr->status == 0) p.hdr->status = 1; }
   if (i < p.n) {
-    const float v = fail ? 0.0f : float(p.xsol[i]);
+    const float v = solved_dx(p, fail, i);
     p.dx[i] = v;
     if (dx_out) dx_out[i] = v;
   }
-}
-
-// y_e = [0 < j_e-t0 < P] dx_j - [0 < i-t0 < P] A_e^T dx_i   (EvT6x1_kernel's `idx <= 0` quirk, :1105)
-__global__ void post_y_kernel(BAParams p) {
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= p.N || p.hdr->status < 0) return;
-  const EdgeRec r = p.erec[q];
-  float y[6] = {0, 0, 0, 0, 0, 0};
-  if (r.slot >= 0) {
-    const int ip = int(p.ii[r.eid]) - p.t0, jpz = r.jpose;
-    if (jpz > 0 && jpz < p.P)
-      for (int c = 0; c < 6; c++) y[c] = p.dx[6 * jpz + c];
-    if (ip > 0 && ip < p.P) {
-      const float* v = p.dx + 6 * ip;
-      const float tx[9] = {0.0f, -r.t[2], r.t[1], r.t[2], 0.0f, -r.t[0], -r.t[1], r.t[0], 0.0f};
-      // A^T v = [R v_tau + [t]x R v_phi ; R v_phi]   (A = [[R^T,0],[-R^T [t]x, R^T]])
-      float Rt[3], Rp[3];
-      for (int a = 0; a < 3; a++) {
-        Rt[a] = r.R[a * 3] * v[0] + r.R[a * 3 + 1] * v[1] + r.R[a * 3 + 2] * v[2];
-        Rp[a] = r.R[a * 3] * v[3] + r.R[a * 3 + 1] * v[4] + r.R[a * 3 + 2] * v[5];
-      }
-      for (int a = 0; a < 3; a++) {
-        y[a] -= Rt[a] + (tx[a * 3] * Rp[0] + tx[a * 3 + 1] * Rp[1] + tx[a * 3 + 2] * Rp[2]);
-        y[3 + a] -= Rp[a];
+  if (i < p.N && !p.motion_only) {
+    const int q = i;
+    const EdgeRec r = p.erec[q];
+    float y[6] = {0, 0, 0, 0, 0, 0};
+    if (r.slot >= 0) {
+      const int ip = int(p.ii[r.eid]) - p.t0, jpz = r.jpose;
+      if (jpz > 0 && jpz < p.P)
+        for (int c = 0; c < 6; c++) y[c] = solved_dx(p, fail, 6 * jpz + c);
+      if (ip > 0 && ip < p.P) {
+        float v[6];
+        for (int c = 0; c < 6; c++) v[c] = solved_dx(p, fail, 6 * ip + c);
+        const float tx[9] = {0.0f, -r.t[2], r.t[1], r.t[2], 0.0f, -r.t[0], -r.t[1], r.t[0], 0.0f};
+        // A^T v = [R v_tau + [t]x R v_phi ; R v_phi]   (A = [[R^T,0],[-R^T [t]x, R^T]])
+        float Rt[3], Rp[3];
+        for (int a = 0; a < 3; a++) {
+          Rt[a] = r.R[a * 3] * v[0] + r.R[a * 3 + 1] * v[1] + r.R[a * 3 + 2] * v[2];
+          Rp[a] = r.R[a * 3] * v[3] + r.R[a * 3 + 1] * v[4] + r.R[a * 3 + 2] * v[5];
+        }
+        for (int a = 0; a < 3; a++) {
+          y[a] -= Rt[a] + (tx[a * 3] * Rp[0] + tx[a * 3 + 1] * Rp[1] + tx[a * 3 + 2] * Rp[2]);
+          y[3 + a] -= Rp[a];
+        }
       }
     }
+    for (int c = 0; c < 6; c++) p.yvec[size_t(q) * 6 + c] = y[c];
   }
-  for (int c = 0; c < 6; c++) p.yvec[size_t(q) * 6 + c] = y[c];
-}
-
-// poses[k] <- Exp(dx[k-t0]) * poses[k]   (retrSE3/expSE3/expSO3, :110-175, :877-895)
-__global__ void pose_retr_kernel(BAParams p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= p.P || p.hdr->status < 0) return;
-  float* pose = p.poses + 7 * size_t(p.t0 + i);
-  const float* xi = p.dx + 6 * i;
-  const float phi[3] = {xi[3], xi[4], xi[5]};
-  float tau[3] = {xi[0], xi[1], xi[2]};
-  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
-  const float theta_p4 = theta_sq * theta_sq;
-  const float theta = sqrtf(theta_sq);
-  float imag, real;
-  if (double(theta_sq) < 1e-8) {
-    imag = float(0.5 - (1.0 / 48.0) * double(theta_sq) + (1.0 / 3840.0) * double(theta_p4));
-    real = float(1.0 - (1.0 / 8.0) * double(theta_sq) + (1.0 / 384.0) * double(theta_p4));
-  } else {
-    imag = sinf(0.5f * theta) / theta;
-    real = cosf(0.5f * theta);
+  if (i < p.P) {
+    float* pose = p.poses + 7 * size_t(p.t0 + i);
+    float xi[6];
+    for (int c = 0; c < 6; c++) xi[c] = solved_dx(p, fail, 6 * i + c);
+    const float phi[3] = {xi[3], xi[4], xi[5]};
+    float tau[3] = {xi[0], xi[1], xi[2]};
+    const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+    const float theta_p4 = theta_sq * theta_sq;
+    const float theta = sqrtf(theta_sq);
+    float imag, real;
+    if (double(theta_sq) < 1e-8) {
+      imag = float(0.5 - (1.0 / 48.0) * double(theta_sq) + (1.0 / 3840.0) * double(theta_p4));
+      real = float(1.0 - (1.0 / 8.0) * double(theta_sq) + (1.0 / 384.0) * double(theta_p4));
+    } else {
+      imag = sinf(0.5f * theta) / theta;
+      real = cosf(0.5f * theta);
+    }
+    const float dq[4] = {imag * phi[0], imag * phi[1], imag * phi[2], real};
+    float dt[3] = {tau[0], tau[1], tau[2]};
+    if (double(theta) > 1e-4) {
+      const float a = (1.0f - cosf(theta)) / theta_sq;
+      float c1[3] = {phi[1] * tau[2] - phi[2] * tau[1], phi[2] * tau[0] - phi[0] * tau[2], phi[0] * tau[1] - phi[1] * tau[0]};
+      dt[0] += a * c1[0]; dt[1] += a * c1[1]; dt[2] += a * c1[2];
+      const float b = (theta - sinf(theta)) / (theta * theta_sq);
+      float c2[3] = {phi[1] * c1[2] - phi[2] * c1[1], phi[2] * c1[0] - phi[0] * c1[2], phi[0] * c1[1] - phi[1] * c1[0]};
+      dt[0] += b * c2[0]; dt[1] += b * c2[1]; dt[2] += b * c2[2];
+    }
+    const float t[3] = {pose[0], pose[1], pose[2]};
+    const float q[4] = {pose[3], pose[4], pose[5], pose[6]};
+    float q1[4], t1[3];
+    q1[0] = dq[3] * q[0] + dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1];
+    q1[1] = dq[3] * q[1] + dq[1] * q[3] + dq[2] * q[0] - dq[0] * q[2];
+    q1[2] = dq[3] * q[2] + dq[2] * q[3] + dq[0] * q[1] - dq[1] * q[0];
+    q1[3] = dq[3] * q[3] - dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2];
+    act_so3(dq, t, t1);
+    pose[0] = t1[0] + dt[0]; pose[1] = t1[1] + dt[1]; pose[2] = t1[2] + dt[2];
+    pose[3] = q1[0]; pose[4] = q1[1]; pose[5] = q1[2]; pose[6] = q1[3];
   }
-  const float dq[4] = {imag * phi[0], imag * phi[1], imag * phi[2], real};
-  float dt[3] = {tau[0], tau[1], tau[2]};
-  if (double(theta) > 1e-4) {
-    const float a = (1.0f - cosf(theta)) / theta_sq;
-    float c1[3] = {phi[1] * tau[2] - phi[2] * tau[1], phi[2] * tau[0] - phi[0] * tau[2], phi[0] * tau[1] - phi[1] * tau[0]};
-    dt[0] += a * c1[0]; dt[1] += a * c1[1]; dt[2] += a * c1[2];
-    const float b = (theta - sinf(theta)) / (theta * theta_sq);
-    float c2[3] = {phi[1] * c1[2] - phi[2] * c1[1], phi[2] * c1[0] - phi[0] * c1[2], phi[0] * c1[1] - phi[1] * c1[0]};
-    dt[0] += b * c2[0]; dt[1] += b * c2[1]; dt[2] += b * c2[2];
-  }
-  const float t[3] = {pose[0], pose[1], pose[2]};
-  const float q[4] = {pose[3], pose[4], pose[5], pose[6]};
-  float q1[4], t1[3];
-  q1[0] = dq[3] * q[0] + dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1];
-  q1[1] = dq[3] * q[1] + dq[1] * q[3] + dq[2] * q[0] - dq[0] * q[2];
-  q1[2] = dq[3] * q[2] + dq[2] * q[3] + dq[0] * q[1] - dq[1] * q[0];
-  q1[3] = dq[3] * q[3] - dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2];
-  act_so3(dq, t, t1);
-  pose[0] = t1[0] + dt[0]; pose[1] = t1[1] + dt[1]; pose[2] = t1[2] + dt[2];
-  pose[3] = q1[0]; pose[4] = q1[1]; pose[5] = q1[2]; pose[6] = q1[3];
 }
 
 static int chol_grid_size(size_t smem) {
@@ -1277,10 +1282,9 @@ extern "C" int db200_debug_chol_trace(long long* device_buffer) {
 namespace db200 {
 
 int ba_post_solve(const BAParams& p, float* dx_out, cudaStream_t st) {
-  post_dx_kernel<<<cdiv(p.n, 256), 256, 0, st>>>(p, dx_out);
-  if (p.N > 0 && !p.motion_only) post_y_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
-  pose_retr_kernel<<<cdiv(p.P, 128), 128, 0, st>>>(p);
-  DB200_COUNT((p.N > 0 && !p.motion_only) ? 2 : 1);
+  int work = p.n > p.P ? p.n : p.P;
+  if (!p.motion_only && p.N > work) work = p.N;
+  post_solve_kernel<<<cdiv(work, 128), 128, 0, st>>>(p, dx_out);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
