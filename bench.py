@@ -353,6 +353,55 @@ def reference_cuda_leg(p, dev, steps=3):
         return dict(unavailable=f"{type(ex).__name__}: {ex}"[:200])
 
 
+def frontend_bench(dev, steps=50):
+    """BASELINE configs[1]: the local BA of the frontend window (synth.config_c2: 25 keyframes, ~100 edges, 48x64,
+    2 iterations per call, `factor_graph.py:199-244`).  Latency-bound: 7 launches per iteration and a one-CTA solve.
+    The reference's CUDA op (host Eigen solve + blocking copies inside) is timed on the same tensors when it is built."""
+    import glob
+    import importlib
+    import torch
+    import droid_backends
+    from droid_b200 import synth
+    p = synth.config_c2()
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    poses0, disps0 = t(p.poses), t(p.disps)
+    a = [t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj)]
+    poses, disps = poses0.clone(), disps0.clone()
+
+    def timed(fn, n):
+        fn(); fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    def ours():
+        poses.copy_(poses0); disps.copy_(disps0)
+        droid_backends.ba(poses, disps, *a, p.t0, p.t1, 2, 1e-4, 0.1, False)
+    ms = timed(ours, steps)
+    out = dict(workload="c2: frontend window BA", keyframes=int(p.t1), edges=int(p.n_edges), itrs_per_call=2, ms_per_call=ms,
+               value=p.n_edges * 2 / (ms * 1e-3), unit=UNIT)
+    refdir = os.path.join(REPO, "baseline", "_ref")
+    if glob.glob(os.path.join(refdir, "droid_backends_ref*.so")):
+        try:
+            if refdir not in sys.path:
+                sys.path.insert(0, refdir)
+            ref = importlib.import_module("droid_backends_ref")
+
+            def theirs():
+                poses.copy_(poses0); disps.copy_(disps0)
+                ref.ba(poses, disps, *a, p.t0, p.t1, 2, 1e-4, 0.1, False)
+            out["reference_cuda_ms"] = timed(theirs, 10)
+        except Exception as ex:
+            out["reference_cuda_ms"] = None
+            out["reference_cuda_error"] = f"{type(ex).__name__}: {ex}"[:200]
+    return out
+
+
 def volume_bench(dev, steps, warmup, hbm_peak):
     """Secondary metric: CorrBlock construction — all-pairs 128-d correlation + 4-level pyramid, f16, 48 edges x 48x64
     (corr.py:30-38,63-71).  Output-write bound: algorithmic bytes = pyramid written once (25.1 MB/edge) + fmaps read."""
@@ -576,6 +625,7 @@ def main_gpu(args, rank, world):
         del target, weight
         torch.cuda.empty_cache()
         line["training_shapes"] = training_bench(dev)
+        line["frontend"] = frontend_bench(dev)
         try:
             tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
             line["lookup"]["roofline"]["traffic"] = tr
