@@ -512,9 +512,15 @@ __device__ __forceinline__ void ldsm_x4(float (&r)[4], unsigned addr) {
   r[0] = __uint_as_float(a); r[1] = __uint_as_float(b); r[2] = __uint_as_float(c); r[3] = __uint_as_float(d);
 }
 
-// one segment (CNT consecutive 16x8 tiles of one M-row) over one chunk: straight-line code, no predicates
+// one segment (CNT consecutive 16x8 tiles of one M-row) over one chunk: straight-line code, no predicates.
+// The chunk's 24 MMAs per tile accumulate into a ZEROED temporary that is then added to the running sums with an ordinary
+// (round-to-nearest) fp32 add: the tensor core's accumulator addition truncates, and over the 24 chunks x 8 k-steps a CTA
+// walks at backend sizes that bias — amplified by the cancellation in D = Hjj - G — showed up as 2e-3 in dx.
 template <int CNT>
 __device__ __forceinline__ void schur_segment(float (&acc)[kSegTiles][4], unsigned aA, unsigned aB, unsigned lo_off) {
+  float tmp[CNT][4];
+#pragma unroll
+  for (int q = 0; q < CNT; q++) { tmp[q][0] = 0.0f; tmp[q][1] = 0.0f; tmp[q][2] = 0.0f; tmp[q][3] = 0.0f; }
 #pragma unroll 1
   for (int k0 = 0; k0 < kChunk; k0 += 8) {
     float ah[4], al[4], bf[CNT][4];
@@ -524,13 +530,15 @@ __device__ __forceinline__ void schur_segment(float (&acc)[kSegTiles][4], unsign
     for (int q = 0; q < CNT; q++) ldsm_x4(bf[q], aB + 4u * unsigned(8 * q * kStride));
     // three passes over the segment's tiles: dependent MMAs on one accumulator are CNT apart
 #pragma unroll
-    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(acc[q], al, bh); }
+    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(tmp[q], al, bh); }
 #pragma unroll
-    for (int q = 0; q < CNT; q++) { const float bl[2] = {bf[q][2], bf[q][3]}; mma_tf32(acc[q], ah, bl); }
+    for (int q = 0; q < CNT; q++) { const float bl[2] = {bf[q][2], bf[q][3]}; mma_tf32(tmp[q], ah, bl); }
 #pragma unroll
-    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(acc[q], ah, bh); }
+    for (int q = 0; q < CNT; q++) { const float bh[2] = {bf[q][0], bf[q][1]}; mma_tf32(tmp[q], ah, bh); }
     aA += 32u; aB += 32u;
   }
+#pragma unroll
+  for (int q = 0; q < CNT; q++) { acc[q][0] += tmp[q][0]; acc[q][1] += tmp[q][1]; acc[q][2] += tmp[q][2]; acc[q][3] += tmp[q][3]; }
 }
 
 // grid = Mcap * S CTAs; CTA (k, s) handles chunks s, s+S, ... of source frame kx[k]; launches are bucketed by
