@@ -920,13 +920,14 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
     return launch_frames<1, true>(p, S, 0, 32, st);
   }
   const int nchunks = cdiv(p.HW, kChunk);
-  // CTAs per launch: ~6 per SM.  For a frontend window (8..25 frames) ~1.3 per SM would be FASTER (25 frames: 45 us at 8
-  // splits against 70 us at 36; the per-CTA set-up dominates), but every split less lengthens the fp32 accumulation chains
-  // of a CTA (partial sums of different CTAs meet in fp64): on the ill-conditioned stereo / invalid-depth test problem the
-  // per-iteration error against the fp64 oracle grows from 7e-5 (48 splits) to 1e-4 (24) and 2.6e-4 (8)
-  // (tools/parity_vs_split.py) — beyond the 1e-4 the drop-in promises.  Precision wins; the way to fewer splits is a
-  // per-chunk flush of the fp32 accumulators into fp64.
-  int S = cdiv(6 * kNumSMs, p.Mcap);
+  // CTAs per launch: ~6 per SM for backend graphs (hundreds of frames); a frontend window (8..25 frames) is fastest with
+  // ~1.3 per SM — its CTAs have few chunks each and the per-CTA set-up dominates (measured: 25 frames best at 8 splits,
+  // 8 frames at 24, 512 frames at 2).  The result does not depend on the split beyond fp32 round-off since the chunk
+  // products are added round-to-nearest (schur_segment): tools/parity_vs_split.py, 6.7e-6 vs 5.8e-6 against the fp64 oracle
+  // at 8 / 36 splits on the frontend problem.
+  int ctas = 2 * p.Mcap;
+  ctas = ctas < 192 ? 192 : (ctas > 6 * kNumSMs ? 6 * kNumSMs : ctas);
+  int S = cdiv(ctas, p.Mcap);
   static const int s_env = getenv("DB200_BA_SPLIT") ? atoi(getenv("DB200_BA_SPLIT")) : 0;   // tuning aid
   if (s_env > 0) S = s_env;
   S = S < 1 ? 1 : (S > nchunks ? nchunks : S);
