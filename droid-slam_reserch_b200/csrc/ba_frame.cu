@@ -930,6 +930,11 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   int S = cdiv(ctas, p.Mcap);
   static const int s_env = getenv("DB200_BA_SPLIT") ? atoi(getenv("DB200_BA_SPLIT")) : 0;   // tuning aid
   if (s_env > 0) S = s_env;
+  // ... but at most 12 chunks per CTA: the per-thread fp32 sums and the running G sums are chains over a CTA's chunks.  On
+  // an ill-conditioned backend graph (160 keyframes / 1600 edges; the fp32 oracle's dx is 1.0e-3 from the fp64 oracle's)
+  // splits 2, 3 (24, 16 chunks per CTA) give 1.9e-3 against the fp64 oracle, splits 4, 6, 8, 12, 24 give 1.0e-3, 2e-4,
+  // 8e-4, 5e-4, 3e-4 — the scatter of any fp32 grouping, the reference's included (tools/parity_vs_split.py).  +5 % time at c3.
+  if (s_env <= 0 && S < cdiv(nchunks, 12)) S = cdiv(nchunks, 12);
   S = S < 1 ? 1 : (S > nchunks ? nchunks : S);
   // degree buckets (shared memory and accumulator registers grow with the bucket's cap); a frame works in exactly one.
   // NSEG = ceil(schur_segs(dcap) / 8): 6, 12, 25, 36 segments of <= 4 tiles for dcap = 8, 14, 22, 28.
