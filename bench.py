@@ -532,8 +532,13 @@ def main_gpu(args, rank, world):
     if world == 1:
         h_in = [pin(a) for a in (p.target, p.weight, p.eta, p.ii, p.jj, p.poses, p.disps)]
     else:
-        h_in = [pin(a) for a in (p.target[sel], p.weight[sel], p.eta, p.ii[sel], p.jj[sel], p.poses, p.disps)]
-    h_poses, h_disps = torch.empty_like(h_in[5]), torch.empty_like(h_in[6])
+        # every rank uploads ITS shard: target/weight of its edges, and the eta / disparity rows of the frames it owns (the
+        # only rows its kernels read — SURVEY.md §8e: "disps/targets/weights/eta sharded with their owner"); poses replicated
+        f_lo, f_hi = runner.own_lo, (p.disps.shape[0] if rank == world - 1 else runner.own_hi)
+        e_lo, e_hi = int(np.searchsorted(runner.kx_all, f_lo)), int(np.searchsorted(runner.kx_all, f_hi))
+        eta_full, disps_full = t(p.eta), t(p.disps)
+        h_in = [pin(a) for a in (p.target[sel], p.weight[sel], p.eta[e_lo:e_hi], p.ii[sel], p.jj[sel], p.poses, p.disps[f_lo:f_hi])]
+    h_poses, h_disps = torch.empty_like(h_in[5]), torch.empty(p.disps.shape, dtype=torch.float32).pin_memory()
     h_dx = torch.empty((P, 6), dtype=torch.float32).pin_memory()
     h2d = sum(a.numel() * a.element_size() for a in h_in)
     d2h = sum(a.numel() * a.element_size() for a in (h_poses, h_disps, h_dx))
@@ -549,7 +554,9 @@ def main_gpu(args, rank, world):
         if world == 1:
             dx, _ = droid_backends.ba(po, di, intr, sens, tg, wg, et, i_, j_, p.t0, p.t1, ITRS, LM, EP, False)
         else:
-            dx, _ = runner.ba(po, di, intr, sens, tg, wg, et, ITRS, LM, EP)
+            eta_full[e_lo:e_hi].copy_(et); disps_full[f_lo:f_hi].copy_(di)      # device-to-device, into the full-size tensors
+            di = disps_full
+            dx, _ = runner.ba(po, di, intr, sens, tg, wg, eta_full, ITRS, LM, EP)
         h_poses.copy_(po, non_blocking=True); h_disps.copy_(di, non_blocking=True); h_dx.copy_(dx, non_blocking=True)
         staged.release()
         torch.cuda.current_stream().synchronize()      # the caller reads the result every step
