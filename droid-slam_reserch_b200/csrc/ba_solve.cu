@@ -936,7 +936,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
 // The local BA of the frontend (factor_graph.py:199-244: ~25 keyframes, ~100 edges, n = 6 P ~ 130) is latency, not
 // throughput: the tiled solver above needs ~35 us per 64 columns of chain (flags, streaming, 9 CTAs) — 107 us at n = 132.
 // Here the damped lower triangle + the right-hand side as one more row live in shared memory ([np+8][np+1] fp64, np = n
-// rounded up to 8), and one CTA runs a blocked right-looking factorisation: 8 columns per step = the redundant 8x8 block
+// rounded up to 8; n <= 152), and one CTA runs a blocked right-looking factorisation: 8 columns per step = the redundant 8x8 block
 // factorisation of factor_panel (one thread per row below the block, paired pivots), then the rank-8 update of the
 // trailing 8x8 tiles by DMMA (tile list from a table built once; eight tiles per warp in flight, the two k-halves in
 // separate accumulators); the rhs row turns into y = L^-1 b on the way.  L^T x = y follows blocked by 8 with the 8x8
@@ -945,10 +945,12 @@ __global__ void __launch_bounds__(kCholThreads, 1) chol_solve_kernel(BAParams p)
 // substitution 12k.  The update is bound by shared-memory wavefronts (8 accesses of a 2..3-way conflicting fragment
 // pattern per tile and two DMMAs), not by the FP64 pipe; next: trailing tiles resident in registers (as in the tiled
 // solver), panel columns staged in a conflict-free side buffer.
-constexpr int kSmallMaxN = 160;          // [168][161] doubles + vectors = 223 KB of the 227 KB a CTA can have
+constexpr int kSmallMaxN = 152;          // [160][153] doubles + vectors + the panel side buffer = 222 KB of the 227 KB a CTA can have
+constexpr int kPS = 12;                  // panel side buffer, column-major [8][np + kPS]: the panel's row-per-lane stores and the
+                                         // DMMA fragment loads (8 rows x 4 columns) are both conflict-free
 constexpr int kSmallThreads = 512;
 
-__device__ __forceinline__ void small_panel(double* A, int ld, int c0, int nrows, int n, int* chol_fail) {
+__device__ __forceinline__ void small_panel(double* A, int ld, int c0, int nrows, int n, int* chol_fail, double* Pb, int ps) {
   const int tid = threadIdx.x;
   if (tid < nrows) {
     const int r = c0 + tid;
@@ -987,7 +989,7 @@ __device__ __forceinline__ void small_panel(double* A, int ld, int c0, int nrows
     }
     if (tid == 0 && bad) atomicExch(chol_fail, 1);      // NaN pivots pass, like Eigen's `d <= 0` test
 #pragma unroll
-    for (int q = 0; q < 8; q++) A[r * ld + c0 + q] = (tid < q) ? 0.0 : x[q];
+    for (int q = 0; q < 8; q++) { const double v = (tid < q) ? 0.0 : x[q]; A[r * ld + c0 + q] = v; Pb[q * ps + r] = v; }
   }
 }
 
@@ -998,6 +1000,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p
   double* A = reinterpret_cast<double*>(smem_raw);          // [np+8][ld]; row np = right-hand side, rows np+1.. zero
   double* xs = A + size_t(np + 8) * ld;                     // [np] solution
   double* Li = xs + np;                                     // [np/8][8][8] inverses of the 8x8 diagonal blocks of L
+  double* Pb = Li + 8 * np;                                 // [8][np+kPS] the current panel's 8 columns (rows > np zero)
   __shared__ unsigned short s_tile[(kSmallMaxN / 8) * (kSmallMaxN / 8 + 1) / 2];   // b -> (ti << 8) | tj of the lower triangle, row by row
   const double* H = p.Hb;
   const double* bsrc = p.Hb + sys_h_elems(n);
@@ -1011,6 +1014,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p
   fine_mark(0);
   // load: zero fill, then the packed lower triangle row by row (coalesced), identity padding and the rhs row
   for (int e = tid; e < (np + 8) * ld; e += kSmallThreads) A[e] = 0.0;
+  for (int e = tid; e < 8 * (np + kPS); e += kSmallThreads) Pb[e] = 0.0;
   __syncthreads();
   // row r of the packed triangle = r+1 contiguous doubles at r(r+1)/2: one warp per row, four rows in flight
   constexpr int kWarps = kSmallThreads / 32;
@@ -1045,7 +1049,7 @@ __global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p
   __syncthreads();
   fine_mark(1);
   for (int c0 = 0; c0 < np; c0 += 8) {
-    small_panel(A, ld, c0, np + 1 - c0, n, &p.hdr->chol_fail);
+    small_panel(A, ld, c0, np + 1 - c0, n, &p.hdr->chol_fail, Pb, np + kPS);
     __syncthreads();
     if (c0 < 64) fine_mark(2 + c0 / 4);
     // trailing update on the FP64 tensor-core path: 8x8 tiles (ti, tj <= ti) of the block-lower part from row/column
@@ -1067,13 +1071,14 @@ __global__ void __launch_bounds__(kSmallThreads, 1) chol_small_kernel(BAParams p
           int ti, tj;
           if (b < ntri) { const int e = s_tile[b]; ti = e >> 8; tj = e & 255; }
           else { ti = mt; tj = b - ntri; }
-          const double* pr = A + (o + 8 * ti + g) * ld + c0 + t;
-          const double* pc = A + (o + 8 * tj + g) * ld + c0 + t;
+          const int ps = np + kPS;
+          const double* pr = Pb + t * ps + o + 8 * ti + g;
+          const double* pc = Pb + t * ps + o + 8 * tj + g;
           cc[u] = A + (o + 8 * ti + g) * ld + o + 8 * tj + 2 * t;
           d1[u][0] = cc[u][0]; d1[u][1] = cc[u][1];
           d2[u][0] = 0.0; d2[u][1] = 0.0;
           dmma884(d1[u], -pr[0], pc[0]);
-          dmma884(d2[u], -pr[4], pc[4]);
+          dmma884(d2[u], -pr[4 * ps], pc[4 * ps]);
         }
       }
 #pragma unroll
@@ -1242,10 +1247,10 @@ static int chol_grid_size(size_t smem) {
 int ba_solve(const BAParams& p, float lm, float ep, cudaStream_t st) {
   if (p.n <= kSmallMaxN && getenv("DB200_CHOL_NO_SMALL") == nullptr) {           // frontend-size systems: one CTA, no flags
     const int np = (p.n + 7) / 8 * 8;
-    const size_t smem_small = sizeof(double) * (size_t(np + 8) * (np + 1) + 9 * size_t(np));
+    const size_t smem_small = sizeof(double) * (size_t(np + 8) * (np + 1) + 9 * size_t(np) + 8 * size_t(np + kPS));
     static bool attr_set = false;
     if (!attr_set) {
-      const size_t mx = sizeof(double) * (size_t(kSmallMaxN + 8) * (kSmallMaxN + 1) + 9 * size_t(kSmallMaxN));
+      const size_t mx = sizeof(double) * (size_t(kSmallMaxN + 8) * (kSmallMaxN + 1) + 9 * size_t(kSmallMaxN) + 8 * size_t(kSmallMaxN + kPS));
       DB200_CUDA(cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx)));
       attr_set = true;
     }
