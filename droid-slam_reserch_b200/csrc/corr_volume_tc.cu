@@ -15,9 +15,8 @@
 // 3 CTAs are resident per SM (64 KB smem, 128 of 512 TMEM columns each), so the TMA / MMA / store phases of different tiles
 // overlap without an in-kernel pipeline.  The op is output-write bound (25 MB written per edge, 2.4 GFLOP).
 // Every mbarrier wait is bounded: a broken descriptor raises DB200_ERR_CUDA through the status word instead of hanging.
-#include <cuda.h>
 #include <cstdlib>
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace db200 {
 
@@ -57,50 +56,6 @@ __global__ void pool_cl_kernel(const __half* __restrict__ src, __half* __restric
                  d = __half22float2(s[size_t(ws) * (C / 2) + C / 2]);
     reinterpret_cast<__half2*>(dst)[i] = __floats2half2_rn((a.x + b.x + c.x + d.x) * 0.25f, (a.y + b.y + c.y + d.y) * 0.25f);
   }
-}
-
-// ---- PTX wrappers ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {      // bounded
-  for (uint32_t it = 0; it < (1u << 20); it++) {
-    uint32_t done;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    if (done) return true;
-  }
-  return false;
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-// K-major operand tile, 128-byte swizzle, rows of 128 bytes: SBO = 8 rows * 128 B, LBO = 1 (ignored), version 1 (sm_100)
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-  return uint64_t((saddr >> 4) & 0x3FFFu) | (uint64_t(1) << 16) | (uint64_t(1024 >> 4) << 32) | (uint64_t(1) << 46) | (uint64_t(2) << 61);
-}
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
-        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 // instruction descriptor: D = F32 (bits 4-5 = 1), A = B = F16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
@@ -202,18 +157,10 @@ corr_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 //                       the accumulator back.  The stores of tile k overlap the MMAs of tile k+1 and the loads of k+2.
 // mbarrier phases: stage s = k & 1 is in its (k >> 1)-th use; "empty"-type barriers are waited with the inverted
 // parity so that the first use passes.  Every wait is bounded (status word instead of a hang).
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-
 constexpr int kPipeThreadsTC = 192;
 // two operand stages (64 KB each) + two output staging tiles (32 KB each) + alignment slack
 constexpr size_t kPipeSmemTC = 2 * (2 * (kTM + kTN) * kTK * 2) + 2 * (kTM * kTN * 2) + 1024;
 
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
-  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }   // the four epilogue warps
 
 // TMA_STORE: the f16 tile is staged in shared memory in the 128-byte-swizzled box layout (bank-conflict free for
@@ -539,22 +486,6 @@ corr_gemm_tc_tf32_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid
 }
 
 // ---- host -------------------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
 // rows x C f16 matrix, row-major; box = 64 columns x 128 rows, 128-byte swizzle
 static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, int C) {
   EncodeTiledFn fn = encode_fn();

@@ -27,13 +27,59 @@ class CorrSampler(torch.autograd.Function):
         return grad_volume, None, None
 
 
+class _VolumePyramid(torch.autograd.Function):
+    """corr.py:30-38,63-71 as ONE op: every pyramid level comes out of the fused GEMM (level l = f1^T pool_l(f2) / 16).
+    backward: with G_l = d loss / d level_l [N, HW, HW_l],
+        d f1 = 1/16 sum_l pool_l(f2) G_l^T,     d pool_l(f2) = 1/16 f1 G_l,   then the adjoint of the 2x2 mean chain —
+    four small library GEMM pairs instead of autograd through a materialised [N,HW,HW] product and three pooling passes."""
+
+    @staticmethod
+    def forward(ctx, f1, f2, num_levels):
+        ctx.save_for_backward(f1, f2)
+        ctx.num_levels = num_levels
+        return tuple(droid_backends.corr_volume_pyramid(f1, f2, num_levels))
+
+    @staticmethod
+    def backward(ctx, *grads):
+        f1, f2 = ctx.saved_tensors
+        N, C, ht, wd = f1.shape
+        a = f1.float().reshape(N, C, ht * wd)
+        pyr = [f2.float()]
+        for _ in range(1, ctx.num_levels):
+            pyr.append(F.avg_pool2d(pyr[-1], 2, stride=2))
+        g1 = torch.zeros_like(a)
+        gp = []
+        for l, g in enumerate(grads):
+            if g is None:
+                gp.append(None)
+                continue
+            G = g.float().reshape(N, ht * wd, -1)
+            g1 += torch.matmul(pyr[l].reshape(N, C, -1), G.transpose(1, 2))
+            gp.append(torch.matmul(a, G).reshape(pyr[l].shape))
+        g2 = None
+        for l in range(ctx.num_levels - 1, -1, -1):                  # adjoint of avg_pool2d(2, stride 2), floor mode
+            if g2 is not None:
+                up = g2.repeat_interleave(2, dim=2).repeat_interleave(2, dim=3) * 0.25
+                g2 = F.pad(up, (0, pyr[l].shape[3] - up.shape[3], 0, pyr[l].shape[2] - up.shape[2]))
+                if gp[l] is not None:
+                    g2 = g2 + gp[l]
+            else:
+                g2 = gp[l]
+        g1 = (g1 / 16.0).reshape(f1.shape).to(f1.dtype)
+        g2 = None if g2 is None else (g2 / 16.0).to(f2.dtype)
+        return g1, g2, None
+
+
 class CorrBlock:
     def __init__(self, fmap1, fmap2, num_levels=4, radius=3):
         self.num_levels, self.radius = num_levels, radius
         batch, num, dim, ht, wd = fmap1.shape
         f1 = fmap1.reshape(batch * num, dim, ht, wd).contiguous()
         f2 = fmap2.reshape(batch * num, dim, ht, wd).contiguous()
-        self.corr_pyramid = droid_backends.corr_volume_pyramid(f1, f2, num_levels)
+        if torch.is_grad_enabled() and (f1.requires_grad or f2.requires_grad):
+            self.corr_pyramid = list(_VolumePyramid.apply(f1, f2, num_levels))
+        else:
+            self.corr_pyramid = droid_backends.corr_volume_pyramid(f1, f2, num_levels)
 
     @staticmethod
     def corr(fmap1, fmap2):
