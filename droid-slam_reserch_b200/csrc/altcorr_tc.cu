@@ -1,0 +1,686 @@
+// altcorr_tc.cu — low-memory correlation (AltCorrBlock) on the 5th-generation tensor cores.
+// Replaces /root/reference/src/altcorr_kernel.cu:27-149 (altcorr_forward) and the per-level index_select + .float()
+// copies of AltCorrBlock.corr_fn (/root/reference/droid_slam/modules/corr.py:109-131) for C = 128, radius = 3.
+//
+// The reference computes, per source pixel, 64 dot products of 128 channels against an 8x8 window of fmap2 (one warp per
+// 4x8 pixel tile, a gather + __syncthreads per tap and channel slab).  Neighbouring pixels reproject to neighbouring
+// windows, so for a TILE of 8x16 = 128 source pixels the windows cover a small region of fmap2; the dot products of the
+// whole tile against a 16x8 = 128-position CELL of that region are one 128x128x128 GEMM:
+//
+//     S[p, n] = sum_c f1[tile pixel p, c] * f2[cell position n, c]            (tcgen05.mma, fp32 accumulator in TMEM)
+//
+// and every pixel then picks its window taps out of its row of S.  Which cells a tile touches is data dependent (the
+// bounding corner of the tile's windows + a 64-bit mask of 8x8 cells relative to it); arbitrary coordinates just touch
+// more cells, so there is no "fast path only for smooth flow" — results are the reference's for any input.
+//
+// One persistent CTA per SM, 10 warps:
+//   warp 0      producer: reads the tile's coordinates, computes per level the cell origin + mask (warp reductions),
+//               publishes them, then feeds the A tile (128 pixels x 128 channels, TMA 4-D box, 128B swizzle) and a ring
+//               of B cells (TMA zero-fills positions outside the image = the reference's `within_bounds` skip);
+//   warp 1      one thread issues 8 (x3 when operands carry lo parts) tcgen05.mma M=128,N=128,K=16 per cell into one of
+//               FOUR 128-column TMEM accumulators; tcgen05.commit hands stages back / accumulators on;
+//   warps 2..9  epilogue: tcgen05.ld of their TMEM lane quarter (two warps per quarter, 64 columns each), scatter of the
+//               taps that belong to the thread's pixel into the per-level tap buffer D[64 taps][128 pixels] (conflict-free),
+//               and per level the bilinear combination + 49 coalesced channel rows to HBM.
+// All 4 pyramid levels of a tile are done by the same CTA (the A tile is loaded once per tile).
+//
+// Precision: operands are fp16.  The fused AltCorrBlock path feeds the fp16 feature pyramid directly (the reference casts
+// the same fp16 values to fp32: products are exact either way).  fp32 callers (droid_backends.altcorr_forward) go through
+// a split kernel x = hi + lo (both fp16, |x - hi - lo| <= 2^-22 |x|); the GEMM then adds hi*lo + lo*hi to hi*hi
+// (3 products, skipped at run time when every lo is zero, i.e. fp16-exact inputs).  Values outside the fp16 range or
+// non-finite set a flag that routes the whole call to the SIMT kernel below, which is also the path for levels whose
+// cells do not fit the 8x8 mask (images wider than 128 / taller than 64 positions with scattered coordinates).
+#include <cstdlib>
+#include "tc_common.cuh"
+
+namespace db200 {
+
+constexpr int kATPy = 8, kATPx = 16;                   // pixel tile
+constexpr int kATCy = 8, kATCx = 16;                   // fmap2 cell
+constexpr int kATMaxL = 4;
+constexpr int kATEpiWarps = 8;
+constexpr int kATThreads = 64 + 32 * kATEpiWarps;      // 320
+constexpr uint32_t kATBlk = 128 * 64 * 2;              // one [128 rows][64 halfs] swizzled block: 16 KB
+constexpr uint32_t kATARegion = 4 * kATBlk;            // 64 KB: one hi+lo A tile, or two hi-only A tiles
+constexpr uint32_t kATBRegion = 8 * kATBlk;            // 128 KB: two hi+lo cells, or four hi-only cells
+constexpr uint32_t kATDBytes = 64 * 128 * 4;           // 32 KB tap buffer
+constexpr size_t kATSmem = kATARegion + kATBRegion + kATDBytes + 1024;
+constexpr uint32_t kATIdesc = (1u << 4) | (uint32_t(128 >> 3) << 17) | (uint32_t(128 >> 4) << 24);   // f16 x f16 -> f32, M = N = 128
+
+struct AltTcParams {
+  CUtensorMap a_hi, a_lo;
+  CUtensorMap b_hi[kATMaxL], b_lo[kATMaxL];
+  const float* coords;
+  long long c_sb, c_ss, c_sp;                          // coords strides (floats): edge, sample, pixel; (x,y) contiguous
+  float* out;
+  long long o_sb, o_ss, o_sc, o_sp;                    // output strides (floats): edge, sample, channel, pixel
+  const long long* idx1;                               // frame of fmap1 per edge (null: edge index)
+  const long long* idx2;                               // frame of fmap2 per edge (null: edge index)
+  const unsigned* flags;                               // bit 0: lo parts present and non-zero; bit 1: whole call on the SIMT path
+  int* status;                                         // [0] error word, [1] number of (task, level) entries for the SIMT kernel
+  int* list;                                           // entries: task * kATMaxL + level
+  int list_cap;
+  int B, S, H1, W1, L;
+  int H2[kATMaxL], W2[kATMaxL];
+  float scale[kATMaxL];                                // level coordinates = coords * scale (2^-l: exact, = coords / 2**l)
+  int tiles_x, tiles_y;
+  int has_lo;
+};
+
+struct AltTaskInfo {
+  int bx0[kATMaxL], by0[kATMaxL];
+  unsigned long long mask[kATMaxL];
+  int skip[kATMaxL];
+};
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar) : "memory");
+}
+
+// window origin of a level coordinate: floor, as int, clamped so that +-7 never overflows (far-away windows are out of
+// every image anyway); NaN -> 0 like cvt.rzi
+__device__ __forceinline__ int alt_floor_clamped(float v, float* frac) {
+  const float f = floorf(v);
+  *frac = v - f;
+  const float c = fminf(fmaxf(f, -1048576.0f), 1048576.0f);
+  return (f == f) ? static_cast<int>(c) : 0;
+}
+
+__device__ __forceinline__ void alt_epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __grid_constant__ AltTcParams P) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[24];           // a_full[2] a_empty[2] b_full[4] b_empty[4] t_full[4] t_empty[4] i_full[2] i_empty[2]
+  __shared__ uint32_t tmem_base_s;
+  __shared__ AltTaskInfo tinfo[2];
+
+  const unsigned flags = P.flags ? *P.flags : 0u;
+  if (flags & 2u) return;                              // non-finite / out-of-range operands: the SIMT kernel does the call
+  const bool lo = P.has_lo && (flags & 1u);
+  const int NA = lo ? 1 : 2, NB = lo ? 2 : 4;
+  const uint32_t tile_bytes = lo ? 4 * kATBlk : 2 * kATBlk;
+
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+  const uint32_t sA = s0, sB = s0 + kATARegion;
+  float* D = reinterpret_cast<float*>(smem_dyn + (s0 - smem_u32(smem_dyn)) + kATARegion + kATBRegion);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto a_full = [&](int i) { return smem_u32(&bars[i]); };
+  auto a_empty = [&](int i) { return smem_u32(&bars[2 + i]); };
+  auto b_full = [&](int i) { return smem_u32(&bars[4 + i]); };
+  auto b_empty = [&](int i) { return smem_u32(&bars[8 + i]); };
+  auto t_full = [&](int i) { return smem_u32(&bars[12 + i]); };
+  auto t_empty = [&](int i) { return smem_u32(&bars[16 + i]); };
+  auto i_full = [&](int i) { return smem_u32(&bars[20 + i]); };
+  auto i_empty = [&](int i) { return smem_u32(&bars[22 + i]); };
+
+  if (tid == 0) {
+    for (int i = 0; i < 16; i++) mbar_init(smem_u32(&bars[i]), 1);
+    for (int i = 0; i < 4; i++) mbar_init(t_empty(i), kATEpiWarps);
+    mbar_init(i_full(0), 1); mbar_init(i_full(1), 1);
+    mbar_init(i_empty(0), 1 + kATEpiWarps); mbar_init(i_empty(1), 1 + kATEpiWarps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int tiles = P.tiles_x * P.tiles_y;
+  const long long total = static_cast<long long>(P.B) * P.S * tiles;
+
+  if (warp == 0) {
+    // ===================================================================== producer
+    long long it = 0;                                  // cells loaded so far (ring position)
+    int k = 0;
+    bool dead = false;
+    for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
+      const int slot = k & 1;
+      const int tile = int(t % tiles);
+      const long long bs = t / tiles;
+      const int s = int(bs % P.S), b = int(bs / P.S);
+      const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
+      if (!mbar_wait(i_empty(slot), ((k >> 1) & 1) ^ 1)) { atomicExch(P.status, 1); break; }
+      float cx[4], cy[4];
+      bool pv[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int p = lane + 32 * j, y = ty0 + (p >> 4), x = tx0 + (p & 15);
+        pv[j] = y < P.H1 && x < P.W1;
+        cx[j] = cy[j] = 0.0f;
+        if (pv[j]) {
+          const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
+          cx[j] = c.x; cy[j] = c.y;
+        }
+      }
+      unsigned long long masks[kATMaxL];
+      int bx0s[kATMaxL], by0s[kATMaxL];
+#pragma unroll
+      for (int l = 0; l < kATMaxL; l++) {
+        masks[l] = 0ull; bx0s[l] = by0s[l] = 0;
+        if (l >= P.L) continue;
+        const int W2 = P.W2[l], H2 = P.H2[l];
+        int lx[4], hx[4], ly[4], hy[4];
+        int minx = 0x7fffffff, miny = 0x7fffffff;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          float fr;
+          const int wx0 = alt_floor_clamped(cx[j] * P.scale[l], &fr) - 3, wy0 = alt_floor_clamped(cy[j] * P.scale[l], &fr) - 3;
+          lx[j] = max(wx0, 0); hx[j] = min(wx0 + 7, W2 - 1);
+          ly[j] = max(wy0, 0); hy[j] = min(wy0 + 7, H2 - 1);
+          if (!pv[j] || lx[j] > hx[j] || ly[j] > hy[j]) { lx[j] = 1; hx[j] = 0; }     // empty
+          else { minx = min(minx, lx[j]); miny = min(miny, ly[j]); }
+        }
+        minx = __reduce_min_sync(0xffffffffu, minx);
+        miny = __reduce_min_sync(0xffffffffu, miny);
+        unsigned mlo = 0u, mhi = 0u;
+        bool ovf = false;
+        if (minx != 0x7fffffff) {
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            if (lx[j] > hx[j]) continue;
+            const int c0 = (lx[j] - minx) >> 4, c1 = (hx[j] - minx) >> 4, r0 = (ly[j] - miny) >> 3, r1 = (hy[j] - miny) >> 3;
+            if (c1 >= 8 || r1 >= 8) { ovf = true; continue; }
+            for (int r = r0; r <= r1; r++)
+              for (int c = c0; c <= c1; c++) {
+                const int bit = r * 8 + c;
+                if (bit < 32) mlo |= 1u << bit; else mhi |= 1u << (bit - 32);
+              }
+          }
+        }
+        mlo = __reduce_or_sync(0xffffffffu, mlo);
+        mhi = __reduce_or_sync(0xffffffffu, mhi);
+        ovf = __any_sync(0xffffffffu, ovf);
+        int skip = 0;
+        if (ovf) {                                     // cells beyond the 8x8 mask: this (task, level) goes to the SIMT kernel
+          mlo = mhi = 0u; skip = 1;
+          if (lane == 0) {
+            const int pos = atomicAdd(P.status + 1, 1);
+            if (pos < P.list_cap) P.list[pos] = int(t * kATMaxL + l);
+            else atomicExch(P.status, 2);
+          }
+        }
+        masks[l] = (static_cast<unsigned long long>(mhi) << 32) | mlo;
+        bx0s[l] = minx == 0x7fffffff ? 0 : minx;
+        by0s[l] = miny == 0x7fffffff ? 0 : miny;
+        if (lane == 0) {
+          tinfo[slot].bx0[l] = bx0s[l]; tinfo[slot].by0[l] = by0s[l];
+          tinfo[slot].mask[l] = masks[l]; tinfo[slot].skip[l] = skip;
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(i_full(slot));
+        const int f1 = P.idx1 ? int(P.idx1[b]) : b, f2 = P.idx2 ? int(P.idx2[b]) : b;
+        const int as = k % NA;
+        if (!mbar_wait(a_empty(as), ((k / NA) & 1) ^ 1)) { atomicExch(P.status, 1); dead = true; }
+        if (!dead) {
+          const uint32_t dst = sA + uint32_t(as) * tile_bytes;
+          mbar_expect_tx(a_full(as), tile_bytes);
+          tma_load_4d(dst, &P.a_hi, 0, tx0, ty0, f1, a_full(as));
+          tma_load_4d(dst + kATBlk, &P.a_hi, 64, tx0, ty0, f1, a_full(as));
+          if (lo) {
+            tma_load_4d(dst + 2 * kATBlk, &P.a_lo, 0, tx0, ty0, f1, a_full(as));
+            tma_load_4d(dst + 3 * kATBlk, &P.a_lo, 64, tx0, ty0, f1, a_full(as));
+          }
+          for (int l = 0; l < P.L && !dead; l++) {
+            unsigned long long m = masks[l];
+            while (m) {
+              const int bit = __ffsll(static_cast<long long>(m)) - 1;
+              m &= m - 1;
+              const int X0 = bx0s[l] + kATCx * (bit & 7), Y0 = by0s[l] + kATCy * (bit >> 3);
+              const int st = int(it % NB);
+              if (!mbar_wait(b_empty(st), (uint32_t(it / NB) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
+              const uint32_t d2 = sB + uint32_t(st) * tile_bytes;
+              mbar_expect_tx(b_full(st), tile_bytes);
+              tma_load_4d(d2, &P.b_hi[l], 0, X0, Y0, f2, b_full(st));
+              tma_load_4d(d2 + kATBlk, &P.b_hi[l], 64, X0, Y0, f2, b_full(st));
+              if (lo) {
+                tma_load_4d(d2 + 2 * kATBlk, &P.b_lo[l], 0, X0, Y0, f2, b_full(st));
+                tma_load_4d(d2 + 3 * kATBlk, &P.b_lo[l], 64, X0, Y0, f2, b_full(st));
+              }
+              it++;
+            }
+          }
+        }
+      }
+      dead = __shfl_sync(0xffffffffu, int(dead), 0) != 0;
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      long long it = 0;
+      int k = 0;
+      bool dead = false;
+      for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
+        const int slot = k & 1;
+        if (!mbar_wait(i_full(slot), (k >> 1) & 1)) { atomicExch(P.status, 1); break; }
+        int cells = 0;
+        for (int l = 0; l < P.L; l++) cells += __popcll(tinfo[slot].mask[l]);
+        mbar_arrive(i_empty(slot));
+        const int as = k % NA;
+        if (!mbar_wait(a_full(as), (k / NA) & 1)) { atomicExch(P.status, 1); break; }
+        const uint32_t aT = sA + uint32_t(as) * tile_bytes;
+        for (int c = 0; c < cells; c++, it++) {
+          const int acc = int(it & 3), st = int(it % NB);
+          if (!mbar_wait(t_empty(acc), (uint32_t(it >> 2) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
+          if (!mbar_wait(b_full(st), uint32_t(it / NB) & 1u)) { atomicExch(P.status, 1); dead = true; break; }
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t bT = sB + uint32_t(st) * tile_bytes;
+          const uint32_t d = tmem_base + uint32_t(acc) * 128u;
+          const int nprod = lo ? 3 : 1;
+          uint32_t first = 0u;
+          for (int pr = 0; pr < nprod; pr++) {           // hi.hi, hi.lo, lo.hi
+            const uint32_t ao = (pr == 2) ? 2 * kATBlk : 0u, bo = (pr == 1) ? 2 * kATBlk : 0u;
+#pragma unroll
+            for (int kb = 0; kb < 2; kb++)
+#pragma unroll
+              for (int kk = 0; kk < 4; kk++) {
+                umma_f16(d, umma_desc_sw128(aT + ao + kb * kATBlk + kk * 32), umma_desc_sw128(bT + bo + kb * kATBlk + kk * 32), kATIdesc, first);
+                first = 1u;
+              }
+          }
+          umma_commit(b_empty(st));
+          umma_commit(t_full(acc));
+        }
+        if (!dead) umma_commit(a_empty(as));
+      }
+    }
+  } else {
+    // ===================================================================== epilogue
+    const int ew = warp - 2;
+    const int q = warp & 3;                            // TMEM lane quarter this warp may read
+    const int h = ew >> 2;                             // which 64 accumulator columns (= cell rows 4h..4h+3)
+    const int p = 32 * q + lane;                       // pixel of the tile = TMEM lane = A row
+    const int et = ew * 32 + lane;                     // 0..255
+    long long it = 0;
+    int k = 0;
+    bool dead = false;
+    for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
+      const int slot = k & 1;
+      const int tile = int(t % tiles);
+      const long long bs = t / tiles;
+      const int s = int(bs % P.S), b = int(bs / P.S);
+      const int y = (tile / P.tiles_x) * kATPy + (p >> 4), x = (tile % P.tiles_x) * kATPx + (p & 15);
+      const bool valid = y < P.H1 && x < P.W1;
+      float pcx = 0.0f, pcy = 0.0f;
+      if (valid) {
+        const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
+        pcx = c.x; pcy = c.y;
+      }
+      if (!mbar_wait(i_full(slot), (k >> 1) & 1)) { if (lane == 0) atomicExch(P.status, 1); break; }
+      float* outp = P.out + b * P.o_sb + s * P.o_ss + (static_cast<long long>(y) * P.W1 + x) * P.o_sp;
+      for (int l = 0; l < P.L && !dead; l++) {
+        alt_epi_bar();                                 // the previous level's output stage has read D
+        {
+          float4* D4 = reinterpret_cast<float4*>(D);
+#pragma unroll
+          for (int i = 0; i < 8; i++) D4[et + 256 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        alt_epi_bar();
+        float dx, dy;
+        const int wx0 = alt_floor_clamped(pcx * P.scale[l], &dx) - 3, wy0 = alt_floor_clamped(pcy * P.scale[l], &dy) - 3;
+        unsigned long long m = tinfo[slot].mask[l];
+        const int bx0 = tinfo[slot].bx0[l], by0 = tinfo[slot].by0[l];
+        while (m) {
+          const int bit = __ffsll(static_cast<long long>(m)) - 1;
+          m &= m - 1;
+          const int relx = wx0 - (bx0 + kATCx * (bit & 7)), rely = wy0 - (by0 + kATCy * (bit >> 3));
+          const int acc = int(it & 3);
+          const bool ok = mbar_wait(t_full(acc), uint32_t(it >> 2) & 1u);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (!ok) { if (lane == 0) atomicExch(P.status, 1); dead = true; break; }
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc * 128 + 64 * h + 32 * j), v);
+#pragma unroll
+            for (int rr = 0; rr < 2; rr++) {
+              const int ty = 4 * h + 2 * j + rr - rely;
+              if (valid && static_cast<unsigned>(ty) < 8u) {
+#pragma unroll
+                for (int c = 0; c < 16; c++) {
+                  const int tx = c - relx;
+                  if (static_cast<unsigned>(tx) < 8u) D[(ty * 8 + tx) * 128 + p] = __uint_as_float(v[rr * 16 + c]);
+                }
+              }
+            }
+          }
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_empty(acc));
+          it++;
+        }
+        if (dead) break;
+        alt_epi_bar();                                 // every tap of this level is in D
+        if (valid && !tinfo[slot].skip[l]) {
+          // bilinear combination (altcorr_kernel.cu:107-140): channel oy + 7 ox =
+          //   (1-dy)(1-dx) S[oy][ox] + (1-dy) dx S[oy][ox+1] + dy (1-dx) S[oy+1][ox] + dy dx S[oy+1][ox+1]
+          const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx, w10 = dy * (1.0f - dx), w11 = dy * dx;
+          const int oy0 = h ? 4 : 0, oy1 = h ? 7 : 4;
+          float up[8], dn[8];
+#pragma unroll
+          for (int c = 0; c < 8; c++) up[c] = D[(oy0 * 8 + c) * 128 + p];
+          float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc;
+          for (int oy = oy0; oy < oy1; oy++) {
+#pragma unroll
+            for (int c = 0; c < 8; c++) dn[c] = D[((oy + 1) * 8 + c) * 128 + p];
+#pragma unroll
+            for (int ox = 0; ox < 7; ox++) {
+              float r = w00 * up[ox];
+              r = fmaf(w01, up[ox + 1], r);
+              r = fmaf(w10, dn[ox], r);
+              r = fmaf(w11, dn[ox + 1], r);
+              ol[static_cast<long long>(oy + 7 * ox) * P.o_sc] = r;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; c++) up[c] = dn[c];
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(i_empty(slot));
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+}
+
+// ---- SIMT path: (task, level) entries the tensor-core kernel handed over, or the whole call when flags bit 1 is set ----
+// One warp per source pixel: lane l holds channels 4l..4l+3 of the pixel's feature vector; a tap is one coalesced read of
+// the fmap2 position, an xor-butterfly finishes the dot product.  T = float reads the caller's fp32 operands unchanged.
+struct AltSimtParams {
+  const void* f1; const void* f2[kATMaxL];
+  const float* coords; long long c_sb, c_ss, c_sp;
+  float* out; long long o_sb, o_ss, o_sc, o_sp;
+  const long long* idx1; const long long* idx2;
+  const unsigned* flags; const int* status; const int* list; int list_cap;
+  int B, S, H1, W1, L, C;
+  int H2[kATMaxL], W2[kATMaxL];
+  float scale[kATMaxL];
+  int tiles_x, tiles_y;
+};
+
+template <typename T> __device__ __forceinline__ float4 alt_ld4(const T* p);
+template <> __device__ __forceinline__ float4 alt_ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 alt_ld4<__half>(const __half* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) altcorr_simt_list_kernel(const __grid_constant__ AltSimtParams P) {
+  __shared__ float sdot[8][64];
+  const unsigned flags = P.flags ? *P.flags : 0u;
+  const int tiles = P.tiles_x * P.tiles_y;
+  const long long total = static_cast<long long>(P.B) * P.S * tiles;
+  const bool all = (flags & 2u) != 0u;
+  const long long entries = all ? total * P.L : min(P.status[1], P.list_cap);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* dots = sdot[warp];
+  for (long long e = blockIdx.x; e < entries; e += gridDim.x) {
+    long long t; int l;
+    if (all) { t = e / P.L; l = int(e % P.L); } else { const int v = P.list[e]; t = v / kATMaxL; l = v % kATMaxL; }
+    const int tile = int(t % tiles);
+    const long long bs = t / tiles;
+    const int s = int(bs % P.S), b = int(bs / P.S);
+    const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
+    const int H2 = P.H2[l], W2 = P.W2[l];
+    const long long fr1 = P.idx1 ? P.idx1[b] : b, fr2 = P.idx2 ? P.idx2[b] : b;
+    const T* f2b = static_cast<const T*>(P.f2[l]) + fr2 * H2 * W2 * P.C;
+    for (int pp = warp; pp < kATPy * kATPx; pp += 8) {
+      const int y = ty0 + (pp >> 4), x = tx0 + (pp & 15);
+      if (y >= P.H1 || x >= P.W1) continue;
+      const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
+      float dx, dy;
+      const int wx0 = alt_floor_clamped(c.x * P.scale[l], &dx) - 3, wy0 = alt_floor_clamped(c.y * P.scale[l], &dy) - 3;
+      const float4 a = alt_ld4<T>(static_cast<const T*>(P.f1) + ((fr1 * P.H1 + y) * P.W1 + x) * P.C + lane * 4);
+      for (int tp = 0; tp < 64; tp++) {
+        const int h2 = wy0 + (tp >> 3), w2 = wx0 + (tp & 7);
+        float acc = 0.0f;
+        if (h2 >= 0 && h2 < H2 && w2 >= 0 && w2 < W2) {
+          const float4 qv = alt_ld4<T>(f2b + (static_cast<long long>(h2) * W2 + w2) * P.C + lane * 4);
+          acc = fmaf(a.x, qv.x, acc); acc = fmaf(a.y, qv.y, acc); acc = fmaf(a.z, qv.z, acc); acc = fmaf(a.w, qv.w, acc);
+          acc = warp_sum(acc);
+        }
+        if (lane == 0) dots[tp] = acc;
+      }
+      __syncwarp();
+      const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx, w10 = dy * (1.0f - dx), w11 = dy * dx;
+      float* ol = P.out + b * P.o_sb + s * P.o_ss + (static_cast<long long>(y) * P.W1 + x) * P.o_sp + static_cast<long long>(l) * 49 * P.o_sc;
+      for (int o = lane; o < 49; o += 32) {
+        const int ox = o / 7, oy = o - ox * 7;
+        float r = w00 * dots[oy * 8 + ox];
+        r = fmaf(w01, dots[oy * 8 + ox + 1], r);
+        r = fmaf(w10, dots[(oy + 1) * 8 + ox], r);
+        r = fmaf(w11, dots[(oy + 1) * 8 + ox + 1], r);
+        ol[static_cast<long long>(o) * P.o_sc] = r;
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// ---- fp32 -> fp16 hi + lo split (the lo parts make the tensor-core product fp32-faithful) -----------------------------
+__global__ void __launch_bounds__(256) altcorr_split_kernel(const float* __restrict__ x, __half* __restrict__ hi, __half* __restrict__ lo,
+                                                            size_t n4, unsigned* __restrict__ flags) {
+  unsigned f = 0u;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    const float a[4] = {v.x, v.y, v.z, v.w};
+    __half hh[4], ll[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      hh[j] = __float2half_rn(a[j]);
+      const float back = __half2float(hh[j]);
+      if (!(fabsf(back) <= 65504.0f)) f |= 2u;          // overflow to inf, or NaN
+      const float r = a[j] - back;
+      ll[j] = __float2half_rn(r);
+      if (r != 0.0f) f |= 1u;
+    }
+    uint2 ph, pl;
+    __half2 h01 = __halves2half2(hh[0], hh[1]), h23 = __halves2half2(hh[2], hh[3]);
+    __half2 l01 = __halves2half2(ll[0], ll[1]), l23 = __halves2half2(ll[2], ll[3]);
+    ph.x = *reinterpret_cast<uint32_t*>(&h01); ph.y = *reinterpret_cast<uint32_t*>(&h23);
+    pl.x = *reinterpret_cast<uint32_t*>(&l01); pl.y = *reinterpret_cast<uint32_t*>(&l23);
+    reinterpret_cast<uint2*>(hi)[i] = ph;
+    reinterpret_cast<uint2*>(lo)[i] = pl;
+  }
+  f = __reduce_or_sync(0xffffffffu, f);
+  if (f && (threadIdx.x & 31) == 0) atomicOr(flags, f);
+}
+
+// ---- host ---------------------------------------------------------------------------------------------------------------
+// feature map [F][H][W][C = 128] fp16 as a 4-D tensor; box = 64 channels x 16 x 8 x 1 frame, 128-byte swizzle:
+// the box lands in shared memory as [8*16 rows][64 halfs], the K-major UMMA operand block.
+static bool alt_make_map(CUtensorMap* m, const void* base, long long F, int H, int W) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[4] = {128, cuuint64_t(W), cuuint64_t(H), cuuint64_t(F)};
+  const cuuint64_t gstride[3] = {256, cuuint64_t(W) * 256, cuuint64_t(H) * W * 256};
+  const cuuint32_t box[4] = {64, kATCx, kATCy, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+bool altcorr_tc_supported(int C, int radius) {
+  static const bool off = getenv("DB200_ALTCORR_NO_TCGEN05") != nullptr;
+  return !off && C == 128 && radius == 3 && encode_fn() != nullptr;
+}
+
+struct AltLaunch {
+  const void* f1_hi; const void* f1_lo;               // [F1][H1][W1][128] fp16 (lo may be null)
+  const void* f2_hi[kATMaxL]; const void* f2_lo[kATMaxL];
+  const void* f1_raw; const void* f2_raw[kATMaxL];    // operands as the caller passed them (SIMT path)
+  int raw_is_half;
+  long long F1, F2;
+  int H1, W1, L;
+  int H2[kATMaxL], W2[kATMaxL];
+  float scale[kATMaxL];
+  const long long* idx1; const long long* idx2;
+  const float* coords; long long c_sb, c_ss, c_sp;
+  float* out; long long o_sb, o_ss, o_sc, o_sp;
+  int B, S;
+  unsigned* flags;                                    // device word (may be null when there are no lo parts)
+  int* status;                                        // device: 2 ints + list
+  int list_cap;
+};
+
+size_t altcorr_tc_status_bytes(int B, int S, int H1, int W1) {
+  const long long tasks = static_cast<long long>(B) * S * cdiv(H1, kATPy) * cdiv(W1, kATPx);
+  return 256 + size_t(tasks) * kATMaxL * sizeof(int);
+}
+
+int altcorr_tc_launch(const AltLaunch& a, cudaStream_t st) {
+  AltTcParams P;
+  AltSimtParams Q;
+  if (!alt_make_map(&P.a_hi, a.f1_hi, a.F1, a.H1, a.W1)) return DB200_ERR_CUDA;
+  if (a.f1_lo) { if (!alt_make_map(&P.a_lo, a.f1_lo, a.F1, a.H1, a.W1)) return DB200_ERR_CUDA; } else P.a_lo = P.a_hi;
+  for (int l = 0; l < kATMaxL; l++) {
+    const int ll = l < a.L ? l : 0;
+    if (!alt_make_map(&P.b_hi[l], a.f2_hi[ll], a.F2, a.H2[ll], a.W2[ll])) return DB200_ERR_CUDA;
+    if (a.f2_lo[ll]) { if (!alt_make_map(&P.b_lo[l], a.f2_lo[ll], a.F2, a.H2[ll], a.W2[ll])) return DB200_ERR_CUDA; } else P.b_lo[l] = P.b_hi[l];
+    P.H2[l] = Q.H2[l] = a.H2[ll]; P.W2[l] = Q.W2[l] = a.W2[ll]; P.scale[l] = Q.scale[l] = a.scale[ll];
+    Q.f2[l] = a.f2_raw[ll];
+  }
+  P.coords = Q.coords = a.coords; P.c_sb = Q.c_sb = a.c_sb; P.c_ss = Q.c_ss = a.c_ss; P.c_sp = Q.c_sp = a.c_sp;
+  P.out = Q.out = a.out; P.o_sb = Q.o_sb = a.o_sb; P.o_ss = Q.o_ss = a.o_ss; P.o_sc = Q.o_sc = a.o_sc; P.o_sp = Q.o_sp = a.o_sp;
+  P.idx1 = Q.idx1 = a.idx1; P.idx2 = Q.idx2 = a.idx2;
+  P.flags = Q.flags = a.flags;
+  P.status = a.status; Q.status = a.status;
+  P.list = a.status + 64; Q.list = a.status + 64; P.list_cap = Q.list_cap = a.list_cap;
+  P.B = Q.B = a.B; P.S = Q.S = a.S; P.H1 = Q.H1 = a.H1; P.W1 = Q.W1 = a.W1; P.L = Q.L = a.L; Q.C = 128;
+  P.tiles_x = Q.tiles_x = cdiv(a.W1, kATPx); P.tiles_y = Q.tiles_y = cdiv(a.H1, kATPy);
+  P.has_lo = a.f1_lo != nullptr;
+  Q.f1 = a.f1_raw;
+  DB200_CUDA(cudaMemsetAsync(a.status, 0, 2 * sizeof(int), st));
+  static bool attr = false;
+  if (!attr) {
+    DB200_CUDA(cudaFuncSetAttribute(altcorr_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kATSmem)));
+    attr = true;
+  }
+  const long long tasks = static_cast<long long>(a.B) * a.S * P.tiles_x * P.tiles_y;
+  const int grid = int(tasks < kNumSMs ? tasks : kNumSMs);
+  altcorr_tc_fwd_kernel<<<grid, kATThreads, kATSmem, st>>>(P);
+  DB200_CHECK_LAUNCH();
+  const int g2 = int(tasks * a.L < 8 * kNumSMs ? tasks * a.L : 8 * kNumSMs);
+  if (a.raw_is_half) altcorr_simt_list_kernel<__half><<<g2, 256, 0, st>>>(Q);
+  else altcorr_simt_list_kernel<float><<<g2, 256, 0, st>>>(Q);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+int altcorr_split(const float* x, void* hi, void* lo, size_t n, unsigned* flags, cudaStream_t st) {
+  if (n % 4 != 0) return DB200_ERR_ARG;
+  const size_t n4 = n / 4;
+  const int blocks = int((n4 + 255) / 256 < size_t(8 * kNumSMs) ? (n4 + 255) / 256 : size_t(8 * kNumSMs));
+  altcorr_split_kernel<<<blocks > 0 ? blocks : 1, 256, 0, st>>>(x, static_cast<__half*>(hi), static_cast<__half*>(lo), n4, flags);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+}  // namespace db200
+
+using namespace db200;
+
+static inline size_t al256(size_t x) { return (x + 255) / 256 * 256; }
+
+// workspace of db200_altcorr_forward_ws: [flags 256 B][status + list][f1 hi][f1 lo][f2 hi][f2 lo]
+extern "C" size_t db200_altcorr_workspace_bytes(int B, int S, int H1, int W1, int H2, int W2, int C) {
+  if (B <= 0 || S <= 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0 || C <= 0) return 0;
+  return 256 + al256(altcorr_tc_status_bytes(B, S, H1, W1)) + 2 * al256(size_t(B) * H1 * W1 * C * 2) + 2 * al256(size_t(B) * H2 * W2 * C * 2);
+}
+
+extern "C" int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B, int S,
+                                        int H1, int W1, int H2, int W2, int C, int radius, void* workspace, size_t workspace_bytes,
+                                        db200_stream_t stream) {
+  if (!altcorr_tc_supported(C, radius) || !workspace)
+    return db200_altcorr_forward(fmap1, fmap2, coords, corr, B, S, H1, W1, H2, W2, C, radius, stream);
+  if (!fmap1 || !fmap2 || !coords || !corr || B < 0 || S < 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0) return DB200_ERR_ARG;
+  if (B == 0 || S == 0) return DB200_OK;
+  if (workspace_bytes < db200_altcorr_workspace_bytes(B, S, H1, W1, H2, W2, C)) return DB200_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* ws = static_cast<char*>(workspace);
+  unsigned* flags = reinterpret_cast<unsigned*>(ws); ws += 256;
+  int* status = reinterpret_cast<int*>(ws); ws += al256(altcorr_tc_status_bytes(B, S, H1, W1));
+  const size_t n1 = size_t(B) * H1 * W1 * C, n2 = size_t(B) * H2 * W2 * C;
+  void* h1 = ws; ws += al256(n1 * 2);
+  void* l1 = ws; ws += al256(n1 * 2);
+  void* h2 = ws; ws += al256(n2 * 2);
+  void* l2 = ws;
+  DB200_CUDA(cudaMemsetAsync(flags, 0, sizeof(unsigned), st));
+  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st);
+  if (rc != DB200_OK) return rc;
+  rc = altcorr_split(fmap2, h2, l2, n2, flags, st);
+  if (rc != DB200_OK) return rc;
+  AltLaunch a{};
+  a.f1_hi = h1; a.f1_lo = l1; a.f2_hi[0] = h2; a.f2_lo[0] = l2;
+  a.f1_raw = fmap1; a.f2_raw[0] = fmap2; a.raw_is_half = 0;
+  a.F1 = B; a.F2 = B; a.H1 = H1; a.W1 = W1; a.L = 1; a.H2[0] = H2; a.W2[0] = W2; a.scale[0] = 1.0f;
+  a.idx1 = nullptr; a.idx2 = nullptr;
+  a.coords = coords; a.c_sb = static_cast<long long>(S) * H1 * W1 * 2; a.c_ss = static_cast<long long>(H1) * W1 * 2; a.c_sp = 2;
+  a.out = corr; a.o_sb = static_cast<long long>(S) * 49 * H1 * W1; a.o_ss = static_cast<long long>(49) * H1 * W1;
+  a.o_sc = static_cast<long long>(H1) * W1; a.o_sp = 1;
+  a.B = B; a.S = S; a.flags = flags; a.status = status;
+  a.list_cap = int((altcorr_tc_status_bytes(B, S, H1, W1) - 256) / sizeof(int));
+  return altcorr_tc_launch(a, st);
+}
+
+extern "C" size_t db200_altcorr_pyramid_workspace_bytes(int B, int S, int H1, int W1) {
+  if (B <= 0 || S <= 0 || H1 <= 0 || W1 <= 0) return 0;
+  return al256(altcorr_tc_status_bytes(B, S, H1, W1));
+}
+
+extern "C" int db200_altcorr_pyramid_forward(const void* fmap1_hi, const void* fmap1_lo, const void* const* fmap2_hi,
+                                             const void* const* fmap2_lo, const unsigned* flags, const float* fmap1_f32,
+                                             const float* const* fmap2_f32, long long frames, int H, int W, int C,
+                                             int num_levels, const int64_t* idx1, const int64_t* idx2, const float* coords,
+                                             long long c_sb, long long c_ss, long long c_sp, float* out, long long o_sb,
+                                             long long o_ss, long long o_sc, long long o_sp, int B, int S, int radius,
+                                             void* workspace, size_t workspace_bytes, db200_stream_t stream) {
+  if (!fmap1_hi || !fmap2_hi || !coords || !out || frames <= 0 || H <= 0 || W <= 0 || num_levels < 1 || num_levels > kATMaxL ||
+      B < 0 || S < 0)
+    return DB200_ERR_ARG;
+  if (!altcorr_tc_supported(C, radius)) return DB200_ERR_ARG;
+  if (B == 0 || S == 0) return DB200_OK;
+  if (!workspace || workspace_bytes < db200_altcorr_pyramid_workspace_bytes(B, S, H, W)) return DB200_ERR_WORKSPACE;
+  const bool has_lo = fmap1_lo != nullptr;
+  if (has_lo != (fmap2_lo != nullptr) || (has_lo && (!flags || !fmap1_f32 || !fmap2_f32))) return DB200_ERR_ARG;
+  AltLaunch a{};
+  a.f1_hi = fmap1_hi; a.f1_lo = fmap1_lo;
+  a.f1_raw = has_lo ? static_cast<const void*>(fmap1_f32) : fmap1_hi; a.raw_is_half = has_lo ? 0 : 1;
+  for (int l = 0; l < num_levels; l++) {
+    if (!fmap2_hi[l] || (H >> l) <= 0 || (W >> l) <= 0 || (has_lo && (!fmap2_lo[l] || !fmap2_f32[l]))) return DB200_ERR_ARG;
+    a.f2_hi[l] = fmap2_hi[l]; a.f2_lo[l] = has_lo ? fmap2_lo[l] : nullptr;
+    a.f2_raw[l] = has_lo ? static_cast<const void*>(fmap2_f32[l]) : fmap2_hi[l];
+    a.H2[l] = H >> l; a.W2[l] = W >> l; a.scale[l] = 1.0f / float(1 << l);
+  }
+  a.F1 = frames; a.F2 = frames; a.H1 = H; a.W1 = W; a.L = num_levels;
+  a.idx1 = reinterpret_cast<const long long*>(idx1); a.idx2 = reinterpret_cast<const long long*>(idx2);
+  a.coords = coords; a.c_sb = c_sb; a.c_ss = c_ss; a.c_sp = c_sp;
+  a.out = out; a.o_sb = o_sb; a.o_ss = o_ss; a.o_sc = o_sc; a.o_sp = o_sp;
+  a.B = B; a.S = S; a.flags = has_lo ? const_cast<unsigned*>(flags) : nullptr; a.status = static_cast<int*>(workspace);
+  a.list_cap = int((altcorr_tc_status_bytes(B, S, H, W) - 256) / sizeof(int));
+  return altcorr_tc_launch(a, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, unsigned* flags, db200_stream_t stream) {
+  if (!x || !hi || !lo || !flags) return DB200_ERR_ARG;
+  if (n == 0) return DB200_OK;
+  return altcorr_split(x, hi, lo, n, flags, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int db200_altcorr_status(const void* status_words, db200_stream_t stream) {
+  int h[2] = {0, 0};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DB200_CUDA(cudaMemcpyAsync(h, status_words, sizeof(h), cudaMemcpyDeviceToHost, st));
+  DB200_CUDA(cudaStreamSynchronize(st));
+  return h[0] != 0 ? DB200_ERR_CUDA : h[1];
+}

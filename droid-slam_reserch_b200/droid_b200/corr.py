@@ -128,17 +128,49 @@ class CorrLayer(torch.autograd.Function):
 
 
 class AltCorrBlock:
+    """corr.py:91-139 with the hot call re-designed: the reference gathers `pyramid[0][:, ii]` / `pyramid[i][:, jj]`, casts
+    both to fp32 and launches one kernel per level for every chunk of edges of every update step
+    (factor_graph.py:261-290).  Here the channels-last pyramid is kept in the tensor-core operand format once (fp16 as it
+    comes from the feature encoder; fp32 features as an fp16 hi + lo split) and `corr_fn` is ONE launch that takes the
+    frame indices: no gathers, no casts, no concat (`droid_backends.altcorr_pyramid_forward`, csrc/altcorr_tc.cu).
+    With autograd (fmaps that require grad) the per-level `CorrLayer` path of the reference is used."""
+
     def __init__(self, fmaps, num_levels=4, radius=3):
         self.num_levels, self.radius = num_levels, radius
         B, N, C, H, W = fmaps.shape
-        fmaps = fmaps.view(B * N, C, H, W) / 4.0
+        x = fmaps.view(B * N, C, H, W) / 4.0
         self.pyramid = []
         for i in range(num_levels):
-            self.pyramid.append(fmaps.permute(0, 2, 3, 1).contiguous().view(B, N, H // 2 ** i, W // 2 ** i, C))
-            fmaps = F.avg_pool2d(fmaps, 2, stride=2)
+            self.pyramid.append(x.permute(0, 2, 3, 1).contiguous().view(B, N, H // 2 ** i, W // 2 ** i, C))
+            x = F.avg_pool2d(x, 2, stride=2)
+        self._dims = (B, N, C, H, W)
+        self._fused = (C == 128 and radius == 3 and fmaps.is_cuda and fmaps.dtype in (torch.float16, torch.float32)
+                       and not (torch.is_grad_enabled() and fmaps.requires_grad))
+        self._lo = self._flags = self._f32 = None
+        if self._fused:
+            flat = [p.view((B * N,) + p.shape[2:]) for p in self.pyramid]
+            if fmaps.dtype == torch.float16:
+                self._hi = flat
+            else:
+                parts = [droid_backends.split_hilo_f16(p) for p in flat]
+                self._hi, self._lo = [q[0] for q in parts], [q[1] for q in parts]
+                self._flags = parts[0][2]
+                for q in parts[1:]:
+                    self._flags |= q[2]
+                self._f32 = flat
 
     def corr_fn(self, coords, ii, jj):
         B, N, H, W, S, _ = coords.shape
+        if self._fused and not (torch.is_grad_enabled() and coords.requires_grad):
+            nf = self._dims[1]
+            ii, jj = ii.to(torch.int64), jj.to(torch.int64)
+            if B > 1:
+                off = (torch.arange(B, device=ii.device) * nf)[:, None]
+                ii, jj = (ii[None] + off).reshape(-1), (jj[None] + off).reshape(-1)
+            out = droid_backends.altcorr_pyramid_forward(self._hi, ii.contiguous(), jj.contiguous(),
+                                                         coords.reshape(B * N, H, W, S, 2).contiguous(), self.radius,
+                                                         lo=self._lo, flags=self._flags, f32=self._f32)
+            return out.view(B, N, -1, H, W, S)
         coords = coords.permute(0, 1, 4, 2, 3, 5)
         out = []
         for i in range(self.num_levels):

@@ -15,7 +15,8 @@ import torch
 from droid_b200 import _capi
 
 __all__ = ["ba", "frame_distance", "projmap", "depth_filter", "iproj", "altcorr_forward", "altcorr_backward",
-           "corr_index_forward", "corr_index_backward", "corr_pyramid_lookup", "corr_volume_pyramid"]
+           "corr_index_forward", "corr_index_backward", "corr_pyramid_lookup", "corr_volume_pyramid", "altcorr_pyramid_forward",
+           "split_hilo_f16"]
 
 _DT = {torch.float32: _capi.F32, torch.float16: _capi.F16, torch.float64: _capi.F64}
 _SYNC_STATUS = os.environ.get("DROID_B200_ASYNC", "0") != "1"
@@ -90,18 +91,80 @@ def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
     return outs
 
 
+CHECK_STATUS = os.environ.get("DROID_B200_CHECK", "0") == "1"   # tests: read the tensor-core kernels' status words back (synchronises)
+
+
+def _altcorr_check(ws_status_ptr, what):
+    rc = _capi.lib().db200_altcorr_status(C.c_void_p(ws_status_ptr), _stream())
+    if rc < 0:
+        raise RuntimeError(f"{what}: tensor-core pipeline reported a protocol error (status {rc})")
+    return rc
+
+
 def altcorr_forward(fmap1, fmap2, coords, radius):
-    """droid.cpp:193-203.  fmap1[B,H1,W1,C], fmap2[B,H2,W2,C], coords[B,S,H1,W1,2] -> [corr[B,S,(2r+1)^2,H1,W1]]"""
+    """droid.cpp:193-203.  fmap1[B,H1,W1,C], fmap2[B,H2,W2,C], coords[B,S,H1,W1,2] -> [corr[B,S,(2r+1)^2,H1,W1]]
+    C = 128, radius = 3: tcgen05 kernel (csrc/altcorr_tc.cu); otherwise the SIMT kernel (csrc/altcorr.cu)."""
     _chk(("fmap1", fmap1), ("fmap2", fmap2), ("coords", coords))
     dt = fmap1.dtype
-    f1, f2 = fmap1.float(), fmap2.float()
+    f1, f2, co = fmap1.float(), fmap2.float(), coords.float()
     B, S, H1, W1, _ = coords.shape
     _, H2, W2, Cc = f2.shape
     rd = 2 * radius + 1
     corr = torch.empty((B, S, rd * rd, H1, W1), dtype=torch.float32, device=f1.device)
-    _capi.check(_capi.lib().db200_altcorr_forward(_ptr(f1), _ptr(f2), _ptr(coords.float()), _ptr(corr), B, S, H1, W1, H2, W2,
-                                                  Cc, radius, _stream()), "altcorr_forward")
+    lib = _capi.lib()
+    wsb = lib.db200_altcorr_workspace_bytes(B, S, H1, W1, H2, W2, Cc) if (Cc == 128 and radius == 3 and B * S > 0) else 0
+    ws = torch.empty(wsb, dtype=torch.uint8, device=f1.device) if wsb else None
+    _capi.check(lib.db200_altcorr_forward_ws(_ptr(f1), _ptr(f2), _ptr(co), _ptr(corr), B, S, H1, W1, H2, W2, Cc, radius,
+                                             _ptr(ws), wsb, _stream()), "altcorr_forward")
+    if CHECK_STATUS and ws is not None:
+        _altcorr_check(ws.data_ptr() + 256, "altcorr_forward")
     return [corr if dt == torch.float32 else corr.to(dt)]
+
+
+def split_hilo_f16(x):
+    """fp32 tensor -> (hi, lo, flags): fp16 tensors with x ~= hi + lo (|x - hi - lo| <= 2^-22 |x|) and a device flag word
+    (bit 0: some lo != 0, bit 1: some value non-finite / outside the fp16 range).  Operand format of the tensor-core
+    altcorr path for fp32 features."""
+    _chk(("x", x))
+    if x.dtype != torch.float32 or x.numel() % 4 != 0:
+        raise RuntimeError("split_hilo_f16: fp32 tensor with numel % 4 == 0 expected")
+    hi = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    lo = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    flags = torch.zeros(1, dtype=torch.int32, device=x.device)
+    _capi.check(_capi.lib().db200_split_hilo_f16(_ptr(x), _ptr(hi), _ptr(lo), x.numel(), _ptr(flags), _stream()), "split_hilo_f16")
+    return hi, lo, flags
+
+
+def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=None, f32=None):
+    """AltCorrBlock.corr_fn in one launch (corr.py:109-131): pyramid[l] = channels-last fp16 [frames, H>>l, W>>l, 128];
+    ii, jj[E] int64 frame indices; coords[E,H,W,2] or [E,H,W,S,2] (level-0 scale) -> [E, 49*L, H, W(, S)] fp32.
+    fp32 features: pass the fp16 split of every level (`pyramid` = hi parts, `lo`, the merged `flags` word) and the fp32
+    levels themselves (`f32`)."""
+    L = len(pyramid)
+    _chk(("coords", coords), ("ii", ii), ("jj", jj), *[(f"pyramid[{l}]", v) for l, v in enumerate(pyramid)])
+    if any(v.dtype != torch.float16 for v in pyramid) or ii.dtype != torch.int64 or jj.dtype != torch.int64:
+        raise RuntimeError("altcorr_pyramid_forward: fp16 pyramid and int64 indices expected")
+    frames, H, W, Cc = pyramid[0].shape
+    co = coords.float()
+    multi = co.dim() == 5
+    E = co.shape[0]
+    S = co.shape[3] if multi else 1
+    out = torch.empty((E, 49 * L, H, W) + ((S,) if multi else ()), dtype=torch.float32, device=co.device)
+    lib = _capi.lib()
+    wsb = lib.db200_altcorr_pyramid_workspace_bytes(E, S, H, W) if E > 0 else 0
+    ws = torch.empty(max(wsb, 16), dtype=torch.uint8, device=co.device)
+    arr = lambda ts: (C.c_void_p * L)(*[t.data_ptr() for t in ts])
+    null = C.POINTER(C.c_void_p)()
+    has_lo = lo is not None
+    rc = lib.db200_altcorr_pyramid_forward(
+        _ptr(pyramid[0]), _ptr(lo[0]) if has_lo else C.c_void_p(0), arr(pyramid), arr(lo) if has_lo else null,
+        _ptr(flags) if has_lo else C.c_void_p(0), _ptr(f32[0]) if has_lo else C.c_void_p(0), arr(f32) if has_lo else null,
+        frames, H, W, Cc, L, _ptr(ii), _ptr(jj), _ptr(co), H * W * S * 2, 2, 2 * S, _ptr(out), 49 * L * H * W * S, 1, H * W * S, S,
+        E, S, radius, _ptr(ws), wsb, _stream())
+    _capi.check(rc, "altcorr_pyramid_forward")
+    if CHECK_STATUS and E > 0:
+        _altcorr_check(ws.data_ptr(), "altcorr_pyramid_forward")
+    return out
 
 
 def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):

@@ -87,6 +87,37 @@ int db200_altcorr_backward(const float* fmap1, const float* fmap2, const float* 
                            float* fmap1_grad, float* fmap2_grad, float* coords_grad, int B, int S, int H1, int W1,
                            int H2, int W2, int C, int radius, db200_stream_t stream);
 
+/* altcorr_forward on the tensor cores (csrc/altcorr_tc.cu; C = 128, radius = 3; other shapes and a NULL workspace take
+ * db200_altcorr_forward): same arguments + a workspace of db200_altcorr_workspace_bytes(...) that holds the fp16 hi/lo
+ * split of the operands and the status words (int[0] error, int[1] tiles handed to the SIMT kernel) at offset 256,
+ * readable with db200_altcorr_status (synchronises). */
+size_t db200_altcorr_workspace_bytes(int B, int S, int H1, int W1, int H2, int W2, int C);
+int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B, int S,
+                             int H1, int W1, int H2, int W2, int C, int radius, void* workspace,
+                             size_t workspace_bytes, db200_stream_t stream);
+int db200_altcorr_status(const void* status_words, db200_stream_t stream);
+/* AltCorrBlock.corr_fn fused (corr.py:109-131 as driven by factor_graph.py:261-277): all `num_levels` levels, the
+ * frame gathers `pyramid[0][:, ii]`, `pyramid[l][:, jj]`, the casts and the channel concat in ONE launch.
+ *   fmap1_hi, fmap2_hi[l] : channels-last fp16 feature pyramid [frames, H>>l, W>>l, C] (fmap1 = level 0 of the same or
+ *                           another pyramid); for fp32 features pass the fp16 split x = hi + lo (db200_split_hilo_f16)
+ *                           with its flag word and the fp32 arrays themselves (used when a value leaves the fp16 range);
+ *                           lo / flags / f32 pointers are NULL for fp16 features.
+ *   idx1, idx2 [B] int64  : frame of the source / target image of every edge;
+ *   coords                : level-0 coordinates (x, y) at coords[b*c_sb + s*c_ss + pixel*c_sp (+0,1)] (strides in floats);
+ *   out                   : out[b*o_sb + s*o_ss + (49*l + iy + 7*ix)*o_sc + pixel*o_sp], every element written.
+ * workspace: db200_altcorr_pyramid_workspace_bytes(B, S, H, W) bytes (status words first). */
+size_t db200_altcorr_pyramid_workspace_bytes(int B, int S, int H1, int W1);
+int db200_altcorr_pyramid_forward(const void* fmap1_hi, const void* fmap1_lo, const void* const* fmap2_hi,
+                                  const void* const* fmap2_lo, const unsigned* flags, const float* fmap1_f32,
+                                  const float* const* fmap2_f32, long long frames, int H, int W, int C, int num_levels,
+                                  const int64_t* idx1, const int64_t* idx2, const float* coords, long long c_sb,
+                                  long long c_ss, long long c_sp, float* out, long long o_sb, long long o_ss,
+                                  long long o_sc, long long o_sp, int B, int S, int radius, void* workspace,
+                                  size_t workspace_bytes, db200_stream_t stream);
+/* x[n] fp32 -> hi[n], lo[n] fp16 with x ~= hi + lo; *flags |= 1 if any lo != 0, |= 2 if any value is non-finite or
+ * outside the fp16 range (flags must be zeroed by the caller). n % 4 == 0. */
+int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, unsigned* flags, db200_stream_t stream);
+
 /* ---- frame_distance (droid.cpp:120-136, droid_kernels.cu:518-657,1438-1460) ----------------- */
 int db200_frame_distance(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
                          const int64_t* jj, int K, int n_poses, int B, int ht, int wd, float beta, float* dist,

@@ -195,3 +195,60 @@ def test_kernel_projmap_iproj_depth_filter_vs_reference_cuda():
     df = droid_backends.depth_filter(_t(p.poses), _t(p.disps), _t(p.intrinsics), torch.arange(n).cuda(),
                                      torch.full((n,), 0.05).cuda())
     np.testing.assert_array_equal(df.cpu().numpy(), Z2["depth_filter"])
+
+
+# ---------------------------------------------------------------- third fixture: the configs the metric is quoted on
+# tests/golden/make_c3_golden.py: reference CUDA extension (ref_cuda_c3.npz, B200) and oracle fp32/fp64 (oracle_c3.npz, CPU)
+# on c3 (512 KF / ~6000 edges / 48x64), c3s (20 % stereo edges + sensor prior, 40x64) and c4 (1536 KF / ~20k edges).
+# What "within tolerance of the reference" can mean at this size is MEASURED, not argued: the reference's own fp32 result
+# sits 5e-4 (c3) .. 1.4e-3 (c3s, 2 iterations) away from exact arithmetic (the fp64 oracle) in dx, so no implementation
+# with a different summation order can be within 1e-4 of it.  Asserted instead, per call:
+#   (a) the kernel is at least as close to exact arithmetic as the reference is: d(kernel, f64) <= max(1e-4, d(ref, f64));
+#   (b) d(kernel, ref) <= max(1e-4, 2 d(ref, f64))   (triangle inequality with (a));
+#   (c) dz (well conditioned) within 1e-4 of the reference for one iteration, d(kernel, f64)-bounded after two.
+ZR = np.load(os.path.join(HERE, "golden", "ref_cuda_c3.npz"))
+ZO = np.load(os.path.join(HERE, "golden", "oracle_c3.npz"))
+
+
+def _c3_cases():
+    import make_c3_golden as G3
+    return G3
+
+
+def test_oracle_c3_vs_reference_cuda_three_way_on_record():
+    """CPU: reference-CUDA vs oracle distances at c3/c3s — the reference's own fp32 noise level at the headline size."""
+    for name in ("c3", "c3s"):
+        for it in (1, 2):
+            ref, o32, o64 = ZR[f"{name}_it{it}_ref_dx"], ZO[f"{name}_it{it}_f32_dx"], ZO[f"{name}_it{it}_f64_dx"]
+            d_ref64, d_3264 = rel(ref, o64), rel(o32, o64)
+            assert 1e-5 < d_ref64 < 5e-3 and d_3264 < 5e-3, (name, it, d_ref64, d_3264)
+            assert rel(ref, o32) <= 2 * max(d_ref64, d_3264)
+            assert rel(ZR[f"{name}_it{it}_ref_dz_sample"], ZO[f"{name}_it{it}_f64_dz_sample"]) <= 3e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c3", "c3s", "c4"])
+def test_kernel_ba_c3_c4_vs_reference_cuda(name):
+    import droid_backends
+    G3 = _c3_cases()
+    p, its = G3.cases((name,))[name]
+    args = [_t(p.intrinsics), _t(p.disps_sens), _t(p.target), _t(p.weight), _t(p.eta), _t(p.ii), _t(p.jj)]
+    for it in its:
+        poses, disps = _t(p.poses), _t(p.disps)
+        dx, dz = droid_backends.ba(poses, disps, *args, p.t0, p.t1, it, G3.LM, G3.EP, False)
+        dx, dz = dx.cpu().numpy(), dz.cpu().numpy()
+        ref_dx, o64_dx = ZR[f"{name}_it{it}_ref_dx"], ZO[f"{name}_it{it}_f64_dx"]
+        r, c = G3.dz_sample_index(*dz.shape)
+        d_ref64 = rel(ref_dx, o64_dx)
+        d_k64, d_kref = rel(dx, o64_dx), rel(dx, ref_dx)
+        dz_kref = rel(dz[r, c], ZR[f"{name}_it{it}_ref_dz_sample"])
+        dz_k64 = rel(dz[r, c], ZO[f"{name}_it{it}_f64_dz_sample"])
+        dz_ref64 = rel(ZR[f"{name}_it{it}_ref_dz_sample"], ZO[f"{name}_it{it}_f64_dz_sample"])
+        print(f"{name} it{it}: dx kernel-f64 {d_k64:.2e} ref-f64 {d_ref64:.2e} kernel-ref {d_kref:.2e}; "
+              f"dz kernel-ref {dz_kref:.2e} kernel-f64 {dz_k64:.2e} ref-f64 {dz_ref64:.2e}")
+        assert d_k64 <= max(1e-4, d_ref64), (d_k64, d_ref64)
+        assert d_kref <= max(1e-4, 2 * d_ref64), (d_kref, d_ref64)
+        assert dz_k64 <= max(1e-4, 2 * dz_ref64) and dz_kref <= max(1e-4, 2 * max(dz_ref64, dz_k64))
+        assert abs(np.linalg.norm(dz.astype(np.float64)) / float(ZR[f"{name}_it{it}_ref_dz_norm"]) - 1) <= 1e-3
+        rn = np.linalg.norm(dz.astype(np.float64), axis=1)
+        assert np.abs(rn - ZR[f"{name}_it{it}_ref_dz_rownorm"]).max() <= 2e-3 * ZR[f"{name}_it{it}_ref_dz_rownorm"].max()
