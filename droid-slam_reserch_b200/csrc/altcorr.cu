@@ -92,7 +92,9 @@ altcorr_fwd_kernel(const float* __restrict__ fmap1, const float* __restrict__ fm
 __global__ void __launch_bounds__(256)
 altcorr_bwd_kernel(const float* __restrict__ fmap1, const float* __restrict__ fmap2, const float* __restrict__ coords,
                    const float* __restrict__ corr_grad, float* __restrict__ fmap1_grad, float* __restrict__ fmap2_grad,
-                   int B, int S, int H1, int W1, int H2, int W2, int C, int r) {
+                   int B, int S, int H1, int W1, int H2, int W2, int C, int r, const unsigned* __restrict__ cond_flags,
+                   const int* __restrict__ cond_status) {
+  if (cond_flags && !((*cond_flags & 2u) || cond_status[1] != 0)) return;     // only when the tensor-core kernel handed the call over
   extern __shared__ __align__(16) float smem[];
   const int rd = 2 * r + 1, wn = rd + 1, nch = rd * rd;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -141,6 +143,27 @@ altcorr_bwd_kernel(const float* __restrict__ fmap1, const float* __restrict__ fm
   }
 }
 
+__global__ void zero_if_kernel(float4* __restrict__ p, size_t n4, const unsigned* __restrict__ cond_flags,
+                               const int* __restrict__ cond_status) {
+  if (!((*cond_flags & 2u) || cond_status[1] != 0)) return;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x)
+    p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+int altcorr_bwd_simt_conditional(const float* fmap1, const float* fmap2, const float* coords, const float* corr_grad,
+                                 float* fmap1_grad, float* fmap2_grad, int B, int S, int H1, int W1, int H2, int W2, int C,
+                                 int radius, const unsigned* flags, const int* status, cudaStream_t st) {
+  const size_t n4 = size_t(B) * H2 * W2 * C / 4;
+  zero_if_kernel<<<kNumSMs * 4, 256, 0, st>>>(reinterpret_cast<float4*>(fmap2_grad), n4, flags, status);
+  DB200_CHECK_LAUNCH();
+  const int rd = 2 * radius + 1;
+  const size_t npix = size_t(B) * H1 * W1;
+  altcorr_bwd_kernel<<<unsigned((npix + 7) / 8), 256, size_t(8) * rd * rd * sizeof(float), st>>>(
+      fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, C, radius, flags, status);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
 }  // namespace db200
 
 using namespace db200;
@@ -178,7 +201,7 @@ extern "C" int db200_altcorr_backward(const float* fmap1, const float* fmap2, co
   const int rd = 2 * radius + 1;
   const size_t npix = size_t(B) * H1 * W1;
   altcorr_bwd_kernel<<<unsigned((npix + 7) / 8), 256, size_t(8) * rd * rd * sizeof(float), st>>>(
-      fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, C, radius);
+      fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, C, radius, nullptr, nullptr);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

@@ -496,6 +496,284 @@ __global__ void __launch_bounds__(256) altcorr_split_kernel(const float* __restr
   if (f && (threadIdx.x & 31) == 0) atomicOr(flags, f);
 }
 
+// ======================================================================================================================
+// Backward (altcorr_kernel.cu:152-286) on the tensor cores, same tile x cell decomposition:
+//   G[p, n]     = d loss / d S[p, n]: the 4-corner combination of corr_grad of pixel p at the window tap that falls on
+//                 cell position n, 0 elsewhere (fp32 -> fp16 hi + lo, written by the threads in the UMMA operand layout);
+//   d f1[tile] += G  . f2[cell]          M = pixels,    K = positions   (A = G K-major,  B = f2 cell  MN-major)
+//   d f2[cell]  = G^T . f1[tile]         M = positions, K = pixels      (A = G MN-major, B = f1 tile  MN-major)
+// The SAME shared-memory image of G serves both products (K-major for the first, MN-major for the second), and the
+// feature tiles are used as TMA delivers them ([rows][128 channels]) through MN-major descriptors.  d f1 accumulates in
+// TMEM over all cells and coordinate samples of the tile and is stored once; d f2 of a cell is drained from TMEM with one
+// vector red.global.add per 4 channels (rows nobody touched are skipped) instead of one atomicAdd per tap and channel.
+struct AltTcBwdParams {
+  CUtensorMap a_hi, a_lo, b_hi, b_lo;
+  const float* coords; long long c_sb, c_ss, c_sp;
+  const float* grad; long long g_sb, g_ss, g_sc, g_sp;
+  float* g1; float* g2;
+  const unsigned* flags;
+  int* status;                                         // [0] error, [1] tiles whose cells left the 8x8 mask (whole call redone on SIMT)
+  int B, S, H1, W1, H2, W2;
+  int tiles_x, tiles_y;
+};
+
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t saddr) {     // MN-major: LBO = next 64-element MN block (16 KB), SBO = next 8 K-rows (1 KB)
+  return uint64_t((saddr >> 4) & 0x3FFFu) | (uint64_t(kATBlk >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (uint64_t(1) << 46) | (uint64_t(2) << 61);
+}
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+constexpr size_t kATBwdSmem = 3 * size_t(4 * kATBlk) + kATDBytes + 1024;       // f1, f2, G (hi+lo each) + tap table
+
+__global__ void __launch_bounds__(256, 1) altcorr_tc_bwd_kernel(const __grid_constant__ AltTcBwdParams P) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[3];            // f1 tile landed, f2 cell landed, MMAs of the cell done
+  __shared__ uint32_t tmem_base_s;
+  __shared__ int s_min[2], s_ovf, s_ncell;
+  __shared__ unsigned s_mask[2];
+  __shared__ short s_cx[64], s_cy[64];
+
+  const unsigned flags = P.flags ? *P.flags : 0u;
+  if (flags & 2u) return;
+  const bool lo = (flags & 1u) != 0u;
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+  unsigned char* g0 = smem_dyn + (s0 - smem_u32(smem_dyn));
+  const uint32_t sF1 = s0, sF2 = s0 + 4 * kATBlk, sG = s0 + 8 * kATBlk;
+  unsigned char* Gp = g0 + 8 * kATBlk;
+  float* T = reinterpret_cast<float*>(g0 + 12 * kATBlk);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t bar_f1 = smem_u32(&bars[0]), bar_f2 = smem_u32(&bars[1]), bar_mma = smem_u32(&bars[2]);
+  if (tid == 0) {
+    mbar_init(bar_f1, 1); mbar_init(bar_f2, 1); mbar_init(bar_mma, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int p = tid & 127, hh = tid >> 7;              // pixel of the tile, and which half of the rows (taps / cell rows) this thread builds
+  const int q = warp & 3, h = warp >> 2;               // TMEM lane quarter / column half for the drains
+  const int tiles = P.tiles_x * P.tiles_y;
+  const long long total = static_cast<long long>(P.B) * tiles;
+  const uint32_t tile_bytes = lo ? 4 * kATBlk : 2 * kATBlk;
+  constexpr uint32_t kIdesc1 = kATIdesc | (1u << 16);                 // A K-major, B MN-major
+  constexpr uint32_t kIdesc2 = kATIdesc | (1u << 15) | (1u << 16);    // both MN-major
+  uint32_t n_cells_done = 0;                           // parity of bar_f2 / bar_mma
+  int k = 0;
+  bool dead = false;
+  for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
+    const int tile = int(t % tiles), b = int(t / tiles);
+    const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
+    const int y = ty0 + (p >> 4), x = tx0 + (p & 15);
+    const bool valid = y < P.H1 && x < P.W1;
+    if (tid == 0) {
+      mbar_expect_tx(bar_f1, tile_bytes);
+      tma_load_4d(sF1, &P.a_hi, 0, tx0, ty0, b, bar_f1);
+      tma_load_4d(sF1 + kATBlk, &P.a_hi, 64, tx0, ty0, b, bar_f1);
+      if (lo) {
+        tma_load_4d(sF1 + 2 * kATBlk, &P.a_lo, 0, tx0, ty0, b, bar_f1);
+        tma_load_4d(sF1 + 3 * kATBlk, &P.a_lo, 64, tx0, ty0, b, bar_f1);
+      }
+    }
+    int task_cells = 0;
+    for (int s = 0; s < P.S && !dead; s++) {
+      if (tid == 0) { s_min[0] = s_min[1] = 0x7fffffff; s_mask[0] = s_mask[1] = 0u; s_ovf = 0; }
+      __syncthreads();
+      float dx = 0.f, dy = 0.f;
+      int wx0 = 0, wy0 = 0, lx = 1, hx = 0, ly = 1, hy = 0;
+      if (valid) {
+        const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
+        wx0 = alt_floor_clamped(c.x, &dx) - 3; wy0 = alt_floor_clamped(c.y, &dy) - 3;
+        lx = max(wx0, 0); hx = min(wx0 + 7, P.W2 - 1); ly = max(wy0, 0); hy = min(wy0 + 7, P.H2 - 1);
+        if (lx > hx || ly > hy) { lx = 1; hx = 0; }
+        else if (hh == 0) { atomicMin(&s_min[0], lx); atomicMin(&s_min[1], ly); }
+      }
+      // tap table T[ty][tx][p] = d loss / d S[p][tap]: rows 4hh..4hh+3 by this thread
+      {
+        const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx, w10 = dy * (1.0f - dx), w11 = dy * dx;
+        const float* gp = P.grad + b * P.g_sb + s * P.g_ss + (static_cast<long long>(y) * P.W1 + x) * P.g_sp;
+        float up[7], cur[7];
+        const int r0 = 4 * hh;
+#pragma unroll
+        for (int ox = 0; ox < 7; ox++) up[ox] = (valid && r0 > 0) ? gp[static_cast<long long>((r0 - 1) + 7 * ox) * P.g_sc] : 0.0f;
+#pragma unroll
+        for (int ty = r0; ty < r0 + 4; ty++) {
+#pragma unroll
+          for (int ox = 0; ox < 7; ox++) cur[ox] = (valid && ty < 7) ? gp[static_cast<long long>(ty + 7 * ox) * P.g_sc] : 0.0f;
+#pragma unroll
+          for (int tx = 0; tx < 8; tx++) {
+            float g = 0.0f;
+            if (tx > 0) { g = fmaf(w11, up[tx - 1], g); g = fmaf(w01, cur[tx - 1], g); }
+            if (tx < 7) { g = fmaf(w10, up[tx], g); g = fmaf(w00, cur[tx], g); }
+            T[(ty * 8 + tx) * 128 + p] = g;
+          }
+#pragma unroll
+          for (int ox = 0; ox < 7; ox++) up[ox] = cur[ox];
+        }
+      }
+      __syncthreads();
+      const int bx0 = s_min[0], by0 = s_min[1];
+      if (hh == 0 && lx <= hx) {
+        const int c0 = (lx - bx0) >> 4, c1 = (hx - bx0) >> 4, r0 = (ly - by0) >> 3, r1 = (hy - by0) >> 3;
+        if (c1 >= 8 || r1 >= 8) s_ovf = 1;
+        else
+          for (int r = r0; r <= r1; r++)
+            for (int c = c0; c <= c1; c++) { const int bit = r * 8 + c; atomicOr(&s_mask[bit >> 5], 1u << (bit & 31)); }
+      }
+      __syncthreads();
+      const bool ovf = s_ovf != 0;                    // cells beyond the 8x8 mask: the SIMT kernel redoes the whole call
+      if (tid == 0 && !ovf) {
+        int n = 0;
+        unsigned long long m = (static_cast<unsigned long long>(s_mask[1]) << 32) | s_mask[0];
+        while (m) { const int bit = __ffsll(static_cast<long long>(m)) - 1; m &= m - 1; s_cx[n] = short(bit & 7); s_cy[n] = short(bit >> 3); n++; }
+        s_ncell = n;
+        if (n > 0) {                                   // first cell of this sample
+          mbar_expect_tx(bar_f2, tile_bytes);
+          const int X0 = bx0 + kATCx * s_cx[0], Y0 = by0 + kATCy * s_cy[0];
+          tma_load_4d(sF2, &P.b_hi, 0, X0, Y0, b, bar_f2);
+          tma_load_4d(sF2 + kATBlk, &P.b_hi, 64, X0, Y0, b, bar_f2);
+          if (lo) { tma_load_4d(sF2 + 2 * kATBlk, &P.b_lo, 0, X0, Y0, b, bar_f2); tma_load_4d(sF2 + 3 * kATBlk, &P.b_lo, 64, X0, Y0, b, bar_f2); }
+        }
+      }
+      __syncthreads();
+      if (ovf) { if (tid == 0) atomicAdd(P.status + 1, 1); continue; }
+      const int ncell = s_ncell;
+      for (int c = 0; c < ncell && !dead; c++, n_cells_done++, task_cells++) {
+        const int X0 = bx0 + kATCx * s_cx[c], Y0 = by0 + kATCy * s_cy[c];
+        // ---- G rows of pixel p for cell rows 4hh..4hh+3 (= operand block hh), hi and lo parts
+        {
+          const int relx = wx0 - X0, rely = wy0 - Y0;
+          unsigned char* ghi = Gp + hh * kATBlk + p * 128;
+          unsigned char* glo = ghi + 2 * kATBlk;
+#pragma unroll
+          for (int yy = 0; yy < 4; yy++) {
+            const int ty = 4 * hh + yy - rely;
+            const bool rowok = valid && static_cast<unsigned>(ty) < 8u;
+            uint32_t wh[8], wl[8];
+#pragma unroll
+            for (int xp = 0; xp < 8; xp++) {
+              float v[2];
+#pragma unroll
+              for (int e = 0; e < 2; e++) {
+                const int tx = 2 * xp + e - relx;
+                v[e] = (rowok && static_cast<unsigned>(tx) < 8u) ? T[(ty * 8 + tx) * 128 + p] : 0.0f;
+              }
+              const __half2 hv = __floats2half2_rn(v[0], v[1]);
+              const float2 back = __half22float2(hv);
+              const __half2 lv = __floats2half2_rn(v[0] - back.x, v[1] - back.y);
+              wh[xp] = *reinterpret_cast<const uint32_t*>(&hv);
+              wl[xp] = *reinterpret_cast<const uint32_t*>(&lv);
+            }
+#pragma unroll
+            for (int ch = 0; ch < 2; ch++) {
+              const int chunk = ((yy * 2 + ch) ^ (p & 7)) << 4;
+              *reinterpret_cast<uint4*>(ghi + chunk) = make_uint4(wh[4 * ch], wh[4 * ch + 1], wh[4 * ch + 2], wh[4 * ch + 3]);
+              *reinterpret_cast<uint4*>(glo + chunk) = make_uint4(wl[4 * ch], wl[4 * ch + 1], wl[4 * ch + 2], wl[4 * ch + 3]);
+            }
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes of G -> visible to the tensor core
+        __syncthreads();
+        if (tid == 0) {
+          bool ok = true;
+          if (task_cells == 0) ok = mbar_wait(bar_f1, k & 1);
+          ok = ok && mbar_wait(bar_f2, n_cells_done & 1u);
+          if (!ok) atomicExch(P.status, 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const int nprod = lo ? 3 : 2;
+          // d f1 (TMEM columns 0..127) += G . f2cell
+          uint32_t acc1 = task_cells == 0 ? 0u : 1u;
+          for (int pr = 0; pr < nprod; pr++) {          // Gh.Fh, Gl.Fh, Gh.Fl
+            const uint32_t go = (pr == 1) ? 2 * kATBlk : 0u, fo = (pr == 2) ? 2 * kATBlk : 0u;
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) {
+              umma_f16(tmem_base, umma_desc_sw128(sG + go + (kk >> 2) * kATBlk + (kk & 3) * 32), umma_desc_sw128_mn(sF2 + fo + kk * 2048), kIdesc1, acc1);
+              acc1 = 1u;
+            }
+          }
+          // d f2cell (TMEM columns 128..255) = G^T . f1tile
+          uint32_t acc2 = 0u;
+          for (int pr = 0; pr < nprod; pr++) {
+            const uint32_t go = (pr == 1) ? 2 * kATBlk : 0u, fo = (pr == 2) ? 2 * kATBlk : 0u;
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) {
+              umma_f16(tmem_base + 128u, umma_desc_sw128_mn(sG + go + kk * 2048), umma_desc_sw128_mn(sF1 + fo + kk * 2048), kIdesc2, acc2);
+              acc2 = 1u;
+            }
+          }
+          umma_commit(bar_mma);
+        }
+        __syncwarp();
+        const bool ok = mbar_wait(bar_mma, n_cells_done & 1u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (!ok) { if (lane == 0) atomicExch(P.status, 1); dead = true; }
+        if (tid == 0 && c + 1 < ncell && ok) {          // the f2 stage is free again: fetch the next cell under the drain
+          mbar_expect_tx(bar_f2, tile_bytes);
+          const int X1 = bx0 + kATCx * s_cx[c + 1], Y1 = by0 + kATCy * s_cy[c + 1];
+          tma_load_4d(sF2, &P.b_hi, 0, X1, Y1, b, bar_f2);
+          tma_load_4d(sF2 + kATBlk, &P.b_hi, 64, X1, Y1, b, bar_f2);
+          if (lo) { tma_load_4d(sF2 + 2 * kATBlk, &P.b_lo, 0, X1, Y1, b, bar_f2); tma_load_4d(sF2 + 3 * kATBlk, &P.b_lo, 64, X1, Y1, b, bar_f2); }
+        }
+        __syncwarp();
+        // ---- drain d f2cell: TMEM lane = cell position
+        {
+          const int n = 32 * q + lane, Y = Y0 + (n >> 4), X = X0 + (n & 15);
+          const bool inb = Y < P.H2 && X < P.W2;
+          float* dst = P.g2 + ((static_cast<long long>(b) * P.H2 + Y) * P.W2 + X) * 128 + 64 * h;
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(128 + 64 * h + 32 * j), v);
+            uint32_t any = 0u;
+#pragma unroll
+            for (int i = 0; i < 32; i++) any |= v[i];
+            if (ok && inb && (any & 0x7fffffffu))
+#pragma unroll
+              for (int i = 0; i < 8; i++)
+                red_add_v4(dst + 32 * j + 4 * i, __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();                               // G, T-dependent state and the d f2 accumulator may be reused
+      }
+    }
+    // ---- d f1 of the tile: TMEM lane = pixel
+    {
+      const int pp = 32 * q + lane, yy = ty0 + (pp >> 4), xx = tx0 + (pp & 15);
+      float* dst = P.g1 + ((static_cast<long long>(b) * P.H1 + yy) * P.W1 + xx) * 128 + 64 * h;
+      const bool pv = yy < P.H1 && xx < P.W1;
+      if (task_cells == 0) {                           // nothing accumulated (all windows outside the image): zeros
+        if (tid == 0 && !mbar_wait(bar_f1, k & 1)) atomicExch(P.status, 1);     // keep the barrier phase in step
+        if (pv)
+#pragma unroll
+          for (int i = 0; i < 16; i++) reinterpret_cast<float4*>(dst)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(64 * h + 32 * j), v);
+          if (pv)
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+              reinterpret_cast<float4*>(dst + 32 * j)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();                                   // f1 stage and the d f1 accumulator are free for the next tile
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(256) : "memory");
+}
+
 // ---- host ---------------------------------------------------------------------------------------------------------------
 // feature map [F][H][W][C = 128] fp16 as a 4-D tensor; box = 64 channels x 16 x 8 x 1 frame, 128-byte swizzle:
 // the box lands in shared memory as [8*16 rows][64 halfs], the K-major UMMA operand block.
@@ -586,6 +864,36 @@ int altcorr_split(const float* x, void* hi, void* lo, size_t n, unsigned* flags,
   return DB200_OK;
 }
 
+
+// SIMT backward of altcorr.cu, run only when the device words ask for it (flags bit 1, or status[1] != 0)
+int altcorr_bwd_simt_conditional(const float* fmap1, const float* fmap2, const float* coords, const float* corr_grad,
+                                 float* fmap1_grad, float* fmap2_grad, int B, int S, int H1, int W1, int H2, int W2, int C,
+                                 int radius, const unsigned* flags, const int* status, cudaStream_t st);
+
+int altcorr_tc_bwd_launch(const void* h1, const void* l1, const void* h2, const void* l2, const float* coords, const float* grad,
+                          float* g1, float* g2, int B, int S, int H1, int W1, int H2, int W2, unsigned* flags, int* status,
+                          cudaStream_t st) {
+  AltTcBwdParams P;
+  if (!alt_make_map(&P.a_hi, h1, B, H1, W1) || !alt_make_map(&P.a_lo, l1, B, H1, W1) || !alt_make_map(&P.b_hi, h2, B, H2, W2) ||
+      !alt_make_map(&P.b_lo, l2, B, H2, W2))
+    return DB200_ERR_CUDA;
+  P.coords = coords; P.c_sb = static_cast<long long>(S) * H1 * W1 * 2; P.c_ss = static_cast<long long>(H1) * W1 * 2; P.c_sp = 2;
+  P.grad = grad; P.g_sb = static_cast<long long>(S) * 49 * H1 * W1; P.g_ss = static_cast<long long>(49) * H1 * W1;
+  P.g_sc = static_cast<long long>(H1) * W1; P.g_sp = 1;
+  P.g1 = g1; P.g2 = g2; P.flags = flags; P.status = status;
+  P.B = B; P.S = S; P.H1 = H1; P.W1 = W1; P.H2 = H2; P.W2 = W2;
+  P.tiles_x = cdiv(W1, kATPx); P.tiles_y = cdiv(H1, kATPy);
+  static bool attr = false;
+  if (!attr) {
+    DB200_CUDA(cudaFuncSetAttribute(altcorr_tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kATBwdSmem)));
+    attr = true;
+  }
+  const long long tasks = static_cast<long long>(B) * P.tiles_x * P.tiles_y;
+  altcorr_tc_bwd_kernel<<<int(tasks < kNumSMs ? tasks : kNumSMs), 256, kATBwdSmem, st>>>(P);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
 }  // namespace db200
 
 using namespace db200;
@@ -631,6 +939,42 @@ extern "C" int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, 
   a.B = B; a.S = S; a.flags = flags; a.status = status;
   a.list_cap = int((altcorr_tc_status_bytes(B, S, H1, W1) - 256) / sizeof(int));
   return altcorr_tc_launch(a, st);
+}
+
+extern "C" int db200_altcorr_backward_ws(const float* fmap1, const float* fmap2, const float* coords, const float* corr_grad,
+                                         float* fmap1_grad, float* fmap2_grad, float* coords_grad, int B, int S, int H1, int W1,
+                                         int H2, int W2, int C, int radius, void* workspace, size_t workspace_bytes,
+                                         db200_stream_t stream) {
+  if (!altcorr_tc_supported(C, radius) || !workspace)
+    return db200_altcorr_backward(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, coords_grad, B, S, H1, W1, H2, W2, C,
+                                  radius, stream);
+  if (!fmap1 || !fmap2 || !coords || !corr_grad || !fmap1_grad || !fmap2_grad || B < 0 || S < 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 ||
+      W2 <= 0)
+    return DB200_ERR_ARG;
+  if (B == 0) return DB200_OK;
+  if (workspace_bytes < db200_altcorr_workspace_bytes(B, S > 0 ? S : 1, H1, W1, H2, W2, C)) return DB200_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DB200_CUDA(cudaMemsetAsync(fmap2_grad, 0, sizeof(float) * size_t(B) * H2 * W2 * C, st));
+  if (coords_grad && S > 0) DB200_CUDA(cudaMemsetAsync(coords_grad, 0, sizeof(float) * size_t(B) * S * H1 * W1 * 2, st));
+  if (S == 0) { DB200_CUDA(cudaMemsetAsync(fmap1_grad, 0, sizeof(float) * size_t(B) * H1 * W1 * C, st)); return DB200_OK; }
+  char* ws = static_cast<char*>(workspace);
+  unsigned* flags = reinterpret_cast<unsigned*>(ws); ws += 256;
+  int* status = reinterpret_cast<int*>(ws); ws += al256(altcorr_tc_status_bytes(B, S, H1, W1));
+  const size_t n1 = size_t(B) * H1 * W1 * C, n2 = size_t(B) * H2 * W2 * C;
+  void* h1 = ws; ws += al256(n1 * 2);
+  void* l1 = ws; ws += al256(n1 * 2);
+  void* h2 = ws; ws += al256(n2 * 2);
+  void* l2 = ws;
+  DB200_CUDA(cudaMemsetAsync(flags, 0, sizeof(unsigned), st));
+  DB200_CUDA(cudaMemsetAsync(status, 0, 2 * sizeof(int), st));
+  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st);
+  if (rc != DB200_OK) return rc;
+  rc = altcorr_split(fmap2, h2, l2, n2, flags, st);
+  if (rc != DB200_OK) return rc;
+  rc = altcorr_tc_bwd_launch(h1, l1, h2, l2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, flags, status, st);
+  if (rc != DB200_OK) return rc;
+  return altcorr_bwd_simt_conditional(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, C, radius, flags,
+                                      status, st);
 }
 
 extern "C" size_t db200_altcorr_pyramid_workspace_bytes(int B, int S, int H1, int W1) {

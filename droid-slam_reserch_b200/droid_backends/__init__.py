@@ -170,13 +170,18 @@ def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=No
 def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):
     """droid.cpp:205-217.  -> [fmap1_grad, fmap2_grad, coords_grad(zeros)]  (float only, like the reference)"""
     _chk(("fmap1", fmap1), ("fmap2", fmap2), ("coords", coords), ("corr_grad", corr_grad))
-    f1, f2, g = fmap1.float(), fmap2.float(), corr_grad.float()
+    f1, f2, g, co = fmap1.float(), fmap2.float(), corr_grad.float(), coords.float()
     B, S, H1, W1, _ = coords.shape
     _, H2, W2, Cc = f2.shape
     g1, g2 = torch.empty_like(f1), torch.empty_like(f2)
     gc = torch.empty((B, S, H1, W1, 2), dtype=torch.float32, device=f1.device)
-    _capi.check(_capi.lib().db200_altcorr_backward(_ptr(f1), _ptr(f2), _ptr(coords.float()), _ptr(g), _ptr(g1), _ptr(g2),
-                                                   _ptr(gc), B, S, H1, W1, H2, W2, Cc, radius, _stream()), "altcorr_backward")
+    lib = _capi.lib()
+    wsb = lib.db200_altcorr_workspace_bytes(B, max(S, 1), H1, W1, H2, W2, Cc) if (Cc == 128 and radius == 3 and B > 0) else 0
+    ws = torch.empty(wsb, dtype=torch.uint8, device=f1.device) if wsb else None
+    _capi.check(lib.db200_altcorr_backward_ws(_ptr(f1), _ptr(f2), _ptr(co), _ptr(g), _ptr(g1), _ptr(g2), _ptr(gc), B, S, H1, W1,
+                                              H2, W2, Cc, radius, _ptr(ws), wsb, _stream()), "altcorr_backward")
+    if CHECK_STATUS and ws is not None and S > 0:
+        _altcorr_check(ws.data_ptr() + 256, "altcorr_backward")
     return [g1, g2, gc]
 
 

@@ -96,6 +96,13 @@ int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, const float
                              int H1, int W1, int H2, int W2, int C, int radius, void* workspace,
                              size_t workspace_bytes, db200_stream_t stream);
 int db200_altcorr_status(const void* status_words, db200_stream_t stream);
+/* altcorr_backward on the tensor cores (same workspace size as the forward; C = 128, radius = 3, else the SIMT kernel):
+ * d fmap1 = G . fmap2[cell], d fmap2[cell] = G^T . fmap1[tile] per pixel tile and target cell, G = the 4-corner combination
+ * of corr_grad; fmap2_grad is accumulated with one vector red per 4 channels and cell position. */
+int db200_altcorr_backward_ws(const float* fmap1, const float* fmap2, const float* coords, const float* corr_grad,
+                              float* fmap1_grad, float* fmap2_grad, float* coords_grad, int B, int S, int H1, int W1,
+                              int H2, int W2, int C, int radius, void* workspace, size_t workspace_bytes,
+                              db200_stream_t stream);
 /* AltCorrBlock.corr_fn fused (corr.py:109-131 as driven by factor_graph.py:261-277): all `num_levels` levels, the
  * frame gathers `pyramid[0][:, ii]`, `pyramid[l][:, jj]`, the casts and the channel concat in ONE launch.
  *   fmap1_hi, fmap2_hi[l] : channels-last fp16 feature pyramid [frames, H>>l, W>>l, C] (fmap1 = level 0 of the same or

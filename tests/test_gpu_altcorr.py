@@ -133,3 +133,36 @@ def test_altcorr_pyramid_forward_vs_oracle(S, dtype):
         got = out[0, :, 49 * l:49 * (l + 1)]
         got = got[:, None] if S is None else np.moveaxis(got, -1, 1)
         assert np.abs(got - ref).max() <= 1e-4 * max(np.abs(ref).max(), 1e-3), l
+
+
+@pytest.mark.parametrize("B,S,H,W,H2,W2,exact,scatter", [
+    (2, 1, 48, 64, 48, 64, False, False),
+    (2, 1, 24, 32, 12, 16, True, False),
+    (1, 2, 21, 29, 10, 14, False, False),            # ragged tiles, two coordinate samples accumulate into the same gradients
+    (1, 1, 16, 32, 24, 32, False, True),
+])
+def test_altcorr_backward_tc_vs_oracle(B, S, H, W, H2, W2, exact, scatter):
+    import droid_backends
+    from oracle import oracle
+    f1, f2, co = _api_case(300 + H + W2, B, S, H, W, H2, W2, exact, scatter)
+    g = np.random.default_rng(5).normal(0, 1, (B, S, 49, H, W)).astype(np.float32)
+    r1, r2, _ = oracle.altcorr_backward(f1, f2, co, g, 3)
+    g1, g2, gc = droid_backends.altcorr_backward(_t(f1), _t(f2), _t(co), _t(g), 3)
+    for name, a, b in (("fmap1_grad", g1, r1), ("fmap2_grad", g2, r2)):
+        a = a.cpu().numpy()
+        assert np.abs(a - b).max() <= 1e-4 * np.abs(b).max(), (name, np.abs(a - b).max() / np.abs(b).max())
+        assert np.linalg.norm(a - b) / np.linalg.norm(b) <= 1e-5, name
+    assert float(gc.abs().max()) == 0.0 and gc.shape == (B, S, H, W, 2)
+
+
+def test_altcorr_backward_handover_to_simt():
+    """cells beyond the 8x8 mask (large scattered target map) and values outside the fp16 range: the SIMT kernel redoes the call"""
+    import droid_backends
+    from oracle import oracle
+    f1, f2, co = _api_case(11, 1, 1, 16, 32, 72, 160, False, True)
+    g = np.random.default_rng(6).normal(0, 1, (1, 1, 49, 16, 32)).astype(np.float32)
+    for f1x in (f1, f1 * np.float32(3e4)):
+        r1, r2, _ = oracle.altcorr_backward(f1x, f2, co, g, 3)
+        g1, g2, _ = droid_backends.altcorr_backward(_t(f1x), _t(f2), _t(co), _t(g), 3)
+        assert np.abs(g1.cpu().numpy() - r1).max() <= 1e-4 * np.abs(r1).max()
+        assert np.abs(g2.cpu().numpy() - r2).max() <= 1e-4 * np.abs(r2).max()

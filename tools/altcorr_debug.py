@@ -92,3 +92,41 @@ if __name__ == "__main__":
                 droid_backends.altcorr_forward(a, pyr[l], cl[l], 3)
         e1.record(); torch.cuda.synchronize()
         print(f"altcorr_forward 88 edges x 4 levels (fp32 API, 4 calls): {e0.elapsed_time(e1) / 5:.3f} ms", flush=True)
+
+
+def run_bwd(name, f1, f2, co, seed=3):
+    B, S, H, W, _ = co.shape
+    g = np.random.default_rng(seed).normal(0, 1, (B, S, 49, H, W)).astype(np.float32)
+    r1, r2, _ = oracle.altcorr_backward(f1, f2, co, g, 3)
+    droid_backends.CHECK_STATUS = False
+    g1, g2, _ = droid_backends.altcorr_backward(t(f1), t(f2), t(co), t(g), 3)
+    torch.cuda.synchronize()
+    for nm, a, b in (("d_fmap1", g1.cpu().numpy(), r1), ("d_fmap2", g2.cpu().numpy(), r2)):
+        err = np.abs(a - b)
+        print(f"[bwd {name}] {nm}: max err {np.nanmax(err):.3e} / ref max {np.abs(b).max():.2f} = {np.nanmax(err) / np.abs(b).max():.2e}; "
+              f"rel norm {np.linalg.norm(a - b) / np.linalg.norm(b):.2e}; nan {np.isnan(a).mean():.3f}", flush=True)
+        if np.nanmax(err) > 1e-4 * np.abs(b).max():
+            idx = np.unravel_index(np.nanargmax(err), err.shape)
+            print("    worst at (b,y,x,c)", idx, "got", a[idx], "want", b[idx])
+            print("    bad fraction per channel block of 16:", np.round((err > 1e-4 * np.abs(b).max()).reshape(-1, 8, 16).mean(axis=(0, 2)), 2).tolist())
+            bad = (err > 1e-4 * np.abs(b).max()).mean(axis=(0, 3))
+            print("    bad fraction per row (first 16 rows):", np.round(bad.mean(axis=1)[:16], 2).tolist())
+
+
+if __name__ == "__main__":
+    run_bwd("1 tile grid exact", *case(1, 1, 1, 8, 16, 8, 16, True, "grid"))
+    run_bwd("1 tile grid fp32", *case(2, 1, 1, 8, 16, 8, 16, False, "grid"))
+    run_bwd("6 tiles smooth", *case(4, 2, 1, 24, 32, 24, 32, False, "smooth"))
+    run_bwd("ragged, S=2", *case(5, 1, 2, 21, 29, 10, 14, False, "smooth"))
+    run_bwd("full size", *case(7, 3, 1, 48, 64, 48, 64, False, "smooth"))
+    f1, f2, co = case(9, 88, 1, 48, 64, 48, 64, False, "smooth")
+    a, c = t(f1), t(co)
+    ga = [torch.randn((88, 1, 49, 48, 64), device="cuda") for _ in range(4)]
+    for rep in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(3):
+            for l in range(4):
+                droid_backends.altcorr_backward(a, pyr[l], cl[l], ga[l], 3)
+        e1.record(); torch.cuda.synchronize()
+        print(f"altcorr_backward 88 edges x 4 levels (fp32 API, 4 calls): {e0.elapsed_time(e1) / 3:.3f} ms", flush=True)
