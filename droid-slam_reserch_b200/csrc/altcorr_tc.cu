@@ -1028,3 +1028,49 @@ extern "C" int db200_altcorr_status(const void* status_words, db200_stream_t str
   DB200_CUDA(cudaStreamSynchronize(st));
   return h[0] != 0 ? DB200_ERR_CUDA : h[1];
 }
+
+// ======================================================================================================================
+// db200_altcorr_forward_static — altcorr_forward for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels as db200_altcorr_forward_ws; the scratch (fp16 hi/lo split of both feature maps, flag and status words,
+// hand-over list) lives in ONE file-scope device array of kAltStaticBytes that every GPU that loads the library holds until
+// exit.  All calls share it: two calls that overlap on the GPU (different streams, or graph branches) race on it.
+// Nothing in it has to survive between calls; the words that must start at zero (flags, status) are cleared on `stream`
+// at the start of every call.
+constexpr size_t kAltStaticBytes = size_t(8) << 20;                   // 8 MiB: e.g. B*S = 2 edges at 48x64 -> 48x64, C = 128
+static __device__ __align__(256) unsigned char g_altcorr_static_scratch[kAltStaticBytes];
+
+namespace {
+// In host code `g_altcorr_static_scratch` is a host-side stand-in, not a device address: resolve it per device, once,
+// with that device current.
+constexpr int kMaxDevices = 64;
+void* g_alt_static_ptr[kMaxDevices] = {};
+int alt_static_scratch(void** out) {
+  int dev = -1;
+  DB200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return DB200_ERR_ARG;
+  if (!g_alt_static_ptr[dev]) {
+    void* p = nullptr;
+    DB200_CUDA(cudaGetSymbolAddress(&p, g_altcorr_static_scratch));
+    if (!p) return DB200_ERR_CUDA;
+    g_alt_static_ptr[dev] = p;                                       // idempotent: racing host threads store the same value
+  }
+  *out = g_alt_static_ptr[dev];
+  return DB200_OK;
+}
+}  // namespace
+
+extern "C" size_t db200_altcorr_static_max_bytes(void) { return kAltStaticBytes; }
+
+extern "C" int db200_altcorr_forward_static(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B,
+                                            int S, int H1, int W1, int H2, int W2, int C, int radius, db200_stream_t stream) {
+  if (!fmap1 || !fmap2 || !coords || !corr || B < 0 || S < 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0 || C <= 0) return DB200_ERR_ARG;
+  if (!altcorr_tc_supported(C, radius)) return DB200_ERR_ARG;         // the scratch-free SIMT entry point serves other shapes
+  if (B == 0 || S == 0) return DB200_OK;
+  const size_t need = db200_altcorr_workspace_bytes(B, S, H1, W1, H2, W2, C);
+  if (need == 0 || need > kAltStaticBytes) return DB200_ERR_STATIC_LIMIT;
+  void* scratch = nullptr;
+  const int rc = alt_static_scratch(&scratch);
+  if (rc != DB200_OK) return rc;
+  return db200_altcorr_forward_ws(fmap1, fmap2, coords, corr, B, S, H1, W1, H2, W2, C, radius, scratch, kAltStaticBytes, stream);
+}

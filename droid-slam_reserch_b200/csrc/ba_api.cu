@@ -189,6 +189,7 @@ extern "C" const char* db200_status_string(int s) {
     case DB200_ERR_CUDA: return "CUDA runtime error";
     case DB200_ERR_WORKSPACE: return "workspace too small";
     case DB200_ERR_INDEX: return "edge index out of range [0, t1)";
+    case DB200_ERR_STATIC_LIMIT: return "problem exceeds the built-in static scratch of this no-allocation entry point (see db200_*_static_max_bytes)";
     case DB200_ERR_ETA: return "eta rows != number of unique frames in cat(arange(t0,t1), ii)";
   }
   return "unknown status";

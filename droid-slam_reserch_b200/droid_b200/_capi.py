@@ -34,6 +34,8 @@ _SIGNATURES = {
     "db200_altcorr_workspace_bytes": (_sz, [_i] * 7),
     "db200_altcorr_forward_ws": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "db200_altcorr_backward_ws": (_i, [_vp] * 7 + [_i] * 8 + [_vp, _sz, _vp]),
+    "db200_altcorr_static_max_bytes": (_sz, []),
+    "db200_altcorr_forward_static": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_altcorr_status": (_i, [_vp, _vp]),
     "db200_altcorr_pyramid_workspace_bytes": (_sz, [_i] * 4),
     "db200_altcorr_pyramid_forward": (_i, [_vp, _vp, C.POINTER(_vp), C.POINTER(_vp), _vp, _vp, C.POINTER(_vp), C.c_longlong, _i, _i,

@@ -22,6 +22,7 @@ extern "C" {
 #define DB200_ERR_WORKSPACE (-3)/* workspace too small */
 #define DB200_ERR_INDEX (-4)    /* (device status) edge index out of range */
 #define DB200_ERR_ETA (-5)      /* (device status) eta rows != |unique(cat(arange(t0,t1), ii))| */
+#define DB200_ERR_STATIC_LIMIT (-6) /* problem needs more scratch than the built-in static array of a *_static entry point holds */
 
 #define DB200_F32 0
 #define DB200_F16 1
@@ -121,6 +122,18 @@ int db200_altcorr_pyramid_forward(const void* fmap1_hi, const void* fmap1_lo, co
                                   long long c_ss, long long c_sp, float* out, long long o_sb, long long o_ss,
                                   long long o_sc, long long o_sp, int B, int S, int radius, void* workspace,
                                   size_t workspace_bytes, db200_stream_t stream);
+/* altcorr_forward WITHOUT any allocation and without a caller workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, kernels and results as db200_altcorr_forward_ws (C = 128, radius = 3 only;
+ * other shapes -> DB200_ERR_ARG, use db200_altcorr_forward, which needs no scratch).  The scratch is a static device array
+ * of db200_altcorr_static_max_bytes() = 8 MiB per GPU that loads the library; a problem whose
+ * db200_altcorr_workspace_bytes(...) exceeds it returns DB200_ERR_STATIC_LIMIT and computes nothing.  The call makes no
+ * cudaMalloc/cudaFree and calls no allocating library routine.  Every call shares the array: calls that overlap on the
+ * GPU (other streams, parallel graph branches) race; calls ordered on one stream are safe (the words that must start at
+ * zero are cleared on `stream` at the start of each call). */
+size_t db200_altcorr_static_max_bytes(void);
+int db200_altcorr_forward_static(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B, int S,
+                                 int H1, int W1, int H2, int W2, int C, int radius, db200_stream_t stream);
 /* x[n] fp32 -> hi[n], lo[n] fp16 with x ~= hi + lo; *flags |= 1 if any lo != 0, |= 2 if any value is non-finite or
  * outside the fp16 range (flags must be zeroed by the caller). n % 4 == 0. */
 int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, unsigned* flags, db200_stream_t stream);
