@@ -18,7 +18,9 @@ namespace db200 {
 
 constexpr int kBAThreads = 256;       // threads per CTA of the frame kernels = pixels per sub-tile
 constexpr int kEStride = kBAThreads + 1;  // padded pixel stride of the E stash (bank-conflict free)
-constexpr int kMaxDeg = 28;           // max pose edges per source frame on the fused path
+constexpr int kMaxDeg = 28;           // max pose edges per source frame on the fused one-CTA-per-frame path
+constexpr int kMaxStereo = 4;         // ... and max stereo (ii == jj) edges beside them; frames beyond either limit take the
+constexpr int kHdChunk = 14;          // high-degree path: work items (frame, pair of kHdChunk-slot chunks), ba_frame.cu
 constexpr int kRec = 16;              // floats per edge record
 constexpr int kCholTile = 64;         // tile edge of the reduced-system Cholesky (ba_solve.cu)
 
@@ -46,11 +48,12 @@ struct BAHeader {
   int chol_fail;   // >0: a pivot <= 0 was met in the current solve
   int any_fail;    // number of iterations whose solve failed
   int max_deg;     // max pose edges per source frame
-  int pad[3];
+  int hd_items;    // work items of the high-degree path (sum over its frames of nc (nc + 1) / 2, nc = ceil(d / kHdChunk))
+  int pad[2];
 };
 
 struct BALayout {
-  size_t header, frame_k, kx, deg_off, nd, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, Lstage, Xstage, total;
+  size_t header, frame_k, kx, deg_off, nd, hd_off, edge_order, fill, erec, yvec, Q, w, Hb, Wk, cflags, xsol, dx, Lstage, Xstage, total;
   int n, nt, ld, Mcap;
 };
 
@@ -60,6 +63,12 @@ struct BALayout {
 __host__ __device__ inline size_t sys_index(int r, int c) { return size_t(r) * size_t(r + 1) / 2 + size_t(c); }
 __host__ __device__ inline size_t sys_h_elems(int n) { return size_t(n) * size_t(n + 1) / 2; }
 __host__ __device__ inline size_t sys_elems(int n) { return sys_h_elems(n) + size_t(n); }
+
+// a source frame leaves the one-CTA-per-frame path when its pose edges or its stereo edges exceed what that CTA stages
+__host__ __device__ inline bool frame_is_hd(int pose_edges, int all_edges) {
+  return pose_edges > kMaxDeg || all_edges - pose_edges > kMaxStereo;
+}
+__host__ __device__ inline int hd_chunks(int pose_edges) { return (pose_edges + kHdChunk - 1) / kHdChunk; }
 
 inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
@@ -79,6 +88,7 @@ inline BALayout ba_layout(int N, int B, int HW, int t0, int t1, int eta_rows, in
   L.kx = take(sizeof(int) * size_t(B));
   L.deg_off = take(sizeof(int) * size_t(B + 1));
   L.nd = take(sizeof(int) * size_t(B));
+  L.hd_off = take(sizeof(int) * size_t(B + 1));
   L.edge_order = take(sizeof(int) * size_t(N > 0 ? N : 1));
   L.fill = take(sizeof(int) * size_t(B));
   L.erec = take(sizeof(EdgeRec) * size_t(N > 0 ? N : 1));
@@ -104,7 +114,7 @@ struct BAParams {
   int N, B, ht, wd, HW, t0, t1, P, eta_rows, motion_only;
   int own_lo, own_hi;   // owned source frames [own_lo, own_hi) (edge-sharded multi-GPU runs; 0, B otherwise)
   // workspace views
-  BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
+  BAHeader* hdr; int* frame_k; int* kx; int* deg_off; int* nd; int* hd_off; int* edge_order; int* fill; EdgeRec* erec; float* yvec;
   float* Q; float* w; double* Hb; double* Wk; unsigned* cflags; double* xsol; float* dx; double* Lstage; double* Xstage;
   int n, nt, ld, Mcap;
   int chol_nd;          // solver: number of diagonal CTAs, -1 = automatic (ba_solve.cu)
@@ -118,6 +128,7 @@ inline BAParams ba_params(const BALayout& L, void* ws) {
   p.kx = reinterpret_cast<int*>(b + L.kx);
   p.deg_off = reinterpret_cast<int*>(b + L.deg_off);
   p.nd = reinterpret_cast<int*>(b + L.nd);
+  p.hd_off = reinterpret_cast<int*>(b + L.hd_off);
   p.edge_order = reinterpret_cast<int*>(b + L.edge_order);
   p.fill = reinterpret_cast<int*>(b + L.fill);
   p.erec = reinterpret_cast<EdgeRec*>(b + L.erec);

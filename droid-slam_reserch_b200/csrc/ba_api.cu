@@ -185,7 +185,7 @@ extern "C" const char* db200_status_string(int s) {
   switch (s) {
     case DB200_OK: return "ok";
     case 1: return "Cholesky breakdown in at least one iteration: zero pose update applied (reference behaviour)";
-    case DB200_ERR_ARG: return "invalid argument (null pointer, bad size, unsupported dtype/radius, or >28 pose edges share a source frame)";
+    case DB200_ERR_ARG: return "invalid argument (null pointer, bad size, unsupported dtype/radius)";
     case DB200_ERR_CUDA: return "CUDA runtime error";
     case DB200_ERR_WORKSPACE: return "workspace too small";
     case DB200_ERR_INDEX: return "edge index out of range [0, t1)";

@@ -19,6 +19,7 @@
 // HBM traffic per edge-pixel: target 8 B + weight 8 B (+ disp 4 B per keyframe-pixel) — the algorithmic
 // 20*HW*N + 16*HW*M of SURVEY.md §8d; the back-substitution re-reads weight (8 B) to recompute E.
 #include <cstdlib>
+#include <mutex>
 #include "ba.cuh"
 
 namespace db200 {
@@ -541,21 +542,26 @@ __device__ __forceinline__ void schur_segment(float (&acc)[kSegTiles][4], unsign
   for (int q = 0; q < CNT; q++) { acc[q][0] += tmp[q][0]; acc[q][1] += tmp[q][1]; acc[q][2] += tmp[q][2]; acc[q][3] += tmp[q][3]; }
 }
 
-// grid = Mcap * S CTAs; CTA (k, s) handles chunks s, s+S, ... of source frame kx[k]; launches are bucketed by
-// degree: only frames with dlo <= nd[k] <= dcap work here (shared memory and NSEG grow with the bucket).
-template <int NSEG>
-__global__ void __launch_bounds__(kBAThreads, (NSEG <= 2 ? 2 : 1))
-ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  if (p.hdr->status < 0) return;
-  const int k = blockIdx.x / S, split = blockIdx.x - k * S;
-  if (k >= p.hdr->M) return;
-  const int d = p.nd[k];
-  if (d < dlo || d > dcap) return;
+// One work item of the Schur accumulation: chunks split, split+S, ... of source frame kx[k].
+//   HD = false: all edges of the frame (d <= kMaxDeg pose edges, <= kMaxStereo stereo edges): C, w, Q are formed here.
+//   HD = true : the pose edges of slot chunks `ca` >= `cb` of a frame beyond those limits; Q, w were written by
+//               ba_hd_depth_kernel.  Local slots: chunk cb first (kHdChunk of them when ca > cb), then chunk ca.  The item
+//               owns the blocks (e, f) inside the chunk when ca == cb, and the cross blocks chunk ca x chunk cb (both
+//               orders) otherwise: every pair of rows of the depth map is covered exactly once over the frame's items,
+//               which is the reference's unbounded pair enumeration (droid_kernels.cu:1244-1272).
+template <int NSEG, bool HD>
+__device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* smem_raw, int k, int split, int S, int dcap,
+                                           int necap, int ca, int cb) {
   const int f = p.kx[k];
-  if (f < p.own_lo || f >= p.own_hi) return;       // depth map owned by another rank
-  const int q_beg = p.deg_off[k], ne = p.deg_off[k + 1] - q_beg;
-  if (ne > necap) { if (threadIdx.x == 0) atomicMin(&p.hdr->status, DB200_ERR_ARG); return; }
+  const int q_beg = p.deg_off[k], ne_all = p.deg_off[k + 1] - q_beg;
+  int d = p.nd[k], ne = ne_all;
+  if (HD) {
+    const int na = min(kHdChunk, d - ca * kHdChunk);
+    d = (ca == cb) ? na : kHdChunk + na;
+    ne = d;
+  }
+  const bool diag_item = !HD || ca == cb;
+  auto own = [&](int e1, int f2) -> bool { return !HD || ca == cb || ((e1 < kHdChunk) != (f2 < kHdChunk)); };
   const SchurSmem sm = schur_carve(smem_raw, dcap, necap);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int HW = p.HW, wd = p.wd;
@@ -581,11 +587,23 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     }
   }
   for (int i = tid; i < 2 * rpad * kStride; i += kBAThreads) sm.shi[i] = 0.0f;
-  for (int qq = tid; qq < ne; qq += kBAThreads) {
-    const int sl = p.erec[q_beg + qq].slot;
-    sm.eslot[qq] = sl;
-    sm.eid[qq] = p.erec[q_beg + qq].eid;
-    if (sl >= 0) sm.slotq[sl] = q_beg + qq;
+  if (HD) {
+    for (int qq = tid; qq < ne_all; qq += kBAThreads) {
+      const int sl = p.erec[q_beg + qq].slot;
+      if (sl < 0) continue;                           // stereo edges: depth terms only, already in Q, w
+      const int c = sl / kHdChunk;
+      int ls = -1;
+      if (c == cb) ls = sl - cb * kHdChunk;
+      else if (c == ca) ls = kHdChunk + sl - ca * kHdChunk;
+      if (ls >= 0) { sm.eslot[ls] = ls; sm.eid[ls] = p.erec[q_beg + qq].eid; sm.slotq[ls] = q_beg + qq; }
+    }
+  } else {
+    for (int qq = tid; qq < ne; qq += kBAThreads) {
+      const int sl = p.erec[q_beg + qq].slot;
+      sm.eslot[qq] = sl;
+      sm.eid[qq] = p.erec[q_beg + qq].eid;
+      if (sl >= 0) sm.slotq[sl] = q_beg + qq;
+    }
   }
   // pixel lanes per edge: minimise (warps touched) x (pixel iterations)
   int L = 1;
@@ -600,7 +618,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   const bool active = ne > 0 && e < ne;
   EdgeRec rec{};
   int sl = -1;
-  if (active) { rec = load_rec(p.erec + q_beg + e); sl = rec.slot; }
+  if (!HD && active) { rec = load_rec(p.erec + q_beg + e); sl = rec.slot; }
   float hacc[27];
 #pragma unroll
   for (int i = 0; i < 27; i++) hacc[i] = 0.0f;
@@ -611,6 +629,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
     for (int q = 0; q < kSegTiles; q++) { accT[u][q][0] = 0.0f; accT[u][q][1] = 0.0f; accT[u][q][2] = 0.0f; accT[u][q][3] = 0.0f; }
   const int gid = lane >> 2, tig = lane & 3;
   __syncthreads();
+  if (HD && active) { rec = load_rec(p.erec + sm.slotq[e]); sl = e; }      // local edge e = local slot e
   // this warp's segments u = 0..NSEG-1 -> segment warp + 8u; ldmatrix row addresses of this lane
   //   A (x4): matrices {rows 0-7,k 0-3}, {rows 8-15,k 0-3}, {rows 0-7,k 4-7}, {rows 8-15,k 4-7}  -> a0..a3
   //   B (x4): matrices {hi,k 0-3}, {hi,k 4-7}, {lo,k 0-3}, {lo,k 4-7} of the 8 rows of one N-tile   -> b0h,b1h,b0l,b1l
@@ -686,8 +705,10 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
         const float tu = se[pp], tv = se[kChunk + pp], wur = se[2 * kChunk + pp], wvr = se[3 * kChunk + pp];
         PixEdge pe_;
         pix_edge(rec, sm.px[pp], sm.px[kChunk + pp], sm.px[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
-        sm.Cw[(size_t(e) * 2 + 0) * kChunk + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
-        sm.Cw[(size_t(e) * 2 + 1) * kChunk + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
+        if (!HD) {
+          sm.Cw[(size_t(e) * 2 + 0) * kChunk + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
+          sm.Cw[(size_t(e) * 2 + 1) * kChunk + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
+        }
         if (sl >= 0) {                                                         // stereo edges: depth terms only
           const float au = pe_.wu * pe_.Jzu, av = pe_.wv * pe_.Jzv;
           float* st = sm.shi + size_t(6 * sl) * kStride + pp;
@@ -718,12 +739,16 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
       const int pp = tid >> 2, part = tid & 3;
       const int pix = base + pp;
       float Csum = 0.0f, wsum = 0.0f;
-      for (int q = part; q < ne; q += 4) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + pp]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + pp]; }
-      Csum += __shfl_xor_sync(0xffffffffu, Csum, 1); wsum += __shfl_xor_sync(0xffffffffu, wsum, 1);
-      Csum += __shfl_xor_sync(0xffffffffu, Csum, 2); wsum += __shfl_xor_sync(0xffffffffu, wsum, 2);
+      if (!HD) {
+        for (int q = part; q < ne; q += 4) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + pp]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + pp]; }
+        Csum += __shfl_xor_sync(0xffffffffu, Csum, 1); wsum += __shfl_xor_sync(0xffffffffu, wsum, 1);
+        Csum += __shfl_xor_sync(0xffffffffu, Csum, 2); wsum += __shfl_xor_sync(0xffffffffu, wsum, 2);
+      }
       if (part == 0) {
         float Q = 0.0f, wv_ = 0.0f;
-        if (pix < HW) {
+        if (HD) {
+          if (pix < HW) { Q = p.Q[size_t(k) * HW + pix]; wv_ = p.w[size_t(k) * HW + pix]; }   // ba_hd_depth_kernel
+        } else if (pix < HW) {
           const float h = sm.px[2 * kChunk + pp];
           const float ds = sm.px[5 * kChunk + pp];
           const float m = ds > 0.0f ? 1.0f : 0.0f;
@@ -805,13 +830,15 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   };
   for (int i = tid; i < d * 6; i += kBAThreads) {
     const int e1 = i / 6, r = i - e1 * 6;
-    sm.cs[i] = double(sm.Hs[e1 * 27 + 21 + r]) - double(sm.G[size_t(6 * d) * gn + i]);
+    sm.cs[i] = diag_item ? double(sm.Hs[e1 * 27 + 21 + r]) - double(sm.G[size_t(6 * d) * gn + i]) : 0.0;
   }
   for (int i = tid; i < d * 36; i += kBAThreads) {   // W_f = sum_e A_e D_ef
     const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c2 = rc - r * 6;
     double s = 0.0;
-    for (int e1 = 0; e1 < d; e1++)
+    for (int e1 = 0; e1 < d; e1++) {
+      if (!own(e1, f2)) continue;
       for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e1 * 36 + r * 6 + kk]) * Dval(e1, f2, kk, c2);
+    }
     sm.Ws[i] = s;
   }
   __syncthreads();
@@ -821,7 +848,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
   for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
     const int ef = i / 36, rc = i - ef * 36, e1 = ef / d, f2 = ef - e1 * d, r = rc / 6, c2 = rc - r * 6;
     const int je = sm.jp[e1], jf = sm.jp[f2];
-    if (je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c2) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c2)], Dval(e1, f2, r, c2));
+    if (own(e1, f2) && je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c2) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c2)], Dval(e1, f2, r, c2));
   }
   if (ip >= 0) {
     for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
@@ -839,7 +866,7 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
       for (int f2 = 0; f2 < d; f2++)
         for (int kk = 0; kk < 6; kk++) s += sm.Ws[f2 * 36 + r * 6 + kk] * double(sm.Am[f2 * 36 + c2 * 6 + kk]);
       if (r >= c2) atomicAdd(&H[sys_index(6 * ip + r, 6 * ip + c2)], s);
-    } else if (tid >= 64 && tid < 70) {                  // b_i += -sum_e A_e c_e
+    } else if (diag_item && tid >= 64 && tid < 70) {     // b_i += -sum_e A_e c_e
       const int r = tid - 64;
       double s = 0.0;
       for (int e1 = 0; e1 < d; e1++)
@@ -847,9 +874,84 @@ ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
       atomicAdd(&bvec[6 * ip + r], -s);
     }
   }
-  for (int i = tid; i < d * 6; i += kBAThreads) {        // b_{j_e} += c_e
-    const int e1 = i / 6;
-    if (sm.jp[e1] >= 0) atomicAdd(&bvec[6 * sm.jp[e1] + (i - e1 * 6)], sm.cs[i]);
+  if (diag_item)
+    for (int i = tid; i < d * 6; i += kBAThreads) {      // b_{j_e} += c_e
+      const int e1 = i / 6;
+      if (sm.jp[e1] >= 0) atomicAdd(&bvec[6 * sm.jp[e1] + (i - e1 * 6)], sm.cs[i]);
+    }
+}
+
+// grid = Mcap * S CTAs; CTA (k, s) handles chunks s, s+S, ... of source frame kx[k]; launches are bucketed by
+// degree: only frames with dlo <= nd[k] <= dcap work here (shared memory and NSEG grow with the bucket).
+template <int NSEG>
+__global__ void __launch_bounds__(kBAThreads, (NSEG <= 2 ? 2 : 1))
+ba_schur_kernel(BAParams p, int S, int dlo, int dcap, int necap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (p.hdr->status < 0) return;
+  const int k = blockIdx.x / S, split = blockIdx.x - k * S;
+  if (k >= p.hdr->M) return;
+  const int d = p.nd[k];
+  if (d < dlo || d > dcap) return;
+  const int f = p.kx[k];
+  if (f < p.own_lo || f >= p.own_hi) return;       // depth map owned by another rank
+  if (frame_is_hd(d, p.deg_off[k + 1] - p.deg_off[k])) return;     // -> ba_schur_hd_kernel
+  schur_item<NSEG, false>(p, smem_raw, k, split, S, dcap, necap, 0, 0);
+}
+
+// ---- high-degree frames (more than kMaxDeg pose edges or kMaxStereo stereo edges) -------------------------------------
+// depth system of the frame over ALL its edges (:1396-1400): thread = pixel, edges in edge order; Q, w -> HBM
+__global__ void __launch_bounds__(kBAThreads)
+ba_hd_depth_kernel(BAParams p) {
+  if (p.hdr->status < 0) return;
+  const int k = blockIdx.y;
+  if (k >= p.hdr->M) return;
+  const int q_beg = p.deg_off[k], ne = p.deg_off[k + 1] - q_beg;
+  if (!frame_is_hd(p.nd[k], ne)) return;
+  const int f = p.kx[k];
+  if (f < p.own_lo || f >= p.own_hi) return;
+  const int pix = blockIdx.x * kBAThreads + threadIdx.x;
+  if (pix >= p.HW) return;
+  const int HW = p.HW;
+  const float fx = p.intr[0], fy = p.intr[1], cx = p.intr[2], cy = p.intr[3];
+  const float h = p.disps[size_t(f) * HW + pix];
+  const float X0 = (float(pix % p.wd) - cx) / fx, X1 = (float(pix / p.wd) - cy) / fy;
+  float Csum = 0.0f, wsum = 0.0f;
+  for (int qq = 0; qq < ne; qq++) {
+    const EdgeRec r = load_rec(p.erec + q_beg + qq);
+    const float* tg = p.target + size_t(r.eid) * 2 * HW;
+    const float* wg = p.weight + size_t(r.eid) * 2 * HW;
+    PixEdge pe_;
+    pix_edge(r, X0, X1, h, fx, fy, cx, cy, __ldg(tg + pix), __ldg(tg + HW + pix), __ldg(wg + pix), __ldg(wg + HW + pix), pe_);
+    Csum += pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;
+    wsum += pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;
+  }
+  const float ds = p.sens[size_t(f) * HW + pix];
+  const float m = ds > 0.0f ? 1.0f : 0.0f;
+  const float C = Csum + m * 0.05f + (1.0f - m) * p.eta[size_t(k) * HW + pix];
+  p.Q[size_t(k) * HW + pix] = 1.0f / C;
+  p.w[size_t(k) * HW + pix] = wsum - m * 0.05f * (h - ds);
+}
+
+// persistent CTAs walk the work items (frame, chunk pair, pixel split); hd_off[] = prefix sums of items per frame
+template <int NSEG>
+__global__ void __launch_bounds__(kBAThreads, 1)
+ba_schur_hd_kernel(BAParams p, int S, int dcap, int necap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (p.hdr->status < 0) return;
+  const int M = p.hdr->M;
+  const long long total = static_cast<long long>(p.hdr->hd_items) * S;
+  for (long long wi = blockIdx.x; wi < total; wi += gridDim.x) {
+    const int item = int(wi / S), split = int(wi - static_cast<long long>(item) * S);
+    int lo = 0, hi = M;                                  // largest k with hd_off[k] <= item
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (p.hd_off[mid] <= item) lo = mid; else hi = mid; }
+    const int k = lo, t = item - p.hd_off[k];
+    int ca = int((sqrtf(8.0f * float(t) + 1.0f) - 1.0f) * 0.5f);
+    while (ca * (ca + 1) / 2 > t) ca--;
+    while ((ca + 1) * (ca + 2) / 2 <= t) ca++;
+    const int cb = t - ca * (ca + 1) / 2;
+    const int f = p.kx[k];
+    if (f >= p.own_lo && f < p.own_hi) schur_item<NSEG, true>(p, smem_raw, k, split, S, dcap, necap, ca, cb);
+    __syncthreads();                                     // the next item reuses the shared-memory carve-up
   }
 }
 
@@ -911,6 +1013,45 @@ static int launch_schur(const BAParams& p, int S, int dlo, int dcap, cudaStream_
   return DB200_OK;
 }
 
+static int launch_schur_hd(const BAParams& p, int S, cudaStream_t st) {
+  dim3 grid(cdiv(p.HW, kBAThreads), p.Mcap);
+  ba_hd_depth_kernel<<<grid, kBAThreads, 0, st>>>(p);
+  DB200_CHECK_LAUNCH();
+  const int dcap = kMaxDeg, necap = kMaxDeg + kMaxStereo;
+  const size_t smem = schur_smem_bytes(dcap, necap);
+  auto kern = ba_schur_hd_kernel<5>;
+  DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  kern<<<kNumSMs, kBAThreads, smem, st>>>(p, S, dcap, necap);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
+// side streams + fork/join events of the accumulate stage, one set per device (a process may drive several GPUs)
+namespace {
+struct AuxStreams {
+  cudaStream_t aux[4] = {};
+  cudaEvent_t fork = nullptr, join[4] = {};
+  bool ok = false;
+};
+AuxStreams* aux_streams() {
+  static AuxStreams table[64];
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  AuxStreams& a = table[dev];
+  if (!a.ok) {
+    if (cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    for (int i = 0; i < 4; i++)
+      if (cudaStreamCreateWithFlags(&a.aux[i], cudaStreamNonBlocking) != cudaSuccess ||
+          cudaEventCreateWithFlags(&a.join[i], cudaEventDisableTiming) != cudaSuccess)
+        return nullptr;
+    a.ok = true;
+  }
+  return &a;
+}
+}  // namespace
+
 int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   DB200_CUDA(cudaMemsetAsync(p.Hb, 0, sizeof(double) * sys_elems(p.n), st));
   if (p.motion_only) {
@@ -941,29 +1082,27 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
   const int dmax_host = p.N < kMaxDeg ? p.N : kMaxDeg;   // the host only knows d <= N
   // The buckets are independent (disjoint frames; the reduced system is updated with atomics), and each one alone
   // leaves SMs idle in its last wave: fork them onto side streams so that they overlap, join before returning.
-  static cudaStream_t aux[3] = {nullptr, nullptr, nullptr};
-  static cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
-  if (!ev_fork) {
-    DB200_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-    for (int i = 0; i < 3; i++) {
-      DB200_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
-      DB200_CUDA(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
-    }
-  }
+  AuxStreams* ax = aux_streams();
+  if (!ax) return DB200_ERR_CUDA;
   const bool b1 = dmax_host > 8, b2 = dmax_host > 14, b3 = dmax_host > 22;
-  if (!b1) return launch_schur<1>(p, S, 0, 8, st);
-  DB200_CUDA(cudaEventRecord(ev_fork, st));
-  int rc = launch_schur<2>(p, S, 9, 14, st);                       // the bucket that carries most frames of a backend graph
+  const bool hd = p.N > kMaxStereo;                      // a frame can only exceed the fused path's limits with > 4 edges
+  if (!b1 && !hd) return launch_schur<1>(p, S, 0, 8, st);
+  DB200_CUDA(cudaEventRecord(ax->fork, st));
+  int rc = b1 ? launch_schur<2>(p, S, 9, 14, st)         // the bucket that carries most frames of a backend graph
+              : launch_schur<1>(p, S, 0, 8, st);
   auto side = [&](int i, auto fn) -> int {
-    DB200_CUDA(cudaStreamWaitEvent(aux[i], ev_fork, 0));
-    const int r = fn(aux[i]);
-    DB200_CUDA(cudaEventRecord(ev_join[i], aux[i]));
-    DB200_CUDA(cudaStreamWaitEvent(st, ev_join[i], 0));
+    DB200_CUDA(cudaStreamWaitEvent(ax->aux[i], ax->fork, 0));
+    const int r = fn(ax->aux[i]);
+    DB200_CUDA(cudaEventRecord(ax->join[i], ax->aux[i]));
+    DB200_CUDA(cudaStreamWaitEvent(st, ax->join[i], 0));
     return r;
   };
-  if (rc == DB200_OK) rc = side(0, [&](cudaStream_t s2) { return launch_schur<1>(p, S, 0, 8, s2); });
+  if (rc == DB200_OK && b1) rc = side(0, [&](cudaStream_t s2) { return launch_schur<1>(p, S, 0, 8, s2); });
   if (rc == DB200_OK && b2) rc = side(1, [&](cudaStream_t s2) { return launch_schur<4>(p, S, 15, 22, s2); });
   if (rc == DB200_OK && b3) rc = side(2, [&](cudaStream_t s2) { return launch_schur<5>(p, S, 23, kMaxDeg, s2); });
+  // frames beyond kMaxDeg pose edges / kMaxStereo stereo edges (known on the device only: both launches return at once
+  // when there are none): depth system over all edges of the frame, then the (frame, chunk pair) work items
+  if (rc == DB200_OK && hd) rc = side(3, [&](cudaStream_t s2) { return launch_schur_hd(p, S, s2); });
   return rc;
 }
 

@@ -20,7 +20,7 @@ __global__ void graph_flags_kernel(BAParams p) {
   }
   if (i == 0) {
     p.deg_off[p.B] = 0;
-    p.hdr->status = 0; p.hdr->M = 0; p.hdr->chol_fail = 0; p.hdr->any_fail = 0; p.hdr->max_deg = 0;
+    p.hdr->status = 0; p.hdr->M = 0; p.hdr->chol_fail = 0; p.hdr->any_fail = 0; p.hdr->max_deg = 0; p.hdr->hd_items = 0;
   }
 }
 
@@ -78,17 +78,23 @@ __global__ void graph_degree_kernel(BAParams p) {
 __global__ void graph_offsets_kernel(BAParams p) {   // single thread block, serial scan over M <= B entries
   if (p.hdr->status < 0) return;
   if (threadIdx.x == 0) {
-    int run = 0, mx = 0;
+    int run = 0, mx = 0, items = 0;
     const int M = p.hdr->M;
     for (int k = 0; k < M; k++) {
       const int c = p.deg_off[k + 1];
       p.deg_off[k] = run;
       run += c;
-      mx = max(mx, p.nd[k]);
+      const int d = p.nd[k];
+      mx = max(mx, d);
+      // frames beyond the fused path's staging limits (the reference has none: droid_kernels.cu:1244-1272 enumerates
+      // every pair of rows of a depth map): items (chunk a >= chunk b) of the high-degree path, ba_frame.cu
+      p.hd_off[k] = items;
+      if (!p.motion_only && frame_is_hd(d, c)) { const int nc = hd_chunks(d); items += nc * (nc + 1) / 2; }
     }
     p.deg_off[M] = run;
+    p.hd_off[M] = items;
     p.hdr->max_deg = mx;
-    if (!p.motion_only && mx > kMaxDeg) atomicMin(&p.hdr->status, DB200_ERR_ARG);
+    p.hdr->hd_items = items;
   }
 }
 

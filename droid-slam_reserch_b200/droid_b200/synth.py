@@ -168,6 +168,54 @@ def backend_edges(n_kf: int, n_edges: int, rng: np.random.Generator, rad: int = 
     return ii, jj
 
 
+def hub_edges(n_kf: int, hubs, rng: np.random.Generator, rad: int = 2):
+    """Temporal graph (i <-> j for i-rad-1 <= j < i) + hub frames: `hubs` = {frame: out-degree}; hub h gets edges h -> j
+    and j -> h to `out-degree` distinct other frames in total (its temporal neighbours count) — the shape of a place that
+    is revisited many times in a global / multisession backend graph (droid_backend.py:32-39 asks for 16 t factors)."""
+    es, seen = [], set()
+
+    def add(i, j):
+        if i != j and (i, j) not in seen:
+            seen.add((i, j)); es.append((i, j))
+
+    for i in range(n_kf):
+        for j in range(max(i - rad - 1, 0), i):
+            add(i, j); add(j, i)
+    for h, deg in hubs.items():
+        have = {j for (i, j) in seen if i == h}
+        others = [j for j in rng.permutation(n_kf).tolist() if j not in hubs and j not in have]   # hubs keep their exact degree
+        for j in others[:max(deg - len(have), 0)]:
+            add(h, j); add(j, h)
+    ii = np.array([e[0] for e in es], np.int64)
+    jj = np.array([e[1] for e in es], np.int64)
+    return ii, jj
+
+
+def hot_place_trajectory(visits: int = 12, arc: int = 8, away: int = 8, radius: float = 1.5):
+    """A camera that walks the same `arc` frames of a circle (looking outward) on every one of `visits` visits and spends
+    `away` frames on an excursion of its own in between: the shape of a multisession / long-term map with one place seen
+    again and again.  `add_proximity_factors` with the backend's budget (max_factors = 16 t, droid_backend.py:32-39) then
+    concentrates its loop-closure edges on the hot frames: 12 visits -> out-degrees up to 36, 18 frames above 28.
+    Returns world->camera poses [visits * (arc + away), 7] f64."""
+    poses = []
+    for v in range(visits):
+        for k in range(arc + away):
+            if k < arc:
+                a = 0.10 * k + 0.004 * v
+                c = np.array([radius * np.cos(a), 0.01 * v, radius * np.sin(a)])
+                yaw = np.pi / 2 - a
+            else:
+                u = k - arc + 1
+                a = 0.10 * (arc - 1)
+                base = np.array([radius * np.cos(a), 0.0, radius * np.sin(a)])
+                ang = 2 * np.pi * v / visits
+                c = base + 0.5 * u * np.array([np.cos(ang), 0.3, np.sin(ang)]) + np.array([0, 2.0 + 0.8 * v, 0]) * min(u, 2) / 2
+                yaw = np.pi / 2 - a + 0.5 * u * (1 if v % 2 else -1)
+            q = se3_exp(np.array([0, 0, 0, 0, yaw, 0.0]))[3:]
+            poses.append(se3_inv(np.concatenate([c, q])))
+    return np.array(poses)
+
+
 # ----------------------------------------------------------------------------- BA problem
 @dataclasses.dataclass
 class BAProblem:
@@ -192,15 +240,18 @@ class BAProblem:
 
 def make_ba_problem(ii, jj, n_kf, ht=48, wd=64, seed=0, buffer=None, t0=1, t1=None,
                     pose_sigma=0.01, disp_sigma=0.05, pix_sigma=0.5, invalid_frac=0.0,
-                    sensor_frac=0.0, intr=None) -> BAProblem:
+                    sensor_frac=0.0, intr=None, poses_gt=None, disps_gt=None) -> BAProblem:
     rng = np.random.default_rng(seed)
     B = buffer or n_kf
     t1 = n_kf if t1 is None else t1
     intr = intrinsics_eighth((ht * 8, wd * 8)) if intr is None else np.asarray(intr, np.float32)
+    given_p, given_d = poses_gt, disps_gt
     poses_gt = np.tile(np.array([0, 0, 0, 0, 0, 0, 1.0]), (B, 1))
-    poses_gt[:n_kf] = helix_trajectory(n_kf, rng)
+    traj = helix_trajectory(n_kf, rng)                      # always drawn: the random stream does not depend on the options
+    poses_gt[:n_kf] = traj if given_p is None else np.asarray(given_p, np.float64)[:n_kf]
     disps_gt = np.ones((B, ht, wd))
-    disps_gt[:n_kf] = smooth_disps(n_kf, ht, wd, rng)
+    sm_d = smooth_disps(n_kf, ht, wd, rng)
+    disps_gt[:n_kf] = sm_d if given_d is None else np.asarray(given_d, np.float64)[:n_kf]
     if invalid_frac > 0:  # make some points land behind / too close to the target camera
         mask = rng.random((n_kf, ht, wd)) < invalid_frac
         disps_gt[:n_kf][mask] = 40.0

@@ -5,9 +5,11 @@ CPU restatement of the reference's edge selection, line by line in plain Python/
   * `__filter_repeated_edges` /root/reference/droid_slam/factor_graph.py:44-55
   * `add_neighborhood_factors` /root/reference/droid_slam/factor_graph.py:302-312
 The pairwise distances `d` come from `oracle.frame_distance` (pinned bit-exactly against the reference's CUDA
-kernel by tests/golden), averaged as depth_video.py:171-181 does.  Pinning of THIS file: the reference's function needs
-a live DepthVideo/CUDA extension, so it cannot be imported here; the restatement keeps its statement order and
-Python indexing semantics (negative flat indices wrap), and tests/test_oracle.py checks it on hand-worked cases.
+kernel by tests/golden), averaged as depth_video.py:171-181 does.  Pinning of THIS file: the reference's three methods
+are run UNMODIFIED (factor_graph.py imported under the lietorch shim, with a stub `video` whose `distance()` is that
+average) by tests/golden/make_pyref_graph_golden.py on the 8 cases of tests/graph_cases.py; the lists are committed as
+tests/golden/pyref_graph_edges.npz and tests/test_oracle.py asserts this restatement reproduces them element for element
+(tests/test_gpu_graph.py asserts the same of db200_proximity_edges).
 `torch.argsort` leaves the order of equal keys unspecified; a stable sort is used (lower flat index first).
 """
 import numpy as np

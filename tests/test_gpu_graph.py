@@ -7,23 +7,14 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _problem(n_kf, seed, ht=24, wd=32):
-    from droid_b200 import synth
-    ii, jj = synth.neighborhood_edges(0, n_kf, 2)
-    return synth.make_ba_problem(ii, jj, n_kf, ht=ht, wd=wd, seed=seed)
+import os
+import sys
 
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from graph_cases import CASES, case_inputs, filter_case, problem as _problem  # noqa: E402
 
-CASES = [
-    # n_kf, t0, t1, rad, nms, beta, thresh, max_factors, stereo, n_old
-    (40, 0, 0, 2, 2, 0.25, 16.0, 400, False, 0),          # global backend call (droid_backend.py)
-    (40, 0, 0, 2, 2, 0.25, 16.0, 400, True, 30),          # stereo + existing edges
-    (40, 35, 15, 2, 2, 0.25, 16.0, 96, False, 20),        # frontend call: t0 = t-5, t1 = t-25 (droid_frontend.py)
-    (33, 0, 0, 1, 0, 0.3, 12.3, 10_000, False, 0),        # nms = 0, threshold not representable in fp32
-    (33, 0, 0, 3, 3, 0.3, 40.0, 10_000, False, 0),        # nms = 3 (49 cells), everything below 100 px is a candidate
-    (33, 0, 0, 2, 2, 0.3, 16.0, 70, False, 0),            # max_factors hit by the neighbourhood edges alone
-    (20, 4, 9, 2, 1, 0.3, 30.0, 500, True, 5),            # t1 > t0: (i,i) and (i,j) cells with j < t1 wrap like d[-k]
-    (12, 12, 0, 2, 2, 0.3, 16.0, 100, False, 0),          # empty candidate rectangle
-]
+# edge lists produced by the reference's OWN factor_graph.py (tests/golden/make_pyref_graph_golden.py)
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pyref_graph_edges.npz"))
 
 
 @pytest.mark.parametrize("case", CASES)
@@ -32,10 +23,8 @@ def test_proximity_edges_equal_the_reference_list(case):
     from oracle import graph_edges as g
     from oracle import oracle
     n_kf, t0, t1, rad, nms, beta, thresh, max_factors, stereo, n_old = case
-    p = _problem(n_kf, 100 + n_kf + nms)
+    p, io, jo = case_inputs(case)
     t = n_kf
-    rng = np.random.default_rng(5)
-    io = rng.integers(0, t, n_old).astype(np.int64); jo = rng.integers(0, t, n_old).astype(np.int64)
     ii, jj, d = g.proximity_distance(oracle.frame_distance, p.poses, p.disps, p.intrinsics, t0, t1, t, beta)
     want = g.add_proximity_factors_edges(ii, jj, d, t0, t1, t, rad, nms, thresh, max_factors, stereo, io, jo)
     cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
@@ -43,6 +32,7 @@ def test_proximity_edges_equal_the_reference_list(case):
                                    stereo, cu(io) if n_old else None, cu(jo) if n_old else None)
     got = list(zip(gi.cpu().tolist(), gj.cpu().tolist()))
     assert got == want
+    assert got == [tuple(e) for e in GOLD[f"case{CASES.index(case)}_es"].tolist()]      # the reference's own list
     if case is CASES[0]:
         assert len(want) > 2 * (2 * t)          # the case does pick loop-closure edges, not only the neighbourhood
 
@@ -50,10 +40,9 @@ def test_proximity_edges_equal_the_reference_list(case):
 def test_filter_repeated_edges_and_neighborhood():
     from droid_b200 import graph
     from oracle import graph_edges as g
-    rng = np.random.default_rng(3)
-    ii, jj = rng.integers(0, 30, 500), rng.integers(0, 30, 500)
-    oi, oj = rng.integers(0, 30, 300), rng.integers(0, 30, 300)
+    ii, jj, oi, oj = filter_case()
     wi, wj = g.filter_repeated_edges(ii, jj, oi, oj)
+    assert wi.tolist() == GOLD["filter_ii"].tolist() and wj.tolist() == GOLD["filter_jj"].tolist()
     cu = lambda a: torch.from_numpy(np.ascontiguousarray(a).astype(np.int64)).cuda()
     gi, gj = graph.filter_repeated_edges(cu(ii), cu(jj), cu(oi), cu(oj))
     assert gi.cpu().tolist() == wi.tolist() and gj.cpu().tolist() == wj.tolist()

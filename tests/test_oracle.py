@@ -254,3 +254,27 @@ def test_reproject_oracle_matches_reference_projective_transform():
     sel = p.ii != 3
     np.testing.assert_array_equal(c2[sel & (p.jj != 3)], coords[sel & (p.jj != 3)])
     assert motn.shape == (len(p.ii), 4, 24, 32) and np.abs(motn).max() <= 64.0
+
+
+def test_edge_selection_oracle_equals_the_reference_factor_graph_lists():
+    """oracle/graph_edges.py against the lists produced by the reference's own `add_proximity_factors`,
+    `__filter_repeated_edges` and `add_neighborhood_factors` (factor_graph.py:44-55,302-379, run unmodified by
+    tests/golden/make_pyref_graph_golden.py): equal element for element on all 8 cases."""
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import graph_cases as GC
+    from oracle import graph_edges as g
+    from oracle import oracle
+    gold = np.load(os.path.join(REPO, "tests", "golden", "pyref_graph_edges.npz"))
+    for c, case in enumerate(GC.CASES):
+        n_kf, t0, t1, rad, nms, beta, thresh, max_factors, stereo, n_old = case
+        p, io, jo = GC.case_inputs(case)
+        ii, jj, d = g.proximity_distance(oracle.frame_distance, p.poses, p.disps, p.intrinsics, t0, t1, n_kf, beta)
+        es = g.add_proximity_factors_edges(ii, jj, d, t0, t1, n_kf, rad, nms, thresh, max_factors, stereo, io, jo)
+        assert es == [tuple(e) for e in gold[f"case{c}_es"].tolist()], c
+    assert len(gold["case0_es"]) > 4 * 40 and str(gold["case7_reference_raised"]) == "ValueError"   # empty list: the reference raises
+    ii, jj, oi, oj = GC.filter_case()
+    wi, wj = g.filter_repeated_edges(ii, jj, oi, oj)
+    assert wi.tolist() == gold["filter_ii"].tolist() and wj.tolist() == gold["filter_jj"].tolist()
+    for stereo in (False, True):
+        ni, nj = g.add_neighborhood_factors_edges(2, 11, 3, stereo)
+        assert np.stack([ni, nj], 1).tolist() == gold[f"nbr_stereo{int(stereo)}"].tolist()
