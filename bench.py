@@ -33,12 +33,40 @@ for _p in (REPO, os.path.join(REPO, "droid-slam_reserch_b200")):
 
 import numpy as np  # noqa: E402
 
-METRIC = "dense BA edge-iterations/s (global backend BA, 512 keyframes / ~6k edges, itrs=2 per call)"
 UNIT = "edge-iters/s"
 ITRS, LM, EP = 2, 1e-5, 1e-2          # factor_graph.py:297-298
-WORKLOAD = dict(workload="c3: stereo-EuRoC global backend BA", keyframes=512, edges_target=6000, ht=48, wd=64,
-                itrs_per_call=ITRS, lm=LM, ep=EP, t0=1)
 STAGES = ["graph", "edge_prep", "accumulate", "solve", "post", "backsub"]
+
+# BASELINE.json configs[2] (the one the metric is quoted on) and configs[3]; c3m is the round-1 graph (no stereo edges, no
+# sensor prior), kept for comparison with BENCH_r01.json
+WORKLOADS = {
+    "c3": dict(workload="c3: stereo-EuRoC global backend BA (512 keyframes, ~6k edges, 20 % of the frames with a stereo "
+                        "ii==jj edge, sensor-depth prior on 20 % of the pixels)", keyframes=512, edges_target=6000, ht=48, wd=64),
+    "c3m": dict(workload="c3m: mono global backend BA (512 keyframes, ~6k edges, no stereo edges, no sensor prior; the "
+                         "round-1 bench graph)", keyframes=512, edges_target=6000, ht=48, wd=64),
+    "c4": dict(workload="c4: multisession BackendAllMaps, 3 fused maps (1536 keyframes, ~20k edges incl. stereo and "
+                        "cross-map edges), maps loaded from reconstruction .npy folders by owner rank", keyframes=1536,
+               edges_target=20000, ht=48, wd=64),
+}
+
+
+def metric_name(wl):
+    w = WORKLOADS[wl]
+    return (f"dense BA edge-iterations/s ({'multisession' if wl == 'c4' else 'global'} backend BA, {w['keyframes']} keyframes / "
+            f"~{w['edges_target'] // 1000}k edges, itrs=2 per call)")
+
+
+def workload_config(wl):
+    return dict(WORKLOADS[wl], itrs_per_call=ITRS, lm=LM, ep=EP, t0=1)
+
+
+def make_problem(wl):
+    from droid_b200 import synth
+    if wl == "c3":
+        return synth.config_c3(stereo_frac=0.2, sensor_frac=0.2)
+    if wl == "c3m":
+        return synth.config_c3()
+    return synth.config_c4()
 
 
 def peaks():
@@ -69,9 +97,19 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([c.strip() for c in line.split(",")] + [time.perf_counter()])
 
-    def stop(self):
+    def wait_first(self, timeout=5.0):
+        """nvidia-smi needs a few hundred ms before its first row: a short timed region would end before it"""
+        t0 = time.perf_counter()
+        while self.proc is not None and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def mark(self):
+        return time.perf_counter()
+
+    def stop(self, t_begin=None, t_end=None):
+        """summary over the samples taken in [t_begin - 0.1 s, t_end + 0.1 s] (all samples when not given)"""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -81,7 +119,11 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
-        for r in self.rows:
+        rows = self.rows
+        if t_begin is not None and t_end is not None:
+            sel = [r for r in rows if t_begin - 0.1 <= r[-1] <= t_end + 0.1]
+            rows = sel if sel else rows          # a region shorter than the sampling period: fall back to the whole run under load
+        for r in rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
             except Exception:
@@ -96,16 +138,12 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------- CPU arm
-def cpu_sample_problem():
-    """Bounded sample of the c3 workload for the CPU arm: the same generator at 128 keyframes / ~1500 edges
-    (1/4 of c3; the scalar+OpenMP port needs ~7 s per Gauss-Newton iteration on 8 cores here)."""
-    from droid_b200 import synth
-    return synth.config_c3(n_kf=128, n_edges=1500), "c3 generator at 128 keyframes / ~1500 edges (1/4 of c3), itrs=2"
-
-
-def run_cpu(steps, warmup):
+def run_cpu(wl, steps, warmup):
+    """The reference's CPU path for this metric = oracle/oracle.cpp (OpenMP restatement of src/droid_kernels.cu ba_cuda,
+    fp32 kernels + fp64 solve) on the FULL workload — the same graph, maps and call as the GPU arm (a c3 call takes
+    ~10-20 s on 16 cores, a c4 call about a minute)."""
     from oracle import oracle
-    p, sample = cpu_sample_problem()
+    p = make_problem(wl)
     cores = oracle.num_threads()
     times = []
     for s in range(warmup + steps):
@@ -114,6 +152,7 @@ def run_cpu(steps, warmup):
         if s >= warmup:
             times.append(time.perf_counter() - t)
     tot = sum(times)
+    sample = f"the full {wl} workload ({p.n_edges} edges, {p.t1} keyframes), {len(times)} timed call(s) of itrs={ITRS}"
     return dict(value=p.n_edges * ITRS * len(times) / tot, unit=UNIT, cores=cores, kind="port", sample=sample,
                 ms_per_step=1e3 * tot / len(times), edges=p.n_edges)
 
@@ -124,15 +163,16 @@ def main_reference(args, rank):
     # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is the CPU path "with all the host threads it
     # can use", and only rank 0 runs it — restore the full core count before the OpenMP runtime of the oracle starts
     os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
-    steps, warmup = min(args.steps, 3), min(args.warmup, 1)
-    r = run_cpu(steps, warmup)
-    line = dict(impl="reference", metric=METRIC, value=r["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warmup,
-                ms_per_step=r["ms_per_step"], higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
-                data="synthetic", config=dict(WORKLOAD, sample=r["sample"], edges=r["edges"]),
+    cap = 1 if args.workload == "c4" else 3            # bounded: a c3 call is ~10-20 s of CPU work, a c4 call ~1 min
+    steps, warmup = max(1, min(args.steps, cap)), min(args.warmup, 1 if args.workload != "c4" else 0)
+    r = run_cpu(args.workload, steps, warmup)
+    line = dict(impl="reference", metric=metric_name(args.workload), value=r["value"], unit=UNIT, n_gpus=args.gpus, steps=steps,
+                warmup=warmup, ms_per_step=r["ms_per_step"], higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
+                data="synthetic", config=dict(workload_config(args.workload), sample=r["sample"], edges=r["edges"]),
                 cpu_baseline=dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"]),
                 e2e=dict(value=r["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 note="reference's CPU arm = oracle/oracle.cpp (OpenMP restatement of src/droid_kernels.cu ba_cuda, fp32 kernels + "
-                     "fp64 solve); steps capped at 3 (each ~15 s)")
+                     f"fp64 solve) on the full workload; steps capped at {cap} (each call is tens of seconds of CPU work)")
     emit(line)
 
 
@@ -152,7 +192,7 @@ def _load_ref_ext():
         return None
 
 
-def lookup_bench(dev, steps, warmup, hbm_peak):
+def lookup_bench(dev, steps, warmup, hbm_peak, world=1):
     """Secondary metric: fused 4-level radius-3 CorrBlock lookup on f16 volumes, 96 edges x 48x64 (c2 window).
     One lookup = one (edge, pixel) producing all 4x49 outputs; algorithmic bytes 912 B/lookup."""
     import torch
@@ -173,11 +213,11 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
         droid_backends.corr_pyramid_lookup(levels, coords, 3)
     ev[1].record()
     torch.cuda.synchronize()
-    ms = ev[0].elapsed_time(ev[1]) / steps
-    lookups = N * ht * wd
-    gbs = lookups * 912 / (ms * 1e-3) / 1e9
+    ms_loc = ev[0].elapsed_time(ev[1]) / steps
+    ms, lookups = _agg(dev, world, ms_loc, N * ht * wd)      # N > 1: every rank looks up its own 96 frontend edges (replicas)
+    gbs = (N * ht * wd) * 912 / (ms_loc * 1e-3) / 1e9       # roofline of THIS rank's kernel
     ref_ms = None
-    ref = _load_ref_ext()
+    ref = _load_ref_ext() if world == 1 else None
     if ref is not None:                      # CorrBlock.__call__ as the reference runs it: 4 launches + cat (corr.py:40-50)
         try:
             cl = [(coords / 2 ** l).contiguous() for l in range(4)]
@@ -190,10 +230,96 @@ def lookup_bench(dev, steps, warmup, hbm_peak):
             ref_ms = ev[0].elapsed_time(ev[1]) / 5
         except Exception:
             ref_ms = None
-    return dict(metric="corr lookups/s (fused 4-level r=3, f16 volumes, 96 edges x 48x64; volumes 2.4 GB > L2)",
+    return dict(metric="corr lookups/s, frontend path (CorrBlock: fused 4-level r=3 lookup on f16 volumes, 96 edges x 48x64 per GPU; "
+                       "volumes 2.4 GB > L2; N > 1 = one such window per rank, no collective)",
                 value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_launch=ms, reference_cuda_ms=ref_ms,
                 roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
-                              algorithmic_bytes_per_launch=lookups * 912))
+                              algorithmic_bytes_per_launch=N * ht * wd * 912))
+
+
+def _agg(dev, world, ms_local, units_local):
+    """(max over ranks of the time, sum over ranks of the units) — edge-parallel blocks have no collective of their own"""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return ms_local, units_local
+    t = torch.tensor([ms_local, -float(units_local)], device=dev, dtype=torch.float64)
+    mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    return float(mx[0].item()), -float(sm[1].item())
+
+
+def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
+    """The backend's lookup (FactorGraph.update_lowmem, factor_graph.py:261-290): one step = AltCorrBlock over ALL edges of
+    the workload in chunks of 8 source frames, exactly as the reference drives it — `corr_op(coords1[:, v], rig * iis,
+    rig * jjs + (iis == jjs))` on the stereo feature buffer fmaps[num, rig = 2, 128, ht, wd] (f16).  Edges are sharded by
+    source frame over the ranks (the BA partition); no collective.  One lookup = one (edge, pixel) with its 4 x 49 values."""
+    import torch
+    from droid_b200 import corr as mirror, dist as bdist, synth
+    n, rig = int(p.t1), 2
+    _, ht, wd = p.disps.shape
+    g = torch.Generator(device=dev); g.manual_seed(33)
+    fmaps = torch.randn((n, rig, 128, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    bounds = bdist.partition_frames(p.ii, p.jj, n, world)
+    sel = bdist.shard_edges(p.ii, bounds, rank)
+    ii_l, jj_l = p.ii[sel], p.jj[sel]
+    co, _ = synth.reproject(p.poses.astype(np.float64), p.disps.astype(np.float64), p.intrinsics, ii_l, jj_l)
+    coords1 = torch.from_numpy(np.nan_to_num(co, nan=0.0, posinf=1e4, neginf=-1e4).astype(np.float32)).to(dev)[None]
+    ii_t, jj_t = torch.from_numpy(ii_l).to(dev), torch.from_numpy(jj_l).to(dev)
+    chunks = []
+    for i in range(0, n, 8):
+        v = (ii_t >= i) & (ii_t < i + 8)
+        if bool(v.any()):
+            chunks.append(v)
+    op = mirror.AltCorrBlock(fmaps.view(1, n * rig, 128, ht, wd))
+
+    def step(o, which):
+        out = None
+        for v in which:
+            iis, jjs = ii_t[v], jj_t[v]
+            out = o(coords1[:, v], rig * iis, rig * jjs + (iis == jjs).long())
+        return out
+
+    for _ in range(warmup):
+        step(op, chunks)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        step(op, chunks)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_loc = e0.elapsed_time(e1) / steps
+    ms, lookups = _agg(dev, world, ms_loc, len(ii_l) * ht * wd)
+    edges = lookups / (ht * wd)
+    out = dict(metric="corr lookups/s, backend path (AltCorrBlock over all edges of the workload per step, chunks of 8 source "
+                      "frames, 4 levels r=3, f16 stereo feature buffer; edge-sharded, no collective)",
+               value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_step=ms, edges=int(edges), chunks_this_rank=len(chunks),
+               tflops_algorithmic=edges * 2 * 64 * 128 * 4 * ht * wd / (ms * 1e-3) / 1e12,
+               output_gbs=edges * 196 * ht * wd * 4 / (ms * 1e-3) / 1e9,
+               bound="tensor pipe / TMEM drain (2.4 MB written per edge is 2 ms per step at the HBM peak: not HBM bound)")
+    if world == 1:
+        try:                                              # the reference's own classes on the reference extension, same tensors
+            sys.path.insert(0, os.path.join(REPO, "tests"))
+            import dropin_cases as D
+            ref_ext = D.load_reference_ext()
+            ref_corr = D.load_reference_corr(ref_ext, "ref_corr_bench") if ref_ext is not None else None
+            if ref_corr is not None:
+                rop = ref_corr.AltCorrBlock(fmaps.view(1, n * rig, 128, ht, wd))
+                sub = chunks[:4]
+                step(rop, sub); torch.cuda.synchronize()
+                e0.record(); step(rop, sub); e1.record(); torch.cuda.synchronize()
+                sub_edges = int(sum(int(v.sum()) for v in sub))
+                ref_ms = e0.elapsed_time(e1) * len(ii_l) / sub_edges
+                out["reference_cuda_ms_per_step"] = ref_ms
+                out["reference_cuda_note"] = (f"unmodified modules/corr.py AltCorrBlock on the reference extension, measured on the first "
+                                              f"{len(sub)} chunks ({sub_edges} edges) and scaled to all {len(ii_l)} edges")
+        except Exception as ex:
+            out["reference_cuda_ms_per_step"] = None
+            out["reference_cuda_error"] = f"{type(ex).__name__}: {ex}"[:200]
+    del fmaps, op, coords1
+    torch.cuda.empty_cache()
+    return out
 
 
 def training_bench(dev, steps=10, warmup=3):
@@ -466,10 +592,37 @@ def main_gpu(args, rank, world):
     lib = _capi.lib()
     hbm_peak, peak_src = peaks()
 
-    p = synth.config_c3()
+    wl = args.workload
+    p = make_problem(wl)
     N, HW, M, P = p.n_edges, p.disps.shape[1] * p.disps.shape[2], p.eta.shape[0], p.t1 - p.t0
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    poses0, disps0 = t(p.poses), t(p.disps)
+    maps_note = None
+    if wl == "c4":
+        # BackendAllMaps.py:43-61,101-138: the three maps come from reconstruction folders on disk.  Rank 0 writes them in the
+        # reference's format (droid.py:92-106), every rank loads the replicated arrays whole and the disparity maps of the
+        # keyframes it OWNS only (droid_b200/maps.py); rows it does not own stay zero and are never read by its kernels.
+        import tempfile
+        from droid_b200 import dist as bdist, maps
+        root = os.path.join(tempfile.gettempdir(), "db200_bench_c4_maps")
+        kf = p.t1 // 3
+        if rank == 0:
+            for m in range(3):
+                sl = slice(m * kf, (m + 1) * kf)
+                maps.save_reconstruction(os.path.join(root, f"map{m + 1}"), tstamps=np.arange(kf, dtype=np.float64), poses=p.poses[sl],
+                                         disps=p.disps[sl], intrinsics=np.tile(p.intrinsics, (kf, 1)))
+        if world > 1:
+            dist.barrier()
+        lo, hi = (0, p.t1) if world == 1 else maps.owned_range_for_rank(p.ii, p.jj, p.disps.shape[0], rank, world)
+        got = maps.load_maps(root, every=1, own_lo=lo, own_hi=hi, device=dev, names=("tstamps", "poses", "intrinsics", "disps"))
+        poses0 = got["poses"].float().contiguous()
+        disps0 = torch.zeros(p.disps.shape, dtype=torch.float32, device=dev)
+        disps0[lo:hi] = got["disps"]
+        if world > 1:                                   # the benchmark resets disps from disps0 every step: assemble it once
+            dist.all_reduce(disps0)
+        assert torch.equal(poses0.cpu(), torch.from_numpy(p.poses)) and torch.equal(disps0.cpu(), torch.from_numpy(p.disps))
+        maps_note = f"maps loaded from {root} (3 folders, .npy, heavy arrays by owner: rank {rank} frames [{lo},{hi}))"
+    else:
+        poses0, disps0 = t(p.poses), t(p.disps)
     intr, sens = t(p.intrinsics), t(p.disps_sens)
 
     if world == 1:
@@ -497,14 +650,32 @@ def main_gpu(args, rank, world):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-
-    # ---- timed region: device-resident inputs
+    parity = None
+    if world > 1:
+        dx_sh, dz_sh = step()
+        dx_sh = dx_sh.clone()
+        if rank == 0:                                   # one un-timed single-GPU call on the full graph for comparison
+            po1, di1 = poses0.clone(), disps0.clone()
+            tg1, wg1 = t(p.target), t(p.weight)
+            dx1, dz1 = droid_backends.ba(po1, di1, intr, sens, tg1, wg1, eta, t(p.ii), t(p.jj), p.t0, p.t1, ITRS, LM, EP, False)
+            rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm())
+            parity = dict(dx_rel_vs_single=rel(dx_sh, dx1), dz_rel_vs_single=rel(dz_sh, dz1),
+                          poses_maxabs_vs_single=float((poses - po1).abs().max()), disps_rel_vs_single=rel(disps, di1),
+                          note="edge-sharded call against droid_backends.ba on one GPU, same inputs; the difference is the fp32 "
+                               "regrouping of the per-frame sums (test tolerance 3e-4, tests/test_gpu_dist.py)")
+            del tg1, wg1, po1, di1
+            torch.cuda.empty_cache()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    if rank == 0:
+        sampler.wait_first()
+
+    # ---- timed region: device-resident inputs
+    t_clk0 = sampler.mark()
     lib.db200_profile_enable(1)
     l0 = lib.db200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -519,7 +690,7 @@ def main_gpu(args, rank, world):
     st_ms = (C.c_double * len(STAGES))(); st_n = (C.c_int * len(STAGES))()
     lib.db200_profile_collect(st_ms, st_n)
     lib.db200_profile_enable(0)
-    clocks = sampler.stop() if rank == 0 else None
+    t_clk1 = sampler.mark()
     if world > 1:
         tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -578,6 +749,21 @@ def main_gpu(args, rank, world):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms_e2e = float(tt.item())
     e2e_value = N * ITRS * e2e_steps / (ms_e2e * 1e-3)
+    # sampled from before the warm-up to here (nvidia-smi, 100 ms period); the summary prefers the samples inside the
+    # device-resident timed region and falls back to the whole loaded interval when that region is shorter than a period
+    clocks = sampler.stop(t_clk0, t_clk1) if rank == 0 else None
+
+    # ---- edge-parallel secondary blocks: every rank works on its share (no collective inside the timed loops)
+    n_loc = int(target.shape[0])
+    del staged, h_in
+    if not args.ba_only:
+        del target, weight
+        torch.cuda.empty_cache()
+    blocks = {}
+    if not args.ba_only:
+        blocks["altcorr"] = altcorr_bench(p, dev, rank, world)
+        if wl != "c4":
+            blocks["lookup"] = lookup_bench(dev, 20, 3, hbm_peak, world)
 
     if rank != 0:
         if world > 1:
@@ -585,7 +771,6 @@ def main_gpu(args, rank, world):
         return
 
     # ---- roofline of the dominant HBM-bound kernel (accumulate): algorithmic bytes per launch / measured launch time
-    n_loc = int(target.shape[0])
     m_loc = M if world == 1 else runner.n_local_frames
     accum_bytes = 16 * HW * n_loc + 20 * HW * m_loc          # target+weight per edge-pixel; disp,eta,sens in + Q,w out per frame-pixel
     stage = {STAGES[i]: dict(ms_per_iter=(st_ms[i] / st_n[i]) if st_n[i] else None, intervals=int(st_n[i])) for i in range(len(STAGES))}
@@ -604,9 +789,13 @@ def main_gpu(args, rank, world):
     sol_ms = stage["solve"]["ms_per_iter"]
     n_sys = 6 * P
     sol_flops = n_sys ** 3 / 3.0 + 2.0 * n_sys ** 2
+    fp64_peak = float(lib.db200_debug_fp64_peak_gflops(C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    if not fp64_peak > 0:
+        fp64_peak = None
     roofline["solver"] = dict(kernel="chol_solve_kernel (cooperative tiled fp64 Cholesky, trailing updates on DMMA + both substitutions)", bound="fp64 pipe / panel-chain latency",
-                              gflops=(sol_flops / (sol_ms * 1e-3) / 1e9) if sol_ms else None, peak_gflops=37200.0,
-                              frac=(sol_flops / (sol_ms * 1e-3) / 1e9 / 37200.0) if sol_ms else None, ms_per_launch=sol_ms,
+                              gflops=(sol_flops / (sol_ms * 1e-3) / 1e9) if sol_ms else None, peak_gflops=fp64_peak,
+                              peak_source="measured in this run: register-only mma.sync.m8n8k4.f64 (DMMA), db200_debug_fp64_peak_gflops",
+                              frac=(sol_flops / (sol_ms * 1e-3) / 1e9 / fp64_peak) if (sol_ms and fp64_peak) else None, ms_per_launch=sol_ms,
                               share_of_iteration=(sol_ms / iter_ms) if sol_ms else None)
     traffic_file = os.path.join(REPO, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
@@ -615,22 +804,26 @@ def main_gpu(args, rank, world):
         except Exception:
             pass
 
-    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+    line = dict(metric=metric_name(wl), value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32 (fp64 reduced system + solve)",
                 data="synthetic",
-                config=dict(WORKLOAD, edges=N, depth_maps=M, poses=P, parallelism=f"edge-shard x{world}" if world > 1 else "single",
-                            l2="inputs (295 MB of target/weight per iteration) larger than the 126 MB L2; no explicit flush"),
+                config=dict(workload_config(wl), edges=N, depth_maps=M, poses=P, parallelism=f"edge-shard x{world}" if world > 1 else "single",
+                            stereo_edges=int((p.ii == p.jj).sum()), sensor_prior_pixels=float((p.disps_sens > 0).mean()),
+                            timed_step="poses/disps reset from device copies (2 small D2D copies) + one droid_backends.ba call",
+                            l2=f"inputs ({16 * HW * N / 1e6:.0f} MB of target/weight per iteration) larger than the 126 MB L2; no explicit flush"),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, steps=e2e_steps,
                          ms_per_step=ms_e2e / e2e_steps,
                          staging="double-buffered: upload of step k+1 (copy stream) overlaps the kernels of step k; "
                                  "result of every step read back and synchronised"),
                 gpu_launches=int(launches), roofline=roofline, stages=stage, clocks=clocks)
-    if world == 1:
-        line["lookup"] = lookup_bench(dev, 20, 3, hbm_peak)
+    if parity is not None:
+        line["parity"] = parity
+    if maps_note:
+        line["config"]["maps"] = maps_note
+    line.update(blocks)
+    if world == 1 and not args.ba_only and wl != "c4":
         line["corr_volume"] = volume_bench(dev, 10, 3, hbm_peak)
         line["graph"] = graph_bench(p, dev)
-        del target, weight
-        torch.cuda.empty_cache()
         line["training_shapes"] = training_bench(dev)
         line["frontend"] = frontend_bench(dev)
         try:
@@ -642,12 +835,12 @@ def main_gpu(args, rank, world):
             line["lookup"]["roofline"]["dram_frac_actual_traffic"] = line["lookup"]["roofline"]["dram_gbs_actual_traffic"] / hbm_peak
         except Exception:
             pass
-        if not args.no_cpu:
-            rc = reference_cuda_leg(p, dev)
-            if rc is not None:
-                line["reference_cuda"] = rc
-            r = run_cpu(1, 0)
-            line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"])
+    if world == 1 and not args.no_cpu:
+        rc = reference_cuda_leg(p, dev, steps=1 if wl == "c4" else 3)
+        if rc is not None:
+            line["reference_cuda"] = rc
+        r = run_cpu(wl, 1, 0)
+        line["cpu_baseline"] = dict(value=r["value"], unit=UNIT, cores=r["cores"], kind=r["kind"], sample=r["sample"])
     emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -682,6 +875,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS), help="c3 = BASELINE configs[2] (default), c4 = configs[3]")
+    ap.add_argument("--ba-only", action="store_true", help="skip the secondary blocks (lookups, volume build, graph, training shapes)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -420,6 +420,7 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
 // fused Schur accumulation on the tensor cores (non-motion BA)
 constexpr int kChunk = 64;                 // pixels per chunk
 constexpr int kStride = kChunk + 4;        // stash row stride (floats): 4*row + col -> conflict-free MMA fragment loads
+constexpr int kCwStride = kChunk + 4;      // Cw row stride: the 4 lanes of a pixel read edges q, q+1, q+2, q+3 -> banks 8 apart
 
 __host__ __device__ inline int schur_rows(int d) { return 6 * d + 1; }                    // E rows + the sqrt(Q) w row
 __host__ __device__ inline int schur_rpad(int d) { return (schur_rows(d) + 15) / 16 * 16; }
@@ -457,7 +458,7 @@ __host__ __device__ inline size_t schur_stage_floats(int necap) {
 }
 __host__ __device__ inline size_t schur_smem_bytes(int dcap, int necap) {
   size_t b = sizeof(double) * size_t(dcap > 0 ? dcap : 1) * 42;
-  b += sizeof(float) * (schur_alias_floats(dcap) + schur_stage_floats(necap) + size_t(necap) * 2 * kChunk + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
+  b += sizeof(float) * (schur_alias_floats(dcap) + schur_stage_floats(necap) + size_t(necap) * 2 * kCwStride + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
   b += sizeof(int) * (size_t(2) * (dcap > 0 ? dcap : 1) + 2 * size_t(necap));
   b += 4 * size_t(schur_segs(dcap) + 8);
   return (b + 15) / 16 * 16;
@@ -473,7 +474,7 @@ __device__ __forceinline__ SchurSmem schur_carve(unsigned char* base, int dcap, 
   s.stage = s.shi + schur_alias_floats(dcap);
   s.red = s.stage;
   s.Cw = s.stage + schur_stage_floats(necap);
-  s.px = s.Cw + size_t(necap) * 2 * kChunk;
+  s.px = s.Cw + size_t(necap) * 2 * kCwStride;
   s.Am = s.px + 7 * kChunk;
   s.Hs = s.Am + size_t(dc) * 36;
   s.jp = reinterpret_cast<int*>(s.Hs + size_t(dc) * 27);
@@ -706,8 +707,8 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
         PixEdge pe_;
         pix_edge(rec, sm.px[pp], sm.px[kChunk + pp], sm.px[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
         if (!HD) {
-          sm.Cw[(size_t(e) * 2 + 0) * kChunk + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
-          sm.Cw[(size_t(e) * 2 + 1) * kChunk + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
+          sm.Cw[(size_t(e) * 2 + 0) * kCwStride + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
+          sm.Cw[(size_t(e) * 2 + 1) * kCwStride + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
         }
         if (sl >= 0) {                                                         // stereo edges: depth terms only
           const float au = pe_.wu * pe_.Jzu, av = pe_.wv * pe_.Jzv;
@@ -740,7 +741,7 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
       const int pix = base + pp;
       float Csum = 0.0f, wsum = 0.0f;
       if (!HD) {
-        for (int q = part; q < ne; q += 4) { Csum += sm.Cw[(size_t(q) * 2) * kChunk + pp]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kChunk + pp]; }
+        for (int q = part; q < ne; q += 4) { Csum += sm.Cw[(size_t(q) * 2) * kCwStride + pp]; wsum += sm.Cw[(size_t(q) * 2 + 1) * kCwStride + pp]; }
         Csum += __shfl_xor_sync(0xffffffffu, Csum, 1); wsum += __shfl_xor_sync(0xffffffffu, wsum, 1);
         Csum += __shfl_xor_sync(0xffffffffu, Csum, 2); wsum += __shfl_xor_sync(0xffffffffu, wsum, 2);
       }

@@ -24,6 +24,7 @@ _SIGNATURES = {
     "db200_profile_enable": (None, [_i]),
     "db200_profile_collect": (_i, [C.POINTER(C.c_double), C.POINTER(_i)]),
     "db200_debug_chol_trace": (_i, [_vp]),
+    "db200_debug_fp64_peak_gflops": (C.c_double, [_vp]),
     "db200_corr_index_forward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_corr_index_backward": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_corr_pyramid_lookup": (_i, [C.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

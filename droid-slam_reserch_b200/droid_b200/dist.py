@@ -65,6 +65,47 @@ def local_depth_rows(ii_all, ii_local, t0: int, t1: int):
     return kx_all, kx_loc, rows
 
 
+def system_pattern(ii, jj, t0: int, t1: int) -> np.ndarray:
+    """Flat indices into the packed reduced system [H (lower triangle, row by row) | b] of every entry the graph can make
+    non-zero: the 6x6 blocks (a, b), a >= b, of all pose pairs that share a depth map — source frame i couples the poses
+    {i} U {j_e : edges i -> j_e} (droid_kernels.cu:1244-1272, 1376-1383) — restricted to the optimised poses [t0, t1), plus b.
+    Sorted ascending.  At BASELINE config 3 this is about a third of the dense triangle; the all-reduce of an iteration moves
+    only these entries (everything else is zero on every rank)."""
+    ii = np.asarray(ii, np.int64); jj = np.asarray(jj, np.int64)
+    P = int(t1) - int(t0)
+    n = 6 * P
+    order = np.argsort(ii, kind="stable")
+    si, sj = ii[order], jj[order]
+    starts = np.flatnonzero(np.concatenate([[True], si[1:] != si[:-1]])) if len(si) else np.zeros(0, np.int64)
+    ends = np.concatenate([starts[1:], [len(si)]]) if len(si) else starts
+    blocks = set()
+    for a, b in zip(starts.tolist(), ends.tolist()):
+        fr = np.unique(np.concatenate([[si[a]], sj[a:b]])) - t0
+        fr = fr[(fr >= 0) & (fr < P)]
+        if fr.size:
+            hi, lo = np.meshgrid(fr, fr, indexing="ij")
+            m = hi >= lo
+            blocks.update((hi[m] * P + lo[m]).tolist())
+    blk = np.fromiter(blocks, np.int64, len(blocks)) if blocks else np.zeros(0, np.int64)
+    ba, bb = blk // max(P, 1), blk % max(P, 1)
+    r = (6 * ba)[:, None, None] + np.arange(6)[None, :, None]           # rows of the block
+    c = (6 * bb)[:, None, None] + np.arange(6)[None, None, :]
+    keep = (r >= c)                                                     # diagonal blocks: their lower triangle only
+    flat = (r * (r + 1) // 2 + c)[np.broadcast_to(keep, np.broadcast_shapes(r.shape, c.shape))]
+    rhs = n * (n + 1) // 2 + np.arange(n, dtype=np.int64)
+    return np.sort(np.concatenate([flat.reshape(-1), rhs])).astype(np.int64)
+
+
+def allreduce_system_sparse(Hb: torch.Tensor, idx: torch.Tensor, group=None) -> torch.Tensor:
+    """all-reduce of the entries `idx` of the packed system only (gather -> all_reduce -> scatter back); the rest of Hb is
+    zero on every rank (db200_ba_accumulate clears it) and stays untouched."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        compact = Hb.index_select(0, idx)
+        dist.all_reduce(compact, op=dist.ReduceOp.SUM, group=group)
+        Hb.index_copy_(0, idx, compact)
+    return Hb
+
+
 def allreduce_system(Hb: torch.Tensor, group=None) -> torch.Tensor:
     """Sum of the per-rank partial reduced systems, in place (fp64, lower triangle of H packed + b: n(n+1)/2 + n values).  NCCL on GPU tensors
     (NVLink 5 / NVSwitch, in-switch reduction when available), gloo on CPU tensors."""
@@ -138,6 +179,18 @@ class ShardedBA:
         self._dz_src = torch.from_numpy(np.nonzero(own)[0]).to(device)
         self._dz_dst = torch.from_numpy(self.eta_rows[own]).to(device)
         self._ws = None
+        # exchange pattern of the reduced system (host-side, once per graph): used when it is clearly smaller than the triangle
+        n = 6 * (self.t1 - self.t0)
+        pat = system_pattern(ii, jj, self.t0, self.t1) if world > 1 else None
+        self.pattern_frac = (len(pat) / float(n * (n + 1) // 2 + n)) if pat is not None else 1.0
+        self._pattern = torch.from_numpy(pat).to(device) if (pat is not None and self.pattern_frac < 0.6) else None
+
+    def exchange(self):
+        """the ONE exchange of an iteration: sum of the partial reduced systems over the ranks"""
+        if self._pattern is not None:
+            allreduce_system_sparse(self.system, self._pattern, self.group)
+        else:
+            allreduce_system(self.system, self.group)
 
     # ---- one call = begin -> (accumulate -> all-reduce of .system -> solve_update) x iterations -> finish
     def begin(self, poses, disps, intrinsics, disps_sens, target, weight, eta, lm, ep, motion_only=False):
@@ -202,17 +255,26 @@ class ShardedBA:
         self.begin(poses, disps, intrinsics, disps_sens, target, weight, eta, lm, ep, motion_only)
         for it in range(int(iterations)):
             self.accumulate(it == 0)
-            allreduce_system(self.system, self.group)
+            self.exchange()
             self.solve_update(it == iterations - 1)
         if motion_only:
             return [self._dx, None]
-        assemble_rows(disps, self.own_lo, self._call["own_hi"], self.group)
-        dz = torch.zeros((len(self.kx_all), self._call["ht"] * self._call["wd"]), dtype=torch.float32, device=self.device)
+        # after the last iteration every rank owns rows of disps and of dz: ONE all-reduce of a row-masked [disps | dz] buffer
+        # assembles both (12 KB per keyframe each)
+        hw = self._call["ht"] * self._call["wd"]
+        B, M = disps.shape[0], len(self.kx_all)
+        lo, hi = self.own_lo, self._call["own_hi"]
         dst, val = self.local_dz_rows()
-        dz.index_copy_(0, dst, val)
-        if self.world > 1 and dist.is_initialized():
-            dist.all_reduce(dz, op=dist.ReduceOp.SUM, group=self.group)
-        return [self._dx, dz]
+        if not (self.world > 1 and dist.is_initialized()):
+            dz = torch.zeros((M, hw), dtype=torch.float32, device=self.device)
+            dz.index_copy_(0, dst, val)
+            return [self._dx, dz]
+        buf = torch.zeros((B + M, hw), dtype=torch.float32, device=self.device)
+        buf[lo:hi] = disps[lo:hi].reshape(hi - lo, hw)
+        buf[B:].index_copy_(0, dst, val)
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
+        disps.copy_(buf[:B].view_as(disps))
+        return [self._dx, buf[B:]]
 
     def status(self):
         from . import _capi

@@ -49,6 +49,9 @@ const char* db200_last_cuda_error(void); /* text of the last CUDA error the libr
 long long db200_launch_count(void);
 void db200_profile_enable(int on);
 int db200_profile_collect(double* ms_out, int* count_out);
+/* FP64 rate (GFLOP/s) of mma.sync.m8n8k4.f64 (DMMA), register-only, measured now on the current device: the denominator
+ * bench.py reports the solver against.  Synchronises; allocates a small sink (debug/bench use only). */
+double db200_debug_fp64_peak_gflops(db200_stream_t stream);
 /* debug timeline of the Cholesky panel chain: device buffer of 8*(2*nt) int64 (globaltimer ns), NULL = off */
 int db200_debug_chol_trace(long long* device_buffer);
 

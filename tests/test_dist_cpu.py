@@ -66,6 +66,13 @@ def _worker(rank, world, port, q):
         part = oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target[sel], p.weight[sel], p.eta[rows],
                          p.ii[sel], p.jj[sel], p.t0, p.t1, 1, 1e-5, 1e-2, dump_system=True)
         Hb = torch.from_numpy(np.concatenate([part["H"].reshape(-1), part["b"]]))
+        # the product's packed layout (lower triangle row by row, then b), exchanged through the graph's block pattern only
+        packed = torch.from_numpy(np.concatenate([part["H"][np.tril_indices(n)], part["b"]]))
+        pat = bdist.system_pattern(p.ii, p.jj, p.t0, p.t1)
+        assert np.isin(np.flatnonzero(packed.numpy()), pat).all()        # every partial non-zero lies inside the pattern
+        sparse = bdist.allreduce_system_sparse(packed.clone(), torch.from_numpy(pat))
+        dense = bdist.allreduce_system(packed.clone())
+        assert torch.equal(sparse, dense) and len(pat) < 0.8 * packed.numel()
         bdist.allreduce_system(Hb)
         # owned disparity rows assembled on every rank
         d = torch.from_numpy(part["disps"].copy())
@@ -146,3 +153,23 @@ def test_gloo_world2_frame_distance_pairs_are_split_and_gathered():
     for rank, d, calls in res:
         np.testing.assert_array_equal(d.view(np.uint32), want.view(np.uint32))      # bit-exact, in pair order, on every rank
     assert res[0][2] == [70] and res[1][2] == [69]
+
+
+def test_system_pattern_is_exactly_the_nonzero_set_of_the_reduced_system():
+    """droid_b200.dist.system_pattern against the oracle's dumped [H | b] (droid_kernels.cu:1244-1272, 1376-1383): with stereo
+    edges, a fixed first pose range (t0 = 2) and a buffer longer than t1"""
+    from oracle import oracle
+    rng = np.random.default_rng(3)
+    ii, jj = synth.backend_edges(30, 200, rng, rad=2, stereo_frac=0.2)
+    p = synth.make_ba_problem(ii, jj, 30, ht=16, wd=24, seed=4, t0=2, buffer=34)
+    r = oracle.ba(p.poses, p.disps, p.intrinsics, p.disps_sens, p.target, p.weight, p.eta, p.ii, p.jj, p.t0, p.t1, 1, 1e-4, .1,
+                  dump_system=True)
+    n = r["H"].shape[0]
+    flat = np.concatenate([r["H"][np.tril_indices(n)], r["b"]])
+    pat = bdist.system_pattern(p.ii, p.jj, p.t0, p.t1)
+    assert np.all(np.diff(pat) > 0) and pat[-1] == len(flat) - 1
+    assert np.array_equal(np.flatnonzero(flat), pat)
+    # a backend graph at BASELINE config 3 size: a small fraction of the dense triangle
+    ii, jj = synth.backend_edges(512, 6000, np.random.default_rng(1237), rad=2, stereo_frac=0.2)
+    pat = bdist.system_pattern(ii, jj, 1, 512)
+    assert len(pat) < 0.25 * (3066 * 3067 // 2 + 3066)

@@ -54,4 +54,19 @@ if "fd" in what:
     for _ in range(2):
         droid_backends.frame_distance(t(p.poses), t(p.disps), t(p.intrinsics), ii.reshape(-1).to(dev), jj.reshape(-1).to(dev), 0.25)
     torch.cuda.synchronize()
+
+if "altcorr" in what:       # BASELINE config-5 shape: 88 edges, fp32 operands, all four levels through the nine-name API
+    N, C_, ht, wd = 88, 128, 48, 64
+    g = torch.Generator(device=dev); g.manual_seed(21)
+    f1 = torch.randn((N, ht, wd, C_), device=dev, generator=g)
+    pyr = [torch.randn((N, ht >> l, wd >> l, C_), device=dev, generator=g) for l in range(4)]
+    yy, xx = torch.meshgrid(torch.arange(ht, device=dev, dtype=torch.float32), torch.arange(wd, device=dev, dtype=torch.float32), indexing="ij")
+    co = (torch.stack([xx, yy], -1)[None, None].repeat(N, 1, 1, 1, 1) + 4.0 * torch.randn((N, 1, ht, wd, 2), device=dev, generator=g)).contiguous()
+    ga = torch.randn((N, 1, 49, ht, wd), device=dev, generator=g)
+    for _ in range(2):
+        for l in range(4):
+            droid_backends.altcorr_forward(f1, pyr[l], (co / 2 ** l).contiguous(), 3)
+        droid_backends.altcorr_backward(f1, pyr[0], co, ga, 3)
+    torch.cuda.synchronize()
+    print("prof_run altcorr done")
 print("prof_run ok", what)
