@@ -256,6 +256,8 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
     source frame over the ranks (the BA partition); no collective.  One lookup = one (edge, pixel) with its 4 x 49 values."""
     import torch
     from droid_b200 import corr as mirror, dist as bdist, synth
+    if os.path.join(REPO, "tests") not in sys.path:
+        sys.path.insert(0, os.path.join(REPO, "tests"))
     n, rig = int(p.t1), 2
     _, ht, wd = p.disps.shape
     g = torch.Generator(device=dev); g.manual_seed(33)
@@ -292,12 +294,37 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
     ms_loc = e0.elapsed_time(e1) / steps
     ms, lookups = _agg(dev, world, ms_loc, len(ii_l) * ht * wd)
     edges = lookups / (ht * wd)
+    # how many (pixel tile x target cell) GEMMs the kernel needed: a property of the coordinates (one un-timed, counted step)
+    import droid_backends
+    droid_backends.COUNT_CELLS = dict(cells=0, tile_levels=0)
+    step(op, chunks)
+    cnt, droid_backends.COUNT_CELLS = droid_backends.COUNT_CELLS, None
+    # the same step on a smooth flow field (affine warp + 1.5 px noise per edge): what co-visible frames of a real map give;
+    # the synthetic graph's long-range "loop closures" are not co-visible and scatter the windows of a tile over many cells
+    import dropin_cases as D
+    coords_w = coords1
+    coords1 = torch.from_numpy(D.smooth_coords(np.random.default_rng(5), len(ii_l), ht, wd, wild=0.0)).to(dev)[None]
+    step(op, chunks)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        step(op, chunks)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_s, _ = _agg(dev, world, e0.elapsed_time(e1) / steps, 0)
+    droid_backends.COUNT_CELLS = dict(cells=0, tile_levels=0)
+    step(op, chunks)
+    cnt_s, droid_backends.COUNT_CELLS = droid_backends.COUNT_CELLS, None
+    coords1 = coords_w
     out = dict(metric="corr lookups/s, backend path (AltCorrBlock over all edges of the workload per step, chunks of 8 source "
                       "frames, 4 levels r=3, f16 stereo feature buffer; edge-sharded, no collective)",
                value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_step=ms, edges=int(edges), chunks_this_rank=len(chunks),
                tflops_algorithmic=edges * 2 * 64 * 128 * 4 * ht * wd / (ms * 1e-3) / 1e12,
                output_gbs=edges * 196 * ht * wd * 4 / (ms * 1e-3) / 1e9,
-               bound="tensor pipe / TMEM drain (2.4 MB written per edge is 2 ms per step at the HBM peak: not HBM bound)")
+               bound="tensor pipe / TMEM drain (2.4 MB written per edge is 2 ms per step at the HBM peak: not HBM bound)",
+               cells_per_tile_level=cnt["cells"] / max(cnt["tile_levels"], 1),
+               smooth_flow=dict(ms_per_step=ms_s, value=lookups / (ms_s * 1e-3), cells_per_tile_level=cnt_s["cells"] / max(cnt_s["tile_levels"], 1),
+                                what="same edges, coordinates = affine warp + 1.5 px noise (co-visible frames)"))
     if world == 1:
         try:                                              # the reference's own classes on the reference extension, same tensors
             sys.path.insert(0, os.path.join(REPO, "tests"))

@@ -13,15 +13,17 @@
 // bounding corner of the tile's windows + a 64-bit mask of 8x8 cells relative to it); arbitrary coordinates just touch
 // more cells, so there is no "fast path only for smooth flow" — results are the reference's for any input.
 //
-// One persistent CTA per SM, 10 warps:
+// One persistent CTA per SM, 18 warps:
 //   warp 0      producer: reads the tile's coordinates, computes per level the cell origin + mask (warp reductions),
 //               publishes them, then feeds the A tile (128 pixels x 128 channels, TMA 4-D box, 128B swizzle) and a ring
 //               of B cells (TMA zero-fills positions outside the image = the reference's `within_bounds` skip);
 //   warp 1      one thread issues 8 (x3 when operands carry lo parts) tcgen05.mma M=128,N=128,K=16 per cell into one of
 //               FOUR 128-column TMEM accumulators; tcgen05.commit hands stages back / accumulators on;
-//   warps 2..9  epilogue: tcgen05.ld of their TMEM lane quarter (two warps per quarter, 64 columns each), scatter of the
-//               taps that belong to the thread's pixel into the per-level tap buffer D[64 taps][128 pixels] (conflict-free),
-//               and per level the bilinear combination + 49 coalesced channel rows to HBM.
+//   warps 2..17 epilogue (the bottleneck: the tensor pipe is < 20 % busy): four warps per TMEM lane quarter, each reads ONE
+//               32-column chunk (2 cell rows) with tcgen05.ld — skipped when no lane has a window row there — and scatters
+//               the taps that belong to its lane's pixel into the tap buffer D[64 taps][128 pixels] (conflict-free); per level
+//               the four warps of a pixel meet at a 128-thread named barrier, combine bilinearly (out-of-image taps are
+//               selected to zero by per-thread row/column masks: D is never cleared) and store 49 coalesced channel rows.
 // All 4 pyramid levels of a tile are done by the same CTA (the A tile is loaded once per tile).
 //
 // Precision: operands are fp16.  The fused AltCorrBlock path feeds the fp16 feature pyramid directly (the reference casts
@@ -38,14 +40,21 @@ namespace db200 {
 constexpr int kATPy = 8, kATPx = 16;                   // pixel tile
 constexpr int kATCy = 8, kATCx = 16;                   // fmap2 cell
 constexpr int kATMaxL = 4;
-constexpr int kATEpiWarps = 8;
-constexpr int kATThreads = 64 + 32 * kATEpiWarps;      // 320
+constexpr int kATEpiWarps = 16;                      // 4 per TMEM lane quarter: one 32-column chunk (2 cell rows) each
+constexpr int kATThreads = 64 + 32 * kATEpiWarps;      // 576
 constexpr uint32_t kATBlk = 128 * 64 * 2;              // one [128 rows][64 halfs] swizzled block: 16 KB
 constexpr uint32_t kATARegion = 4 * kATBlk;            // 64 KB: one hi+lo A tile, or two hi-only A tiles
 constexpr uint32_t kATBRegion = 8 * kATBlk;            // 128 KB: two hi+lo cells, or four hi-only cells
 constexpr uint32_t kATDBytes = 64 * 128 * 4;           // 32 KB tap buffer
 constexpr size_t kATSmem = kATARegion + kATBRegion + kATDBytes + 1024;
 constexpr uint32_t kATIdesc = (1u << 4) | (uint32_t(128 >> 3) << 17) | (uint32_t(128 >> 4) << 24);   // f16 x f16 -> f32, M = N = 128
+
+struct AltTaskInfo {                                   // 80 bytes: the plan entry of one pixel tile
+  int bx0[kATMaxL], by0[kATMaxL];                      // bounding corner of the tile's windows in the target map, per level
+  unsigned long long mask[kATMaxL];                    // 8x8 mask of 16x8 cells relative to it
+  int skip[kATMaxL];                                   // cells beyond the mask: this (tile, level) is on the SIMT list
+};
+static_assert(sizeof(AltTaskInfo) == 80, "plan entry size");
 
 struct AltTcParams {
   CUtensorMap a_hi, a_lo;
@@ -57,25 +66,25 @@ struct AltTcParams {
   const long long* idx1;                               // frame of fmap1 per edge (null: edge index)
   const long long* idx2;                               // frame of fmap2 per edge (null: edge index)
   const unsigned* flags;                               // bit 0: lo parts present and non-zero; bit 1: whole call on the SIMT path
-  int* status;                                         // [0] error word, [1] number of (task, level) entries for the SIMT kernel
+  int* status;                                         // [0] error word, [1] number of (task, level) entries for the SIMT kernel,
+                                                       // [2] cells (tile x cell GEMMs) issued — instrumentation
   int* list;                                           // entries: task * kATMaxL + level
   int list_cap;
+  AltTaskInfo* plan;                                   // [tasks], written by altcorr_plan_kernel
   int B, S, H1, W1, L;
   int H2[kATMaxL], W2[kATMaxL];
   float scale[kATMaxL];                                // level coordinates = coords * scale (2^-l: exact, = coords / 2**l)
   int tiles_x, tiles_y;
   int has_lo;
+  int dbg;                                             // timing experiments only (env DB200_ALT_DBG): 1 no tap scatter, 2 no output
+                                                       // stores, 4 no TMEM reads, 8 no per-level barriers; results are then wrong
 };
 
-struct AltTaskInfo {
-  int bx0[kATMaxL], by0[kATMaxL];
-  unsigned long long mask[kATMaxL];
-  int skip[kATMaxL];
-};
 
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
-  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
-               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar) : "memory");
+// one box = both 64-channel blocks of a 16 x 8 position tile of frame f: [2][8][16][64] halfs = 32 KB, the two K-blocks of the operand
+__device__ __forceinline__ void tma_load_tile(uint32_t dst, const CUtensorMap* map, int x, int y, int f, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+               ::"r"(dst), "l"(map), "r"(0), "r"(x), "r"(y), "r"(0), "r"(f), "r"(bar) : "memory");
 }
 
 // window origin of a level coordinate: floor, as int, clamped so that +-7 never overflows (far-away windows are out of
@@ -87,64 +96,28 @@ __device__ __forceinline__ int alt_floor_clamped(float v, float* frac) {
   return (f == f) ? static_cast<int>(c) : 0;
 }
 
-__device__ __forceinline__ void alt_epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+// the four epilogue warps that share a TMEM lane quarter q (one per 32-column chunk of the accumulator) are the only threads
+// that touch the tap columns of pixels 32q..32q+31: they synchronise among themselves (named barrier 1 + q, 128 threads)
+__device__ __forceinline__ void alt_pair_bar(int q) { asm volatile("bar.sync %0, 128;" ::"r"(1 + q) : "memory"); }
 
-__global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __grid_constant__ AltTcParams P) {
-  extern __shared__ unsigned char smem_dyn[];
-  __shared__ __align__(8) uint64_t bars[24];           // a_full[2] a_empty[2] b_full[4] b_empty[4] t_full[4] t_empty[4] i_full[2] i_empty[2]
-  __shared__ uint32_t tmem_base_s;
-  __shared__ AltTaskInfo tinfo[2];
-
+// ---- plan: which target cells every pixel tile needs, per level (one warp per tile; thousands of warps in flight) --------
+// In the first version the persistent kernel's producer warp did this itself, tile after tile: ~2000 dependent instructions of
+// ONE warp per tile (~6 us) in front of that tile's loads — with the whole epilogue switched off the kernel still took 82 % of
+// its time.  Computed up front it costs a few microseconds for the whole call.
+__global__ void __launch_bounds__(256) altcorr_plan_kernel(const __grid_constant__ AltTcParams P) {
   const unsigned flags = P.flags ? *P.flags : 0u;
-  if (flags & 2u) return;                              // non-finite / out-of-range operands: the SIMT kernel does the call
-  const bool lo = P.has_lo && (flags & 1u);
-  const int NA = lo ? 1 : 2, NB = lo ? 2 : 4;
-  const uint32_t tile_bytes = lo ? 4 * kATBlk : 2 * kATBlk;
-
-  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
-  const uint32_t sA = s0, sB = s0 + kATARegion;
-  float* D = reinterpret_cast<float*>(smem_dyn + (s0 - smem_u32(smem_dyn)) + kATARegion + kATBRegion);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  auto a_full = [&](int i) { return smem_u32(&bars[i]); };
-  auto a_empty = [&](int i) { return smem_u32(&bars[2 + i]); };
-  auto b_full = [&](int i) { return smem_u32(&bars[4 + i]); };
-  auto b_empty = [&](int i) { return smem_u32(&bars[8 + i]); };
-  auto t_full = [&](int i) { return smem_u32(&bars[12 + i]); };
-  auto t_empty = [&](int i) { return smem_u32(&bars[16 + i]); };
-  auto i_full = [&](int i) { return smem_u32(&bars[20 + i]); };
-  auto i_empty = [&](int i) { return smem_u32(&bars[22 + i]); };
-
-  if (tid == 0) {
-    for (int i = 0; i < 16; i++) mbar_init(smem_u32(&bars[i]), 1);
-    for (int i = 0; i < 4; i++) mbar_init(t_empty(i), kATEpiWarps);
-    mbar_init(i_full(0), 1); mbar_init(i_full(1), 1);
-    mbar_init(i_empty(0), 1 + kATEpiWarps); mbar_init(i_empty(1), 1 + kATEpiWarps);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(512) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = tmem_base_s;
-
+  if (flags & 2u) return;
+  const int lane = threadIdx.x & 31;
   const int tiles = P.tiles_x * P.tiles_y;
   const long long total = static_cast<long long>(P.B) * P.S * tiles;
-
-  if (warp == 0) {
-    // ===================================================================== producer
-    long long it = 0;                                  // cells loaded so far (ring position)
-    int k = 0;
-    bool dead = false;
-    for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
-      const int slot = k & 1;
-      const int tile = int(t % tiles);
-      const long long bs = t / tiles;
-      const int s = int(bs % P.S), b = int(bs / P.S);
-      const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
-      if (!mbar_wait(i_empty(slot), ((k >> 1) & 1) ^ 1)) { atomicExch(P.status, 1); break; }
+  const long long t = static_cast<long long>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (t >= total) return;
+  const int tile = int(t % tiles);
+  const long long bs = t / tiles;
+  const int s = int(bs % P.S), b = int(bs / P.S);
+  const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
+  AltTaskInfo* out = P.plan + t;
+  {
       float cx[4], cy[4];
       bool pv[4];
 #pragma unroll
@@ -208,41 +181,116 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         bx0s[l] = minx == 0x7fffffff ? 0 : minx;
         by0s[l] = miny == 0x7fffffff ? 0 : miny;
         if (lane == 0) {
-          tinfo[slot].bx0[l] = bx0s[l]; tinfo[slot].by0[l] = by0s[l];
-          tinfo[slot].mask[l] = masks[l]; tinfo[slot].skip[l] = skip;
+          (*out).bx0[l] = bx0s[l]; (*out).by0[l] = by0s[l];
+          (*out).mask[l] = masks[l]; (*out).skip[l] = skip;
         }
       }
+    if (lane == 0) {
+      int ncell = 0;
+      for (int l = 0; l < P.L; l++) ncell += __popcll(masks[l]);
+      if (ncell) atomicAdd(P.status + 2, ncell);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __grid_constant__ AltTcParams P) {
+  extern __shared__ unsigned char smem_dyn[];
+  __shared__ __align__(8) uint64_t bars[24];           // a_full[2] a_empty[2] b_full[4] b_empty[4] t_full[4] t_empty[4] i_full[2] i_empty[2]
+  __shared__ uint32_t tmem_base_s;
+  __shared__ AltTaskInfo tinfo[2];
+
+  const unsigned flags = P.flags ? *P.flags : 0u;
+  if (flags & 2u) return;                              // non-finite / out-of-range operands: the SIMT kernel does the call
+  const bool lo = P.has_lo && (flags & 1u);
+  const int NA = lo ? 1 : 2, NB = lo ? 2 : 4;            // powers of two: ring positions by mask / shift (no division per cell)
+  const int na_shift = lo ? 0 : 1, nb_shift = lo ? 1 : 2;
+  const uint32_t tile_bytes = lo ? 4 * kATBlk : 2 * kATBlk;
+
+  const uint32_t s0 = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+  const uint32_t sA = s0, sB = s0 + kATARegion;
+  float* D = reinterpret_cast<float*>(smem_dyn + (s0 - smem_u32(smem_dyn)) + kATARegion + kATBRegion);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto a_full = [&](int i) { return smem_u32(&bars[i]); };
+  auto a_empty = [&](int i) { return smem_u32(&bars[2 + i]); };
+  auto b_full = [&](int i) { return smem_u32(&bars[4 + i]); };
+  auto b_empty = [&](int i) { return smem_u32(&bars[8 + i]); };
+  auto t_full = [&](int i) { return smem_u32(&bars[12 + i]); };
+  auto t_empty = [&](int i) { return smem_u32(&bars[16 + i]); };
+  auto i_full = [&](int i) { return smem_u32(&bars[20 + i]); };
+  auto i_empty = [&](int i) { return smem_u32(&bars[22 + i]); };
+
+  if (tid == 0) {
+    for (int i = 0; i < 16; i++) mbar_init(smem_u32(&bars[i]), 1);
+    for (int i = 0; i < 4; i++) mbar_init(t_empty(i), kATEpiWarps);
+    mbar_init(i_full(0), 1); mbar_init(i_full(1), 1);
+    mbar_init(i_empty(0), 1 + kATEpiWarps); mbar_init(i_empty(1), 1 + kATEpiWarps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int tiles = P.tiles_x * P.tiles_y;
+  const long long total = static_cast<long long>(P.B) * P.S * tiles;
+  // debug (P.dbg & 16): cycles each role spends in each wait, summed over the CTAs into status words 8.. (long long[12])
+  long long tw[6] = {0, 0, 0, 0, 0, 0};
+  const bool timing = (P.dbg & 16) != 0;
+  auto twait = [&](int slot_, uint32_t bar_, uint32_t par_) -> bool {
+    if (!timing) return mbar_wait(bar_, par_);
+    const long long c0 = clock64();
+    const bool ok_ = mbar_wait(bar_, par_);
+    tw[slot_] += clock64() - c0;
+    return ok_;
+  };
+  const long long t_start = clock64();
+
+  if (warp == 0) {
+    // ===================================================================== producer
+    // the cell origins / masks of every tile were computed by altcorr_plan_kernel: the producer reads its 80-byte plan
+    // entry (the next tile's entry is prefetched), hands it to the other roles through shared memory and issues the loads
+    uint32_t it = 0;                                   // cells loaded so far (ring position); only its low bits matter
+    int k = 0;
+    bool dead = false;
+    int pre = 0;
+    if (lane < 20 && static_cast<long long>(blockIdx.x) < total) pre = reinterpret_cast<const int*>(P.plan + blockIdx.x)[lane];
+    for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
+      const int slot = k & 1;
+      const int tile = int(t % tiles);
+      const long long bs = t / tiles;
+      const int b = int(bs / P.S);
+      const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
+      if (!twait(0, i_empty(slot), ((k >> 1) & 1) ^ 1)) { atomicExch(P.status, 1); break; }
+      if (lane < 20) reinterpret_cast<int*>(&tinfo[slot])[lane] = pre;
+      if (lane < 20 && t + gridDim.x < total) pre = reinterpret_cast<const int*>(P.plan + t + gridDim.x)[lane];
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(i_full(slot));
         const int f1 = P.idx1 ? int(P.idx1[b]) : b, f2 = P.idx2 ? int(P.idx2[b]) : b;
-        const int as = k % NA;
-        if (!mbar_wait(a_empty(as), ((k / NA) & 1) ^ 1)) { atomicExch(P.status, 1); dead = true; }
+        const int as = k & (NA - 1);
+        if (!twait(1, a_empty(as), ((k >> na_shift) & 1) ^ 1)) { atomicExch(P.status, 1); dead = true; }
         if (!dead) {
           const uint32_t dst = sA + uint32_t(as) * tile_bytes;
           mbar_expect_tx(a_full(as), tile_bytes);
-          tma_load_4d(dst, &P.a_hi, 0, tx0, ty0, f1, a_full(as));
-          tma_load_4d(dst + kATBlk, &P.a_hi, 64, tx0, ty0, f1, a_full(as));
-          if (lo) {
-            tma_load_4d(dst + 2 * kATBlk, &P.a_lo, 0, tx0, ty0, f1, a_full(as));
-            tma_load_4d(dst + 3 * kATBlk, &P.a_lo, 64, tx0, ty0, f1, a_full(as));
-          }
+          tma_load_tile(dst, &P.a_hi, tx0, ty0, f1, a_full(as));
+          if (lo) tma_load_tile(dst + 2 * kATBlk, &P.a_lo, tx0, ty0, f1, a_full(as));
           for (int l = 0; l < P.L && !dead; l++) {
-            unsigned long long m = masks[l];
+            unsigned long long m = tinfo[slot].mask[l];
+            const int bx0 = tinfo[slot].bx0[l], by0 = tinfo[slot].by0[l];
             while (m) {
               const int bit = __ffsll(static_cast<long long>(m)) - 1;
               m &= m - 1;
-              const int X0 = bx0s[l] + kATCx * (bit & 7), Y0 = by0s[l] + kATCy * (bit >> 3);
-              const int st = int(it % NB);
-              if (!mbar_wait(b_empty(st), (uint32_t(it / NB) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
+              const int X0 = bx0 + kATCx * (bit & 7), Y0 = by0 + kATCy * (bit >> 3);
+              const int st = int(it & uint32_t(NB - 1));
+              if (!twait(2, b_empty(st), ((it >> nb_shift) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
               const uint32_t d2 = sB + uint32_t(st) * tile_bytes;
               mbar_expect_tx(b_full(st), tile_bytes);
-              tma_load_4d(d2, &P.b_hi[l], 0, X0, Y0, f2, b_full(st));
-              tma_load_4d(d2 + kATBlk, &P.b_hi[l], 64, X0, Y0, f2, b_full(st));
-              if (lo) {
-                tma_load_4d(d2 + 2 * kATBlk, &P.b_lo[l], 0, X0, Y0, f2, b_full(st));
-                tma_load_4d(d2 + 3 * kATBlk, &P.b_lo[l], 64, X0, Y0, f2, b_full(st));
-              }
+              tma_load_tile(d2, &P.b_hi[l], X0, Y0, f2, b_full(st));
+              if (lo) tma_load_tile(d2 + 2 * kATBlk, &P.b_lo[l], X0, Y0, f2, b_full(st));
               it++;
             }
           }
@@ -250,25 +298,32 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
       }
       dead = __shfl_sync(0xffffffffu, int(dead), 0) != 0;
     }
+    if (timing && lane == 0) {
+      long long* dt = reinterpret_cast<long long*>(P.status + 8);
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 0), static_cast<unsigned long long>(tw[0]));
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 1), static_cast<unsigned long long>(tw[1]));
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 2), static_cast<unsigned long long>(tw[2]));
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 3), static_cast<unsigned long long>(clock64() - t_start));
+    }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
     if (lane == 0) {
-      long long it = 0;
+      uint32_t it = 0;
       int k = 0;
       bool dead = false;
       for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
         const int slot = k & 1;
-        if (!mbar_wait(i_full(slot), (k >> 1) & 1)) { atomicExch(P.status, 1); break; }
+        if (!twait(0, i_full(slot), (k >> 1) & 1)) { atomicExch(P.status, 1); break; }
         int cells = 0;
         for (int l = 0; l < P.L; l++) cells += __popcll(tinfo[slot].mask[l]);
         mbar_arrive(i_empty(slot));
-        const int as = k % NA;
-        if (!mbar_wait(a_full(as), (k / NA) & 1)) { atomicExch(P.status, 1); break; }
+        const int as = k & (NA - 1);
+        if (!twait(1, a_full(as), (k >> na_shift) & 1)) { atomicExch(P.status, 1); break; }
         const uint32_t aT = sA + uint32_t(as) * tile_bytes;
         for (int c = 0; c < cells; c++, it++) {
-          const int acc = int(it & 3), st = int(it % NB);
-          if (!mbar_wait(t_empty(acc), (uint32_t(it >> 2) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
-          if (!mbar_wait(b_full(st), uint32_t(it / NB) & 1u)) { atomicExch(P.status, 1); dead = true; break; }
+          const int acc = int(it & 3u), st = int(it & uint32_t(NB - 1));
+          if (!twait(2, t_empty(acc), (uint32_t(it >> 2) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
+          if (!twait(3, b_full(st), (it >> nb_shift) & 1u)) { atomicExch(P.status, 1); dead = true; break; }
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t bT = sB + uint32_t(st) * tile_bytes;
           const uint32_t d = tmem_base + uint32_t(acc) * 128u;
@@ -280,7 +335,7 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
             for (int kb = 0; kb < 2; kb++)
 #pragma unroll
               for (int kk = 0; kk < 4; kk++) {
-                umma_f16(d, umma_desc_sw128(aT + ao + kb * kATBlk + kk * 32), umma_desc_sw128(bT + bo + kb * kATBlk + kk * 32), kATIdesc, first);
+                if (!(P.dbg & 32)) umma_f16(d, umma_desc_sw128(aT + ao + kb * kATBlk + kk * 32), umma_desc_sw128(bT + bo + kb * kATBlk + kk * 32), kATIdesc, first);
                 first = 1u;
               }
           }
@@ -289,15 +344,19 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         }
         if (!dead) umma_commit(a_empty(as));
       }
+      if (timing) {
+        long long* dt = reinterpret_cast<long long*>(P.status + 8);
+        for (int i = 0; i < 4; i++) atomicAdd(reinterpret_cast<unsigned long long*>(dt + 4 + i), static_cast<unsigned long long>(tw[i]));
+        atomicAdd(reinterpret_cast<unsigned long long*>(dt + 8), static_cast<unsigned long long>(clock64() - t_start));
+      }
     }
   } else {
     // ===================================================================== epilogue
     const int ew = warp - 2;
     const int q = warp & 3;                            // TMEM lane quarter this warp may read
-    const int h = ew >> 2;                             // which 64 accumulator columns (= cell rows 4h..4h+3)
+    const int h = ew >> 2;                             // which 32 accumulator columns (= cell rows 2h, 2h+1); output rows 2h, 2h+1
     const int p = 32 * q + lane;                       // pixel of the tile = TMEM lane = A row
-    const int et = ew * 32 + lane;                     // 0..255
-    long long it = 0;
+    uint32_t it = 0;
     int k = 0;
     bool dead = false;
     for (long long t = blockIdx.x; t < total && !dead; t += gridDim.x, k++) {
@@ -312,18 +371,20 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
         pcx = c.x; pcy = c.y;
       }
-      if (!mbar_wait(i_full(slot), (k >> 1) & 1)) { if (lane == 0) atomicExch(P.status, 1); break; }
+      if (!twait(0, i_full(slot), (k >> 1) & 1)) { if (lane == 0) atomicExch(P.status, 1); break; }
       float* outp = P.out + b * P.o_sb + s * P.o_ss + (static_cast<long long>(y) * P.W1 + x) * P.o_sp;
       for (int l = 0; l < P.L && !dead; l++) {
-        alt_epi_bar();                                 // the previous level's output stage has read D
-        {
-          float4* D4 = reinterpret_cast<float4*>(D);
-#pragma unroll
-          for (int i = 0; i < 8; i++) D4[et + 256 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        alt_epi_bar();
+        if (!(P.dbg & 8)) alt_pair_bar(q);             // the partner warps' output stage of the previous level has read D
         float dx, dy;
         const int wx0 = alt_floor_clamped(pcx * P.scale[l], &dx) - 3, wy0 = alt_floor_clamped(pcy * P.scale[l], &dy) - 3;
+        // taps inside the target image: exactly these are written by the visited cells (the masks cover every in-image tap
+        // of every valid pixel); the others are selected to zero in the combination below — D is never cleared
+        unsigned rowok = 0u, colok = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          rowok |= (static_cast<unsigned>(wy0 + i) < static_cast<unsigned>(P.H2[l]) ? 1u : 0u) << i;
+          colok |= (static_cast<unsigned>(wx0 + i) < static_cast<unsigned>(P.W2[l]) ? 1u : 0u) << i;
+        }
         unsigned long long m = tinfo[slot].mask[l];
         const int bx0 = tinfo[slot].bx0[l], by0 = tinfo[slot].by0[l];
         while (m) {
@@ -331,23 +392,28 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
           m &= m - 1;
           const int relx = wx0 - (bx0 + kATCx * (bit & 7)), rely = wy0 - (by0 + kATCy * (bit >> 3));
           const int acc = int(it & 3);
-          const bool ok = mbar_wait(t_full(acc), uint32_t(it >> 2) & 1u);
+          const bool ok = twait(1, t_full(acc), uint32_t(it >> 2) & 1u);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           if (!ok) { if (lane == 0) atomicExch(P.status, 1); dead = true; break; }
-#pragma unroll
-          for (int j = 0; j < 2; j++) {
+          {
+            // cell rows 2h, 2h + 1: skip the TMEM read when no lane of this warp has a window row there
+            const int ty0 = 2 * h - rely;
+            const bool need = valid && (static_cast<unsigned>(ty0) < 8u || static_cast<unsigned>(ty0 + 1) < 8u) &&
+                              relx > -8 && relx < 16;
+            if (__any_sync(0xffffffffu, need) && !(P.dbg & 4)) {
             uint32_t v[32];
-            tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc * 128 + 64 * h + 32 * j), v);
+            tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc * 128 + 32 * h), v);
 #pragma unroll
             for (int rr = 0; rr < 2; rr++) {
-              const int ty = 4 * h + 2 * j + rr - rely;
-              if (valid && static_cast<unsigned>(ty) < 8u) {
+              const int ty = 2 * h + rr - rely;
+              if (valid && static_cast<unsigned>(ty) < 8u && !(P.dbg & 1)) {
 #pragma unroll
                 for (int c = 0; c < 16; c++) {
                   const int tx = c - relx;
                   if (static_cast<unsigned>(tx) < 8u) D[(ty * 8 + tx) * 128 + p] = __uint_as_float(v[rr * 16 + c]);
                 }
               }
+            }
             }
           }
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -356,19 +422,19 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
           it++;
         }
         if (dead) break;
-        alt_epi_bar();                                 // every tap of this level is in D
-        if (valid && !tinfo[slot].skip[l]) {
+        if (!(P.dbg & 8)) alt_pair_bar(q);             // all four chunks' taps of this level are in D
+        if (valid && !tinfo[slot].skip[l] && !(P.dbg & 2)) {
           // bilinear combination (altcorr_kernel.cu:107-140): channel oy + 7 ox =
           //   (1-dy)(1-dx) S[oy][ox] + (1-dy) dx S[oy][ox+1] + dy (1-dx) S[oy+1][ox] + dy dx S[oy+1][ox+1]
           const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx, w10 = dy * (1.0f - dx), w11 = dy * dx;
-          const int oy0 = h ? 4 : 0, oy1 = h ? 7 : 4;
+          const int oy0 = 2 * h, oy1 = min(2 * h + 2, 7);   // the 7 output rows over the 4 warps of the pixel: 2, 2, 2, 1
           float up[8], dn[8];
 #pragma unroll
-          for (int c = 0; c < 8; c++) up[c] = D[(oy0 * 8 + c) * 128 + p];
+          for (int c = 0; c < 8; c++) up[c] = ((rowok >> oy0) & (colok >> c) & 1u) ? D[(oy0 * 8 + c) * 128 + p] : 0.0f;
           float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc;
           for (int oy = oy0; oy < oy1; oy++) {
 #pragma unroll
-            for (int c = 0; c < 8; c++) dn[c] = D[((oy + 1) * 8 + c) * 128 + p];
+            for (int c = 0; c < 8; c++) dn[c] = ((rowok >> (oy + 1)) & (colok >> c) & 1u) ? D[((oy + 1) * 8 + c) * 128 + p] : 0.0f;
 #pragma unroll
             for (int ox = 0; ox < 7; ox++) {
               float r = w00 * up[ox];
@@ -384,6 +450,12 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(i_empty(slot));
+    }
+    if (timing && ew == 0 && lane == 0) {
+      long long* dt = reinterpret_cast<long long*>(P.status + 8);
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 9), static_cast<unsigned long long>(tw[0]));
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 10), static_cast<unsigned long long>(tw[1]));
+      atomicAdd(reinterpret_cast<unsigned long long*>(dt + 11), static_cast<unsigned long long>(clock64() - t_start));
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -408,6 +480,14 @@ struct AltSimtParams {
 
 template <typename T> __device__ __forceinline__ float4 alt_ld4(const T* p);
 template <> __device__ __forceinline__ float4 alt_ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// address of channels 4 * lane .. 4 * lane + 3 of position `pos` (= (frame * H + y) * W + x): channels-last fp32 / blocked fp16
+template <typename T> __device__ __forceinline__ const T* alt_chan_ptr(const T* base, long long frame, long long hw, long long pix, int lane);
+template <> __device__ __forceinline__ const float* alt_chan_ptr<float>(const float* base, long long frame, long long hw, long long pix, int lane) {
+  return base + (frame * hw + pix) * 128 + lane * 4;
+}
+template <> __device__ __forceinline__ const __half* alt_chan_ptr<__half>(const __half* base, long long frame, long long hw, long long pix, int lane) {
+  return base + ((frame * 2 + (lane >> 4)) * hw + pix) * 64 + (lane & 15) * 4;
+}
 template <> __device__ __forceinline__ float4 alt_ld4<__half>(const __half* p) {
   const uint2 u = *reinterpret_cast<const uint2*>(p);
   const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
@@ -433,19 +513,20 @@ __global__ void __launch_bounds__(256) altcorr_simt_list_kernel(const __grid_con
     const int ty0 = (tile / P.tiles_x) * kATPy, tx0 = (tile % P.tiles_x) * kATPx;
     const int H2 = P.H2[l], W2 = P.W2[l];
     const long long fr1 = P.idx1 ? P.idx1[b] : b, fr2 = P.idx2 ? P.idx2[b] : b;
-    const T* f2b = static_cast<const T*>(P.f2[l]) + fr2 * H2 * W2 * P.C;
+    const T* f2b = static_cast<const T*>(P.f2[l]);
+    const long long hw2 = static_cast<long long>(H2) * W2, hw1 = static_cast<long long>(P.H1) * P.W1;
     for (int pp = warp; pp < kATPy * kATPx; pp += 8) {
       const int y = ty0 + (pp >> 4), x = tx0 + (pp & 15);
       if (y >= P.H1 || x >= P.W1) continue;
       const float2 c = *reinterpret_cast<const float2*>(P.coords + b * P.c_sb + s * P.c_ss + (static_cast<long long>(y) * P.W1 + x) * P.c_sp);
       float dx, dy;
       const int wx0 = alt_floor_clamped(c.x * P.scale[l], &dx) - 3, wy0 = alt_floor_clamped(c.y * P.scale[l], &dy) - 3;
-      const float4 a = alt_ld4<T>(static_cast<const T*>(P.f1) + ((fr1 * P.H1 + y) * P.W1 + x) * P.C + lane * 4);
+      const float4 a = alt_ld4<T>(alt_chan_ptr<T>(static_cast<const T*>(P.f1), fr1, hw1, static_cast<long long>(y) * P.W1 + x, lane));
       for (int tp = 0; tp < 64; tp++) {
         const int h2 = wy0 + (tp >> 3), w2 = wx0 + (tp & 7);
         float acc = 0.0f;
         if (h2 >= 0 && h2 < H2 && w2 >= 0 && w2 < W2) {
-          const float4 qv = alt_ld4<T>(f2b + (static_cast<long long>(h2) * W2 + w2) * P.C + lane * 4);
+          const float4 qv = alt_ld4<T>(alt_chan_ptr<T>(f2b, fr2, hw2, static_cast<long long>(h2) * W2 + w2, lane));
           acc = fmaf(a.x, qv.x, acc); acc = fmaf(a.y, qv.y, acc); acc = fmaf(a.z, qv.z, acc); acc = fmaf(a.w, qv.w, acc);
           acc = warp_sum(acc);
         }
@@ -468,8 +549,9 @@ __global__ void __launch_bounds__(256) altcorr_simt_list_kernel(const __grid_con
 }
 
 // ---- fp32 -> fp16 hi + lo split (the lo parts make the tensor-core product fp32-faithful) -----------------------------
+// x: channels-last [F][HW][128] fp32  ->  hi, lo: channel-blocked [F][2][HW][64] fp16 (hw = 0: same layout as x)
 __global__ void __launch_bounds__(256) altcorr_split_kernel(const float* __restrict__ x, __half* __restrict__ hi, __half* __restrict__ lo,
-                                                            size_t n4, unsigned* __restrict__ flags) {
+                                                            size_t n4, unsigned* __restrict__ flags, size_t hw) {
   unsigned f = 0u;
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
     const float4 v = reinterpret_cast<const float4*>(x)[i];
@@ -489,8 +571,13 @@ __global__ void __launch_bounds__(256) altcorr_split_kernel(const float* __restr
     __half2 l01 = __halves2half2(ll[0], ll[1]), l23 = __halves2half2(ll[2], ll[3]);
     ph.x = *reinterpret_cast<uint32_t*>(&h01); ph.y = *reinterpret_cast<uint32_t*>(&h23);
     pl.x = *reinterpret_cast<uint32_t*>(&l01); pl.y = *reinterpret_cast<uint32_t*>(&l23);
-    reinterpret_cast<uint2*>(hi)[i] = ph;
-    reinterpret_cast<uint2*>(lo)[i] = pl;
+    size_t o = i;
+    if (hw) {                                           // i = (pos * 128 + c) / 4 -> ((f * 2 + c / 64) * hw + pix) * 64 + c % 64
+      const size_t pos = i >> 5, c4 = i & 31, f = pos / hw, pix = pos - f * hw;
+      o = (((f * 2 + (c4 >> 4)) * hw + pix) << 4) + (c4 & 15);
+    }
+    reinterpret_cast<uint2*>(hi)[o] = ph;
+    reinterpret_cast<uint2*>(lo)[o] = pl;
   }
   f = __reduce_or_sync(0xffffffffu, f);
   if (f && (threadIdx.x & 31) == 0) atomicOr(flags, f);
@@ -574,12 +661,8 @@ __global__ void __launch_bounds__(256, 1) altcorr_tc_bwd_kernel(const __grid_con
     const bool valid = y < P.H1 && x < P.W1;
     if (tid == 0) {
       mbar_expect_tx(bar_f1, tile_bytes);
-      tma_load_4d(sF1, &P.a_hi, 0, tx0, ty0, b, bar_f1);
-      tma_load_4d(sF1 + kATBlk, &P.a_hi, 64, tx0, ty0, b, bar_f1);
-      if (lo) {
-        tma_load_4d(sF1 + 2 * kATBlk, &P.a_lo, 0, tx0, ty0, b, bar_f1);
-        tma_load_4d(sF1 + 3 * kATBlk, &P.a_lo, 64, tx0, ty0, b, bar_f1);
-      }
+      tma_load_tile(sF1, &P.a_hi, tx0, ty0, b, bar_f1);
+      if (lo) tma_load_tile(sF1 + 2 * kATBlk, &P.a_lo, tx0, ty0, b, bar_f1);
     }
     int task_cells = 0;
     for (int s = 0; s < P.S && !dead; s++) {
@@ -636,9 +719,8 @@ __global__ void __launch_bounds__(256, 1) altcorr_tc_bwd_kernel(const __grid_con
         if (n > 0) {                                   // first cell of this sample
           mbar_expect_tx(bar_f2, tile_bytes);
           const int X0 = bx0 + kATCx * s_cx[0], Y0 = by0 + kATCy * s_cy[0];
-          tma_load_4d(sF2, &P.b_hi, 0, X0, Y0, b, bar_f2);
-          tma_load_4d(sF2 + kATBlk, &P.b_hi, 64, X0, Y0, b, bar_f2);
-          if (lo) { tma_load_4d(sF2 + 2 * kATBlk, &P.b_lo, 0, X0, Y0, b, bar_f2); tma_load_4d(sF2 + 3 * kATBlk, &P.b_lo, 64, X0, Y0, b, bar_f2); }
+          tma_load_tile(sF2, &P.b_hi, X0, Y0, b, bar_f2);
+          if (lo) tma_load_tile(sF2 + 2 * kATBlk, &P.b_lo, X0, Y0, b, bar_f2);
         }
       }
       __syncthreads();
@@ -716,9 +798,8 @@ __global__ void __launch_bounds__(256, 1) altcorr_tc_bwd_kernel(const __grid_con
         if (tid == 0 && c + 1 < ncell && ok) {          // the f2 stage is free again: fetch the next cell under the drain
           mbar_expect_tx(bar_f2, tile_bytes);
           const int X1 = bx0 + kATCx * s_cx[c + 1], Y1 = by0 + kATCy * s_cy[c + 1];
-          tma_load_4d(sF2, &P.b_hi, 0, X1, Y1, b, bar_f2);
-          tma_load_4d(sF2 + kATBlk, &P.b_hi, 64, X1, Y1, b, bar_f2);
-          if (lo) { tma_load_4d(sF2 + 2 * kATBlk, &P.b_lo, 0, X1, Y1, b, bar_f2); tma_load_4d(sF2 + 3 * kATBlk, &P.b_lo, 64, X1, Y1, b, bar_f2); }
+          tma_load_tile(sF2, &P.b_hi, X1, Y1, b, bar_f2);
+          if (lo) tma_load_tile(sF2 + 2 * kATBlk, &P.b_lo, X1, Y1, b, bar_f2);
         }
         __syncwarp();
         // ---- drain d f2cell: TMEM lane = cell position
@@ -775,16 +856,20 @@ __global__ void __launch_bounds__(256, 1) altcorr_tc_bwd_kernel(const __grid_con
 }
 
 // ---- host ---------------------------------------------------------------------------------------------------------------
-// feature map [F][H][W][C = 128] fp16 as a 4-D tensor; box = 64 channels x 16 x 8 x 1 frame, 128-byte swizzle:
-// the box lands in shared memory as [8*16 rows][64 halfs], the K-major UMMA operand block.
+// Operand layout of the tensor-core kernels: CHANNEL-BLOCKED fp16 feature maps [F][2][H][W][64] (channel c of position
+// (y, x) of frame f at ((f * 2 + c / 64) * H * W + y * W + x) * 64 + c % 64).  The 128-byte swizzle limits a TMA box to 64
+// channels; in a channels-last [F][H][W][128] array such a box is 128 separate 128-byte segments (positions are 256 bytes
+// apart) and the TMA unit of the SM, not the tensor pipe or the epilogue, bounded the kernel (1.5 us per cell: 82 % of the
+// time remained with the whole epilogue switched off).  Blocked, a box [64 ch x 16 x 8 x 2 blocks x 1 frame] is 16 runs of 2 KB and ONE TMA instruction per operand tile.
+// It lands in shared memory as [8*16 rows][64 halfs], the K-major UMMA operand block.
 static bool alt_make_map(CUtensorMap* m, const void* base, long long F, int H, int W) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
-  const cuuint64_t gdim[4] = {128, cuuint64_t(W), cuuint64_t(H), cuuint64_t(F)};
-  const cuuint64_t gstride[3] = {256, cuuint64_t(W) * 256, cuuint64_t(H) * W * 256};
-  const cuuint32_t box[4] = {64, kATCx, kATCy, 1};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
-  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  const cuuint64_t gdim[5] = {64, cuuint64_t(W), cuuint64_t(H), 2, cuuint64_t(F)};
+  const cuuint64_t gstride[4] = {128, cuuint64_t(W) * 128, cuuint64_t(H) * W * 128, cuuint64_t(H) * W * 256};
+  const cuuint32_t box[5] = {64, kATCx, kATCy, 2, 1};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -811,9 +896,12 @@ struct AltLaunch {
   int list_cap;
 };
 
+// status area of a call: [256 B status words][SIMT hand-over list: tasks * kATMaxL ints][plan: tasks * 80 B]
+static inline long long alt_tasks(int B, int S, int H1, int W1) { return static_cast<long long>(B) * S * cdiv(H1, kATPy) * cdiv(W1, kATPx); }
+static inline size_t alt_list_bytes(long long tasks) { return (size_t(tasks) * kATMaxL * sizeof(int) + 15) / 16 * 16; }
 size_t altcorr_tc_status_bytes(int B, int S, int H1, int W1) {
-  const long long tasks = static_cast<long long>(B) * S * cdiv(H1, kATPy) * cdiv(W1, kATPx);
-  return 256 + size_t(tasks) * kATMaxL * sizeof(int);
+  const long long tasks = alt_tasks(B, S, H1, W1);
+  return 256 + alt_list_bytes(tasks) + size_t(tasks) * sizeof(AltTaskInfo);
 }
 
 int altcorr_tc_launch(const AltLaunch& a, cudaStream_t st) {
@@ -833,18 +921,23 @@ int altcorr_tc_launch(const AltLaunch& a, cudaStream_t st) {
   P.idx1 = Q.idx1 = a.idx1; P.idx2 = Q.idx2 = a.idx2;
   P.flags = Q.flags = a.flags;
   P.status = a.status; Q.status = a.status;
-  P.list = a.status + 64; Q.list = a.status + 64; P.list_cap = Q.list_cap = a.list_cap;
+  const long long tasks = alt_tasks(a.B, a.S, a.H1, a.W1);
+  P.list = a.status + 64; Q.list = a.status + 64; P.list_cap = Q.list_cap = int(tasks * kATMaxL);
+  P.plan = reinterpret_cast<AltTaskInfo*>(reinterpret_cast<char*>(a.status) + 256 + alt_list_bytes(tasks));
   P.B = Q.B = a.B; P.S = Q.S = a.S; P.H1 = Q.H1 = a.H1; P.W1 = Q.W1 = a.W1; P.L = Q.L = a.L; Q.C = 128;
   P.tiles_x = Q.tiles_x = cdiv(a.W1, kATPx); P.tiles_y = Q.tiles_y = cdiv(a.H1, kATPy);
   P.has_lo = a.f1_lo != nullptr;
+  static const int dbg_env = getenv("DB200_ALT_DBG") ? atoi(getenv("DB200_ALT_DBG")) : 0;
+  P.dbg = dbg_env;
   Q.f1 = a.f1_raw;
-  DB200_CUDA(cudaMemsetAsync(a.status, 0, 2 * sizeof(int), st));
+  DB200_CUDA(cudaMemsetAsync(a.status, 0, 32 * sizeof(int), st));
   static bool attr = false;
   if (!attr) {
     DB200_CUDA(cudaFuncSetAttribute(altcorr_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kATSmem)));
     attr = true;
   }
-  const long long tasks = static_cast<long long>(a.B) * a.S * P.tiles_x * P.tiles_y;
+  altcorr_plan_kernel<<<unsigned((tasks + 7) / 8), 256, 0, st>>>(P);
+  DB200_CHECK_LAUNCH();
   const int grid = int(tasks < kNumSMs ? tasks : kNumSMs);
   altcorr_tc_fwd_kernel<<<grid, kATThreads, kATSmem, st>>>(P);
   DB200_CHECK_LAUNCH();
@@ -855,11 +948,11 @@ int altcorr_tc_launch(const AltLaunch& a, cudaStream_t st) {
   return DB200_OK;
 }
 
-int altcorr_split(const float* x, void* hi, void* lo, size_t n, unsigned* flags, cudaStream_t st) {
-  if (n % 4 != 0) return DB200_ERR_ARG;
+int altcorr_split(const float* x, void* hi, void* lo, size_t n, unsigned* flags, cudaStream_t st, size_t hw = 0) {
+  if (n % 4 != 0 || (hw && n % (hw * 128) != 0)) return DB200_ERR_ARG;
   const size_t n4 = n / 4;
   const int blocks = int((n4 + 255) / 256 < size_t(8 * kNumSMs) ? (n4 + 255) / 256 : size_t(8 * kNumSMs));
-  altcorr_split_kernel<<<blocks > 0 ? blocks : 1, 256, 0, st>>>(x, static_cast<__half*>(hi), static_cast<__half*>(lo), n4, flags);
+  altcorr_split_kernel<<<blocks > 0 ? blocks : 1, 256, 0, st>>>(x, static_cast<__half*>(hi), static_cast<__half*>(lo), n4, flags, hw);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
@@ -924,9 +1017,9 @@ extern "C" int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, 
   void* h2 = ws; ws += al256(n2 * 2);
   void* l2 = ws;
   DB200_CUDA(cudaMemsetAsync(flags, 0, sizeof(unsigned), st));
-  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st);
+  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st, size_t(H1) * W1);
   if (rc != DB200_OK) return rc;
-  rc = altcorr_split(fmap2, h2, l2, n2, flags, st);
+  rc = altcorr_split(fmap2, h2, l2, n2, flags, st, size_t(H2) * W2);
   if (rc != DB200_OK) return rc;
   AltLaunch a{};
   a.f1_hi = h1; a.f1_lo = l1; a.f2_hi[0] = h2; a.f2_lo[0] = l2;
@@ -937,7 +1030,7 @@ extern "C" int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, 
   a.out = corr; a.o_sb = static_cast<long long>(S) * 49 * H1 * W1; a.o_ss = static_cast<long long>(49) * H1 * W1;
   a.o_sc = static_cast<long long>(H1) * W1; a.o_sp = 1;
   a.B = B; a.S = S; a.flags = flags; a.status = status;
-  a.list_cap = int((altcorr_tc_status_bytes(B, S, H1, W1) - 256) / sizeof(int));
+  a.list_cap = 0;                                     // set by altcorr_tc_launch
   return altcorr_tc_launch(a, st);
 }
 
@@ -967,9 +1060,9 @@ extern "C" int db200_altcorr_backward_ws(const float* fmap1, const float* fmap2,
   void* l2 = ws;
   DB200_CUDA(cudaMemsetAsync(flags, 0, sizeof(unsigned), st));
   DB200_CUDA(cudaMemsetAsync(status, 0, 2 * sizeof(int), st));
-  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st);
+  int rc = altcorr_split(fmap1, h1, l1, n1, flags, st, size_t(H1) * W1);
   if (rc != DB200_OK) return rc;
-  rc = altcorr_split(fmap2, h2, l2, n2, flags, st);
+  rc = altcorr_split(fmap2, h2, l2, n2, flags, st, size_t(H2) * W2);
   if (rc != DB200_OK) return rc;
   rc = altcorr_tc_bwd_launch(h1, l1, h2, l2, coords, corr_grad, fmap1_grad, fmap2_grad, B, S, H1, W1, H2, W2, flags, status, st);
   if (rc != DB200_OK) return rc;
@@ -1011,14 +1104,29 @@ extern "C" int db200_altcorr_pyramid_forward(const void* fmap1_hi, const void* f
   a.coords = coords; a.c_sb = c_sb; a.c_ss = c_ss; a.c_sp = c_sp;
   a.out = out; a.o_sb = o_sb; a.o_ss = o_ss; a.o_sc = o_sc; a.o_sp = o_sp;
   a.B = B; a.S = S; a.flags = has_lo ? const_cast<unsigned*>(flags) : nullptr; a.status = static_cast<int*>(workspace);
-  a.list_cap = int((altcorr_tc_status_bytes(B, S, H, W) - 256) / sizeof(int));
+  a.list_cap = 0;
   return altcorr_tc_launch(a, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, unsigned* flags, db200_stream_t stream) {
+extern "C" int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, size_t hw, unsigned* flags, db200_stream_t stream) {
   if (!x || !hi || !lo || !flags) return DB200_ERR_ARG;
   if (n == 0) return DB200_OK;
-  return altcorr_split(x, hi, lo, n, flags, static_cast<cudaStream_t>(stream));
+  return altcorr_split(x, hi, lo, n, flags, static_cast<cudaStream_t>(stream), hw);
+}
+
+extern "C" int db200_debug_altcorr_waits(const void* status_words, long long* out12, db200_stream_t stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DB200_CUDA(cudaMemcpyAsync(out12, static_cast<const char*>(status_words) + 32, 12 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+  DB200_CUDA(cudaStreamSynchronize(st));
+  return DB200_OK;
+}
+
+extern "C" long long db200_altcorr_cells(const void* status_words, db200_stream_t stream) {
+  int h[4] = {0, 0, 0, 0};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cudaMemcpyAsync(h, status_words, sizeof(h), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
+    return -1;
+  return h[2];
 }
 
 extern "C" int db200_altcorr_status(const void* status_words, db200_stream_t stream) {

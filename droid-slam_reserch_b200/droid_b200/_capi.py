@@ -38,11 +38,13 @@ _SIGNATURES = {
     "db200_altcorr_static_max_bytes": (_sz, []),
     "db200_altcorr_forward_static": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_altcorr_status": (_i, [_vp, _vp]),
+    "db200_altcorr_cells": (C.c_longlong, [_vp, _vp]),
+    "db200_debug_altcorr_waits": (_i, [_vp, _vp, _vp]),
     "db200_altcorr_pyramid_workspace_bytes": (_sz, [_i] * 4),
     "db200_altcorr_pyramid_forward": (_i, [_vp, _vp, C.POINTER(_vp), C.POINTER(_vp), _vp, _vp, C.POINTER(_vp), C.c_longlong, _i, _i,
                                            _i, _i, _vp, _vp, _vp, C.c_longlong, C.c_longlong, C.c_longlong, _vp, C.c_longlong,
                                            C.c_longlong, C.c_longlong, C.c_longlong, _i, _i, _i, _vp, _sz, _vp]),
-    "db200_split_hilo_f16": (_i, [_vp, _vp, _vp, _sz, _vp, _vp]),
+    "db200_split_hilo_f16": (_i, [_vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "db200_frame_distance": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp]),
     "db200_proximity_workspace_bytes": (_sz, [_i, _i, _i]),
     "db200_proximity_max_edges": (_i, [_i, _i, _i, _i, _i]),

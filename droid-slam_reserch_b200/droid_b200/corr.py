@@ -150,7 +150,7 @@ class AltCorrBlock:
         if self._fused:
             flat = [p.view((B * N,) + p.shape[2:]) for p in self.pyramid]
             if fmaps.dtype == torch.float16:
-                self._hi = flat
+                self._hi = [droid_backends.to_channel_blocked(p) for p in flat]     # once per block: the kernels' operand layout
             else:
                 parts = [droid_backends.split_hilo_f16(p) for p in flat]
                 self._hi, self._lo = [q[0] for q in parts], [q[1] for q in parts]

@@ -16,7 +16,7 @@ from droid_b200 import _capi
 
 __all__ = ["ba", "frame_distance", "projmap", "depth_filter", "iproj", "altcorr_forward", "altcorr_backward",
            "corr_index_forward", "corr_index_backward", "corr_pyramid_lookup", "corr_volume_pyramid", "altcorr_pyramid_forward",
-           "split_hilo_f16"]
+           "split_hilo_f16", "to_channel_blocked"]
 
 _DT = {torch.float32: _capi.F32, torch.float16: _capi.F16, torch.float64: _capi.F64}
 _SYNC_STATUS = os.environ.get("DROID_B200_ASYNC", "0") != "1"
@@ -45,7 +45,8 @@ def corr_index_forward(volume, coords, radius):
     N, h1, w1, h2, w2 = volume.shape
     rd = 2 * radius + 1
     corr = torch.empty((N, rd, rd, h1, w1), dtype=volume.dtype, device=volume.device)
-    _capi.check(_capi.lib().db200_corr_index_forward(_ptr(volume), _ptr(coords.float()), _ptr(corr), N, h1, w1, h2, w2,
+    co = coords.float()                      # kept alive in a local for the duration of the call
+    _capi.check(_capi.lib().db200_corr_index_forward(_ptr(volume), _ptr(co), _ptr(corr), N, h1, w1, h2, w2,
                                                      radius, _DT[volume.dtype], _stream()), "corr_index_forward")
     return [corr]
 
@@ -56,7 +57,8 @@ def corr_index_backward(volume, coords, corr_grad, radius):
     N, h1, w1, h2, w2 = volume.shape
     grad = torch.empty_like(volume)
     g = corr_grad.to(volume.dtype)
-    _capi.check(_capi.lib().db200_corr_index_backward(_ptr(coords.float()), _ptr(g), _ptr(grad), N, h1, w1, h2, w2, radius,
+    co = coords.float()
+    _capi.check(_capi.lib().db200_corr_index_backward(_ptr(co), _ptr(g), _ptr(grad), N, h1, w1, h2, w2, radius,
                                                       _DT[volume.dtype], _stream()), "corr_index_backward")
     return [grad]
 
@@ -70,7 +72,8 @@ def corr_pyramid_lookup(levels, coords, radius):
     rd = 2 * radius + 1
     out = torch.empty((N, L * rd * rd, h1, w1), dtype=levels[0].dtype, device=coords.device)
     arr = (C.c_void_p * L)(*[v.data_ptr() for v in levels])
-    _capi.check(_capi.lib().db200_corr_pyramid_lookup(arr, _ptr(coords.float()), _ptr(out), N, h1, w1, h2, w2, L, radius,
+    co = coords.float()
+    _capi.check(_capi.lib().db200_corr_pyramid_lookup(arr, _ptr(co), _ptr(out), N, h1, w1, h2, w2, L, radius,
                                                       _DT[levels[0].dtype], _stream()), "corr_pyramid_lookup")
     return out
 
@@ -91,6 +94,8 @@ def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
     return outs
 
 
+WAIT_TIMES = None
+COUNT_CELLS = None      # set to {"cells": 0, "tile_levels": 0} to count the tile x cell GEMMs of altcorr_pyramid_forward
 CHECK_STATUS = os.environ.get("DROID_B200_CHECK", "0") == "1"   # tests: read the tensor-core kernels' status words back (synchronises)
 
 
@@ -121,22 +126,36 @@ def altcorr_forward(fmap1, fmap2, coords, radius):
     return [corr if dt == torch.float32 else corr.to(dt)]
 
 
-def split_hilo_f16(x):
-    """fp32 tensor -> (hi, lo, flags): fp16 tensors with x ~= hi + lo (|x - hi - lo| <= 2^-22 |x|) and a device flag word
-    (bit 0: some lo != 0, bit 1: some value non-finite / outside the fp16 range).  Operand format of the tensor-core
-    altcorr path for fp32 features."""
+def split_hilo_f16(x, blocked=True):
+    """fp32 channels-last feature maps x[F, H, W, 128] -> (hi, lo, flags): fp16 tensors with x ~= hi + lo (|x - hi - lo| <=
+    2^-22 |x|) in the CHANNEL-BLOCKED operand layout [F, 2, H, W, 64] of the tensor-core altcorr kernels (`blocked=False`: same
+    element order as x), and a device flag word (bit 0: some lo != 0, bit 1: some value non-finite / outside the fp16 range)."""
     _chk(("x", x))
     if x.dtype != torch.float32 or x.numel() % 4 != 0:
         raise RuntimeError("split_hilo_f16: fp32 tensor with numel % 4 == 0 expected")
-    hi = torch.empty(x.shape, dtype=torch.float16, device=x.device)
-    lo = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    hw = 0
+    shape = x.shape
+    if blocked:
+        if x.dim() != 4 or x.shape[-1] != 128:
+            raise RuntimeError("split_hilo_f16: channels-last [F, H, W, 128] expected")
+        hw = int(x.shape[1] * x.shape[2])
+        shape = (x.shape[0], 2, x.shape[1], x.shape[2], 64)
+    hi = torch.empty(shape, dtype=torch.float16, device=x.device)
+    lo = torch.empty(shape, dtype=torch.float16, device=x.device)
     flags = torch.zeros(1, dtype=torch.int32, device=x.device)
-    _capi.check(_capi.lib().db200_split_hilo_f16(_ptr(x), _ptr(hi), _ptr(lo), x.numel(), _ptr(flags), _stream()), "split_hilo_f16")
+    _capi.check(_capi.lib().db200_split_hilo_f16(_ptr(x), _ptr(hi), _ptr(lo), x.numel(), hw, _ptr(flags), _stream()), "split_hilo_f16")
     return hi, lo, flags
 
 
+def to_channel_blocked(x):
+    """fp16 channels-last feature maps [F, H, W, 128] -> the channel-blocked operand layout [F, 2, H, W, 64]"""
+    F_, H, W, Cc = x.shape
+    return x.view(F_, H, W, 2, Cc // 2).permute(0, 3, 1, 2, 4).contiguous()
+
+
 def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=None, f32=None):
-    """AltCorrBlock.corr_fn in one launch (corr.py:109-131): pyramid[l] = channels-last fp16 [frames, H>>l, W>>l, 128];
+    """AltCorrBlock.corr_fn in one launch (corr.py:109-131): pyramid[l] = channel-blocked fp16 [frames, 2, H>>l, W>>l, 64]
+    (`to_channel_blocked` / `split_hilo_f16`);
     ii, jj[E] int64 frame indices; coords[E,H,W,2] or [E,H,W,S,2] (level-0 scale) -> [E, 49*L, H, W(, S)] fp32.
     fp32 features: pass the fp16 split of every level (`pyramid` = hi parts, `lo`, the merged `flags` word) and the fp32
     levels themselves (`f32`)."""
@@ -144,7 +163,10 @@ def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=No
     _chk(("coords", coords), ("ii", ii), ("jj", jj), *[(f"pyramid[{l}]", v) for l, v in enumerate(pyramid)])
     if any(v.dtype != torch.float16 for v in pyramid) or ii.dtype != torch.int64 or jj.dtype != torch.int64:
         raise RuntimeError("altcorr_pyramid_forward: fp16 pyramid and int64 indices expected")
-    frames, H, W, Cc = pyramid[0].shape
+    if pyramid[0].dim() != 5 or pyramid[0].shape[1] != 2 or pyramid[0].shape[4] != 64:
+        raise RuntimeError("altcorr_pyramid_forward: channel-blocked pyramid [frames, 2, H, W, 64] expected")
+    frames, _, H, W, _ = pyramid[0].shape
+    Cc = 128
     co = coords.float()
     multi = co.dim() == 5
     E = co.shape[0]
@@ -164,6 +186,13 @@ def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=No
     _capi.check(rc, "altcorr_pyramid_forward")
     if CHECK_STATUS and E > 0:
         _altcorr_check(ws.data_ptr(), "altcorr_pyramid_forward")
+    if WAIT_TIMES is not None and E > 0:         # debug (DB200_ALT_DBG=16): where the roles of the forward kernel wait
+        buf = (C.c_longlong * 12)()
+        lib.db200_debug_altcorr_waits(C.c_void_p(ws.data_ptr()), buf, _stream())
+        WAIT_TIMES.append(list(buf))
+    if COUNT_CELLS is not None and E > 0:        # instrumentation (bench.py): synchronises
+        COUNT_CELLS["cells"] += int(lib.db200_altcorr_cells(C.c_void_p(ws.data_ptr()), _stream()))
+        COUNT_CELLS["tile_levels"] += E * S * ((H + 7) // 8) * ((W + 15) // 16) * L
     return out
 
 
@@ -229,16 +258,24 @@ def projmap(poses, disps, intrinsics, ii, jj):
 
 
 # ------------------------------------------------------------------------------------------------ bundle adjustment
-_WS_CACHE = {}
+_WS_CACHE = {}          # (device, stream) -> workspace; least recently used entries are dropped beyond _WS_CACHE_MAX
+_WS_CACHE_MAX = 4
 
 
 def _workspace(nbytes, device):
     key = (device.index, torch.cuda.current_stream().cuda_stream)
-    ws = _WS_CACHE.get(key)
+    ws = _WS_CACHE.pop(key, None)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes * 1.25) + 1024, dtype=torch.uint8, device=device)
-        _WS_CACHE[key] = ws
+    _WS_CACHE[key] = ws                      # re-inserted last = most recently used
+    while len(_WS_CACHE) > _WS_CACHE_MAX:
+        _WS_CACHE.pop(next(iter(_WS_CACHE)))
     return ws
+
+
+def release_workspaces():
+    """drop the cached BA workspaces (they are re-created on the next call)"""
+    _WS_CACHE.clear()
 
 
 def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations, lm, ep, motion_only):
@@ -249,10 +286,23 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
          ("disps_sens", disps_sens), ("ii", ii), ("jj", jj))
     if eta is not None:
         eta = eta.contiguous()
+    # the reference's packed_accessor32<float / long> would throw on a wrong dtype; raw pointers would silently misread it
+    for name, x in (("poses", poses), ("disps", disps), ("intrinsics", intrinsics), ("disps_sens", disps_sens), ("targets", targets),
+                    ("weights", weights), ("eta", eta)):
+        if x is not None and x.dtype != torch.float32:
+            raise RuntimeError(f"ba: {name} must be float32, got {x.dtype}")
+    for name, x in (("ii", ii), ("jj", jj)):
+        if x.dtype != torch.int64:
+            raise RuntimeError(f"ba: {name} must be int64, got {x.dtype}")
     B, ht, wd = disps.shape
     N = int(ii.shape[0])
     P = int(t1) - int(t0)
     M = int(eta.shape[0]) if (eta is not None and not motion_only) else 0
+    if (poses.dim() != 2 or poses.shape[1] != 7 or poses.shape[0] < B or intrinsics.numel() < 4 or jj.shape != ii.shape
+            or tuple(targets.shape) != (N, 2, ht, wd) or tuple(weights.shape) != (N, 2, ht, wd)
+            or (not motion_only and (tuple(disps_sens.shape) != (B, ht, wd) or eta is None or tuple(eta.shape[1:]) != (ht, wd)))):
+        raise RuntimeError("ba: tensor shapes do not match (poses[>=B,7], disps/disps_sens[B,ht,wd], targets/weights[N,2,ht,wd], "
+                           "eta[M,ht,wd], ii/jj[N])")
     lib = _capi.lib()
     wsb = lib.db200_ba_workspace_bytes(N, B, ht, wd, int(t0), int(t1), M, int(bool(motion_only)))
     if wsb == 0:

@@ -100,6 +100,13 @@ int db200_altcorr_forward_ws(const float* fmap1, const float* fmap2, const float
                              int H1, int W1, int H2, int W2, int C, int radius, void* workspace,
                              size_t workspace_bytes, db200_stream_t stream);
 int db200_altcorr_status(const void* status_words, db200_stream_t stream);
+/* instrumentation: number of (pixel tile x target cell) GEMMs the last forward launch issued (synchronises).  It depends on
+ * the coordinates: ~10 per tile for smooth flow over 4 levels, up to 64 per level for scattered coordinates. */
+long long db200_altcorr_cells(const void* status_words, db200_stream_t stream);
+/* debug (env DB200_ALT_DBG & 16): cycles summed over the CTAs that the producer / MMA / one epilogue thread of the forward
+ * kernel spent in each of their waits: out12 = {producer: plan slot, A stage, B stage, total | MMA: plan, A landed, accumulator
+ * free, B landed, total | epilogue: plan, accumulator ready, total}. */
+int db200_debug_altcorr_waits(const void* status_words, long long* out12, db200_stream_t stream);
 /* altcorr_backward on the tensor cores (same workspace size as the forward; C = 128, radius = 3, else the SIMT kernel):
  * d fmap1 = G . fmap2[cell], d fmap2[cell] = G^T . fmap1[tile] per pixel tile and target cell, G = the 4-corner combination
  * of corr_grad; fmap2_grad is accumulated with one vector red per 4 channels and cell position. */
@@ -109,8 +116,10 @@ int db200_altcorr_backward_ws(const float* fmap1, const float* fmap2, const floa
                               db200_stream_t stream);
 /* AltCorrBlock.corr_fn fused (corr.py:109-131 as driven by factor_graph.py:261-277): all `num_levels` levels, the
  * frame gathers `pyramid[0][:, ii]`, `pyramid[l][:, jj]`, the casts and the channel concat in ONE launch.
- *   fmap1_hi, fmap2_hi[l] : channels-last fp16 feature pyramid [frames, H>>l, W>>l, C] (fmap1 = level 0 of the same or
- *                           another pyramid); for fp32 features pass the fp16 split x = hi + lo (db200_split_hilo_f16)
+ *   fmap1_hi, fmap2_hi[l] : fp16 feature pyramid in the CHANNEL-BLOCKED operand layout [frames, 2, H>>l, W>>l, 64] (channel c of a
+ *                           position in block c / 64: a TMA box of 64 channels x 16 x 8 positions is then 8 runs of 2 KB instead of
+ *                           128 segments of 128 bytes; db200_split_hilo_f16 with hw = (H>>l)*(W>>l) writes it from channels-last
+ *                           fp32) (fmap1 = level 0 of the same or another pyramid); for fp32 features pass the fp16 split x = hi + lo (db200_split_hilo_f16)
  *                           with its flag word and the fp32 arrays themselves (used when a value leaves the fp16 range);
  *                           lo / flags / f32 pointers are NULL for fp16 features.
  *   idx1, idx2 [B] int64  : frame of the source / target image of every edge;
@@ -137,9 +146,10 @@ int db200_altcorr_pyramid_forward(const void* fmap1_hi, const void* fmap1_lo, co
 size_t db200_altcorr_static_max_bytes(void);
 int db200_altcorr_forward_static(const float* fmap1, const float* fmap2, const float* coords, float* corr, int B, int S,
                                  int H1, int W1, int H2, int W2, int C, int radius, db200_stream_t stream);
-/* x[n] fp32 -> hi[n], lo[n] fp16 with x ~= hi + lo; *flags |= 1 if any lo != 0, |= 2 if any value is non-finite or
+/* x[n] fp32 (channels-last [F, hw, 128] when hw != 0) -> hi[n], lo[n] fp16 with x ~= hi + lo, written channel-blocked
+ * [F, 2, hw, 64] when hw != 0 (hw = 0: same element order as x); *flags |= 1 if any lo != 0, |= 2 if any value is non-finite or
  * outside the fp16 range (flags must be zeroed by the caller). n % 4 == 0. */
-int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, unsigned* flags, db200_stream_t stream);
+int db200_split_hilo_f16(const float* x, void* hi, void* lo, size_t n, size_t hw, unsigned* flags, db200_stream_t stream);
 
 /* ---- frame_distance (droid.cpp:120-136, droid_kernels.cu:518-657,1438-1460) ----------------- */
 int db200_frame_distance(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,

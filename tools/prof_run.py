@@ -69,4 +69,33 @@ if "altcorr" in what:       # BASELINE config-5 shape: 88 edges, fp32 operands, 
         droid_backends.altcorr_backward(f1, pyr[0], co, ga, 3)
     torch.cuda.synchronize()
     print("prof_run altcorr done")
+if "altcorr16" in what:     # the fused backend lookup as bench.py's `altcorr` block runs it: f16 stereo buffer, one chunk of ~94 edges
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    import dropin_cases as D
+    from droid_b200 import corr as mirror
+    n, rig, ht, wd, E = 64, 2, 48, 64, int(os.environ.get("ALT16_EDGES", "94"))
+    g = torch.Generator(device=dev); g.manual_seed(33)
+    fmaps = torch.randn((n, rig, 128, ht, wd), device=dev, dtype=torch.float16, generator=g)
+    op = mirror.AltCorrBlock(fmaps.view(1, n * rig, 128, ht, wd))
+    rng = np.random.default_rng(5)
+    co = torch.from_numpy(D.smooth_coords(rng, E, ht, wd, wild=0.0)).to(dev)[None]
+    ii = torch.from_numpy(rng.integers(0, n, E)).to(dev); jj = torch.from_numpy(rng.integers(0, n, E)).to(dev)
+    for _ in range(3):
+        out = op(co, rig * ii, rig * jj + (ii == jj).long())
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        out = op(co, rig * ii, rig * jj + (ii == jj).long())
+    e1.record(); torch.cuda.synchronize()
+    print(f"prof_run altcorr16: {E} edges x 4 levels fused f16: {e0.elapsed_time(e1) / 10:.3f} ms per call")
+if "altcorr16" in what and os.environ.get("DB200_ALT_DBG", "0") not in ("", "0") and int(os.environ["DB200_ALT_DBG"]) & 16:
+    droid_backends.WAIT_TIMES = []
+    out = op(co, rig * ii, rig * jj + (ii == jj).long())
+    w = droid_backends.WAIT_TIMES[-1]
+    ctas = 148
+    names = ["prod: plan slot", "prod: A stage free", "prod: B stage free", "prod: TOTAL", "mma: plan", "mma: A landed", "mma: accumulator free",
+             "mma: B landed", "mma: TOTAL", "epi: plan", "epi: accumulator ready", "epi: TOTAL"]
+    for n_, v_ in zip(names, w):
+        print(f"   {n_:24s} {v_ / ctas / 1.9e3:9.1f} us per CTA")
 print("prof_run ok", what)
