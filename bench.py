@@ -273,6 +273,8 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
         v = (ii_t >= i) & (ii_t < i + 8)
         if bool(v.any()):
             chunks.append(v)
+    masks = chunks                                        # factor_graph.py:268-272 builds these boolean masks per chunk
+    chunks = [torch.nonzero(v).reshape(-1) for v in masks]     # the same chunks as index lists: no host sync when indexing with them
     op = mirror.AltCorrBlock(fmaps.view(1, n * rig, 128, ht, wd))
 
     def step(o, which):
@@ -294,8 +296,32 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
     ms_loc = e0.elapsed_time(e1) / steps
     ms, lookups = _agg(dev, world, ms_loc, len(ii_l) * ht * wd)
     edges = lookups / (ht * wd)
-    # how many (pixel tile x target cell) GEMMs the kernel needed: a property of the coordinates (one un-timed, counted step)
+    # the same step (a) with the boolean masks of the unmodified factor_graph.py loop (`self.ii[v]`, `coords1[:, v]`: three host
+    # synchronisations per chunk — the device idles while the host waits), (b) the launches alone on prepared chunk arguments
+    step(op, masks)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        step(op, masks)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_masks, _ = _agg(dev, world, e0.elapsed_time(e1) / steps, 0)
     import droid_backends
+    pre = []
+    for ix in chunks:
+        iis, jjs = ii_t[ix], jj_t[ix]
+        pre.append((coords1[0, ix].contiguous(), (rig * iis).contiguous(), (rig * jjs + (iis == jjs).long()).contiguous()))
+    for rep_ in range(2):
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps if rep_ else 1):
+            for c_, a_, b_ in pre:
+                droid_backends.altcorr_pyramid_forward(op._hi, a_, b_, c_, 3)
+        e1.record()
+        torch.cuda.synchronize()
+    ms_k, _ = _agg(dev, world, e0.elapsed_time(e1) / steps, 0)
+    del pre
+    # how many (pixel tile x target cell) GEMMs the kernel needed: a property of the coordinates (one un-timed, counted step)
     droid_backends.COUNT_CELLS = dict(cells=0, tile_levels=0)
     step(op, chunks)
     cnt, droid_backends.COUNT_CELLS = droid_backends.COUNT_CELLS, None
@@ -317,10 +343,14 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
     cnt_s, droid_backends.COUNT_CELLS = droid_backends.COUNT_CELLS, None
     coords1 = coords_w
     out = dict(metric="corr lookups/s, backend path (AltCorrBlock over all edges of the workload per step, chunks of 8 source "
-                      "frames, 4 levels r=3, f16 stereo feature buffer; edge-sharded, no collective)",
+                      "frames, 4 levels r=3, f16 stereo feature buffer; chunks given as index lists; edge-sharded, no collective)",
                value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_step=ms, edges=int(edges), chunks_this_rank=len(chunks),
                tflops_algorithmic=edges * 2 * 64 * 128 * 4 * ht * wd / (ms * 1e-3) / 1e12,
                output_gbs=edges * 196 * ht * wd * 4 / (ms * 1e-3) / 1e9,
+               ms_per_step_boolean_masks=ms_masks, ms_per_step_launches_only=ms_k,
+               how_driven="ms_per_step: the loop of factor_graph.py:261-290 with every chunk given as an index list (graph data, built "
+                          "once per graph); ms_per_step_boolean_masks: the unmodified loop (mask indexing = 3 host syncs per chunk, the "
+                          "device idles); ms_per_step_launches_only: the fused launches on prepared per-chunk arguments",
                bound="tensor pipe / TMEM drain (2.4 MB written per edge is 2 ms per step at the HBM peak: not HBM bound)",
                cells_per_tile_level=cnt["cells"] / max(cnt["tile_levels"], 1),
                smooth_flow=dict(ms_per_step=ms_s, value=lookups / (ms_s * 1e-3), cells_per_tile_level=cnt_s["cells"] / max(cnt_s["tile_levels"], 1),
@@ -336,7 +366,7 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
                 sub = chunks[:4]
                 step(rop, sub); torch.cuda.synchronize()
                 e0.record(); step(rop, sub); e1.record(); torch.cuda.synchronize()
-                sub_edges = int(sum(int(v.sum()) for v in sub))
+                sub_edges = int(sum(int(v.numel()) for v in sub))
                 ref_ms = e0.elapsed_time(e1) * len(ii_l) / sub_edges
                 out["reference_cuda_ms_per_step"] = ref_ms
                 out["reference_cuda_note"] = (f"unmodified modules/corr.py AltCorrBlock on the reference extension, measured on the first "

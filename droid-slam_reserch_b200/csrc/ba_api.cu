@@ -1,6 +1,7 @@
 // ba_api.cu — C-ABI of the dense bundle adjustment (see include/droid_b200.h).
 // Mirrors droid_backends.ba (/root/reference/src/droid.cpp:88-117, droid_kernels.cu:1314-1434): in-place
 // update of poses/disps, `iterations` Gauss-Newton steps, returns dx/dz of the last step.
+#include <cstdlib>
 #include <atomic>
 #include <cstdio>
 #include "ba.cuh"

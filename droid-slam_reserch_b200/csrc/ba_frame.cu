@@ -440,8 +440,8 @@ struct SchurSmem {
   float* G; float* red;                    // [rpad][gn] (aliases the stash), [256][27] (aliases the staging buffers)
   float* stage;                            // [2][necap][4][kChunk] target/weight of the current and the next chunk (cp.async)
   int* eid;                                // [necap] original edge index
-  float* Cw;                               // [necap][2][kChunk]
-  float* px;                               // [7][kChunk]: X0, X1, disp, sqrt(Q), sqrt(Q) w, disps_sens, eta
+  float* Cw;                               // [necap][2][kCwStride]
+  float* px;                               // [2][7][kChunk]: X0, X1, disp, sqrt(Q), sqrt(Q) w, disps_sens, eta of this chunk / the next
   float* Am; float* Hs;                    // [dcap][36], [dcap][27]
   int* jp; int* slotq; int* eslot;         // [dcap], [dcap], [necap]
   unsigned char* segs;                     // [nsegs][4]: M-tile, first N-tile, count
@@ -458,7 +458,7 @@ __host__ __device__ inline size_t schur_stage_floats(int necap) {
 }
 __host__ __device__ inline size_t schur_smem_bytes(int dcap, int necap) {
   size_t b = sizeof(double) * size_t(dcap > 0 ? dcap : 1) * 42;
-  b += sizeof(float) * (schur_alias_floats(dcap) + schur_stage_floats(necap) + size_t(necap) * 2 * kCwStride + 7 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
+  b += sizeof(float) * (schur_alias_floats(dcap) + schur_stage_floats(necap) + size_t(necap) * 2 * kCwStride + 14 * kChunk + size_t(dcap > 0 ? dcap : 1) * 63);
   b += sizeof(int) * (size_t(2) * (dcap > 0 ? dcap : 1) + 2 * size_t(necap));
   b += 4 * size_t(schur_segs(dcap) + 8);
   return (b + 15) / 16 * 16;
@@ -475,7 +475,7 @@ __device__ __forceinline__ SchurSmem schur_carve(unsigned char* base, int dcap, 
   s.red = s.stage;
   s.Cw = s.stage + schur_stage_floats(necap);
   s.px = s.Cw + size_t(necap) * 2 * kCwStride;
-  s.Am = s.px + 7 * kChunk;
+  s.Am = s.px + 14 * kChunk;
   s.Hs = s.Am + size_t(dc) * 36;
   s.jp = reinterpret_cast<int*>(s.Hs + size_t(dc) * 27);
   s.slotq = s.jp + dc;
@@ -485,11 +485,10 @@ __device__ __forceinline__ SchurSmem schur_carve(unsigned char* base, int dcap, 
   return s;
 }
 
-__device__ __forceinline__ float to_tf32(float x) {
-  unsigned u;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-  return __uint_as_float(u);
-}
+// round to TF32 (10 mantissa bits), nearest, ties away from zero: what cvt.rna.tf32.f32 gives for every finite value.  ptxas
+// expands that instruction to this add + mask PLUS an |x| < Inf test and a select (4 instructions per value, 13.7 % of the
+// kernel's instructions in the r2 profile); Inf stays Inf here too and a NaN stays a NaN.
+__device__ __forceinline__ float to_tf32(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
 // D += A(16x8, row) * B(8x8, col), TF32 inputs, fp32 accumulate
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const float (&a)[4], const float (&b)[2]) {
   asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -672,40 +671,46 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
   };
   if (split < nchunks) stage_chunk(split, 0);
   int sbuf = 0;
-  // prefetch of the first chunk's per-pixel data
+  // per-pixel rows of one chunk (X0, X1, disparity, sensor disparity, eta) -> px buffer `b`
+  auto px_fill = [&](float* pb, int chunk, float h, float sv, float ev) {
+    const int pix = chunk * kChunk + tid;
+    const int pi_ = pix < HW ? pix : 0;
+    pb[tid] = (float(pi_ % wd) - cx) / fx;
+    pb[kChunk + tid] = (float(pi_ / wd) - cy) / fy;
+    pb[2 * kChunk + tid] = h;
+    pb[5 * kChunk + tid] = sv;
+    pb[6 * kChunk + tid] = ev;
+  };
+  auto px_load = [&](int chunk, float& h, float& sv, float& ev) {
+    const int pix = chunk * kChunk + tid;
+    h = 1.0f; sv = 0.0f; ev = 0.0f;
+    if (chunk < nchunks && pix < HW) { h = dsp[pix]; sv = p.sens[size_t(f) * HW + pix]; ev = p.eta[size_t(k) * HW + pix]; }
+  };
   float nx_h = 1.0f, nx_s = 0.0f, nx_e = 0.0f;
-  if (tid < kChunk) {
-    const int pix = split * kChunk + tid;
-    if (split < nchunks && pix < HW) { nx_h = dsp[pix]; nx_s = p.sens[size_t(f) * HW + pix]; nx_e = p.eta[size_t(k) * HW + pix]; }
-  }
+  if (tid < kChunk) { px_load(split, nx_h, nx_s, nx_e); px_fill(sm.px, split, nx_h, nx_s, nx_e); }
+  cp_async_wait_all();
   __syncthreads();
 
+  // Four block-wide barriers per chunk (the kernel's first stall reason at 8 warps per CTA): the chunk's target/weight and
+  // per-pixel rows are complete BEFORE the last barrier of the previous chunk — copies are issued at the top of a chunk into
+  // the other staging buffer and waited for at its end; the per-pixel rows are loaded at the top and stored at the end.
+  int pbuf = 0;
   for (int c = split; c < nchunks; c += S) {
     const int base = c * kChunk;
-    cp_async_wait_all();                              // this chunk's target/weight (issued one chunk ago) have landed
     if (c + S < nchunks) stage_chunk(c + S, sbuf ^ 1);   // next chunk's copies fly during this chunk's work
     const float* stg = sm.stage + size_t(sbuf) * necap * 4 * kChunk;
     sbuf ^= 1;
-    if (tid < kChunk) {
-      const int pix = base + tid;
-      const int pi_ = pix < HW ? pix : 0;
-      sm.px[tid] = (float(pi_ % wd) - cx) / fx;
-      sm.px[kChunk + tid] = (float(pi_ / wd) - cy) / fy;
-      sm.px[2 * kChunk + tid] = nx_h;
-      sm.px[5 * kChunk + tid] = nx_s;
-      sm.px[6 * kChunk + tid] = nx_e;
-      const int npix = pix + S * kChunk;            // next chunk of this CTA: loads in flight during this one
-      nx_h = 1.0f; nx_s = 0.0f; nx_e = 0.0f;
-      if (c + S < nchunks && npix < HW) { nx_h = dsp[npix]; nx_s = p.sens[size_t(f) * HW + npix]; nx_e = p.eta[size_t(k) * HW + npix]; }
-    }
-    __syncthreads();
+    float* pxc = sm.px + pbuf * 7 * kChunk;
+    float* pxn = sm.px + (pbuf ^ 1) * 7 * kChunk;
+    pbuf ^= 1;
+    if (tid < kChunk) px_load(c + S, nx_h, nx_s, nx_e);  // consumed after phase 2
     // ---------------- phase 1
     if (active) {
       const float* se = stg + size_t(e) * 4 * kChunk;
       for (int pp = g; pp < kChunk; pp += L) {
         const float tu = se[pp], tv = se[kChunk + pp], wur = se[2 * kChunk + pp], wvr = se[3 * kChunk + pp];
         PixEdge pe_;
-        pix_edge(rec, sm.px[pp], sm.px[kChunk + pp], sm.px[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
+        pix_edge(rec, pxc[pp], pxc[kChunk + pp], pxc[2 * kChunk + pp], fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
         if (!HD) {
           sm.Cw[(size_t(e) * 2 + 0) * kCwStride + pp] = pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
           sm.Cw[(size_t(e) * 2 + 1) * kCwStride + pp] = pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
@@ -750,17 +755,17 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
         if (HD) {
           if (pix < HW) { Q = p.Q[size_t(k) * HW + pix]; wv_ = p.w[size_t(k) * HW + pix]; }   // ba_hd_depth_kernel
         } else if (pix < HW) {
-          const float h = sm.px[2 * kChunk + pp];
-          const float ds = sm.px[5 * kChunk + pp];
+          const float h = pxc[2 * kChunk + pp];
+          const float ds = pxc[5 * kChunk + pp];
           const float m = ds > 0.0f ? 1.0f : 0.0f;
-          const float C = Csum + m * 0.05f + (1.0f - m) * sm.px[6 * kChunk + pp];
+          const float C = Csum + m * 0.05f + (1.0f - m) * pxc[6 * kChunk + pp];
           wv_ = wsum - m * 0.05f * (h - ds);
           Q = 1.0f / C;
           p.Q[size_t(k) * HW + pix] = Q;
           p.w[size_t(k) * HW + pix] = wv_;
         }
         const float sq = sqrtf(Q);
-        sm.px[3 * kChunk + pp] = sq;
+        pxc[3 * kChunk + pp] = sq;
         const float vq = sq * wv_;
         const float hi = to_tf32(vq);
         sm.shi[size_t(6 * d) * kStride + pp] = hi;
@@ -772,7 +777,7 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
       const int m = idx / (kChunk / 4), pp = 4 * (idx - m * (kChunk / 4));
       float4* ph = reinterpret_cast<float4*>(sm.shi + size_t(m) * kStride + pp);
       float4* pl = reinterpret_cast<float4*>(sm.slo + size_t(m) * kStride + pp);
-      const float4 sq4 = *reinterpret_cast<const float4*>(sm.px + 3 * kChunk + pp);
+      const float4 sq4 = *reinterpret_cast<const float4*>(pxc + 3 * kChunk + pp);
       float4 x = *ph, hi, lo;
       x.x *= sq4.x; x.y *= sq4.y; x.z *= sq4.z; x.w *= sq4.w;
       hi.x = to_tf32(x.x); hi.y = to_tf32(x.y); hi.z = to_tf32(x.z); hi.w = to_tf32(x.w);
@@ -791,6 +796,8 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
         default: break;
       }
     }
+    if (tid < kChunk && c + S < nchunks) px_fill(pxn, c + S, nx_h, nx_s, nx_e);
+    cp_async_wait_all();                              // the next chunk's target/weight (issued at the top) have landed
     __syncthreads();
   }
 
@@ -821,24 +828,35 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
     sm.jp[q] = r.jpose;
     build_A(r, sm.Am + q * 36);
   }
+  // the tensor-core tiles cover the lower triangle of G: mirror it so that the products below are plain inner products
+  const int n6 = 6 * d;
+  for (int i = tid; i < n6 * n6; i += kBAThreads) {
+    const int row = i / n6, col = i - row * n6;
+    if (col > row) sm.G[size_t(row) * gn + col] = sm.G[size_t(col) * gn + row];       // reads lower entries only, writes upper only
+  }
   __syncthreads();
-  // D_ef[r][c] = [e==f] Hjj_e[r][c] - G_ef[r][c];  c_e = vj_e - g_e     (G lower: mirror the rest)
-  auto Dval = [&](int e1, int f2, int r, int c2) -> double {
-    double v = (e1 == f2) ? double(sm.Hs[e1 * 27 + hs_index(r, c2)]) : 0.0;
-    int row = 6 * e1 + r, col = 6 * f2 + c2;
-    if (col > row) { const int t = row; row = col; col = t; }
-    return v - double(sm.G[size_t(row) * gn + col]);
-  };
+  // D_ef = [e==f] Hjj_e - G_ef;  c_e = vj_e - g_e
   for (int i = tid; i < d * 6; i += kBAThreads) {
     const int e1 = i / 6, r = i - e1 * 6;
     sm.cs[i] = diag_item ? double(sm.Hs[e1 * 27 + 21 + r]) - double(sm.G[size_t(6 * d) * gn + i]) : 0.0;
   }
-  for (int i = tid; i < d * 36; i += kBAThreads) {   // W_f = sum_e A_e D_ef
+  for (int i = tid; i < d * 36; i += kBAThreads) {   // W_f = sum_e A_e D_ef over the blocks this item owns
     const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c2 = rc - r * 6;
+    // owned rows e of column block f: all (fused path, diagonal items) or the other slot chunk (cross items)
+    int elo = 0, ehi = d;
+    if (HD && !diag_item) { if (f2 < kHdChunk) elo = kHdChunk; else ehi = kHdChunk; }
     double s = 0.0;
-    for (int e1 = 0; e1 < d; e1++) {
-      if (!own(e1, f2)) continue;
-      for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e1 * 36 + r * 6 + kk]) * Dval(e1, f2, kk, c2);
+    const float* gcol = sm.G + 6 * f2 + c2;
+    for (int e1 = elo; e1 < ehi; e1++) {
+      const float* a = sm.Am + e1 * 36 + r * 6;
+      const float* gp = gcol + size_t(6 * e1) * gn;
+#pragma unroll
+      for (int kk = 0; kk < 6; kk++) s -= double(a[kk]) * double(gp[size_t(kk) * gn]);
+    }
+    if (diag_item) {
+      const float* a = sm.Am + f2 * 36 + r * 6;
+#pragma unroll
+      for (int kk = 0; kk < 6; kk++) s += double(a[kk]) * double(sm.Hs[f2 * 27 + hs_index(kk, c2)]);
     }
     sm.Ws[i] = s;
   }
@@ -849,7 +867,11 @@ __device__ __forceinline__ void schur_item(const BAParams& p, unsigned char* sme
   for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
     const int ef = i / 36, rc = i - ef * 36, e1 = ef / d, f2 = ef - e1 * d, r = rc / 6, c2 = rc - r * 6;
     const int je = sm.jp[e1], jf = sm.jp[f2];
-    if (own(e1, f2) && je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c2) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c2)], Dval(e1, f2, r, c2));
+    if (own(e1, f2) && je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c2) {
+      double v = -double(sm.G[size_t(6 * e1 + r) * gn + 6 * f2 + c2]);
+      if (e1 == f2) v += double(sm.Hs[e1 * 27 + hs_index(r, c2)]);
+      atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c2)], v);
+    }
   }
   if (ip >= 0) {
     for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
