@@ -17,7 +17,6 @@
 namespace db200 {
 
 constexpr int kBAThreads = 256;       // threads per CTA of the frame kernels = pixels per sub-tile
-constexpr int kEStride = kBAThreads + 1;  // padded pixel stride of the E stash (bank-conflict free)
 constexpr int kMaxDeg = 28;           // max pose edges per source frame on the fused one-CTA-per-frame path
 constexpr int kMaxStereo = 4;         // ... and max stereo (ii == jj) edges beside them; frames beyond either limit take the
 constexpr int kHdChunk = 14;          // high-degree path: work items (frame, pair of kHdChunk-slot chunks), ba_frame.cu

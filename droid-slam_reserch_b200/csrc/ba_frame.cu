@@ -15,7 +15,7 @@
 //           accumulators persistent in registers over the CTA's chunks.
 //   epilogue: fp64 6x6 transforms with A_e and scatter of this CTA's contribution into the reduced
 //           system with fp64 red.global.add (the only atomics; they carry ~d^2*36 values per CTA).
-// ba_frame_kernel<.,true> (motion-only BA): thread = pixel, shuffle-butterfly reduction of the 27 sums.
+// ba_motion_kernel (motion-only BA): thread = pixel, shuffle-butterfly reduction of the 27 sums.
 // HBM traffic per edge-pixel: target 8 B + weight 8 B (+ disp 4 B per keyframe-pixel) — the algorithmic
 // 20*HW*N + 16*HW*M of SURVEY.md §8d; the back-substitution re-reads weight (8 B) to recompute E.
 #include <cstdlib>
@@ -84,10 +84,6 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) 
   return v[0];
 }
 
-__device__ __forceinline__ int pair_index(int e, int f, int d) {  // e <= f
-  return e * d - (e * (e - 1)) / 2 + (f - e);
-}
-
 // A_e = [[R^T, 0], [-R^T [t]x, R^T]]  (J_i = -A_e J_j; adjSE3, droid_kernels.cu:79-94)
 __device__ __forceinline__ void build_A(const EdgeRec& r, float* A) {
   const float tx[9] = {0.0f, -r.t[2], r.t[1], r.t[2], 0.0f, -r.t[0], -r.t[1], r.t[0], 0.0f};
@@ -109,67 +105,47 @@ __device__ __forceinline__ int hs_index(int a, int b) {  // symmetric access int
 }
 
 // ------------------------------------------------------------------------------------------------
-// shared-memory carve-up (all sizes derive from `dcap` = max pose edges per frame in this launch)
+// motion-only BA (droid_kernels.cu:1336-1346 with motion_only = true: the depth terms are dropped, the pose system is
+// H = sum_e [A_e; I]^T Hjj_e [A_e; I]).  Shared-memory carve-up (sizes derive from `dcap` = pose edges handled per pass)
 struct FrameSmem {
-  float* stash;   // [dcap][6][kEStride]   (aliased by the epilogue item buffer)
-  float* Qs;      // [256]
-  float* Qws;     // [256]
-  float* wacc;    // [8][dcap][27]
   double* Ws;     // [dcap][36]
   double* cs;     // [dcap][6]
+  float* wacc;    // [8][dcap][27]
   float* Am;      // [dcap][36]
   float* Hs;      // [dcap][27]
   int* jp;        // [dcap]
   int* slotq;     // [dcap]
-  unsigned short* pr;  // [np_cap][2]
 };
 
-__host__ __device__ inline size_t stash_floats(int dcap, bool motion) {
-  if (motion) return 64;
-  size_t s = size_t(dcap) * 6 * kEStride;
-  const size_t min_items = 42 * 4 * 8;   // tiny d: room for a few epilogue items
-  return s < min_items ? min_items : s;
-}
-
-__host__ __device__ inline size_t frame_smem_bytes(int dcap, bool motion) {
-  const int np = dcap * (dcap + 1) / 2;
-  size_t b = 0;
-  b += sizeof(double) * size_t(dcap) * 42;                       // Ws, cs (first: 8-byte aligned)
-  b += sizeof(float) * (stash_floats(dcap, motion) + 512 + size_t(8) * dcap * 27 + size_t(dcap) * 63);
+__host__ __device__ inline size_t frame_smem_bytes(int dcap) {
+  size_t b = sizeof(double) * size_t(dcap) * 42;                  // Ws, cs (first: 8-byte aligned)
+  b += sizeof(float) * (size_t(8) * dcap * 27 + size_t(dcap) * 63);
   b += sizeof(int) * size_t(dcap) * 2;
-  b += sizeof(unsigned short) * 2 * size_t(np > 0 ? np : 1);
   return (b + 15) / 16 * 16;
 }
 
-__device__ __forceinline__ FrameSmem carve(unsigned char* base, int dcap, bool motion) {
+__device__ __forceinline__ FrameSmem carve(unsigned char* base, int dcap) {
   FrameSmem s;
   s.Ws = reinterpret_cast<double*>(base);
   s.cs = s.Ws + size_t(dcap) * 36;
-  s.stash = reinterpret_cast<float*>(s.cs + size_t(dcap) * 6);
-  s.Qs = s.stash + stash_floats(dcap, motion);
-  s.Qws = s.Qs + 256;
-  s.wacc = s.Qws + 256;
+  s.wacc = reinterpret_cast<float*>(s.cs + size_t(dcap) * 6);
   s.Am = s.wacc + size_t(8) * dcap * 27;
   s.Hs = s.Am + size_t(dcap) * 36;
   s.jp = reinterpret_cast<int*>(s.Hs + size_t(dcap) * 27);
   s.slotq = s.jp + dcap;
-  s.pr = reinterpret_cast<unsigned short*>(s.slotq + dcap);
   return s;
 }
 
-// ------------------------------------------------------------------------------------------------
-// grid = Mcap * S CTAs; CTA (k, s) handles sub-tiles s, s+S, ... of source frame kx[k].
-// Non-motion launches are bucketed by degree: only frames with dlo <= nd[k] <= dcap do work here.
-template <int PPT, bool MOTION>
+// grid = Mcap * S CTAs; CTA (k, s) handles sub-tiles s, s+S, ... of source frame kx[k], thread = pixel.  The pose edges of
+// the frame are handled in passes of `dcap` slots (no cross-edge coupling without the depth terms: any degree).
 __global__ void __launch_bounds__(kBAThreads)
-ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
+ba_motion_kernel(BAParams p, int S, int dcap) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   if (p.hdr->status < 0) return;
   const int k = blockIdx.x / S, split = blockIdx.x - k * S;
   if (k >= p.hdr->M) return;
   const int dtot = p.nd[k];
-  if (!MOTION && (dtot < dlo || dtot > dcap)) return;
-  const FrameSmem sm = carve(smem_raw, dcap, MOTION);
+  const FrameSmem sm = carve(smem_raw, dcap);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int f = p.kx[k];
   if (f < p.own_lo || f >= p.own_hi) return;       // depth map owned by another rank
@@ -180,43 +156,15 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
   const int nsub = cdiv(HW, kBAThreads);
   const float* dsp = p.disps + size_t(f) * HW;
 
-  // MOTION handles its pose edges in chunks of `dcap` slots (no cross-edge coupling); the fused path
-  // has exactly one chunk (dtot <= dcap).
-  for (int c0 = 0; c0 < (MOTION ? max(dtot, 1) : 1); c0 += dcap) {
-    const int d = MOTION ? min(dcap, dtot - c0) : dtot;   // pose edges in this chunk
-    const int np = d * (d + 1) / 2;
-    int kg = 1;
-    if (!MOTION && np > 0) {
-      kg = min(4, (kBAThreads * PPT) / np);
-      while (kg > 1 && size_t(np) * kg * 42 > stash_floats(dcap, false)) kg--;
-    }
-    const int items = np * kg;
+  for (int c0 = 0; c0 < dtot; c0 += dcap) {
+    const int d = min(dcap, dtot - c0);             // pose edges in this pass
     __syncthreads();
     for (int i = tid; i < 8 * dcap * 27; i += kBAThreads) sm.wacc[i] = 0.0f;
-    if (!MOTION) {
-      for (int e = tid; e < d; e += kBAThreads) {      // pair table: rows of pair (e, f>=e) are consecutive
-        int pidx = pair_index(e, e, d);
-        for (int g = e; g < d; g++) { sm.pr[2 * pidx] = (unsigned short)e; sm.pr[2 * pidx + 1] = (unsigned short)g; pidx++; }
-      }
-    }
     for (int qq = tid; qq < ne; qq += kBAThreads) {    // slot -> sorted edge position
       const int sl = p.erec[q_beg + qq].slot - c0;
       if (sl >= 0 && sl < d) sm.slotq[sl] = q_beg + qq;
     }
     __syncthreads();
-
-    float acc[PPT][36], gacc[PPT][6];
-    int pe[PPT], pf[PPT], pg[PPT];
-#pragma unroll
-    for (int s = 0; s < PPT; s++) {
-#pragma unroll
-      for (int i = 0; i < 36; i++) acc[s][i] = 0.0f;
-#pragma unroll
-      for (int i = 0; i < 6; i++) gacc[s][i] = 0.0f;
-      const int item = tid + kBAThreads * s;
-      if (!MOTION && item < items) { const int pi = item / kg; pe[s] = sm.pr[2 * pi]; pf[s] = sm.pr[2 * pi + 1]; pg[s] = item - pi * kg; }
-      else { pe[s] = -1; pf[s] = 0; pg[s] = 0; }
-    }
 
     for (int sub = split; sub < nsub; sub += S) {
       const int pix = sub * kBAThreads + tid;
@@ -224,30 +172,16 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
       const int pi_ = inb ? pix : 0;
       const float h = inb ? dsp[pi_] : 1.0f;
       const float X0 = (float(pi_ % wd) - cx) / fx, X1 = (float(pi_ / wd) - cy) / fy;
-      float Csum = 0.0f, wsum = 0.0f;
-      // ---------------- phase 1
       for (int qq = 0; qq < ne; qq++) {
         const EdgeRec r = load_rec(p.erec + q_beg + qq);
         const int sl = (r.slot < 0) ? -1 : r.slot - c0;
-        if (MOTION && (sl < 0 || sl >= d)) continue;
-        if (!MOTION && c0 != 0) continue;
+        if (sl < 0 || sl >= d) continue;            // stereo edges carry depth terms only: nothing to do here
         const float* tg = p.target + size_t(r.eid) * 2 * HW;
         const float* wg = p.weight + size_t(r.eid) * 2 * HW;
         const float tu = inb ? __ldg(tg + pi_) : 0.0f, tv = inb ? __ldg(tg + HW + pi_) : 0.0f;
         const float wur = inb ? __ldg(wg + pi_) : 0.0f, wvr = inb ? __ldg(wg + HW + pi_) : 0.0f;
         PixEdge pe_;
         pix_edge(r, X0, X1, h, fx, fy, cx, cy, tu, tv, wur, wvr, pe_);
-        if (!MOTION) {
-          Csum += pe_.wu * pe_.Jzu * pe_.Jzu + pe_.wv * pe_.Jzv * pe_.Jzv;   // Cii (:320,353)
-          wsum += pe_.wu * pe_.ru * pe_.Jzu + pe_.wv * pe_.rv * pe_.Jzv;     // bz  (:321,354)
-        }
-        if (sl < 0) continue;                                                 // stereo edge: depth terms only
-        const float au = pe_.wu * pe_.Jzu, av = pe_.wv * pe_.Jzv;
-        if (!MOTION) {
-          float* st = sm.stash + size_t(sl) * 6 * kEStride + tid;
-#pragma unroll
-          for (int n = 0; n < 6; n++) st[n * kEStride] = au * pe_.Ju[n] + av * pe_.Jv[n];   // Eij (:339,372)
-        }
         float hv[32];
         {
           float wJu[6], wJv[6];
@@ -271,69 +205,10 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
         const float tot = warp_transpose_sum32(hv, lane);
         if (lane < 27) sm.wacc[(size_t(warp) * dcap + sl) * 27 + lane] += tot;
       }
-      if (!MOTION) {
-        // depth system of this pixel (:1396-1400): C = sum Cii + m*alpha + (1-m)*eta; w = sum bz - m*alpha*(d - d_sens)
-        float Q = 0.0f, wv_ = 0.0f;
-        if (inb) {
-          const float ds = p.sens[size_t(f) * HW + pix];
-          const float m = ds > 0.0f ? 1.0f : 0.0f;
-          const float C = Csum + m * 0.05f + (1.0f - m) * p.eta[size_t(k) * HW + pix];
-          wv_ = wsum - m * 0.05f * (h - ds);
-          Q = 1.0f / C;
-          p.Q[size_t(k) * HW + pix] = Q;
-          p.w[size_t(k) * HW + pix] = wv_;
-        }
-        sm.Qs[tid] = inb ? Q : 0.0f;
-        sm.Qws[tid] = inb ? Q * wv_ : 0.0f;
-        if (!inb) {   // keep the stash finite for padded pixels
-          for (int sl = 0; sl < d; sl++)
-            for (int n = 0; n < 6; n++) sm.stash[(size_t(sl) * 6 + n) * kEStride + tid] = 0.0f;
-        }
-        __syncthreads();
-        // ---------------- phase 2: G_ef += (E_e Q) E_f^T, g_e += E_e (Q w)   (EEt6x6/Ev6x1, :1001-1093)
-#pragma unroll
-        for (int s = 0; s < PPT; s++) {
-          if (pe[s] < 0) continue;
-          const float* Ee = sm.stash + size_t(pe[s]) * 6 * kEStride;
-          const float* Ef = sm.stash + size_t(pf[s]) * 6 * kEStride;
-          const bool diag = pe[s] == pf[s];
-          for (int px = pg[s]; px < kBAThreads; px += kg) {
-            const float q = sm.Qs[px];
-            float ee[6], ff[6];
-#pragma unroll
-            for (int n = 0; n < 6; n++) { ee[n] = Ee[n * kEStride + px]; ff[n] = Ef[n * kEStride + px]; }
-            if (diag) {
-              const float qw = sm.Qws[px];
-#pragma unroll
-              for (int n = 0; n < 6; n++) gacc[s][n] = fmaf(qw, ee[n], gacc[s][n]);
-            }
-#pragma unroll
-            for (int n = 0; n < 6; n++) {
-              const float eq = ee[n] * q;
-#pragma unroll
-              for (int m = 0; m < 6; m++) acc[s][n * 6 + m] = fmaf(eq, ff[m], acc[s][n * 6 + m]);
-            }
-          }
-        }
-        __syncthreads();
-      }
     }
     __syncthreads();
 
-    // ---------------- epilogue: reduce, transform with A_e in fp64, scatter into the reduced system
-    float* itembuf = sm.stash;                       // [items][42], aliases the stash (phase 2 is done)
-    if (!MOTION) {
-#pragma unroll
-      for (int s = 0; s < PPT; s++) {
-        const int item = tid + kBAThreads * s;
-        if (pe[s] >= 0) {
-#pragma unroll
-          for (int i = 0; i < 36; i++) itembuf[size_t(item) * 42 + i] = acc[s][i];
-#pragma unroll
-          for (int i = 0; i < 6; i++) itembuf[size_t(item) * 42 + 36 + i] = gacc[s][i];
-        }
-      }
-    }
+    // ---------------- epilogue: reduce, transform with A_e in fp64, scatter into the pose system
     for (int i = tid; i < d * 27; i += kBAThreads) {  // per-edge sums over the 8 warps, fixed order
       float s = 0.0f;
       for (int w = 0; w < 8; w++) s += sm.wacc[size_t(w) * dcap * 27 + i];
@@ -345,61 +220,33 @@ ba_frame_kernel(BAParams p, int S, int dlo, int dcap) {
       build_A(r, sm.Am + e * 36);
     }
     __syncthreads();
-    if (!MOTION) {                                     // sum the k-groups of each pair into its first item
-      for (int i = tid; i < np * 42; i += kBAThreads) {
-        const int pi = i / 42, c = i - pi * 42;
-        float s = 0.0f;
-        for (int g = 0; g < kg; g++) s += itembuf[(size_t(pi) * kg + g) * 42 + c];
-        itembuf[size_t(pi) * kg * 42 + c] = s;
-      }
-      __syncthreads();
-    }
-    // D_ef[r][c] = [e==f] Hjj_e[r][c] - G_ef[r][c];  c_e = vj_e - g_e
-    auto Dval = [&](int e, int f2, int r, int c) -> double {
-      double v = (e == f2) ? double(sm.Hs[e * 27 + hs_index(r, c)]) : 0.0;
-      if (!MOTION) {
-        v -= (e <= f2) ? double(itembuf[size_t(pair_index(e, f2, d)) * kg * 42 + r * 6 + c])
-                       : double(itembuf[size_t(pair_index(f2, e, d)) * kg * 42 + c * 6 + r]);
-      }
-      return v;
-    };
-    for (int i = tid; i < d * 6; i += kBAThreads) {
-      const int e = i / 6, r = i - e * 6;
-      double v = double(sm.Hs[e * 27 + 21 + r]);
-      if (!MOTION) v -= double(itembuf[size_t(pair_index(e, e, d)) * kg * 42 + 36 + r]);
-      sm.cs[i] = v;
-    }
-    for (int i = tid; i < d * 36; i += kBAThreads) {   // W_f = sum_e A_e D_ef
-      const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c = rc - r * 6;
+    for (int i = tid; i < d * 6; i += kBAThreads) sm.cs[i] = double(sm.Hs[(i / 6) * 27 + 21 + (i % 6)]);    // c_e = vj_e
+    for (int i = tid; i < d * 36; i += kBAThreads) {   // W_e = A_e Hjj_e
+      const int e = i / 36, rc = i - e * 36, r = rc / 6, c = rc - r * 6;
       double s = 0.0;
-      for (int e = 0; e < d; e++)
-        for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e * 36 + r * 6 + kk]) * Dval(e, f2, kk, c);
+      for (int kk = 0; kk < 6; kk++) s += double(sm.Am[e * 36 + r * 6 + kk]) * double(sm.Hs[e * 27 + hs_index(kk, c)]);
       sm.Ws[i] = s;
     }
     __syncthreads();
     const int n = p.n;
     double* H = p.Hb;
     double* bvec = p.Hb + sys_h_elems(n);
-    for (int i = tid; i < d * d * 36; i += kBAThreads) {   // (j_e, j_f) += D_ef
-      const int ef = i / 36, rc = i - ef * 36, e = ef / d, f2 = ef - e * d, r = rc / 6, c = rc - r * 6;
-      const int je = sm.jp[e], jf = sm.jp[f2];
-      if (je >= 0 && jf >= 0 && 6 * je + r >= 6 * jf + c) atomicAdd(&H[sys_index(6 * je + r, 6 * jf + c)], Dval(e, f2, r, c));
+    for (int i = tid; i < d * 36; i += kBAThreads) {
+      const int e = i / 36, rc = i - e * 36, r = rc / 6, c = rc - r * 6;
+      const int je = sm.jp[e];
+      if (je < 0) continue;
+      if (r >= c) atomicAdd(&H[sys_index(6 * je + r, 6 * je + c)], double(sm.Hs[e * 27 + hs_index(r, c)]));   // (j_e, j_e) += Hjj_e
+      if (ip >= 0) {                                       // (i, j_e) += -W_e ; (j_e, i) += -W_e^T: one of the two is in the lower triangle
+        const int ra = 6 * ip + r, ca = 6 * je + c;
+        atomicAdd(&H[ra >= ca ? sys_index(ra, ca) : sys_index(ca, ra)], -sm.Ws[i]);
+      }
     }
     if (ip >= 0) {
-      for (int i = tid; i < d * 36; i += kBAThreads) {     // (i, j_f) += -W_f ; (j_f, i) += -W_f^T
-        const int f2 = i / 36, rc = i - f2 * 36, r = rc / 6, c = rc - r * 6;
-        const int jf = sm.jp[f2];
-        if (jf >= 0) {
-          const double v = -sm.Ws[i];
-          const int ra = 6 * ip + r, ca = 6 * jf + c;      // the element and its mirror: one of them is in the lower triangle
-          atomicAdd(&H[ra >= ca ? sys_index(ra, ca) : sys_index(ca, ra)], v);
-        }
-      }
-      if (tid < 36) {                                      // (i, i) += sum_f W_f A_f^T
+      if (tid < 36) {                                      // (i, i) += sum_e W_e A_e^T
         const int r = tid / 6, c = tid - r * 6;
         double s = 0.0;
-        for (int f2 = 0; f2 < d; f2++)
-          for (int kk = 0; kk < 6; kk++) s += sm.Ws[f2 * 36 + r * 6 + kk] * double(sm.Am[f2 * 36 + c * 6 + kk]);
+        for (int e = 0; e < d; e++)
+          for (int kk = 0; kk < 6; kk++) s += sm.Ws[e * 36 + r * 6 + kk] * double(sm.Am[e * 36 + c * 6 + kk]);
         if (r >= c) atomicAdd(&H[sys_index(6 * ip + r, 6 * ip + c)], s);
       } else if (tid >= 64 && tid < 70) {                  // b_i += -sum_e A_e c_e
         const int r = tid - 64;
@@ -1015,12 +862,10 @@ ba_backsub_kernel(BAParams p, float* __restrict__ dz_out) {
   if (dz_out) dz_out[o] = dz;
 }
 
-template <int PPT, bool MOTION>
-static int launch_frames(const BAParams& p, int S, int dlo, int dcap, cudaStream_t st) {
-  const size_t smem = frame_smem_bytes(dcap, MOTION);
-  auto kern = ba_frame_kernel<PPT, MOTION>;
-  if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  kern<<<p.Mcap * S, kBAThreads, smem, st>>>(p, S, dlo, dcap);
+static int launch_motion(const BAParams& p, int S, int dcap, cudaStream_t st) {
+  const size_t smem = frame_smem_bytes(dcap);
+  if (smem > 48 * 1024) DB200_CUDA(cudaFuncSetAttribute(ba_motion_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  ba_motion_kernel<<<p.Mcap * S, kBAThreads, smem, st>>>(p, S, dcap);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }
@@ -1081,7 +926,7 @@ int ba_accumulate_frames(const BAParams& p, cudaStream_t st) {
     const int nsub = cdiv(p.HW, kBAThreads);
     int S = cdiv(4 * kNumSMs, p.Mcap);
     S = S < 1 ? 1 : (S > nsub ? nsub : S);
-    return launch_frames<1, true>(p, S, 0, 32, st);
+    return launch_motion(p, S, 32, st);
   }
   const int nchunks = cdiv(p.HW, kChunk);
   // CTAs per launch: ~6 per SM for backend graphs (hundreds of frames); a frontend window (8..25 frames) is fastest with

@@ -132,3 +132,14 @@ def test_ba_high_degree_repeatable_and_status_ok():
             first = dx
         else:
             assert rel(dx, first) < 1e-8
+
+
+def test_ba_motion_only_hub_frame():
+    """motion-only BA has no cross-edge coupling (no depth terms): ba_motion_kernel handles a frame of any degree in passes
+    of 32 slots — here 45 pose edges = two passes, plus a stereo edge that must contribute nothing"""
+    from droid_b200 import synth
+    n_kf = 60
+    ii, jj = synth.hub_edges(n_kf, {10: 45}, np.random.default_rng(21))
+    ii, jj = np.concatenate([ii, [10]]), np.concatenate([jj, [10]])
+    p = synth.make_ba_problem(ii, jj, n_kf, seed=21)
+    check(p, 2, 1e-4, 0.1, motion_only=True)
