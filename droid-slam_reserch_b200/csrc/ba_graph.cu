@@ -98,42 +98,47 @@ __global__ void graph_offsets_kernel(BAParams p) {   // single thread block, ser
   }
 }
 
-// one CTA per depth row k: ordered (stable) fill of its edges, and pose-edge slots
+// O(N): every edge takes the next free position of its source frame's segment (arrival order, not yet the final order)
+__global__ void graph_scatter_kernel(BAParams p) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= p.N || p.hdr->status < 0) return;
+  const int k = p.frame_k[p.ii[e]];
+  const int pos = atomicAdd(&p.fill[k], 1);
+  p.edge_order[p.deg_off[k] + pos] = e;
+}
+
+// one CTA per depth row k: its edges in the order of their edge ids (the reference's stable argsort, droid_kernels.cu:948-998
+// — and the order the fp32 sums of a frame are formed in, so results do not depend on the arrival order above), and the
+// pose-edge slots.  Rank of an edge = number of edges of the segment with a smaller id: O(sum_k ne_k^2) instead of the
+// M x N scan of the first version (ne ~ 12; 0.5 GB of index reads per call at 1536 frames x 20 000 edges).
+constexpr int kFillStage = 1024;           // segment entries staged in shared memory; longer segments rank from global memory
 __global__ void graph_fill_kernel(BAParams p) {
   if (p.hdr->status < 0) return;
   const int k = blockIdx.x;
   if (k >= p.hdr->M) return;
   const int f = p.kx[k];
-  const int base = p.deg_off[k];
-  __shared__ int s_count, s_slots;
-  __shared__ int s_warp[8], s_warp2[8];
-  if (threadIdx.x == 0) { s_count = 0; s_slots = 0; }
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int e0 = 0; e0 < p.N; e0 += blockDim.x) {
-    const int e = e0 + threadIdx.x;
-    const bool mine = (e < p.N) && (p.ii[e] == f);
-    const bool pose = mine && (p.jj[e] != f);
-    const unsigned bm = __ballot_sync(0xffffffffu, mine), bp = __ballot_sync(0xffffffffu, pose);
-    if (lane == 0) { s_warp[warp] = __popc(bm); s_warp2[warp] = __popc(bp); }
+  const int base = p.deg_off[k], ne = p.deg_off[k + 1] - base;
+  const int* seg = p.edge_order + base;
+  __shared__ int s_key[kFillStage];          // (edge id << 1) | is-pose-edge: ordered like the edge ids
+  auto key = [&](int b) -> int { const int e2 = seg[b]; return (e2 << 1) | int(p.jj[e2] != f); };
+  const bool staged = ne <= kFillStage;
+  if (staged) {
+    for (int a = threadIdx.x; a < ne; a += blockDim.x) s_key[a] = key(a);
     __syncthreads();
-    int off = s_count, off2 = s_slots;
-    for (int w = 0; w < warp; w++) { off += s_warp[w]; off2 += s_warp2[w]; }
-    const unsigned lt = (1u << lane) - 1u;
-    if (mine) {
-      const int q = base + off + __popc(bm & lt);
-      p.edge_order[q] = e;
-      EdgeRec& r = p.erec[q];
-      r.eid = e;
-      r.jpose = int(p.jj[e]) - p.t0;
-      r.slot = pose ? (off2 + __popc(bp & lt)) : -1;
-      r.pad = 0;
+  }
+  for (int a = threadIdx.x; a < ne; a += blockDim.x) {
+    const int v = staged ? s_key[a] : key(a);
+    int rank = 0, slot = 0;
+    for (int b = 0; b < ne; b++) {
+      const int w = staged ? s_key[b] : key(b);
+      if (w < v) { rank++; slot += w & 1; }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int w = 0; w < 8; w++) { s_count += s_warp[w]; s_slots += s_warp2[w]; }
-    }
-    __syncthreads();
+    const int e = v >> 1;
+    EdgeRec& r = p.erec[base + rank];
+    r.eid = e;
+    r.jpose = int(p.jj[e]) - p.t0;
+    r.slot = (v & 1) ? slot : -1;
+    r.pad = 0;
   }
 }
 
@@ -168,8 +173,9 @@ int ba_build_graph(const BAParams& p, cudaStream_t st) {
   graph_scan_kernel<<<1, 1024, 0, st>>>(p);
   if (p.N > 0) graph_degree_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
   graph_offsets_kernel<<<1, 32, 0, st>>>(p);
-  if (p.N > 0) graph_fill_kernel<<<p.Mcap, 256, 0, st>>>(p);
-  DB200_COUNT(p.N > 0 ? 5 : 2);
+  if (p.N > 0) graph_scatter_kernel<<<cdiv(p.N, 256), 256, 0, st>>>(p);
+  if (p.N > 0) graph_fill_kernel<<<p.Mcap, 128, 0, st>>>(p);
+  DB200_COUNT(p.N > 0 ? 6 : 2);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
 }

@@ -143,3 +143,16 @@ def test_ba_motion_only_hub_frame():
     ii, jj = np.concatenate([ii, [10]]), np.concatenate([jj, [10]])
     p = synth.make_ba_problem(ii, jj, n_kf, seed=21)
     check(p, 2, 1e-4, 0.1, motion_only=True)
+
+
+def test_ba_frame_with_more_than_1024_edges():
+    """graph build: a segment longer than the 1024 entries `graph_fill_kernel` stages in shared memory is ranked from global
+    memory — 1100 stereo (ii == jj) duplicates on one frame of a small neighbourhood graph (depth terms of all of them
+    enter C and w in edge order; no pose blocks), edge list shuffled so that arrival order != edge order"""
+    from droid_b200 import synth
+    rng = np.random.default_rng(8)
+    ii, jj = synth.neighborhood_edges(0, 8, 3)
+    ii, jj = np.concatenate([ii, np.full(1100, 4)]), np.concatenate([jj, np.full(1100, 4)])
+    perm = rng.permutation(len(ii))
+    p = synth.make_ba_problem(ii[perm], jj[perm], 8, ht=16, wd=24, seed=14)
+    check(p, 2, 1e-4, 0.1)
