@@ -200,6 +200,24 @@ def test_ba_solver_regimes_parity_and_repeatability(n_kf):
             assert rel(dx, first) < 1e-7
 
 
+@pytest.mark.parametrize("n_kf", [700, 1024])
+def test_ba_solver_intermediate_schedules(n_kf):
+    """Between c3 (48 tiles per side: 16 diagonal CTAs) and c4 (144 tiles: 8) the number of diagonal CTAs follows 8 G / nt:
+    700 keyframes -> 66 tiles, 16 diagonal CTAs; a full 1024-frame buffer -> 96 tiles, 12.  The solve stage alone (no oracle
+    run at this size): the GPU's dx against an fp64 solve of the GPU's own reduced system, and the same update twice."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from ba_system import check_solve
+    from droid_b200 import synth
+    p = synth.config_c3(seed=3000 + n_kf, n_kf=n_kf, n_edges=8 * n_kf, ht=16, wd=24)
+    e = check_solve(p, 1e-5, 1e-2)
+    print(f"{n_kf} keyframes: dx vs fp64 solve of the GPU system {e:.1e}")
+    _, _, dx1, _ = run_gpu(p, 1, 1e-5, 1e-2)
+    _, _, dx2, _ = run_gpu(p, 1, 1e-5, 1e-2)
+    assert np.isfinite(dx1).all() and rel(dx2, dx1) < 1e-7
+
+
 def test_ba_backend_graph_full_resolution_parity():
     """Backend-like graph at the full 48x64 map size with hundreds of edges per GPU wave — the regime of c3, where the
     accumulate stage uses few splits per frame and its fp32 chains are longest.  Two precision bugs lived here unseen while
