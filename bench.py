@@ -766,10 +766,15 @@ def main_gpu(args, rank, world):
         e_lo, e_hi = int(np.searchsorted(runner.kx_all, f_lo)), int(np.searchsorted(runner.kx_all, f_hi))
         eta_full, disps_full = t(p.eta), t(p.disps)
         h_in = [pin(a) for a in (p.target[sel], p.weight[sel], p.eta[e_lo:e_hi], p.ii[sel], p.jj[sel], p.poses, p.disps[f_lo:f_hi])]
-    h_poses, h_disps = torch.empty_like(h_in[5]), torch.empty(p.disps.shape, dtype=torch.float32).pin_memory()
+    # results read back every step: poses and dx (replicated) and the disparity rows this rank owns (all of them at N = 1)
+    h_poses, h_disps = torch.empty_like(h_in[5]), torch.empty(h_in[6].shape, dtype=torch.float32).pin_memory()
     h_dx = torch.empty((P, 6), dtype=torch.float32).pin_memory()
     h2d = sum(a.numel() * a.element_size() for a in h_in)
     d2h = sum(a.numel() * a.element_size() for a in (h_poses, h_disps, h_dx))
+    if world > 1:                                      # whole-job bytes per step: summed over the ranks
+        bb = torch.tensor([h2d, d2h], device=dev, dtype=torch.int64)
+        dist.all_reduce(bb, op=dist.ReduceOp.SUM)
+        h2d, d2h = int(bb[0].item()), int(bb[1].item())
     # Every step uploads ITS inputs from pinned host memory and reads ITS result back; the upload of step k+1 runs on
     # a copy stream while step k's kernels run (droid_b200/staging.py) — the caller still synchronises on every result.
     from droid_b200.staging import HostStagedCalls
@@ -785,7 +790,8 @@ def main_gpu(args, rank, world):
             eta_full[e_lo:e_hi].copy_(et); disps_full[f_lo:f_hi].copy_(di)      # device-to-device, into the full-size tensors
             di = disps_full
             dx, _ = runner.ba(po, di, intr, sens, tg, wg, eta_full, ITRS, LM, EP)
-        h_poses.copy_(po, non_blocking=True); h_disps.copy_(di, non_blocking=True); h_dx.copy_(dx, non_blocking=True)
+        h_poses.copy_(po, non_blocking=True); h_dx.copy_(dx, non_blocking=True)
+        h_disps.copy_(di if world == 1 else di[f_lo:f_hi], non_blocking=True)
         staged.release()
         torch.cuda.current_stream().synchronize()      # the caller reads the result every step
 
@@ -871,7 +877,8 @@ def main_gpu(args, rank, world):
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, steps=e2e_steps,
                          ms_per_step=ms_e2e / e2e_steps,
                          staging="double-buffered: upload of step k+1 (copy stream) overlaps the kernels of step k; "
-                                 "result of every step read back and synchronised"),
+                                 "result of every step read back and synchronised; at N > 1 every rank uploads its shard and reads "
+                                 "back poses, dx and the disparity rows it owns, bytes summed over the ranks"),
                 gpu_launches=int(launches), roofline=roofline, stages=stage, clocks=clocks)
     if parity is not None:
         line["parity"] = parity
