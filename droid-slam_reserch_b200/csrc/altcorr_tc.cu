@@ -13,7 +13,7 @@
 // bounding corner of the tile's windows + a 64-bit mask of 8x8 cells relative to it); arbitrary coordinates just touch
 // more cells, so there is no "fast path only for smooth flow" — results are the reference's for any input.
 //
-// One persistent CTA per SM, 18 warps:
+// One persistent CTA per SM, 19 warps (warp 18 = a second MMA issuer for the odd cells):
 //   warp 0      producer: reads the tile's coordinates, computes per level the cell origin + mask (warp reductions),
 //               publishes them, then feeds the A tile (128 pixels x 128 channels, TMA 4-D box, 128B swizzle) and a ring
 //               of B cells (TMA zero-fills positions outside the image = the reference's `within_bounds` skip);
@@ -41,7 +41,8 @@ constexpr int kATPy = 8, kATPx = 16;                   // pixel tile
 constexpr int kATCy = 8, kATCx = 16;                   // fmap2 cell
 constexpr int kATMaxL = 4;
 constexpr int kATEpiWarps = 16;                      // 4 per TMEM lane quarter: one 32-column chunk (2 cell rows) each
-constexpr int kATThreads = 64 + 32 * kATEpiWarps;      // 576
+constexpr int kATMmaWarpB = 2 + kATEpiWarps;            // warp 18: the second MMA issuer (odd cells); warp 1 takes the even ones
+constexpr int kATThreads = 64 + 32 * kATEpiWarps + 32;  // 608
 constexpr uint32_t kATBlk = 128 * 64 * 2;              // one [128 rows][64 halfs] swizzled block: 16 KB
 constexpr uint32_t kATARegion = 4 * kATBlk;            // 64 KB: one hi+lo A tile, or two hi-only A tiles
 constexpr uint32_t kATBRegion = 8 * kATBlk;            // 128 KB: two hi+lo cells, or four hi-only cells
@@ -221,9 +222,10 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
 
   if (tid == 0) {
     for (int i = 0; i < 16; i++) mbar_init(smem_u32(&bars[i]), 1);
+    mbar_init(a_empty(0), 2); mbar_init(a_empty(1), 2);                    // both MMA issuers release an A tile
     for (int i = 0; i < 4; i++) mbar_init(t_empty(i), kATEpiWarps);
     mbar_init(i_full(0), 1); mbar_init(i_full(1), 1);
-    mbar_init(i_empty(0), 1 + kATEpiWarps); mbar_init(i_empty(1), 1 + kATEpiWarps);
+    mbar_init(i_empty(0), 2 + kATEpiWarps); mbar_init(i_empty(1), 2 + kATEpiWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -305,9 +307,14 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
       atomicAdd(reinterpret_cast<unsigned long long*>(dt + 2), static_cast<unsigned long long>(tw[2]));
       atomicAdd(reinterpret_cast<unsigned long long*>(dt + 3), static_cast<unsigned long long>(clock64() - t_start));
     }
-  } else if (warp == 1) {
-    // ===================================================================== MMA issuer
+  } else if (warp == 1 || warp == kATMmaWarpB) {
+    // ===================================================================== MMA issuers
+    // Two single-thread issuers: the fixed cost of a cell in the issuing thread (8 tcgen05.mma, two commits, two or three
+    // barrier waits: ~0.65 us) exceeded the epilogue's once that was trimmed; cells alternate between the two threads by the
+    // parity of the running cell counter (ring stage and accumulator follow from the same counter, so each thread has its own
+    // stages {par, par + 2} and accumulators {par, par + 2}); both wait for the A tile and both release it (count 2).
     if (lane == 0) {
+      const uint32_t par = (warp == 1) ? 0u : 1u;
       uint32_t it = 0;
       int k = 0;
       bool dead = false;
@@ -321,6 +328,7 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         if (!twait(1, a_full(as), (k >> na_shift) & 1)) { atomicExch(P.status, 1); break; }
         const uint32_t aT = sA + uint32_t(as) * tile_bytes;
         for (int c = 0; c < cells; c++, it++) {
+          if ((P.dbg & 64) ? (par != 0u) : ((it & 1u) != par)) continue;     // dbg 64: issuer A takes every cell
           const int acc = int(it & 3u), st = int(it & uint32_t(NB - 1));
           if (!twait(2, t_empty(acc), (uint32_t(it >> 2) & 1u) ^ 1u)) { atomicExch(P.status, 1); dead = true; break; }
           if (!twait(3, b_full(st), (it >> nb_shift) & 1u)) { atomicExch(P.status, 1); dead = true; break; }
@@ -344,7 +352,7 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         }
         if (!dead) umma_commit(a_empty(as));
       }
-      if (timing) {
+      if (timing && par == 0u) {
         long long* dt = reinterpret_cast<long long*>(P.status + 8);
         for (int i = 0; i < 4; i++) atomicAdd(reinterpret_cast<unsigned long long*>(dt + 4 + i), static_cast<unsigned long long>(tw[i]));
         atomicAdd(reinterpret_cast<unsigned long long*>(dt + 8), static_cast<unsigned long long>(clock64() - t_start));
@@ -403,15 +411,21 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
             if (__any_sync(0xffffffffu, need) && !(P.dbg & 4)) {
             uint32_t v[32];
             tmem_ld32(tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc * 128 + 32 * h), v);
+            // D[(ty * 8 + tx) * 128 + p] with ty = ty0 + rr, tx = c - relx: ONE base address, the column c and the row rr are
+            // immediate offsets (c * 128 and rr * 1024 floats); never dereferenced where the predicate is false
+            if (!(P.dbg & 1)) {
+              float* dbase = D + ((ty0 * 8 - relx) * 128 + p);
+              // bit c of cm: column c of the cell row is one of the window's 8 columns (relx <= c <= relx + 7)
+              const unsigned cm = (relx > -8 && relx < 16) ? (((0xFFu << (relx + 8)) >> 8) & 0xFFFFu) : 0u;
+              if (valid && static_cast<unsigned>(ty0) < 8u) {
 #pragma unroll
-            for (int rr = 0; rr < 2; rr++) {
-              const int ty = 2 * h + rr - rely;
-              if (valid && static_cast<unsigned>(ty) < 8u && !(P.dbg & 1)) {
+                for (int c = 0; c < 16; c++)
+                  if (cm & (1u << c)) dbase[c * 128] = __uint_as_float(v[c]);
+              }
+              if (valid && static_cast<unsigned>(ty0 + 1) < 8u) {
 #pragma unroll
-                for (int c = 0; c < 16; c++) {
-                  const int tx = c - relx;
-                  if (static_cast<unsigned>(tx) < 8u) D[(ty * 8 + tx) * 128 + p] = __uint_as_float(v[rr * 16 + c]);
-                }
+                for (int c = 0; c < 16; c++)
+                  if (cm & (1u << c)) dbase[c * 128 + 1024] = __uint_as_float(v[16 + c]);
               }
             }
             }
@@ -430,18 +444,31 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
           const int oy0 = 2 * h, oy1 = min(2 * h + 2, 7);   // the 7 output rows over the 4 warps of the pixel: 2, 2, 2, 1
           float up[8], dn[8];
 #pragma unroll
-          for (int c = 0; c < 8; c++) up[c] = ((rowok >> oy0) & (colok >> c) & 1u) ? D[(oy0 * 8 + c) * 128 + p] : 0.0f;
-          float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc;
-          for (int oy = oy0; oy < oy1; oy++) {
+          for (int c = 0; c < 8; c++) up[c] = 0.0f;
+          {
+            const unsigned mk = ((rowok >> oy0) & 1u) ? colok : 0u;            // bit c: tap (oy0, c) lies inside the target image
 #pragma unroll
-            for (int c = 0; c < 8; c++) dn[c] = ((rowok >> (oy + 1)) & (colok >> c) & 1u) ? D[((oy + 1) * 8 + c) * 128 + p] : 0.0f;
+            for (int c = 0; c < 8; c++) if (mk & (1u << c)) up[c] = D[(oy0 * 8 + c) * 128 + p];
+          }
+          float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc + static_cast<long long>(oy0) * P.o_sc;   // channel oy + 7 ox
+          const long long ostep = 7 * P.o_sc;
+          for (int oy = oy0; oy < oy1; oy++, ol += P.o_sc) {
 #pragma unroll
-            for (int ox = 0; ox < 7; ox++) {
+            for (int c = 0; c < 8; c++) dn[c] = 0.0f;
+            {
+              const unsigned mk = ((rowok >> (oy + 1)) & 1u) ? colok : 0u;
+              const float* drow = D + ((oy + 1) * 8) * 128 + p;
+#pragma unroll
+              for (int c = 0; c < 8; c++) if (mk & (1u << c)) dn[c] = drow[c * 128];
+            }
+            float* po = ol;
+#pragma unroll
+            for (int ox = 0; ox < 7; ox++, po += ostep) {
               float r = w00 * up[ox];
               r = fmaf(w01, up[ox + 1], r);
               r = fmaf(w10, dn[ox], r);
               r = fmaf(w11, dn[ox + 1], r);
-              ol[static_cast<long long>(oy + 7 * ox) * P.o_sc] = r;
+              *po = r;
             }
 #pragma unroll
             for (int c = 0; c < 8; c++) up[c] = dn[c];
