@@ -387,12 +387,12 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
         const int wx0 = alt_floor_clamped(pcx * P.scale[l], &dx) - 3, wy0 = alt_floor_clamped(pcy * P.scale[l], &dy) - 3;
         // taps inside the target image: exactly these are written by the visited cells (the masks cover every in-image tap
         // of every valid pixel); the others are selected to zero in the combination below — D is never cleared
-        unsigned rowok = 0u, colok = 0u;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          rowok |= (static_cast<unsigned>(wy0 + i) < static_cast<unsigned>(P.H2[l]) ? 1u : 0u) << i;
-          colok |= (static_cast<unsigned>(wx0 + i) < static_cast<unsigned>(P.W2[l]) ? 1u : 0u) << i;
-        }
+        // bit i: 0 <= w0 + i < size, i = 0..7 — a contiguous run of bits [max(0, -w0), min(8, size - w0))
+        auto inrange = [](int w0, int size) -> unsigned {
+          const int lo_ = max(0, -w0), hi_ = min(8, size - w0);
+          return hi_ > lo_ ? ((1u << hi_) - (1u << lo_)) : 0u;
+        };
+        const unsigned rowok = inrange(wy0, P.H2[l]), colok = inrange(wx0, P.W2[l]);
         unsigned long long m = tinfo[slot].mask[l];
         const int bx0 = tinfo[slot].bx0[l], by0 = tinfo[slot].by0[l];
         while (m) {
@@ -441,27 +441,18 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
           // bilinear combination (altcorr_kernel.cu:107-140): channel oy + 7 ox =
           //   (1-dy)(1-dx) S[oy][ox] + (1-dy) dx S[oy][ox+1] + dy (1-dx) S[oy+1][ox] + dy dx S[oy+1][ox+1]
           const float w00 = (1.0f - dy) * (1.0f - dx), w01 = (1.0f - dy) * dx, w10 = dy * (1.0f - dx), w11 = dy * dx;
-          const int oy0 = 2 * h, oy1 = min(2 * h + 2, 7);   // the 7 output rows over the 4 warps of the pixel: 2, 2, 2, 1
-          float up[8], dn[8];
+          // the 7 output rows over the 4 warps of the pixel: 2, 2, 2, 1 — rows oy0 (and oy0 + 1 for h < 3), straight-line code
+          const int oy0 = 2 * h;
+          auto tap_row = [&](int ty, float (&r)[8]) {        // taps of window row ty, out-of-image ones as zeros
+            const unsigned mk = ((rowok >> ty) & 1u) ? colok : 0u;
+            const float* drow = D + (ty * 8) * 128 + p;
 #pragma unroll
-          for (int c = 0; c < 8; c++) up[c] = 0.0f;
-          {
-            const unsigned mk = ((rowok >> oy0) & 1u) ? colok : 0u;            // bit c: tap (oy0, c) lies inside the target image
+            for (int c = 0; c < 8; c++) r[c] = 0.0f;
 #pragma unroll
-            for (int c = 0; c < 8; c++) if (mk & (1u << c)) up[c] = D[(oy0 * 8 + c) * 128 + p];
-          }
-          float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc + static_cast<long long>(oy0) * P.o_sc;   // channel oy + 7 ox
+            for (int c = 0; c < 8; c++) if (mk & (1u << c)) r[c] = drow[c * 128];
+          };
           const long long ostep = 7 * P.o_sc;
-          for (int oy = oy0; oy < oy1; oy++, ol += P.o_sc) {
-#pragma unroll
-            for (int c = 0; c < 8; c++) dn[c] = 0.0f;
-            {
-              const unsigned mk = ((rowok >> (oy + 1)) & 1u) ? colok : 0u;
-              const float* drow = D + ((oy + 1) * 8) * 128 + p;
-#pragma unroll
-              for (int c = 0; c < 8; c++) if (mk & (1u << c)) dn[c] = drow[c * 128];
-            }
-            float* po = ol;
+          auto out_row = [&](float* po, const float (&up)[8], const float (&dn)[8]) {   // channels oy + 7 ox, ox = 0..6
 #pragma unroll
             for (int ox = 0; ox < 7; ox++, po += ostep) {
               float r = w00 * up[ox];
@@ -470,8 +461,15 @@ __global__ void __launch_bounds__(kATThreads, 1) altcorr_tc_fwd_kernel(const __g
               r = fmaf(w11, dn[ox + 1], r);
               *po = r;
             }
-#pragma unroll
-            for (int c = 0; c < 8; c++) up[c] = dn[c];
+          };
+          float* ol = outp + static_cast<long long>(l) * 49 * P.o_sc + static_cast<long long>(oy0) * P.o_sc;
+          float ra[8], rb[8];
+          tap_row(oy0, ra);
+          tap_row(oy0 + 1, rb);
+          out_row(ol, ra, rb);
+          if (h < 3) {
+            tap_row(oy0 + 2, ra);
+            out_row(ol + P.o_sc, rb, ra);
           }
         }
       }
