@@ -274,7 +274,9 @@ def altcorr_bench(p, dev, rank, world, steps=3, warmup=1):
         if bool(v.any()):
             chunks.append(v)
     masks = chunks                                        # factor_graph.py:268-272 builds these boolean masks per chunk
-    chunks = [torch.nonzero(v).reshape(-1) for v in masks]     # the same chunks as index lists: no host sync when indexing with them
+    from droid_b200 import graph as bgraph
+    chunks = bgraph.edge_chunks(ii_t, n, 8)                   # the same chunks as index lists: no host sync when indexing with them
+    assert len(chunks) == len(masks) and all(torch.equal(ii_t[c], ii_t[m]) for c, m in zip(chunks, masks))
     op = mirror.AltCorrBlock(fmaps.view(1, n * rig, 128, ht, wd))
 
     def step(o, which):

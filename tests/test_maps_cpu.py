@@ -65,3 +65,23 @@ def test_owner_sharded_load_keeps_only_owned_heavy_rows(tmp_path):
         assert np.all(covered == 1)
     empty = maps.load_maps(str(tmp_path), every=N, own_lo=5, own_hi=5)
     assert empty["fmaps"].shape[0] == 0 and empty["poses"].shape[0] == T
+
+
+def test_edge_chunks_select_what_the_reference_masks_select():
+    """droid_b200.graph.edge_chunks against the mask loop of FactorGraph.update_lowmem (factor_graph.py:268-272)"""
+    import torch
+    from droid_b200 import graph
+    g = torch.Generator().manual_seed(5)
+    for n_frames, n_edges, step in ((37, 400, 8), (8, 20, 8), (64, 1, 8), (50, 300, 5)):
+        ii = torch.randint(0, n_frames, (n_edges,), generator=g)
+        jj = torch.randint(0, n_frames, (n_edges,), generator=g)
+        want = []
+        for i in range(0, n_frames, step):
+            v = (ii >= i) & (ii < i + step)
+            if v.any():
+                want.append((ii[v], jj[v]))
+        got = graph.edge_chunks(ii, n_frames, step)
+        assert len(got) == len(want)
+        for idx, (wi, wj) in zip(got, want):
+            assert torch.equal(ii[idx], wi) and torch.equal(jj[idx], wj)
+    assert graph.edge_chunks(torch.zeros(0, dtype=torch.int64), 10) == []
