@@ -13,17 +13,21 @@
 // bounding corner of the tile's windows + a 64-bit mask of 8x8 cells relative to it); arbitrary coordinates just touch
 // more cells, so there is no "fast path only for smooth flow" — results are the reference's for any input.
 //
-// One persistent CTA per SM, 19 warps (warp 18 = a second MMA issuer for the odd cells):
-//   warp 0      producer: reads the tile's coordinates, computes per level the cell origin + mask (warp reductions),
-//               publishes them, then feeds the A tile (128 pixels x 128 channels, TMA 4-D box, 128B swizzle) and a ring
-//               of B cells (TMA zero-fills positions outside the image = the reference's `within_bounds` skip);
-//   warp 1      one thread issues 8 (x3 when operands carry lo parts) tcgen05.mma M=128,N=128,K=16 per cell into one of
-//               FOUR 128-column TMEM accumulators; tcgen05.commit hands stages back / accumulators on;
-//   warps 2..17 epilogue (the bottleneck: the tensor pipe is < 20 % busy): four warps per TMEM lane quarter, each reads ONE
-//               32-column chunk (2 cell rows) with tcgen05.ld — skipped when no lane has a window row there — and scatters
-//               the taps that belong to its lane's pixel into the tap buffer D[64 taps][128 pixels] (conflict-free); per level
-//               the four warps of a pixel meet at a 128-thread named barrier, combine bilinearly (out-of-image taps are
-//               selected to zero by per-thread row/column masks: D is never cleared) and store 49 coalesced channel rows.
+// altcorr_plan_kernel (one warp per tile) writes the per-level cell origin + mask of every tile first; then one persistent
+// CTA per SM, 19 warps:
+//   warp 0      producer: reads the tile's plan entry (the next one is prefetched), publishes it to the other roles, then
+//               feeds the A tile (128 pixels x 128 channels) and a ring of B cells, each as ONE 5-D TMA box
+//               [64 ch x 16 x 8 x 2 channel blocks x 1 frame] of the channel-blocked fp16 pyramid, 128B swizzle (the TMA
+//               zero-fills positions outside the image = the reference's `within_bounds` skip);
+//   warps 1, 18 two single-thread MMA issuers (even / odd cells): 8 (x3 when operands carry lo parts) tcgen05.mma
+//               M=128,N=128,K=16 per cell into one of FOUR 128-column TMEM accumulators; tcgen05.commit hands stages back /
+//               accumulators on;
+//   warps 2..17 epilogue (the bottleneck: issue bound, the tensor pipe is 30 % busy): four warps per TMEM lane quarter, each
+//               reads ONE 32-column chunk (2 cell rows) with tcgen05.ld — skipped when no lane has a window row there — and
+//               scatters the taps that belong to its lane's pixel into the tap buffer D[64 taps][128 pixels] (conflict-free,
+//               one base address, predicates from a column bit mask); per level the four warps of a pixel meet at a
+//               128-thread named barrier, combine bilinearly (out-of-image taps are selected to zero by per-thread
+//               row/column masks: D is never cleared) and store 49 coalesced channel rows.
 // All 4 pyramid levels of a tile are done by the same CTA (the A tile is loaded once per tile).
 //
 // Precision: operands are fp16.  The fused AltCorrBlock path feeds the fp16 feature pyramid directly (the reference casts
