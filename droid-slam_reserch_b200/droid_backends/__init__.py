@@ -308,8 +308,10 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
     if wsb == 0:
         raise RuntimeError("ba: invalid sizes")
     ws = _workspace(wsb, poses.device)
-    dx = torch.empty((max(P, 0), 6), dtype=torch.float32, device=poses.device)
-    dz = None if motion_only else torch.empty((M, ht * wd), dtype=torch.float32, device=poses.device)
+    # the kernels write every element of dx / dz in every iteration; with no iteration the reference returns its torch::zeros
+    alloc = torch.empty if int(iterations) > 0 else torch.zeros
+    dx = alloc((max(P, 0), 6), dtype=torch.float32, device=poses.device)
+    dz = None if motion_only else alloc((M, ht * wd), dtype=torch.float32, device=poses.device)
     rc = lib.db200_ba(_ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(disps_sens), _ptr(targets), _ptr(weights), _ptr(eta),
                       _ptr(ii), _ptr(jj), N, B, ht, wd, int(t0), int(t1), int(iterations), float(lm), float(ep),
                       int(bool(motion_only)), M, _ptr(dx), _ptr(dz), _ptr(ws), ws.numel(), _stream())

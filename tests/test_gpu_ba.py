@@ -118,6 +118,35 @@ def test_ba_motion_only():
     check_chained(p, 3, 1e-4, 0.1, motion_only=True)
 
 
+def test_ba_degenerate_calls():
+    """what a young map gives: ONE optimised pose (2 keyframes, t0 = 1); an EMPTY edge list (depths move by the sensor prior
+    only, dx = 0: kx = arange(t0, t1), droid_kernels.cu:1336-1344); zero iterations (nothing changes, outputs are the zeros of
+    the reference's torch::zeros, droid_kernels.cu:1350-1355)"""
+    import droid_backends
+    from droid_b200 import synth
+    from oracle import oracle
+    p = synth.make_ba_problem(np.array([0, 1]), np.array([1, 0]), 2, seed=3, t0=1)
+    check(p, 2, 1e-4, 0.1)
+    # empty edge list, sensor prior on every pixel
+    q = synth.make_ba_problem(np.array([0, 1]), np.array([1, 0]), 4, seed=4, t0=1, sensor_frac=1.0)
+    e = np.zeros(0, np.int64)
+    z = np.zeros((0, 2) + q.disps.shape[1:], np.float32)
+    eta = np.full((q.t1 - q.t0,) + q.disps.shape[1:], 1e-3, np.float32)
+    ref = oracle.ba(q.poses, q.disps, q.intrinsics, q.disps_sens, z, z, eta, e, e, q.t0, q.t1, 1, 1e-4, 0.1)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    poses, disps = t(q.poses), t(q.disps)
+    dx, dz = droid_backends.ba(poses, disps, t(q.intrinsics), t(q.disps_sens), t(z), t(z), t(eta), t(e), t(e), q.t0, q.t1, 1, 1e-4, 0.1, False)
+    assert float(dx.abs().max()) == 0.0 and np.array_equal(poses.cpu().numpy(), q.poses)
+    assert np.abs(ref["dz"]).max() > 0 and rel(dz.cpu().numpy(), ref["dz"]) <= RTOL
+    assert rel(disps.cpu().numpy(), ref["disps"]) <= 1e-6
+    # zero iterations
+    poses, disps = t(p.poses), t(p.disps)
+    dx, dz = droid_backends.ba(poses, disps, t(p.intrinsics), t(p.disps_sens), t(p.target), t(p.weight), t(p.eta), t(p.ii), t(p.jj),
+                               p.t0, p.t1, 0, 1e-4, 0.1, False)
+    assert np.array_equal(poses.cpu().numpy(), p.poses) and np.array_equal(disps.cpu().numpy(), p.disps)
+    assert float(dx.abs().max()) == 0.0 and float(dz.abs().max()) == 0.0
+
+
 def test_ba_cholesky_failure_gives_zero_pose_update():
     from droid_b200 import synth
     import droid_backends
