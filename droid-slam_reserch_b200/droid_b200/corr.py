@@ -93,11 +93,12 @@ class CorrBlock:
         batch, num, ht, wd, _ = coords.shape
         c = coords.permute(0, 1, 4, 2, 3).contiguous().view(batch * num, 2, ht, wd)
         if torch.is_grad_enabled() and any(v.requires_grad for v in self.corr_pyramid):
-            outs = [CorrSampler.apply(self.corr_pyramid[i], c / 2 ** i, self.radius).view(batch, num, -1, ht, wd)
+            nch = (2 * self.radius + 1) ** 2
+            outs = [CorrSampler.apply(self.corr_pyramid[i], c / 2 ** i, self.radius).view(batch, num, nch, ht, wd)
                     for i in range(self.num_levels)]
             return torch.cat(outs, dim=2)
         out = droid_backends.corr_pyramid_lookup(self.corr_pyramid, c, self.radius)
-        return out.view(batch, num, -1, ht, wd)
+        return out.view(batch, num, self.num_levels * (2 * self.radius + 1) ** 2, ht, wd)     # explicit: an empty batch has no -1
 
     def cat(self, other):
         for i in range(self.num_levels):
@@ -170,7 +171,7 @@ class AltCorrBlock:
             out = droid_backends.altcorr_pyramid_forward(self._hi, ii.contiguous(), jj.contiguous(),
                                                          coords.reshape(B * N, H, W, S, 2).contiguous(), self.radius,
                                                          lo=self._lo, flags=self._flags, f32=self._f32)
-            return out.view(B, N, -1, H, W, S)
+            return out.view(B, N, 49 * self.num_levels, H, W, S)
         coords = coords.permute(0, 1, 4, 2, 3, 5)
         out = []
         for i in range(self.num_levels):

@@ -45,6 +45,8 @@ def corr_index_forward(volume, coords, radius):
     N, h1, w1, h2, w2 = volume.shape
     rd = 2 * radius + 1
     corr = torch.empty((N, rd, rd, h1, w1), dtype=volume.dtype, device=volume.device)
+    if corr.numel() == 0:                    # empty batch: the reference launches a zero-block grid (an error); nothing to do
+        return [corr]
     co = coords.float()                      # kept alive in a local for the duration of the call
     _capi.check(_capi.lib().db200_corr_index_forward(_ptr(volume), _ptr(co), _ptr(corr), N, h1, w1, h2, w2,
                                                      radius, _DT[volume.dtype], _stream()), "corr_index_forward")
@@ -56,6 +58,8 @@ def corr_index_backward(volume, coords, corr_grad, radius):
     _chk(("volume", volume), ("coords", coords), ("corr_grad", corr_grad))
     N, h1, w1, h2, w2 = volume.shape
     grad = torch.empty_like(volume)
+    if grad.numel() == 0:
+        return [grad]
     g = corr_grad.to(volume.dtype)
     co = coords.float()
     _capi.check(_capi.lib().db200_corr_index_backward(_ptr(co), _ptr(g), _ptr(grad), N, h1, w1, h2, w2, radius,
@@ -71,6 +75,8 @@ def corr_pyramid_lookup(levels, coords, radius):
     L = len(levels)
     rd = 2 * radius + 1
     out = torch.empty((N, L * rd * rd, h1, w1), dtype=levels[0].dtype, device=coords.device)
+    if out.numel() == 0:
+        return out
     arr = (C.c_void_p * L)(*[v.data_ptr() for v in levels])
     co = coords.float()
     _capi.check(_capi.lib().db200_corr_pyramid_lookup(arr, _ptr(co), _ptr(out), N, h1, w1, h2, w2, L, radius,
@@ -85,6 +91,8 @@ def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
     N, Cc, ht, wd = fmap1.shape
     dt = _DT[fmap1.dtype]
     outs = [torch.empty((N, ht, wd, ht >> l, wd >> l), dtype=fmap1.dtype, device=fmap1.device) for l in range(num_levels)]
+    if N == 0:
+        return outs
     lib = _capi.lib()
     wsb = lib.db200_corr_volume_workspace_bytes(N, Cc, ht, wd, num_levels, dt) if N > 0 else 0
     ws = torch.empty(max(wsb, 16), dtype=torch.uint8, device=fmap1.device)
@@ -116,6 +124,8 @@ def altcorr_forward(fmap1, fmap2, coords, radius):
     _, H2, W2, Cc = f2.shape
     rd = 2 * radius + 1
     corr = torch.empty((B, S, rd * rd, H1, W1), dtype=torch.float32, device=f1.device)
+    if corr.numel() == 0:
+        return [corr.to(dt)]
     lib = _capi.lib()
     wsb = lib.db200_altcorr_workspace_bytes(B, S, H1, W1, H2, W2, Cc) if (Cc == 128 and radius == 3 and B * S > 0) else 0
     ws = torch.empty(wsb, dtype=torch.uint8, device=f1.device) if wsb else None
@@ -172,6 +182,8 @@ def altcorr_pyramid_forward(pyramid, ii, jj, coords, radius=3, lo=None, flags=No
     E = co.shape[0]
     S = co.shape[3] if multi else 1
     out = torch.empty((E, 49 * L, H, W) + ((S,) if multi else ()), dtype=torch.float32, device=co.device)
+    if out.numel() == 0:
+        return out
     lib = _capi.lib()
     wsb = lib.db200_altcorr_pyramid_workspace_bytes(E, S, H, W) if E > 0 else 0
     ws = torch.empty(max(wsb, 16), dtype=torch.uint8, device=co.device)
@@ -204,6 +216,8 @@ def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):
     _, H2, W2, Cc = f2.shape
     g1, g2 = torch.empty_like(f1), torch.empty_like(f2)
     gc = torch.empty((B, S, H1, W1, 2), dtype=torch.float32, device=f1.device)
+    if gc.numel() == 0:                      # no coordinate samples: zero gradients
+        return [torch.zeros_like(f1), torch.zeros_like(f2), gc]
     lib = _capi.lib()
     wsb = lib.db200_altcorr_workspace_bytes(B, max(S, 1), H1, W1, H2, W2, Cc) if (Cc == 128 and radius == 3 and B > 0) else 0
     ws = torch.empty(wsb, dtype=torch.uint8, device=f1.device) if wsb else None
@@ -220,6 +234,8 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta):
     _chk(("poses", poses), ("disps", disps), ("intrinsics", intrinsics), ("ii", ii), ("jj", jj))
     K = ii.shape[0]
     dist = torch.empty(K, dtype=torch.float32, device=poses.device)
+    if K == 0:
+        return dist
     _capi.check(_capi.lib().db200_frame_distance(_ptr(poses), _ptr(disps), _ptr(intrinsics), _ptr(ii), _ptr(jj), K,
                                                  poses.shape[0], disps.shape[0], disps.shape[1], disps.shape[2], float(beta),
                                                  _ptr(dist), _stream()), "frame_distance")

@@ -167,3 +167,26 @@ def test_mirror_altcorrblock(mods):
     b = theirs.AltCorrBlock(fm.view(1, num * rig, ch, ht, wd))(_t(co), _t(ii), _t(jj))
     assert a.shape == b.shape and a.dtype == b.dtype
     assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max())
+
+
+def test_empty_batches_return_empty_outputs():
+    """no edges / no pairs: correctly shaped empty outputs and no launch (the reference launches a zero-block grid, which is a
+    CUDA launch error) — through the nine-name operators and the mirror classes"""
+    import droid_backends as B
+    from droid_b200 import corr as mirror
+    dev, H, W = "cuda", 24, 32
+    vol = torch.zeros((0, H, W, H, W), device=dev, dtype=torch.float16)
+    co = torch.zeros((0, 2, H, W), device=dev)
+    assert B.corr_index_forward(vol, co, 3)[0].shape == (0, 7, 7, H, W)
+    assert B.corr_index_backward(vol.float(), co, torch.zeros((0, 7, 7, H, W), device=dev), 3)[0].shape == vol.shape
+    f, c5 = torch.zeros((0, H, W, 128), device=dev), torch.zeros((0, 1, H, W, 2), device=dev)
+    assert B.altcorr_forward(f, f, c5, 3)[0].shape == (0, 1, 49, H, W)
+    g1, g2, gc = B.altcorr_backward(f, f, c5, torch.zeros((0, 1, 49, H, W), device=dev), 3)
+    assert g1.shape == f.shape and g2.shape == f.shape and gc.shape == c5.shape
+    poses = torch.zeros((4, 7), device=dev); poses[:, 6] = 1
+    e = torch.zeros(0, dtype=torch.int64, device=dev)
+    assert B.frame_distance(poses, torch.ones((4, H, W), device=dev), torch.tensor([50., 50., 16., 12.], device=dev), e, e, 0.3).shape == (0,)
+    fm = torch.randn((1, 6, 128, H, W), device=dev, dtype=torch.float16)
+    assert mirror.AltCorrBlock(fm)(torch.zeros((1, 0, H, W, 2), device=dev), e, e).shape == (1, 0, 196, H, W)
+    assert mirror.CorrBlock(fm[:, :0], fm[:, :0])(torch.zeros((1, 0, H, W, 2), device=dev)).shape[:2] == (1, 0)
+    torch.cuda.synchronize()
