@@ -200,20 +200,30 @@ def lookup_bench(dev, steps, warmup, hbm_peak, world=1):
     N, ht, wd = 96, 48, 64
     g = torch.Generator(device=dev); g.manual_seed(7)
     levels = [torch.randn((N, ht, wd, ht >> l, wd >> l), device=dev, dtype=torch.float16, generator=g) for l in range(4)]
+    # the CorrBlock path keeps its wide levels in the tiled slice layout (include/droid_b200.h); the nine-name operators and a
+    # caller that owns its volumes read row-major ones: both are timed, the CorrBlock path is the block's headline
+    mask = droid_backends.corr_tiled_levels(128, ht, wd, 4, torch.float16)
+    tiled = [droid_backends.tile_level(v).contiguous() if (mask >> l) & 1 else v for l, v in enumerate(levels)]
     yy, xx = torch.meshgrid(torch.arange(ht, device=dev, dtype=torch.float32), torch.arange(wd, device=dev, dtype=torch.float32),
                             indexing="ij")
     coords = torch.stack([xx, yy], 0)[None].repeat(N, 1, 1, 1) + 6.0 * torch.randn((N, 2, ht, wd), device=dev, generator=g)
     coords = coords.contiguous()
-    for _ in range(warmup):
-        droid_backends.corr_pyramid_lookup(levels, coords, 3)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    torch.cuda.synchronize()
-    ev[0].record()
-    for _ in range(steps):
-        droid_backends.corr_pyramid_lookup(levels, coords, 3)
-    ev[1].record()
-    torch.cuda.synchronize()
-    ms_loc = ev[0].elapsed_time(ev[1]) / steps
+
+    def timed(lv, m):
+        for _ in range(warmup):
+            droid_backends.corr_pyramid_lookup(lv, coords, 3, tiled_mask=m)
+        torch.cuda.synchronize()
+        ev[0].record()
+        for _ in range(steps):
+            droid_backends.corr_pyramid_lookup(lv, coords, 3, tiled_mask=m)
+        ev[1].record()
+        torch.cuda.synchronize()
+        return ev[0].elapsed_time(ev[1]) / steps
+    same = bool(torch.equal(droid_backends.corr_pyramid_lookup(levels, coords, 3),
+                            droid_backends.corr_pyramid_lookup(tiled, coords, 3, tiled_mask=mask)))
+    ms_row = timed(levels, 0)
+    ms_loc = timed(tiled, mask)
     ms, lookups = _agg(dev, world, ms_loc, N * ht * wd)      # N > 1: every rank looks up its own 96 frontend edges (replicas)
     gbs = (N * ht * wd) * 912 / (ms_loc * 1e-3) / 1e9       # roofline of THIS rank's kernel
     ref_ms = None
@@ -233,6 +243,8 @@ def lookup_bench(dev, steps, warmup, hbm_peak, world=1):
     return dict(metric="corr lookups/s, frontend path (CorrBlock: fused 4-level r=3 lookup on f16 volumes, 96 edges x 48x64 per GPU; "
                        "volumes 2.4 GB > L2; N > 1 = one such window per rank, no collective)",
                 value=lookups / (ms * 1e-3), unit="lookups/s", ms_per_launch=ms, reference_cuda_ms=ref_ms,
+                layout=f"CorrBlock's private pyramid: levels {[l for l in range(4) if (mask >> l) & 1]} in 4x8-element tiles",
+                ms_per_launch_row_major=ms_row, tiled_equals_row_major=same,
                 roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
                               algorithmic_bytes_per_launch=N * ht * wd * 912))
 
@@ -893,7 +905,7 @@ def main_gpu(args, rank, world):
         line["training_shapes"] = training_bench(dev)
         line["frontend"] = frontend_bench(dev)
         try:
-            tr = json.load(open(traffic_file)).get("corr_lookup_r3_kernel_bytes_per_launch")
+            tr = json.load(open(traffic_file)).get("corr_lookup_r3_direct_kernel_bytes_per_launch")
             line["lookup"]["roofline"]["traffic"] = tr
             # what the kernel actually moves (ncu dram bytes) over the live launch time: the 16-byte window rows cost
             # whole 64-byte DRAM bursts, so the DRAM interface is far busier than the algorithmic figure says

@@ -97,6 +97,15 @@ __device__ __forceinline__ void rel_se3(const float* pi, const float* pj, float*
   tij[0] = tj[0] - Y[0]; tij[1] = tj[1] - Y[1]; tij[2] = tj[2] - Y[2];
 }
 
+// Tiled slice layout (private to CorrBlock's fused path; include/droid_b200.h, "tiled levels"): the [h2][w2] slice of a source
+// pixel is stored as 4x8-element tiles (64 bytes of fp16 = one DRAM burst), tiles in row-major order, the 4 rows of a tile 16
+// bytes apart — so the 8x8-sample window of a lookup touches ~5 bursts instead of 8-10 (in the row-major layout every 16-byte
+// row segment of a window costs a whole burst).  A level is tiled when its height is a multiple of 4 and its width a multiple
+// of 8 and at least 32 (smaller levels already sit in a few bursts).
+__host__ __device__ inline bool level_is_tiled(int h2l, int w2l) { return h2l % 4 == 0 && w2l % 8 == 0 && w2l >= 32; }
+// position of element (y, x) inside a tiled [h][w] slice
+__host__ __device__ inline int tiled_index(int y, int x, int w) { return (((y >> 2) * (w >> 3) + (x >> 3)) << 5) + ((y & 3) << 3) + (x & 7); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -269,9 +269,11 @@ struct PipeDesc {                    // one stage of window descriptors
 };
 
 template <typename T>
-__host__ __device__ constexpr size_t pipe_smem_bytes() {
-  return 2 * size_t(kPipeWin) * pipe_win_bytes<T>() + size_t(kMaxLevels) * 49 * kPipePX * sizeof(T) + 2 * sizeof(PipeDesc);
+__host__ __device__ constexpr size_t pipe_smem_bytes(bool tiled = false) {
+  return 2 * size_t(kPipeWin) * pipe_win_bytes<T>() + size_t(kMaxLevels) * 49 * kPipePX * sizeof(T) + 2 * sizeof(PipeDesc) +
+         (tiled ? 2 * size_t(kPipeWin) * sizeof(int) : 0);
 }
+
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
   const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
@@ -293,16 +295,17 @@ __device__ __forceinline__ void pipe_row_half(const unsigned char* rowp, int q, 
 
 __device__ __forceinline__ __half2 as_h2(unsigned u) { return *reinterpret_cast<__half2*>(&u); }
 
-template <typename T>
+template <typename T, bool TILED>
 __global__ void __launch_bounds__(kPipeThreads)
 corr_lookup_r3_pipe_kernel(LevelPtrs levels, const float* __restrict__ coords, T* __restrict__ out, int N, int h1, int w1,
-                           int h2, int w2, int num_levels, int num_tiles) {
+                           int h2, int w2, int num_levels, int num_tiles, unsigned tiled_mask) {
   using Cfg = PipeCfg<T>;
   constexpr int CE = Cfg::CE, CH = Cfg::CH, WINB = pipe_win_bytes<T>(), PX = kPipePX, kCh = 49;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   unsigned char* win = smem_raw;                                                        // [2][kPipeWin][WINB]
   T* sout = reinterpret_cast<T*>(smem_raw + 2 * size_t(kPipeWin) * WINB);               // [L*49][PX]
   PipeDesc* desc = reinterpret_cast<PipeDesc*>(reinterpret_cast<unsigned char*>(sout) + size_t(kMaxLevels) * kCh * PX * sizeof(T));
+  int* ykbuf = reinterpret_cast<int*>(desc + 2);                   // TILED: [2][kPipeWin] window origin (row | first chunk << 16)
   const int tid = threadIdx.x;
   const int nwin = num_levels * PX;
   const int tiles_x = (w1 + PX - 1) / PX;
@@ -343,8 +346,13 @@ corr_lookup_r3_pipe_kernel(LevelPtrs levels, const float* __restrict__ coords, T
       m |= static_cast<unsigned>(o) << 16;
       m |= 1u << 31;                                               // live pixel
     }
-    desc[s].base[tid] = ((static_cast<long long>(n) * h1 + y) * w1 + x) * (static_cast<long long>(h2l) * w2l) +
-                        static_cast<long long>(yb) * w2l + static_cast<long long>(k0) * CE;
+    const long long slice = ((static_cast<long long>(n) * h1 + y) * w1 + x) * (static_cast<long long>(h2l) * w2l);
+    if (TILED && ((tiled_mask >> my_l) & 1u)) {                    // tile addresses are formed per row/chunk in issue()
+      desc[s].base[tid] = slice;
+      ykbuf[s * kPipeWin + tid] = (max(-8, min(32767, yb)) & 0xffff) | (max(-8, min(32767, k0)) << 16);
+    } else {
+      desc[s].base[tid] = slice + static_cast<long long>(yb) * w2l + static_cast<long long>(k0) * CE;
+    }
     desc[s].mask[tid] = m;
     desc[s].dx[tid] = x0 - fx;
     desc[s].dy[tid] = y0 - fy;
@@ -364,7 +372,14 @@ corr_lookup_r3_pipe_kernel(LevelPtrs levels, const float* __restrict__ coords, T
             const int w = l * PX + wl;
             const unsigned m = desc[s].mask[w];
             const bool ok = ((m >> row) & (m >> (8 + c)) & 1u) != 0;
-            const T* src = ok ? lp + (desc[s].base[w] + static_cast<long long>(row) * w2l + c * CE) : lp;
+            const T* src = lp;
+            if (TILED && ((tiled_mask >> l) & 1u)) {
+              const int yk = ykbuf[s * kPipeWin + w];
+              const int yy = static_cast<short>(yk & 0xffff) + row, kc = (yk >> 16) + c;
+              if (ok) src = lp + (desc[s].base[w] + ((((yy >> 2) * (w2l >> 3) + kc) << 5) + ((yy & 3) << 3)));
+            } else if (ok) {
+              src = lp + (desc[s].base[w] + static_cast<long long>(row) * w2l + c * CE);
+            }
             cp_async16_zfill(wbase + size_t(w) * WINB + row * (CH * 16) + c * 16, src, ok);
           }
         }
@@ -481,6 +496,135 @@ corr_lookup_r3_pipe_kernel(LevelPtrs levels, const float* __restrict__ coords, T
   asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 }
 
+// ---- direct radius-3 fp16 path: thread = window, the window lives in registers -----------------------------------------------
+// No shared memory, no barriers, no staging pass: every thread loads the 8 rows x 2 aligned 16-byte chunks that cover its window
+// straight into registers (16 independent 128-bit loads in flight per thread; rows/chunks outside the slice are never read and
+// stay zero = the reference's skipped `within_bounds` samples), interpolates with the same packed half2 sequence as the
+// pipelined kernel (bit-identical), and writes its 49 values itself: the 32 lanes of a warp are 32 consecutive source pixels
+// of ONE level, so every channel store of the warp is one contiguous 64-byte run.  With 80 registers per thread 6 CTAs are
+// resident per SM (24 warps) — against 8 warps for the staged kernel, which holds two tiles of windows in shared memory — and a
+// lookup costs 33 M warp instructions per 96 edges instead of 57 M (no descriptor round trip, no cp.async address pass, no
+// shared-memory transposition).  That matters once the tiled slice layout (common.cuh) has cut the DRAM bytes: the staged
+// kernel then runs at 42 % DRAM utilisation, bound by its instruction stream (0.122 ms; ncu, tools/tiled_ncu.py), this one at
+// 0.093 ms and back on the DRAM pins (377 MB read + 116 MB written per launch at 5.3 TB/s).  On row-major levels the staged
+// kernel stays the default (0.108 against 0.112 ms: there the bytes, not the instructions, are the bound).
+// 16 bytes from global memory (read-only path, no L1 allocation) if row yy lies inside the level and the chunk is valid, else
+// zeros.  The predicate is formed right at the load from plain integers: with 16 such loads in flight per thread the compiler
+// otherwise keeps 16 predicates alive at once and spills them through general registers.
+__device__ __forceinline__ uint4 ldg16_if(const void* p, unsigned yy, unsigned h2l, int chunk_ok) {
+  uint4 v;
+  asm("{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 q, %7, 0;\n\t"
+      "setp.lt.and.u32 p, %5, %6, q;\n\t"
+      "mov.b32 %0, 0;\n\tmov.b32 %1, 0;\n\tmov.b32 %2, 0;\n\tmov.b32 %3, 0;\n\t"
+      "@p ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
+      : "=&r"(v.x), "=&r"(v.y), "=&r"(v.z), "=&r"(v.w) : "l"(p), "r"(yy), "r"(h2l), "r"(chunk_ok));
+  return v;
+}
+
+__device__ __forceinline__ void direct_row_half(const uint4& a, const uint4& b, int q, unsigned sel_a, unsigned sel_s,
+                                                unsigned (&A)[4], unsigned (&S)[4]) {
+  const bool s2 = q & 2, s1 = q & 1;
+  const unsigned t0 = s2 ? a.z : a.x, t1 = s2 ? a.w : a.y, t2 = s2 ? b.x : a.z, t3 = s2 ? b.y : a.w, t4 = s2 ? b.z : b.x,
+                 t5 = s2 ? b.w : b.y;
+  const unsigned u0 = s1 ? t1 : t0, u1 = s1 ? t2 : t1, u2 = s1 ? t3 : t2, u3 = s1 ? t4 : t3, u4 = s1 ? t5 : t4;
+  A[0] = __byte_perm(u0, u1, sel_a); A[1] = __byte_perm(u1, u2, sel_a); A[2] = __byte_perm(u2, u3, sel_a); A[3] = __byte_perm(u3, u4, sel_a);
+  S[0] = __byte_perm(u0, u1, sel_s); S[1] = __byte_perm(u1, u2, sel_s); S[2] = __byte_perm(u2, u3, sel_s); S[3] = __byte_perm(u3, u4, sel_s);
+}
+
+constexpr int kDirectThreads = 128;
+#ifndef DIRECT_CTAS
+#define DIRECT_CTAS 6                    // resident CTAs per SM the register budget is set for (80 registers)
+#endif
+
+// block = 32 * num_levels threads: warp = level, lane = source pixel; one CTA per source tile (32 pixels of one row), tiles in
+// memory order.  Launched one-shot on purpose: CTAs that are resident together then work on neighbouring tiles, whose output
+// rows and coordinates share DRAM pages — a persistent grid-stride walk of the same kernel (6 CTAs per SM) measured 0.105 ms
+// against 0.093 ms one-shot for 96 edges (the loop stays for grids clipped to 2^31 - 1 CTAs)
+template <bool TILED>
+__global__ void __launch_bounds__(kDirectThreads, DIRECT_CTAS)
+corr_lookup_r3_direct_kernel(LevelPtrs levels, const float* __restrict__ coords, __half* __restrict__ out, int num_tiles, int h1,
+                             int w1, int h2, int w2, int num_levels, unsigned tiled_mask) {
+  const int lane = threadIdx.x & 31, l = threadIdx.x >> 5;
+  const unsigned tiles_x = unsigned(w1 + 31) >> 5;
+  const size_t plane = size_t(h1) * w1;
+ for (unsigned tile = blockIdx.x; tile < unsigned(num_tiles); tile += gridDim.x) {
+  const unsigned rest = tile / tiles_x;
+  const int n = int(rest / unsigned(h1)), y = int(rest - unsigned(n) * unsigned(h1));
+  const int x = int(tile - rest * tiles_x) * 32 + lane;
+  if (x >= w1) continue;                                           // no warp-wide operation below
+  const size_t o = size_t(y) * w1 + x;
+  const float cx = __ldg(coords + (size_t(n) * 2 + 0) * plane + o), cy = __ldg(coords + (size_t(n) * 2 + 1) * plane + o);
+  const int h2l = h2 >> l, w2l = w2 >> l;
+  // coords / 2^l (corr.py:46): the quotient by a power of two is the exact product with its reciprocal (both are the correctly
+  // rounded value of the same real number), so this is the reference's float sequence bit for bit
+  const float inv = __int_as_float((127 - l) << 23);
+  const float x0 = cx * inv, y0 = cy * inv;
+  const float fx = floorf(x0), fy = floorf(y0);
+  constexpr int kFar = 1 << 20;                                    // anything this far out is all zeros either way
+  const int xb = max(-kFar, min(kFar, static_cast<int>(fx))) - 3, yb = max(-kFar, min(kFar, static_cast<int>(fy))) - 3;
+  const int k0 = xb >> 3, off = xb & 7;
+  const int nck = w2l >> 3;
+  const int c0ok = static_cast<unsigned>(k0) < static_cast<unsigned>(nck);
+  const int c1ok = static_cast<unsigned>(k0 + 1) < static_cast<unsigned>(nck) && off > 0;
+  const void* lp = l == 0 ? levels.p[0] : l == 1 ? levels.p[1] : l == 2 ? levels.p[2] : levels.p[3];   // no local copy of the array
+  const __half* sl = static_cast<const __half*>(lp) + ((static_cast<long long>(n) * h1 + y) * w1 + x) * (static_cast<long long>(h2l) * w2l);
+  const bool tl = TILED && ((tiled_mask >> l) & 1u);
+  // element offset of (row yy, chunk k) inside the slice: row-major yy * w2l + 8 k; tiled 8 yy + (yy >> 2) * (32 nck - 32) + 32 k
+  const int rs = tl ? 8 : w2l, ts = tl ? 32 * nck - 32 : 0, cs = tl ? 32 : 8;
+  const __half* b0 = sl + static_cast<long long>(k0) * cs;
+  const __half* b1 = b0 + cs;
+  uint4 ra[8], rb[8];
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int yy = yb + r;
+    const int roff = yy * rs + (yy >> 2) * ts;                     // never dereferenced when yy is outside the level
+    ra[r] = ldg16_if(b0 + roff, unsigned(yy), unsigned(h2l), c0ok);
+    rb[r] = ldg16_if(b1 + roff, unsigned(yy), unsigned(h2l), c1ok);
+  }
+  const float dx = x0 - fx, dy = y0 - fy;
+  const __half2 w00 = __half2half2(__float2half_rn((1.0f - dx) * (1.0f - dy)));
+  const __half2 w01 = __half2half2(__float2half_rn((1.0f - dx) * dy));
+  const __half2 w10 = __half2half2(__float2half_rn(dx * (1.0f - dy)));
+  const __half2 w11 = __half2half2(__float2half_rn(dx * dy));
+  const __half2 zero = __half2half2(__float2half_rn(0.0f));
+  const int q = off >> 1;
+  const unsigned sel_a = (off & 1) ? 0x5432u : 0x3210u, sel_s = (off & 1) ? 0x7654u : 0x5432u;
+  __half* ob = out + (size_t(n) * num_levels + l) * 49 * plane + o;        // channel (l*49 + i*7 + j) of this pixel: ob[(i*7 + j) * plane]
+  unsigned A0[4], S0[4], A1[4], S1[4];
+  direct_row_half(ra[0], rb[0], q, sel_a, sel_s, A0, S0);
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    direct_row_half(ra[j + 1], rb[j + 1], q, sel_a, sel_s, A1, S1);
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+      __half2 acc = __hadd2_rn(zero, __hmul2_rn(as_h2(A0[p]), w00));       // x offsets i = 2p (low), 2p+1 (high)
+      acc = __hadd2_rn(acc, __hmul2_rn(as_h2(A1[p]), w01));
+      acc = __hadd2_rn(acc, __hmul2_rn(as_h2(S0[p]), w10));
+      acc = __hadd2_rn(acc, __hmul2_rn(as_h2(S1[p]), w11));
+      ob[size_t((2 * p) * 7 + j) * plane] = __low2half(acc);
+      if (p < 3) ob[size_t((2 * p + 1) * 7 + j) * plane] = __high2half(acc);
+    }
+#pragma unroll
+    for (int p = 0; p < 4; p++) { A0[p] = A1[p]; S0[p] = S1[p]; }
+  }
+ }
+}
+
+template <bool TILED>
+int launch_direct(const LevelPtrs& lv, const float* coords, void* out, int N, int h1, int w1, int h2, int w2, int L, unsigned tiled_mask,
+                  cudaStream_t st) {
+  const long long tiles = static_cast<long long>(N) * h1 * cdiv(w1, 32);
+  if (tiles > 0x7fffffffLL) return DB200_ERR_ARG;
+  static const int per_sm = getenv("DB200_LOOKUP_CTAS") ? atoi(getenv("DB200_LOOKUP_CTAS")) : 0;   // > 0: persistent walk (experiments)
+  const long long cap = per_sm > 0 ? static_cast<long long>(per_sm) * kNumSMs : tiles;
+  const int grid = int(tiles < cap ? tiles : cap);
+  corr_lookup_r3_direct_kernel<TILED><<<grid, 32 * L, 0, st>>>(lv, coords, static_cast<__half*>(out), int(tiles), h1, w1, h2, w2, L,
+                                                               tiled_mask);
+  DB200_CHECK_LAUNCH();
+  return DB200_OK;
+}
+
 // Backward: one warp per source pixel writes the WHOLE h2*w2 slice of volume_grad (zeros outside the
 // window), so no separate memset pass is needed.  Gradient value per window sample follows
 // correlation_kernels.cu:108-121 (g accumulates the 4 contributions in that order, then 0 + g).
@@ -523,7 +667,29 @@ corr_lookup_bwd_kernel(const float* __restrict__ coords, const T* __restrict__ c
 
 template <typename T>
 int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h1, int w1, int h2, int w2, int L, int r,
-               cudaStream_t st) {
+               cudaStream_t st, unsigned tiled_mask = 0) {
+  if (tiled_mask != 0) {
+    // tiled levels exist for the pipelined fp16 radius-3 kernel only (CorrBlock's private pyramid); no other path reads them
+    if constexpr (sizeof(T) == 2) {
+      bool ok = (r == 3) && (tiled_mask >> L) == 0;
+      for (int l = 0; l < L && ok; l++) {
+        ok = ((w2 >> l) % 8 == 0) && ((h2 >> l) > 0) && (reinterpret_cast<uintptr_t>(lv.p[l]) % 16 == 0);
+        if (ok && ((tiled_mask >> l) & 1u)) ok = level_is_tiled(h2 >> l, w2 >> l) && (h2 >> l) < 32768 && (w2 >> l) < 32768 * 8;
+      }
+      const long long tiles = static_cast<long long>(N) * h1 * cdiv(w1, kPipePX);
+      if (!ok || tiles > 0x7fffffff) return DB200_ERR_ARG;
+      static const bool staged = getenv("DB200_LOOKUP_STAGED") != nullptr;     // the cp.async-staged kernel (comparison runs)
+      if (!staged) return launch_direct<true>(lv, coords, out, N, h1, w1, h2, w2, L, tiled_mask, st);
+      const size_t smem = pipe_smem_bytes<T>(true);
+      auto kern = corr_lookup_r3_pipe_kernel<T, true>;
+      DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+      const int grid = int(tiles < 2LL * kNumSMs ? tiles : 2LL * kNumSMs);
+      kern<<<grid, kPipeThreads, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, int(tiles), tiled_mask);
+      DB200_CHECK_LAUNCH();
+      return DB200_OK;
+    }
+    return DB200_ERR_ARG;
+  }
   if constexpr (sizeof(T) <= 4) {
     // pipelined path: every level's width must be whole 16-byte chunks and the level bases 16-byte aligned
     constexpr int CE = 16 / int(sizeof(T));
@@ -533,12 +699,16 @@ int launch_fwd(const LevelPtrs& lv, const float* coords, void* out, int N, int h
     if (ok) {
       const long long tiles = static_cast<long long>(N) * h1 * cdiv(w1, kPipePX);
       if (tiles > 0x7fffffff) return DB200_ERR_ARG;
+      if constexpr (sizeof(T) == 2) {
+        static const bool direct = getenv("DB200_LOOKUP_DIRECT") != nullptr;   // register-resident windows on the row-major layout
+        if (direct) return launch_direct<false>(lv, coords, out, N, h1, w1, h2, w2, L, 0u, st);
+      }
       const size_t smem = pipe_smem_bytes<T>();
-      auto kern = corr_lookup_r3_pipe_kernel<T>;
+      auto kern = corr_lookup_r3_pipe_kernel<T, false>;
       DB200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
       const int per_sm = smem <= 110 * 1024 ? 2 : 1;
       const int grid = int(tiles < static_cast<long long>(per_sm) * kNumSMs ? tiles : static_cast<long long>(per_sm) * kNumSMs);
-      kern<<<grid, kPipeThreads, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, int(tiles));
+      kern<<<grid, kPipeThreads, smem, st>>>(lv, coords, static_cast<T*>(out), N, h1, w1, h2, w2, L, int(tiles), 0u);
       DB200_CHECK_LAUNCH();
       return DB200_OK;
     }
@@ -579,8 +749,8 @@ int launch_bwd(const float* coords, const void* g, void* vg, int N, int h1, int 
 
 using namespace db200;
 
-extern "C" int db200_corr_pyramid_lookup(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
-                                         int h2, int w2, int num_levels, int radius, int dtype, db200_stream_t stream) {
+static int pyramid_lookup(const void* const* levels, const float* coords, void* out, int N, int h1, int w1, int h2, int w2,
+                          int num_levels, int radius, int dtype, unsigned tiled_mask, db200_stream_t stream) {
   if (!levels || !coords || !out || N < 0 || h1 <= 0 || w1 <= 0 || h2 <= 0 || w2 <= 0 || radius < 0 || radius > 7 ||
       num_levels < 1 || num_levels > kMaxLevels)
     return DB200_ERR_ARG;
@@ -592,11 +762,22 @@ extern "C" int db200_corr_pyramid_lookup(const void* const* levels, const float*
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (dtype) {
-    case DB200_F32: return launch_fwd<float>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
-    case DB200_F16: return launch_fwd<__half>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
-    case DB200_F64: return launch_fwd<double>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st);
+    case DB200_F32: return launch_fwd<float>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st, tiled_mask);
+    case DB200_F16: return launch_fwd<__half>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st, tiled_mask);
+    case DB200_F64: return launch_fwd<double>(lv, coords, out, N, h1, w1, h2, w2, num_levels, radius, st, tiled_mask);
   }
   return DB200_ERR_ARG;
+}
+
+extern "C" int db200_corr_pyramid_lookup(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
+                                         int h2, int w2, int num_levels, int radius, int dtype, db200_stream_t stream) {
+  return pyramid_lookup(levels, coords, out, N, h1, w1, h2, w2, num_levels, radius, dtype, 0u, stream);
+}
+
+extern "C" int db200_corr_pyramid_lookup_tiled(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
+                                               int h2, int w2, int num_levels, int radius, int dtype, unsigned tiled_mask,
+                                               db200_stream_t stream) {
+  return pyramid_lookup(levels, coords, out, N, h1, w1, h2, w2, num_levels, radius, dtype, tiled_mask, stream);
 }
 
 extern "C" int db200_corr_index_forward(const void* volume, const float* coords, void* corr, int N, int h1, int w1,

@@ -131,7 +131,7 @@ corr_gemm_f32_kernel(const float* __restrict__ f1, const float* __restrict__ f2,
 size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels);
 bool corr_tc_supported(int C, int ht, int wd);
 int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
-                           int num_levels, void* workspace, cudaStream_t st);
+                           int num_levels, void* workspace, cudaStream_t st, unsigned tiled_mask);
 
 size_t corr_tc_f32_workspace_bytes(int N, int C, int ht, int wd, int num_levels);
 bool corr_tc_f32_supported(int C, int ht, int wd, int num_levels);
@@ -166,9 +166,19 @@ extern "C" size_t db200_corr_volume_workspace_bytes(int N, int C, int ht, int wd
   return tot;
 }
 
-extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C, int ht,
-                                         int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
-                                         db200_stream_t stream) {
+extern "C" unsigned db200_corr_tiled_levels(int C, int ht, int wd, int num_levels, int dtype) {
+  if (num_levels < 1 || num_levels > 4 || C <= 0 || ht <= 0 || wd <= 0 || !use_tc_path(C, ht, wd, dtype)) return 0u;
+  unsigned m = 0;
+  for (int l = 0; l < num_levels; l++) {
+    if ((wd >> l) % 8 != 0 || (ht >> l) <= 0) return 0u;          // the fused lookup kernel wants whole 16-byte chunks per row
+    if (level_is_tiled(ht >> l, wd >> l)) m |= 1u << l;
+  }
+  return m;
+}
+
+static int volume_pyramid(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
+                          int num_levels, int dtype, void* workspace, size_t workspace_bytes, unsigned tiled_mask,
+                          db200_stream_t stream) {
   if (!fmap1 || !fmap2 || !levels_out || N < 0 || C <= 0 || ht <= 0 || wd <= 0 || num_levels < 1 || num_levels > 4)
     return DB200_ERR_ARG;
   if (dtype != DB200_F16 && dtype != DB200_F32) return DB200_ERR_ARG;
@@ -181,8 +191,9 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
   if (use_tc_path(C, ht, wd, dtype)) {
     if (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)) return DB200_ERR_WORKSPACE;
     return corr_volume_pyramid_tc(static_cast<const __half*>(fmap1), static_cast<const __half*>(fmap2), levels_out, N, C, ht, wd,
-                                  num_levels, workspace, st);
+                                  num_levels, workspace, st, tiled_mask);
   }
+  if (tiled_mask != 0) return DB200_ERR_ARG;                       // tiled levels exist on the tcgen05 fp16 path only
   if (dtype == DB200_F32 && use_tc_f32_path(C, ht, wd, num_levels)) {
     if (!workspace || workspace_bytes < db200_corr_volume_workspace_bytes(N, C, ht, wd, num_levels, dtype)) return DB200_ERR_WORKSPACE;
     return corr_volume_pyramid_tc_f32(static_cast<const float*>(fmap1), static_cast<const float*>(fmap2), levels_out, N, C, ht, wd,
@@ -221,4 +232,17 @@ extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, v
   DB200_COUNT(num_levels - 1);
   DB200_CHECK_LAUNCH();
   return DB200_OK;
+}
+
+extern "C" int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C, int ht,
+                                         int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
+                                         db200_stream_t stream) {
+  return volume_pyramid(fmap1, fmap2, levels_out, N, C, ht, wd, num_levels, dtype, workspace, workspace_bytes, 0u, stream);
+}
+
+extern "C" int db200_corr_volume_pyramid_tiled(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C, int ht,
+                                               int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
+                                               unsigned tiled_mask, db200_stream_t stream) {
+  if (tiled_mask != 0 && (tiled_mask & ~db200_corr_tiled_levels(C, ht, wd, num_levels, dtype)) != 0) return DB200_ERR_ARG;
+  return volume_pyramid(fmap1, fmap2, levels_out, N, C, ht, wd, num_levels, dtype, workspace, workspace_bytes, tiled_mask, stream);
 }

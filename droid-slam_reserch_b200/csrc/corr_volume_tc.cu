@@ -26,7 +26,9 @@ constexpr int kTM = 128, kTN = 128, kTK = 64;            // tile, and K per TMA 
 
 // ---- prep: [N][C][hs*ws] -> [N][(hs>>l)*(ws>>l)][C] with 2^l x 2^l mean (l = 0: plain transpose), fp32 mean rounded once per level
 // (level l+1 is pooled from the ROUNDED level l, like F.avg_pool2d applied to an f16 tensor)
-__global__ void __launch_bounds__(256) transpose_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW) {
+// wt > 0: destination rows in the tiled order of a [HW / wt][wt] map (common.cuh tiled_index) — the GEMM then writes its output
+// columns, i.e. the [h2][w2] slice of every source pixel, in that order with no other change
+__global__ void __launch_bounds__(256) transpose_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW, int wt = 0) {
   __shared__ __half tile[32][33];
   const int n = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -37,12 +39,14 @@ __global__ void __launch_bounds__(256) transpose_cl_kernel(const __half* __restr
   __syncthreads();
   for (int r = ty; r < 32; r += 8) {
     const int p = p0 + r, c = c0 + tx;
-    if (p < HW && c < C) dst[(size_t(n) * HW + p) * C + c] = tile[tx][r];
+    if (p < HW && c < C) dst[(size_t(n) * HW + (wt > 0 ? tiled_index(p / wt, p % wt, wt) : p)) * C + c] = tile[tx][r];
   }
 }
 
 // channels-last pooling: dst[n][y][x][c] = mean of the 2x2 block of src (floor mode)
-__global__ void pool_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int N, int hs, int ws, int C) {
+// (src_tiled / dst_tiled: that map's rows are in tiled order)
+__global__ void pool_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int N, int hs, int ws, int C,
+                               bool src_tiled = false, bool dst_tiled = false) {
   const int hd = hs >> 1, wd = ws >> 1;
   const size_t total = size_t(N) * hd * wd * (C / 2);
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
@@ -51,10 +55,21 @@ __global__ void pool_cl_kernel(const __half* __restrict__ src, __half* __restric
     const int x = int(r % wd); r /= wd;
     const int y = int(r % hd);
     const size_t n = r / hd;
-    const __half2* s = reinterpret_cast<const __half2*>(src + ((n * hs + 2 * y) * ws + 2 * x) * size_t(C)) + c2;
-    const float2 a = __half22float2(s[0]), b = __half22float2(s[C / 2]), c = __half22float2(s[size_t(ws) * (C / 2)]),
-                 d = __half22float2(s[size_t(ws) * (C / 2) + C / 2]);
-    reinterpret_cast<__half2*>(dst)[i] = __floats2half2_rn((a.x + b.x + c.x + d.x) * 0.25f, (a.y + b.y + c.y + d.y) * 0.25f);
+    float2 a, b, c, d;
+    if (src_tiled) {
+      const __half2* sn = reinterpret_cast<const __half2*>(src + n * hs * ws * size_t(C)) + c2;
+      a = __half22float2(sn[size_t(tiled_index(2 * y, 2 * x, ws)) * (C / 2)]);
+      b = __half22float2(sn[size_t(tiled_index(2 * y, 2 * x + 1, ws)) * (C / 2)]);
+      c = __half22float2(sn[size_t(tiled_index(2 * y + 1, 2 * x, ws)) * (C / 2)]);
+      d = __half22float2(sn[size_t(tiled_index(2 * y + 1, 2 * x + 1, ws)) * (C / 2)]);
+    } else {
+      const __half2* s = reinterpret_cast<const __half2*>(src + ((n * hs + 2 * y) * ws + 2 * x) * size_t(C)) + c2;
+      a = __half22float2(s[0]); b = __half22float2(s[C / 2]); c = __half22float2(s[size_t(ws) * (C / 2)]);
+      d = __half22float2(s[size_t(ws) * (C / 2) + C / 2]);
+    }
+    const __half2 v = __floats2half2_rn((a.x + b.x + c.x + d.x) * 0.25f, (a.y + b.y + c.y + d.y) * 0.25f);
+    const size_t o = dst_tiled ? ((n * hd * wd + tiled_index(y, x, wd)) * size_t(C / 2) + c2) : i;
+    reinterpret_cast<__half2*>(dst)[o] = v;
   }
 }
 
@@ -521,7 +536,7 @@ size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels) {
 bool corr_tc_supported(int C, int ht, int wd) { return C == 2 * kTK && (ht * wd) % 8 == 0 && encode_fn() != nullptr; }
 
 int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const* levels_out, int N, int C, int ht, int wd,
-                           int num_levels, void* workspace, cudaStream_t st) {
+                           int num_levels, void* workspace, cudaStream_t st, unsigned tiled_mask) {
   char* ws = static_cast<char*>(workspace);
   int* err = reinterpret_cast<int*>(ws);
   ws += 256;
@@ -545,18 +560,21 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
     attr = true;
   }
   const __half* prev = nullptr;
+  bool prev_tiled = false;
   int h = ht, w = wd;
   for (int l = 0; l < num_levels; l++) {
     if (h == 0 || w == 0) return DB200_ERR_ARG;
+    const bool tiled = ((tiled_mask >> l) & 1u) != 0;                // the level's [h][w] slices come out in tiled order
+    if (tiled && !level_is_tiled(h, w)) return DB200_ERR_ARG;
     __half* f2T = reinterpret_cast<__half*>(ws);
     ws += align_up256(size_t(N) * C * h * w * 2);
     if (l == 0) {
       dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
-      transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap2, f2T, C, HW);
+      transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap2, f2T, C, HW, tiled ? w : 0);
     } else {
       const size_t cnt = size_t(N) * h * w * (C / 2);
       const int blocks = int((cnt + 255) / 256 < 2368 ? (cnt + 255) / 256 : 2368);
-      pool_cl_kernel<<<blocks, 256, 0, st>>>(prev, f2T, N, h << 1, w << 1, C);
+      pool_cl_kernel<<<blocks, 256, 0, st>>>(prev, f2T, N, h << 1, w << 1, C, prev_tiled, tiled);
     }
     DB200_CHECK_LAUNCH();
     const int N2 = h * w;
@@ -580,6 +598,7 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
     }
     DB200_CHECK_LAUNCH();
     prev = f2T;
+    prev_tiled = tiled;
     h >>= 1; w >>= 1;
   }
   return DB200_OK;

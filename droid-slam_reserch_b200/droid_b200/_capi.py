@@ -30,6 +30,9 @@ _SIGNATURES = {
     "db200_corr_pyramid_lookup": (_i, [C.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_corr_volume_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "db200_corr_volume_pyramid": (_i, [_vp, _vp, C.POINTER(_vp), _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "db200_corr_tiled_levels": (C.c_uint, [_i, _i, _i, _i, _i]),
+    "db200_corr_volume_pyramid_tiled": (_i, [_vp, _vp, C.POINTER(_vp), _i, _i, _i, _i, _i, _i, _vp, _sz, C.c_uint, _vp]),
+    "db200_corr_pyramid_lookup_tiled": (_i, [C.POINTER(_vp), _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, C.c_uint, _vp]),
     "db200_altcorr_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_altcorr_backward": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "db200_altcorr_workspace_bytes": (_sz, [_i] * 7),

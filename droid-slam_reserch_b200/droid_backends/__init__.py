@@ -16,6 +16,7 @@ from droid_b200 import _capi
 
 __all__ = ["ba", "frame_distance", "projmap", "depth_filter", "iproj", "altcorr_forward", "altcorr_backward",
            "corr_index_forward", "corr_index_backward", "corr_pyramid_lookup", "corr_volume_pyramid", "altcorr_pyramid_forward",
+           "corr_tiled_levels", "tile_level", "untile_level",
            "split_hilo_f16", "to_channel_blocked"]
 
 _DT = {torch.float32: _capi.F32, torch.float16: _capi.F16, torch.float64: _capi.F64}
@@ -67,9 +68,10 @@ def corr_index_backward(volume, coords, corr_grad, radius):
     return [grad]
 
 
-def corr_pyramid_lookup(levels, coords, radius):
+def corr_pyramid_lookup(levels, coords, radius, tiled_mask=0):
     """Fused CorrBlock.__call__ (corr.py:40-50): levels = list of [N,h1,w1,h2>>l,w2>>l]; coords[N,2,h1,w1]
-    at level-0 scale -> out[N, L*(2r+1)^2, h1, w1]."""
+    at level-0 scale -> out[N, L*(2r+1)^2, h1, w1].  tiled_mask: bit l set = level l is stored in the tiled slice
+    layout of `corr_volume_pyramid(..., tiled=True)` (fp16, radius 3; same output bits)."""
     _chk(("coords", coords), *[(f"levels[{i}]", v) for i, v in enumerate(levels)])
     N, h1, w1, h2, w2 = levels[0].shape
     L = len(levels)
@@ -79,24 +81,56 @@ def corr_pyramid_lookup(levels, coords, radius):
         return out
     arr = (C.c_void_p * L)(*[v.data_ptr() for v in levels])
     co = coords.float()
+    if tiled_mask:
+        _capi.check(_capi.lib().db200_corr_pyramid_lookup_tiled(arr, _ptr(co), _ptr(out), N, h1, w1, h2, w2, L, radius,
+                                                                _DT[levels[0].dtype], int(tiled_mask), _stream()),
+                    "corr_pyramid_lookup (tiled levels)")
+        return out
     _capi.check(_capi.lib().db200_corr_pyramid_lookup(arr, _ptr(co), _ptr(out), N, h1, w1, h2, w2, L, radius,
                                                       _DT[levels[0].dtype], _stream()), "corr_pyramid_lookup")
     return out
 
 
-def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
+def corr_tiled_levels(C_, ht, wd, num_levels, dtype):
+    """bit mask of the pyramid levels `corr_volume_pyramid(..., tiled=True)` stores in the tiled slice layout (0: none)"""
+    if dtype not in _DT:
+        return 0
+    return int(_capi.lib().db200_corr_tiled_levels(C_, ht, wd, num_levels, _DT[dtype]))
+
+
+def untile_level(v):
+    """tiled slices [..., h2, w2] (4x8-element tiles, include/droid_b200.h) -> the reference's row-major slices (a copy)"""
+    h2, w2 = v.shape[-2:]
+    lead = v.shape[:-2]
+    return v.reshape(*lead, h2 // 4, w2 // 8, 4, 8).transpose(-3, -2).reshape(*lead, h2, w2)
+
+
+def tile_level(v):
+    """inverse of `untile_level`"""
+    h2, w2 = v.shape[-2:]
+    lead = v.shape[:-2]
+    return v.reshape(*lead, h2 // 4, 4, w2 // 8, 8).transpose(-3, -2).reshape(*lead, h2, w2)
+
+
+def corr_volume_pyramid(fmap1, fmap2, num_levels=4, tiled=False):
     """CorrBlock.corr + avg-pool pyramid (corr.py:30-38,63-71).  fmap1,fmap2[N,C,ht,wd] (f16/f32) ->
-    list of volumes [N,ht,wd,ht>>l,wd>>l]."""
+    list of volumes [N,ht,wd,ht>>l,wd>>l].  tiled=True -> (levels, tiled_mask): the levels of `tiled_mask` hold their
+    [h2,w2] slices in the tiled layout that `corr_pyramid_lookup(..., tiled_mask)` reads (mask 0 when the shape has none)."""
     _chk(("fmap1", fmap1), ("fmap2", fmap2))
     N, Cc, ht, wd = fmap1.shape
     dt = _DT[fmap1.dtype]
     outs = [torch.empty((N, ht, wd, ht >> l, wd >> l), dtype=fmap1.dtype, device=fmap1.device) for l in range(num_levels)]
-    if N == 0:
-        return outs
     lib = _capi.lib()
+    mask = int(lib.db200_corr_tiled_levels(Cc, ht, wd, num_levels, dt)) if tiled else 0
+    if N == 0:
+        return (outs, mask) if tiled else outs
     wsb = lib.db200_corr_volume_workspace_bytes(N, Cc, ht, wd, num_levels, dt) if N > 0 else 0
     ws = torch.empty(max(wsb, 16), dtype=torch.uint8, device=fmap1.device)
     arr = (C.c_void_p * num_levels)(*[v.data_ptr() for v in outs])
+    if tiled:
+        _capi.check(lib.db200_corr_volume_pyramid_tiled(_ptr(fmap1), _ptr(fmap2), arr, N, Cc, ht, wd, num_levels, dt, _ptr(ws),
+                                                        wsb, mask, _stream()), "corr_volume_pyramid (tiled levels)")
+        return outs, mask
     _capi.check(lib.db200_corr_volume_pyramid(_ptr(fmap1), _ptr(fmap2), arr, N, Cc, ht, wd, num_levels, dt, _ptr(ws), wsb,
                                               _stream()), "corr_volume_pyramid")
     return outs

@@ -80,6 +80,24 @@ int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, void* const*
                               int ht, int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
                               db200_stream_t stream);
 
+/* ---- tiled levels: CorrBlock's private pyramid layout (no counterpart in the reference; corr.py:23-50 keeps the volumes
+ * behind the class, so their layout is the implementation's choice as long as corr_pyramid[i] can be materialised) ----
+ * The [h2][w2] slice of every source pixel is stored as 4x8-element tiles (64 bytes of fp16 = one DRAM burst; tiles row-major,
+ * the 4 rows of a tile 16 bytes apart): element (y, x) sits at ((y>>2)*(w2>>3) + (x>>3))*32 + (y&3)*8 + (x&7).  The 8x8-sample
+ * window of a radius-3 lookup then touches ~5 DRAM bursts instead of 8-10 (row-major: one burst per 16-byte window row).
+ * db200_corr_tiled_levels: bit l set = level l of a (C, ht, wd, num_levels, dtype) pyramid may be tiled (fp16, C = 128 on the
+ *   tcgen05 path; level height % 4 == 0, width % 8 == 0 and >= 32); 0 = not supported for this shape.
+ * db200_corr_volume_pyramid_tiled: db200_corr_volume_pyramid with the levels of `tiled_mask` (a subset of the above) written
+ *   in tiled order — same values, the GEMM's B operand rows are permuted, nothing else changes.
+ * db200_corr_pyramid_lookup_tiled: db200_corr_pyramid_lookup reading such a pyramid (fp16, radius 3); bit-identical output. */
+unsigned db200_corr_tiled_levels(int C, int ht, int wd, int num_levels, int dtype);
+int db200_corr_volume_pyramid_tiled(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C,
+                                    int ht, int wd, int num_levels, int dtype, void* workspace, size_t workspace_bytes,
+                                    unsigned tiled_mask, db200_stream_t stream);
+int db200_corr_pyramid_lookup_tiled(const void* const* levels, const float* coords, void* out, int N, int h1, int w1,
+                                    int h2, int w2, int num_levels, int radius, int dtype, unsigned tiled_mask,
+                                    db200_stream_t stream);
+
 /* ---- low-memory correlation (altcorr) ------------------------------------------------------
  * altcorr_forward (droid.cpp:193-203, altcorr_kernel.cu:27-149,290-319), fp32:
  *   fmap1[B,H1,W1,C], fmap2[B,H2,W2,C], coords[B,S,H1,W1,2] -> corr[B,S,(2r+1)^2,H1,W1], channel = iy + (2r+1)*ix */

@@ -141,6 +141,30 @@ def test_mirror_corrblock_f16(mods):
     assert float((a.float() - b.float()).abs().max()) <= 4e-3 * float(b.float().abs().max())
 
 
+def test_mirror_corrblock_tiled_levels_are_private():
+    """The mirror's inference CorrBlock keeps levels 0 and 1 in the tiled slice layout: lookups, cat and indexing work on
+    it directly; `corr_pyramid` hands out the reference's row-major volumes (converting the block once) and the lookup of
+    the converted block gives the same bits."""
+    from droid_b200 import corr as mirror
+    f1, f2, co = D.corrblock_case(ht=48, wd=64, n=3)
+    blk = mirror.CorrBlock(_t(f1), _t(f2))
+    assert blk._tiled == 0b0011
+    a = blk(_t(co))
+    two = mirror.CorrBlock(_t(f1), _t(f2)).cat(mirror.CorrBlock(_t(f1), _t(f2)))
+    assert two._tiled == 0b0011 and two._pyr[0].shape[0] == 6
+    co2 = _t(np.concatenate([co, co], 1))
+    aa = two(co2)
+    assert torch.equal(_bits(aa[:, :3]), _bits(a)) and torch.equal(_bits(aa[:, 3:]), _bits(a))
+    sel = two[torch.tensor([4, 0], device="cuda")]
+    assert torch.equal(_bits(sel(co2[:, [4, 0]])), _bits(a[:, [1, 0]]))
+    rows = blk.corr_pyramid                                          # converts: row-major from here on
+    assert blk._tiled == 0 and [tuple(v.shape) for v in rows] == [(3, 48, 64, 48 >> l, 64 >> l) for l in range(4)]
+    assert torch.equal(_bits(blk(_t(co))), _bits(a))
+    fresh = mirror.CorrBlock(_t(f1), _t(f2))
+    mixed = fresh.cat(blk)                                           # tiled + row-major: both end up row-major
+    assert mixed._tiled == 0 and torch.equal(_bits(mixed(co2)), _bits(aa))
+
+
 def test_mirror_corrblock_fp32_grads(mods):
     """the mirror's fused volume build must not drop the gradients to the feature maps."""
     _, theirs = mods

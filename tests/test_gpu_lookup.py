@@ -198,3 +198,59 @@ def test_corr_volume_pyramid_full_size_f32():
         err = float((outs[l].double() - ref).abs().max())
         assert err <= 1e-4 * scale, (l, err)                 # measured ~2e-6: the dropped lo*lo terms and fp32 accumulation
         corr = torch.nn.functional.avg_pool2d(corr, 2, stride=2)
+
+
+# ---- tiled levels (CorrBlock's private pyramid layout; include/droid_b200.h) ---------------------------------------------
+@pytest.mark.parametrize("N,h1,w1,h2,w2,L,mask", [
+    (2, 48, 64, 48, 64, 4, 0b0011),         # the frontend shape: levels 0 and 1 tiled
+    (2, 5, 40, 16, 64, 4, 0b0011),          # ragged last source tile; level 1 = 8 x 32
+    (1, 6, 33, 24, 32, 2, 0b0001),          # only level 0 can be tiled (level 1 is 12 x 16)
+    (1, 7, 32, 48, 64, 4, 0b0010),          # a mixed pyramid: level 1 tiled, level 0 row-major
+])
+def test_corr_pyramid_lookup_tiled_bit_exact(N, h1, w1, h2, w2, L, mask):
+    import droid_backends
+    rng = np.random.default_rng(21)
+    levels = [torch.from_numpy(rng.normal(0, 1, (N, h1, w1, h2 >> l, w2 >> l)).astype(np.float16)).cuda() for l in range(L)]
+    co = torch.from_numpy(_coords(N, h1, w1, h2, w2, 22)).cuda()
+    want = droid_backends.corr_pyramid_lookup(levels, co, 3)
+    tiled = [droid_backends.tile_level(v).contiguous() if (mask >> l) & 1 else v for l, v in enumerate(levels)]
+    for l in range(L):
+        if (mask >> l) & 1:
+            assert torch.equal(droid_backends.untile_level(tiled[l]), levels[l])
+    out = droid_backends.corr_pyramid_lookup(tiled, co, 3, tiled_mask=mask)
+    assert torch.equal(out.view(torch.int16), want.view(torch.int16))
+
+
+def test_corr_pyramid_lookup_tiled_rejects_other_shapes():
+    import droid_backends
+    lv = [torch.zeros((1, 4, 8, 12, 16), dtype=torch.float16, device="cuda")]
+    co = torch.zeros((1, 2, 4, 8), device="cuda")
+    with pytest.raises(RuntimeError):
+        droid_backends.corr_pyramid_lookup(lv, co, 3, tiled_mask=1)          # 12 x 16 is not a tiled level
+    lv32 = [torch.zeros((1, 4, 8, 48, 64), dtype=torch.float32, device="cuda")]
+    with pytest.raises(RuntimeError):
+        droid_backends.corr_pyramid_lookup(lv32, co, 3, tiled_mask=1)        # fp16 only
+
+
+def test_corr_volume_pyramid_tiled_equals_row_major():
+    import droid_backends
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    N, C_, ht, wd = 3, 128, 48, 64
+    f1 = torch.randn((N, C_, ht, wd), device="cuda", dtype=torch.float16, generator=g)
+    f2 = torch.randn((N, C_, ht, wd), device="cuda", dtype=torch.float16, generator=g)
+    want = droid_backends.corr_volume_pyramid(f1, f2, 4)
+    got, mask = droid_backends.corr_volume_pyramid(f1, f2, 4, tiled=True)
+    assert mask == 0b0011 == droid_backends.corr_tiled_levels(C_, ht, wd, 4, torch.float16)
+    for l in range(4):
+        v = droid_backends.untile_level(got[l]) if (mask >> l) & 1 else got[l]
+        assert torch.equal(v.view(torch.int16), want[l].view(torch.int16)), l
+    co = torch.from_numpy(_coords(N, ht, wd, ht, wd, 23)).cuda()
+    a = droid_backends.corr_pyramid_lookup(want, co, 3)
+    b = droid_backends.corr_pyramid_lookup(got, co, 3, tiled_mask=mask)
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    # shapes without tiled levels: mask 0, plain pyramid
+    f1s, f2s = f1[:, :, :12, :16].contiguous(), f2[:, :, :12, :16].contiguous()
+    got_s, mask_s = droid_backends.corr_volume_pyramid(f1s, f2s, 2, tiled=True)
+    assert mask_s == 0
+    want_s = droid_backends.corr_volume_pyramid(f1s, f2s, 2)
+    assert all(torch.equal(x, y) for x, y in zip(got_s, want_s))
