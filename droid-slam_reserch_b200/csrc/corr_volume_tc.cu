@@ -26,20 +26,36 @@ constexpr int kTM = 128, kTN = 128, kTK = 64;            // tile, and K per TMA 
 
 // ---- prep: [N][C][hs*ws] -> [N][(hs>>l)*(ws>>l)][C] with 2^l x 2^l mean (l = 0: plain transpose), fp32 mean rounded once per level
 // (level l+1 is pooled from the ROUNDED level l, like F.avg_pool2d applied to an f16 tensor)
+// 64 pixels x 64 channels per CTA: 128-byte reads along the pixels (half2 per lane), 128-byte writes along the channels.
 // wt > 0: destination rows in the tiled order of a [HW / wt][wt] map (common.cuh tiled_index) — the GEMM then writes its output
-// columns, i.e. the [h2][w2] slice of every source pixel, in that order with no other change
+// columns, i.e. the [h2][w2] slice of every source pixel, in that order with no other change.
+// (the 32x32-element version moved 64-byte segments and took 47 us per 48-edge map: 1.6 TB/s)
 __global__ void __launch_bounds__(256) transpose_cl_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW, int wt = 0) {
-  __shared__ __half tile[32][33];
-  const int n = blockIdx.z, c0 = blockIdx.y * 32, p0 = blockIdx.x * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  for (int r = ty; r < 32; r += 8) {
-    const int c = c0 + r, p = p0 + tx;
-    tile[r][tx] = (c < C && p < HW) ? src[(size_t(n) * C + c) * HW + p] : __float2half(0.0f);
+  __shared__ __half tileT[64][66];                                     // [pixel][channel], pitch 33 words
+  const int n = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool pair_ok = (HW % 2 == 0);                                  // half2 reads need an even row pitch
+  for (int r = warp; r < 64; r += 8) {
+    const int c = c0 + r, p = p0 + 2 * lane;
+    __half a = __float2half(0.0f), b = a;
+    if (c < C) {
+      const __half* sp = src + (size_t(n) * C + c) * HW + p;
+      if (pair_ok && p + 1 < HW) { const __half2 v = *reinterpret_cast<const __half2*>(sp); a = __low2half(v); b = __high2half(v); }
+      else { if (p < HW) a = sp[0]; if (p + 1 < HW) b = sp[1]; }
+    }
+    tileT[2 * lane][r] = a;
+    tileT[2 * lane + 1][r] = b;
   }
   __syncthreads();
-  for (int r = ty; r < 32; r += 8) {
-    const int p = p0 + r, c = c0 + tx;
-    if (p < HW && c < C) dst[(size_t(n) * HW + (wt > 0 ? tiled_index(p / wt, p % wt, wt) : p)) * C + c] = tile[tx][r];
+  const bool cpair_ok = (C % 2 == 0);
+  for (int r = warp; r < 64; r += 8) {
+    const int p = p0 + r, c = c0 + 2 * lane;
+    if (p >= HW) continue;
+    const size_t drow = size_t(n) * HW + (wt > 0 ? tiled_index(p / wt, p % wt, wt) : p);
+    const __half2 v = *reinterpret_cast<const __half2*>(&tileT[r][2 * lane]);
+    __half* dp = dst + drow * C + c;
+    if (cpair_ok && c + 1 < C) *reinterpret_cast<__half2*>(dp) = v;
+    else { if (c < C) dp[0] = __low2half(v); if (c + 1 < C) dp[1] = __high2half(v); }
   }
 }
 
@@ -175,17 +191,35 @@ corr_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 constexpr int kPipeThreadsTC = 192;
 // two operand stages (64 KB each) + two output staging tiles (32 KB each) + alignment slack
 constexpr size_t kPipeSmemTC = 2 * (2 * (kTM + kTN) * kTK * 2) + 2 * (kTM * kTN * 2) + 1024;
+// FUSED: staging of the pooled levels for their TMA stores, two buffers each: level 1 [128 rows][2 tiles][16 halfs], level 2
+// [128 rows][8 halfs]
+constexpr uint32_t kFusedL1Stage = kTM * 64, kFusedL2Stage = kTM * 16;
+constexpr size_t kPipeSmemFused = kPipeSmemTC + 2 * (kFusedL1Stage + kFusedL2Stage);
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }   // the four epilogue warps
+template <int THREADS>
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }   // the epilogue warps
 
 // TMA_STORE: the f16 tile is staged in shared memory in the 128-byte-swizzled box layout (bank-conflict free for
 // thread = row) and leaves as two asynchronous bulk tensor stores (full lines, clipped per edge by the 3-D tensor map);
 // otherwise every thread writes its row segments directly (any N2).
-template <bool TMA_STORE>
+//
+// FUSED (CorrBlock's private pyramid, 64-wide maps, level 0 and 1 tiled): the pooled levels come out of the SAME launch.  The
+// columns of the product are in tiled order, so the 32 accumulator columns of one tcgen05.ld are one 4x8-pixel tile of the
+// (h2, w2) map: its 2x2 / 4x4 means are level-1 / level-2 values, complete in the thread's registers; level 3 (8x8) needs
+// the tile row below, which is two n-tiles later in the SAME CTA — a CTA takes the n-tiles in groups of four (= two tile
+// rows), carrying eight partial sums.  The pooled values are means of the fp32 accumulators, rounded to fp16 once (the
+// unfused path rounds pooled fp16 operands first; the reference rounds at every level: all within fp16 rounding of the
+// exact mean).  No pooled operand copies, no further GEMM launches, fmap1 is read once.
+struct FusedOut {
+  __half* l1; __half* l2; __half* l3;     // level 1 (tiled slices), level 2 and 3 (row-major slices); NULL = level not wanted
+};
+
+template <bool TMA_STORE, bool FUSED>
 __global__ void __launch_bounds__(kPipeThreadsTC, 1)
 corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmO, __half* __restrict__ out, int M, int N2, int E,
-                         int* __restrict__ err) {
+                         int* __restrict__ err, FusedOut fo, const __grid_constant__ CUtensorMap tmL1,
+                         const __grid_constant__ CUtensorMap tmL2) {
   extern __shared__ unsigned char smem_dyn[];
   __shared__ __align__(8) uint64_t bars[8];          // full[2], empty[2], tfull[2], tempty[2]
   __shared__ uint32_t tmem_base_s;
@@ -194,6 +228,12 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int MT = (M + kTM - 1) / kTM, NT = (N2 + kTN - 1) / kTN;
   const long long tiles = static_cast<long long>(E) * MT * NT;
+  // tile sequence of this CTA: plain = blockIdx.x, + gridDim.x, ...; FUSED = units of 4 consecutive n-tiles (NT % 4 == 0, so a
+  // unit stays inside one (edge, m-tile)): unit u -> tiles 4u .. 4u+3
+  auto tile_at = [&](long long k) -> long long {
+    if (FUSED) return 4 * (blockIdx.x + (k >> 2) * static_cast<long long>(gridDim.x)) + (k & 3);
+    return blockIdx.x + k * static_cast<long long>(gridDim.x);
+  };
   auto bar = [&](int i) { return smem_u32(&bars[i]); };
 
   if (tid == 0) {
@@ -213,7 +253,7 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       int k = 0;
-      for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+      for (long long t = tile_at(0); t < tiles; t = tile_at(++k)) {
         const int s = k & 1, use = k >> 1;
         const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
         if (!mbar_wait(bar(2 + s), (use & 1) ^ 1)) { atomicExch(err, 1); break; }
@@ -228,7 +268,7 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   } else if (warp == 1) {
     if (lane == 0) {
       int k = 0;
-      for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+      for (long long t = tile_at(0); t < tiles; t = tile_at(++k)) {
         const int s = k & 1, use = k >> 1;
         if (!mbar_wait(bar(6 + s), (use & 1) ^ 1)) { atomicExch(err, 1); break; }     // accumulator s drained
         if (!mbar_wait(bar(s), use & 1)) { atomicExch(err, 1); break; }               // operands landed
@@ -249,8 +289,11 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   } else {
     const int quarter = warp & 3;                                      // TMEM lane quarter this warp may read
     const bool vec = (N2 % 8 == 0);
+    constexpr int kEpiThreads = 128;
+    float p3[8], f3[4];                                                // FUSED: level-3 partial sums of the upper tile row, finished values
+    uint32_t w1[2][4], w2[4];                                          // FUSED: packed level-1 / level-2 values of the running tile
     int k = 0;
-    for (long long t = blockIdx.x; t < tiles; t += gridDim.x, k++) {
+    for (long long t = tile_at(0); t < tiles; t = tile_at(++k)) {
       const int s = k & 1, use = k >> 1;
       const int nt = int(t % NT), mt = int((t / NT) % MT), e = int(t / (static_cast<long long>(NT) * MT));
       const bool ok = mbar_wait(bar(4 + s), use & 1);
@@ -260,12 +303,51 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if constexpr (TMA_STORE) {
         const int trow = 32 * quarter + lane;                          // row inside the tile
         const uint32_t stg = s0 + 2 * kStageBytes + uint32_t(s) * (kTM * kTN * 2);
+        const uint32_t l1stg = s0 + 2 * kStageBytes + 2 * (kTM * kTN * 2) + uint32_t(s) * kFusedL1Stage;   // FUSED only
+        const uint32_t l2stg = s0 + 2 * kStageBytes + 2 * (kTM * kTN * 2) + 2 * kFusedL1Stage + uint32_t(s) * kFusedL2Stage;
         if (tid == 64) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read this buffer
-        epi_bar();
-#pragma unroll 1
+        epi_bar<kEpiThreads>();
+#pragma unroll(FUSED ? 4 : 1)
         for (int cb = 0; cb < kTN; cb += 32) {
           uint32_t v[32];
           tmem_ld32(tmem_base + (uint32_t(32 * quarter) << 16) + uint32_t(s * kTN + cb), v);
+          if constexpr (FUSED) {
+            // v = one 4x8 tile (ty, tx) of the (h2, w2) map, v[8 * yi + xi]; ty = nt >> 1, tx = 4 * (nt & 1) + cb / 32.
+            // Levels 1 and 2 are staged in shared memory (thread = volume row) and leave with the tile's TMA stores: direct
+            // stores would be 32 different slices per warp instruction, and the L1/TEX path of ~10 such stores per tile and
+            // thread set the tile period (68 % L1/TEX, 308 us per 48 edges instead of the 202 us of level 0 alone).
+            const int ty = nt >> 1, q = cb >> 5;                       // q: static after unrolling
+            float s1[2][4];
+#pragma unroll
+            for (int r = 0; r < 2; r++)
+#pragma unroll
+              for (int c = 0; c < 4; c++)
+                s1[r][c] = (__uint_as_float(v[16 * r + 2 * c]) + __uint_as_float(v[16 * r + 2 * c + 1])) +
+                           (__uint_as_float(v[16 * r + 8 + 2 * c]) + __uint_as_float(v[16 * r + 8 + 2 * c + 1]));
+            const float s2a = (s1[0][0] + s1[0][1]) + (s1[1][0] + s1[1][1]), s2b = (s1[0][2] + s1[0][3]) + (s1[1][2] + s1[1][3]);
+            const float s3 = s2a + s2b;
+            auto pk = [](float a, float b) { const __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<const uint32_t*>(&h); };
+#pragma unroll
+            for (int r = 0; r < 2; r++) {                              // level 1: rows 2ty + r, columns 4tx .. 4tx + 3
+              w1[r][2 * (q & 1)] = pk(s1[r][0] * 0.015625f, s1[r][1] * 0.015625f);
+              w1[r][2 * (q & 1) + 1] = pk(s1[r][2] * 0.015625f, s1[r][3] * 0.015625f);
+            }
+            w2[q] = pk(s2a * 0.00390625f, s2b * 0.00390625f);          // level 2: row ty, columns 2tx, 2tx + 1
+            if (q & 1) {                                               // chunks (q-1, q) = the row pair of one 4x8 level-1 tile: 32 bytes
+              const uint32_t a = l1stg + uint32_t(trow) * 64 + uint32_t(q >> 1) * 32;
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(w1[0][0]), "r"(w1[0][1]), "r"(w1[0][2]), "r"(w1[0][3]) : "memory");
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a + 16), "r"(w1[1][0]), "r"(w1[1][1]), "r"(w1[1][2]), "r"(w1[1][3]) : "memory");
+            }
+            if (q == 3)                                                // 8 level-2 columns of row ty: 16 bytes
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(l2stg + uint32_t(trow) * 16), "r"(w2[0]), "r"(w2[1]), "r"(w2[2]), "r"(w2[3]) : "memory");
+            if ((ty & 1) == 0) {                                       // level 3 = 8x8 means: upper tile row kept, lower one completes it
+              if (nt & 1) p3[4 + q] = s3; else p3[q] = s3;             // static register indices
+            } else {
+              f3[q] = (((nt & 1) ? p3[4 + q] : p3[q]) + s3) * 0.0009765625f;
+              if (q == 3 && fo.l3 && row < M)                          // 4 level-3 columns of row ty >> 1 (1/64 of the bytes: direct store)
+                *reinterpret_cast<uint2*>(fo.l3 + (size_t(e) * M + row) * size_t(N2 >> 6) + (ty >> 1) * 8 + 4 * (nt & 1)) = make_uint2(pk(f3[0], f3[1]), pk(f3[2], f3[3]));
+            }
+          }
           const uint32_t box = stg + uint32_t(cb >> 6) * (kTM * 128) + uint32_t(trow) * 128;
           const int ch0 = (cb & 63) >> 3;
 #pragma unroll
@@ -284,10 +366,16 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(6 + s));                        // accumulator drained: the next MMAs may start
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the TMA
-        epi_bar();
+        epi_bar<kEpiThreads>();
         if (tid == 64) {
           tma_store_3d(&tmO, stg, n0, mt * kTM, e);
           if (n0 + 64 < N2) tma_store_3d(&tmO, stg + kTM * 128, n0 + 64, mt * kTM, e);
+          if constexpr (FUSED) {                                       // same bulk group: the staging buffers are reused together
+            const int ty = nt >> 1;
+            // level 1 as [16 halfs = 2 tile rows][row pair][tile column][tile row][volume row]; level 2 as [16][12][volume row]
+            if (fo.l1) tma_store_5d(&tmL1, l1stg, 0, ty & 1, 2 * (nt & 1), ty >> 1, e * M + mt * kTM);
+            if (fo.l2) tma_store_3d(&tmL2, l2stg, 8 * (nt & 1), ty, e * M + mt * kTM);
+          }
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
         continue;
@@ -467,7 +555,7 @@ corr_gemm_tc_tf32_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid
       if (!ok) { if (lane == 0) atomicExch(err, 1); break; }
       const int n0 = nt * kTN, trow = 32 * quarter + lane;
       if (tid == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");      // the single staging tile is free again
-      epi_bar();
+      epi_bar<128>();
 #pragma unroll 1
       for (int cb = 0; cb < kTN; cb += 32) {
         uint32_t v[32];
@@ -485,7 +573,7 @@ corr_gemm_tc_tf32_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty(acc));
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      epi_bar();
+      epi_bar<128>();
       if (tid == 64) {
 #pragma unroll
         for (int b = 0; b < 4; b++)
@@ -525,6 +613,33 @@ static bool make_out_map(CUtensorMap* m, void* base, int N2, int M, int E) {
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// FUSED pyramid: level 1 in tiled slices seen as [2 rows x 8 = 16 halfs][2 row pairs][w1/8 tile columns][h1/4 tile rows][rows of
+// the volume]; box = the row pair of two neighbouring tiles for 128 volume rows.  Level 2 (row-major [h2][w2] slices): box = 8
+// columns of one row for 128 volume rows.
+static bool make_fused_maps(CUtensorMap* m1, CUtensorMap* m2, void* l1, void* l2, int ht, int wd, uint64_t rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const int h1 = ht >> 1, w1 = wd >> 1, h2 = ht >> 2, w2 = wd >> 2;
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  if (l1) {
+    const cuuint64_t gdim[5] = {16, 2, cuuint64_t(w1 / 8), cuuint64_t(h1 / 4), rows};
+    const cuuint64_t gstride[4] = {32, 64, cuuint64_t(w1 / 8) * 64, cuuint64_t(h1) * w1 * 2};
+    const cuuint32_t box[5] = {16, 1, 2, 1, cuuint32_t(kTM)};
+    if (fn(m1, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, l1, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+           CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+  }
+  if (l2) {
+    const cuuint64_t gdim[3] = {cuuint64_t(w2), cuuint64_t(h2), rows};
+    const cuuint64_t gstride[2] = {cuuint64_t(w2) * 2, cuuint64_t(h2) * w2 * 2};
+    const cuuint32_t box[3] = {8, 1, cuuint32_t(kTM)};
+    if (fn(m2, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, l2, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+           CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
+  }
+  return true;
+}
+
 size_t corr_tc_workspace_bytes(int N, int C, int ht, int wd, int num_levels) {
   size_t tot = 256 + 256;                                           // status word
   tot += align_up256(size_t(N) * C * ht * wd * 2);                  // f1T
@@ -545,7 +660,7 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
   __half* f1T = reinterpret_cast<__half*>(ws);
   ws += align_up256(size_t(N) * C * HW * 2);
   {
-    dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+    dim3 grid(cdiv(HW, 64), cdiv(C, 64), N);
     transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap1, f1T, C, HW);
     DB200_CHECK_LAUNCH();
   }
@@ -555,8 +670,9 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
   static bool attr = false;
   if (!attr) {
     DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
-    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemTC)));
+    DB200_CUDA(cudaFuncSetAttribute(corr_gemm_tc_pipe_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kPipeSmemFused)));
     attr = true;
   }
   const __half* prev = nullptr;
@@ -569,7 +685,7 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
     __half* f2T = reinterpret_cast<__half*>(ws);
     ws += align_up256(size_t(N) * C * h * w * 2);
     if (l == 0) {
-      dim3 grid(cdiv(HW, 32), cdiv(C, 32), N);
+      dim3 grid(cdiv(HW, 64), cdiv(C, 64), N);
       transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap2, f2T, C, HW, tiled ? w : 0);
     } else {
       const size_t cnt = size_t(N) * h * w * (C / 2);
@@ -591,10 +707,27 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
       CUtensorMap tmO = tmB;                                           // placeholder when the direct-store epilogue is used
       const bool tma_store = !no_tma_store && N2 % 64 == 0 && (reinterpret_cast<uintptr_t>(levels_out[l]) % 16 == 0) &&
                              make_out_map(&tmO, levels_out[l], N2, HW, N);
+      // fused pyramid: 64-wide maps whose level 0 (and level 1, if wanted) are tiled; a unit of four n-tiles = two tile rows
+      static const bool no_fused = getenv("DB200_CORR_NO_FUSED_PYRAMID") != nullptr;
+      bool fused = l == 0 && !no_fused && tma_store && wd == 64 && ht % 8 == 0 && (tiled_mask & 1u) && num_levels <= 4 &&
+                   (num_levels < 2 || (tiled_mask & 2u)) && (tiled_mask >> 2) == 0 && HW % kTM == 0;
+      for (int q = 1; q < num_levels && fused; q++) fused = reinterpret_cast<uintptr_t>(levels_out[q]) % 16 == 0;
+      if (fused) {                                                   // all levels from this one launch
+        FusedOut fo{num_levels > 1 ? static_cast<__half*>(levels_out[1]) : nullptr, num_levels > 2 ? static_cast<__half*>(levels_out[2]) : nullptr,
+                    num_levels > 3 ? static_cast<__half*>(levels_out[3]) : nullptr};
+        CUtensorMap tmL1 = tmB, tmL2 = tmB;                            // placeholders for levels that are not wanted
+        if (!make_fused_maps(&tmL1, &tmL2, fo.l1, fo.l2, ht, wd, uint64_t(N) * HW)) return DB200_ERR_CUDA;
+        const long long units = tiles / 4;
+        const int g4 = int(units < kNumSMs ? units : kNumSMs);
+        corr_gemm_tc_pipe_kernel<true, true><<<g4, kPipeThreadsTC, kPipeSmemFused, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N,
+                                                                                         err, fo, tmL1, tmL2);
+        DB200_CHECK_LAUNCH();
+        return DB200_OK;
+      }
       if (tma_store)
-        corr_gemm_tc_pipe_kernel<true><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err);
+        corr_gemm_tc_pipe_kernel<true, false><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err, FusedOut{}, tmB, tmB);
       else
-        corr_gemm_tc_pipe_kernel<false><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err);
+        corr_gemm_tc_pipe_kernel<false, false><<<grid, kPipeThreadsTC, kPipeSmemTC, st>>>(tmA, tmB, tmO, static_cast<__half*>(levels_out[l]), HW, N2, N, err, FusedOut{}, tmB, tmB);
     }
     DB200_CHECK_LAUNCH();
     prev = f2T;

@@ -233,6 +233,9 @@ def test_corr_pyramid_lookup_tiled_rejects_other_shapes():
 
 
 def test_corr_volume_pyramid_tiled_equals_row_major():
+    """Level 0 of the tiled pyramid is the row-major level 0 bit for bit (same dot products, permuted columns).  On 64-wide
+    maps the pooled levels come out of the same launch as means of the fp32 accumulators rounded once: compared with the
+    exact fp32 pyramid (within half an fp16 spacing at the value scale) and with the unfused row-major levels."""
     import droid_backends
     g = torch.Generator(device="cuda"); g.manual_seed(5)
     N, C_, ht, wd = 3, 128, 48, 64
@@ -241,13 +244,32 @@ def test_corr_volume_pyramid_tiled_equals_row_major():
     want = droid_backends.corr_volume_pyramid(f1, f2, 4)
     got, mask = droid_backends.corr_volume_pyramid(f1, f2, 4, tiled=True)
     assert mask == 0b0011 == droid_backends.corr_tiled_levels(C_, ht, wd, 4, torch.float16)
-    for l in range(4):
-        v = droid_backends.untile_level(got[l]) if (mask >> l) & 1 else got[l]
-        assert torch.equal(v.view(torch.int16), want[l].view(torch.int16)), l
+    rows = [droid_backends.untile_level(v) if (mask >> l) & 1 else v for l, v in enumerate(got)]
+    assert torch.equal(rows[0].view(torch.int16), want[0].view(torch.int16))
+    exact = torch.matmul(f1.float().reshape(N, C_, -1).transpose(1, 2), f2.float().reshape(N, C_, -1)).reshape(N * ht * wd, 1, ht, wd) / 16.0
+    for l in range(1, 4):
+        exact = torch.nn.functional.avg_pool2d(exact, 2, stride=2)
+        ref = exact.reshape(N, ht, wd, ht >> l, wd >> l)
+        ulp = 2.0 ** (np.floor(np.log2(float(ref.abs().max()))) - 10)
+        d_new = float((rows[l].float() - ref).abs().max()) / ulp
+        d_old = float((want[l].float() - ref).abs().max()) / ulp
+        print(f"level {l}: fused pyramid {d_new:.3f}, unfused {d_old:.3f} fp16 spacings from the exact mean")
+        assert d_new <= 0.51 and d_old <= 2.0, (l, d_new, d_old)
     co = torch.from_numpy(_coords(N, ht, wd, ht, wd, 23)).cuda()
-    a = droid_backends.corr_pyramid_lookup(want, co, 3)
+    a = droid_backends.corr_pyramid_lookup(rows, co, 3)
     b = droid_backends.corr_pyramid_lookup(got, co, 3, tiled_mask=mask)
     assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    # fewer levels than four through the fused launch
+    got2, mask2 = droid_backends.corr_volume_pyramid(f1, f2, 2, tiled=True)
+    assert mask2 == 0b11 and torch.equal(got2[0], got[0]) and torch.equal(got2[1], got[1])
+    # other widths: tiled where the shape allows it, every level from its own GEMM (bit-equal to the row-major pyramid)
+    f1w, f2w = f1[:, :, :24, :32].contiguous(), f2[:, :, :24, :32].contiguous()
+    got_w, mask_w = droid_backends.corr_volume_pyramid(f1w, f2w, 3, tiled=True)
+    want_w = droid_backends.corr_volume_pyramid(f1w, f2w, 3)
+    assert mask_w == 0b001
+    for l in range(3):
+        v = droid_backends.untile_level(got_w[l]) if (mask_w >> l) & 1 else got_w[l]
+        assert torch.equal(v.view(torch.int16), want_w[l].view(torch.int16)), l
     # shapes without tiled levels: mask 0, plain pyramid
     f1s, f2s = f1[:, :, :12, :16].contiguous(), f2[:, :, :12, :16].contiguous()
     got_s, mask_s = droid_backends.corr_volume_pyramid(f1s, f2s, 2, tiled=True)
