@@ -608,20 +608,24 @@ def volume_bench(dev, steps, warmup, hbm_peak):
     g = torch.Generator(device=dev); g.manual_seed(11)
     f1 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
     f2 = torch.randn((N, C_, ht, wd), device=dev, dtype=torch.float16, generator=g)
-    for _ in range(warmup):
-        droid_backends.corr_volume_pyramid(f1, f2, 4)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    torch.cuda.synchronize()
-    ev[0].record()
-    for _ in range(steps):
-        droid_backends.corr_volume_pyramid(f1, f2, 4)
-    ev[1].record()
-    torch.cuda.synchronize()
-    ms = ev[0].elapsed_time(ev[1]) / steps
+
+    def timed(tiled):
+        for _ in range(warmup):
+            droid_backends.corr_volume_pyramid(f1, f2, 4, tiled=tiled)
+        torch.cuda.synchronize()
+        ev[0].record()
+        for _ in range(steps):
+            droid_backends.corr_volume_pyramid(f1, f2, 4, tiled=tiled)
+        ev[1].record()
+        torch.cuda.synchronize()
+        return ev[0].elapsed_time(ev[1]) / steps
+    ms_row = timed(False)                    # the reference's row-major volumes (one GEMM launch per level)
+    ms = timed(True)                         # CorrBlock's private pyramid: tiled levels 0-1, all levels from one launch
     hw = ht * wd
     out_bytes = N * hw * sum((ht >> l) * (wd >> l) for l in range(4)) * 2
     in_bytes = 2 * N * C_ * hw * 2
-    flops = 2.0 * N * hw * C_ * sum((ht >> l) * (wd >> l) for l in range(4))
+    flops = 2.0 * N * hw * C_ * hw           # the level-0 product (the pooled levels are means of its accumulators)
     gbs = (out_bytes + in_bytes) / (ms * 1e-3) / 1e9
 
     def ref_build():                         # CorrBlock.__init__ of the reference in f16 (corr.py:23-38,63-71): cuBLAS + 3 avg_pool2d
@@ -644,6 +648,8 @@ def volume_bench(dev, steps, warmup, hbm_peak):
         pass
     return dict(metric="CorrBlock build edges/s (all-pairs 128-d GEMM + 4-level pyramid, f16, 48 edges x 48x64)",
                 value=N / (ms * 1e-3), unit="edges/s", ms_per_call=ms, tflops=flops / (ms * 1e-3) / 1e12,
+                layout="CorrBlock's private pyramid (levels 0-1 in 4x8-element tiles, pooled levels from the level-0 launch)",
+                ms_per_call_row_major=ms_row,
                 reference_torch_ms=ref_ms,
                 roofline=dict(bound="hbm", achieved=gbs, peak=hbm_peak, unit="GB/s", frac=gbs / hbm_peak, traffic=None,
                               algorithmic_bytes_per_call=out_bytes + in_bytes))

@@ -196,6 +196,12 @@ constexpr size_t kPipeSmemTC = 2 * (2 * (kTM + kTN) * kTK * 2) + 2 * (kTM * kTN 
 constexpr uint32_t kFusedL1Stage = kTM * 64, kFusedL2Stage = kTM * 16;
 constexpr size_t kPipeSmemFused = kPipeSmemTC + 2 * (kFusedL1Stage + kFusedL2Stage);
 
+// MN-major operand tile, 128-byte swizzle: blocks of 64 MN-elements x K rows of 128 bytes; LBO = next 64-element MN block
+// (16 KB: the second TMA box), SBO = next 8 K-rows (1 KB).  Used for fmap1 as it lies in memory ([C][HW], pixels contiguous).
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t saddr) {
+  return uint64_t((saddr >> 4) & 0x3FFFu) | (uint64_t(16384 >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (uint64_t(1) << 46) | (uint64_t(2) << 61);
+}
+
 template <int THREADS>
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); }   // the epilogue warps
 
@@ -259,8 +265,13 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (!mbar_wait(bar(2 + s), (use & 1) ^ 1)) { atomicExch(err, 1); break; }
         const uint32_t sA = s0 + s * kStageBytes, sB = sA + 2 * kTM * kTK * 2;
         mbar_expect_tx(bar(s), kStageBytes);
-        tma_load_2d(sA, &tmA, 0, e * M + mt * kTM, bar(s));
-        tma_load_2d(sA + kTM * kTK * 2, &tmA, kTK, e * M + mt * kTM, bar(s));
+        if constexpr (FUSED) {                                         // fmap1 untransposed: [64 pixels][128 channels] per box
+          tma_load_2d(sA, &tmA, mt * kTM, e * 2 * kTK, bar(s));
+          tma_load_2d(sA + kTM * kTK * 2, &tmA, mt * kTM + 64, e * 2 * kTK, bar(s));
+        } else {
+          tma_load_2d(sA, &tmA, 0, e * M + mt * kTM, bar(s));
+          tma_load_2d(sA + kTM * kTK * 2, &tmA, kTK, e * M + mt * kTM, bar(s));
+        }
         tma_load_2d(sB, &tmB, 0, e * N2 + nt * kTN, bar(s));
         tma_load_2d(sB + kTN * kTK * 2, &tmB, kTK, e * N2 + nt * kTN, bar(s));
       }
@@ -278,9 +289,9 @@ corr_gemm_tc_pipe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         for (int kb = 0; kb < 2; kb++)
 #pragma unroll
           for (int kk = 0; kk < kTK / 16; kk++) {
-            const uint64_t ad = umma_desc_sw128(sA + kb * kTM * kTK * 2 + kk * 32);
+            const uint64_t ad = FUSED ? umma_desc_sw128_mn(sA + (kb * (kTK / 16) + kk) * 2048) : umma_desc_sw128(sA + kb * kTM * kTK * 2 + kk * 32);
             const uint64_t bd = umma_desc_sw128(sB + kb * kTN * kTK * 2 + kk * 32);
-            umma_f16(tmem_base + uint32_t(s * kTN), ad, bd, kIdescF16, (kb | kk) != 0 ? 1u : 0u);
+            umma_f16(tmem_base + uint32_t(s * kTN), ad, bd, FUSED ? (kIdescF16 | (1u << 15)) : kIdescF16, (kb | kk) != 0 ? 1u : 0u);
           }
         umma_commit(bar(2 + s));                                       // stage free once these MMAs have read it
         umma_commit(bar(4 + s));                                       // accumulator ready for the epilogue
@@ -601,6 +612,18 @@ static bool make_map(CUtensorMap* m, const void* base, uint64_t rows, int C) {
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// fmap [rows = E*C][HW] f16, pixels contiguous: box = 64 pixels x 128 channel rows (one 16 KB MN block of an MN-major operand)
+static bool make_map_mn(CUtensorMap* m, const void* base, int HW, uint64_t rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[2] = {cuuint64_t(HW), rows};
+  const cuuint64_t gstride[1] = {cuuint64_t(HW) * 2};
+  const cuuint32_t box[2] = {64, cuuint32_t(2 * kTK)};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // output level [E][M][N2] f16 as a 3-D tensor: box = 64 columns x 128 rows x 1 edge, 128-byte swizzle
 static bool make_out_map(CUtensorMap* m, void* base, int N2, int M, int E) {
   EncodeTiledFn fn = encode_fn();
@@ -657,15 +680,23 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
   ws += 256;
   DB200_CUDA(cudaMemsetAsync(err, 0, sizeof(int), st));
   const int HW = ht * wd;
+  // fused pyramid: 64-wide maps whose level 0 (and level 1, if wanted) are tiled; every level from ONE launch, fmap1 read in place
+  static const bool no_fused = getenv("DB200_CORR_NO_FUSED_PYRAMID") != nullptr || getenv("DB200_CORR_TC_ONESHOT") != nullptr ||
+                               getenv("DB200_CORR_TC_NO_TMA_STORE") != nullptr;
+  bool fused = !no_fused && wd == 64 && ht % 8 == 0 && (tiled_mask & 1u) && num_levels <= 4 && (num_levels < 2 || (tiled_mask & 2u)) &&
+               (tiled_mask >> 2) == 0 && HW % kTM == 0 && reinterpret_cast<uintptr_t>(fmap1) % 16 == 0;
+  for (int q = 0; q < num_levels && fused; q++) fused = reinterpret_cast<uintptr_t>(levels_out[q]) % 16 == 0;
   __half* f1T = reinterpret_cast<__half*>(ws);
   ws += align_up256(size_t(N) * C * HW * 2);
-  {
+  CUtensorMap tmA;
+  if (fused) {                                                       // [C][HW] as it lies in memory: an MN-major operand
+    if (!make_map_mn(&tmA, fmap1, HW, uint64_t(N) * C)) return DB200_ERR_CUDA;
+  } else {
     dim3 grid(cdiv(HW, 64), cdiv(C, 64), N);
     transpose_cl_kernel<<<grid, 256, 0, st>>>(fmap1, f1T, C, HW);
     DB200_CHECK_LAUNCH();
+    if (!make_map(&tmA, f1T, uint64_t(N) * HW, C)) return DB200_ERR_CUDA;
   }
-  CUtensorMap tmA;
-  if (!make_map(&tmA, f1T, uint64_t(N) * HW, C)) return DB200_ERR_CUDA;
   const size_t smem = size_t(2) * (kTM + kTN) * kTK * 2 + 1024;
   static bool attr = false;
   if (!attr) {
@@ -707,11 +738,7 @@ int corr_volume_pyramid_tc(const __half* fmap1, const __half* fmap2, void* const
       CUtensorMap tmO = tmB;                                           // placeholder when the direct-store epilogue is used
       const bool tma_store = !no_tma_store && N2 % 64 == 0 && (reinterpret_cast<uintptr_t>(levels_out[l]) % 16 == 0) &&
                              make_out_map(&tmO, levels_out[l], N2, HW, N);
-      // fused pyramid: 64-wide maps whose level 0 (and level 1, if wanted) are tiled; a unit of four n-tiles = two tile rows
-      static const bool no_fused = getenv("DB200_CORR_NO_FUSED_PYRAMID") != nullptr;
-      bool fused = l == 0 && !no_fused && tma_store && wd == 64 && ht % 8 == 0 && (tiled_mask & 1u) && num_levels <= 4 &&
-                   (num_levels < 2 || (tiled_mask & 2u)) && (tiled_mask >> 2) == 0 && HW % kTM == 0;
-      for (int q = 1; q < num_levels && fused; q++) fused = reinterpret_cast<uintptr_t>(levels_out[q]) % 16 == 0;
+      if (fused && !tma_store) return DB200_ERR_CUDA;
       if (fused) {                                                   // all levels from this one launch
         FusedOut fo{num_levels > 1 ? static_cast<__half*>(levels_out[1]) : nullptr, num_levels > 2 ? static_cast<__half*>(levels_out[2]) : nullptr,
                     num_levels > 3 ? static_cast<__half*>(levels_out[3]) : nullptr};
