@@ -196,6 +196,22 @@ def test_droid_backends_surface_and_no_cpu_fallback():
         droid_backends.corr_index_forward(torch.zeros(1, 2, 2, 2, 4)[..., ::2], torch.zeros(1, 2, 2, 2), 3)
 
 
+def test_tiled_slice_layout_helpers_match_the_header_formula():
+    """include/droid_b200.h, "tiled levels": element (y, x) of a [h2][w2] slice sits at ((y>>2)*(w2>>3) + (x>>3))*32 + (y&3)*8 + (x&7).
+    `tile_level` / `untile_level` are the host-side converters (pure tensor reshapes: no GPU needed) and are inverse to each other."""
+    import torch
+    import droid_backends
+    for h2, w2 in [(48, 64), (24, 32), (8, 40)]:
+        v = torch.arange(3 * h2 * w2, dtype=torch.int32).reshape(3, 1, h2, w2)
+        t = droid_backends.tile_level(v)
+        assert t.shape == v.shape and torch.equal(droid_backends.untile_level(t), v)
+        flat = t.reshape(3, -1)
+        for y, x in [(0, 0), (3, 7), (4, 8), (h2 - 1, w2 - 1), (5, 17), (h2 // 2, w2 // 2 + 3)]:
+            idx = ((y >> 2) * (w2 >> 3) + (x >> 3)) * 32 + (y & 3) * 8 + (x & 7)
+            assert int(flat[1, idx]) == int(v[1, 0, y, x]), (h2, w2, y, x)
+    assert droid_backends.corr_tiled_levels(128, 48, 64, 4, torch.float64) == 0      # fp16 only
+
+
 # ------------------------------------------------------------------------------------------ edge selection (§8f-2)
 def test_proximity_edges_oracle_hand_worked_case():
     """6 frames, rad=1, nms=1: 18 neighbourhood edges, then picks (5,0), (4,1), (3,0), (5,2) — (4,0), (5,1) fall to the
