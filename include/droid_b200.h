@@ -88,7 +88,11 @@ int db200_corr_volume_pyramid(const void* fmap1, const void* fmap2, void* const*
  * db200_corr_tiled_levels: bit l set = level l of a (C, ht, wd, num_levels, dtype) pyramid may be tiled (fp16, C = 128 on the
  *   tcgen05 path; level height % 4 == 0, width % 8 == 0 and >= 32); 0 = not supported for this shape.
  * db200_corr_volume_pyramid_tiled: db200_corr_volume_pyramid with the levels of `tiled_mask` (a subset of the above) written
- *   in tiled order — same values, the GEMM's B operand rows are permuted, nothing else changes.
+ *   in tiled order.  Level 0 holds the same bits as the row-major call (the GEMM's B operand rows are permuted, nothing else
+ *   changes).  When wd == 64, ht % 8 == 0 and the mask is the full db200_corr_tiled_levels mask, every level comes from ONE
+ *   launch: fmap1 is read in place, and levels 1..3 are the 2x2 / 4x4 / 8x8 means of the level-0 fp32 accumulators rounded to
+ *   fp16 once (within half an fp16 spacing of the exact mean; the row-major call pools fp16 operands first, the reference
+ *   pools the rounded level below: all within fp16 rounding, not the same bits — DESIGN.md §5).
  * db200_corr_pyramid_lookup_tiled: db200_corr_pyramid_lookup reading such a pyramid (fp16, radius 3); bit-identical output. */
 unsigned db200_corr_tiled_levels(int C, int ht, int wd, int num_levels, int dtype);
 int db200_corr_volume_pyramid_tiled(const void* fmap1, const void* fmap2, void* const* levels_out, int N, int C,
